@@ -1,0 +1,150 @@
+/* dlco_b200.h -- C ABI of the B200-native DLCO training hot path.
+ *
+ * The reference (cbalint13/opencv-dlco) has no plugin/FFI seam: its hot loops are written
+ * inline in the tools' main() bodies.  Each entry point below replaces one of those loop
+ * bodies (cited as file:line relative to the reference tree) so that a maintainer can
+ * swap the body for one call -- see INTEGRATION.md for the stubs.
+ *
+ * Conventions
+ *  - every function returns 0 on success, a negative DLCO_E* code otherwise; the message
+ *    is available from dlco_last_error() (thread-local).  No exceptions, no exit().
+ *  - "d_" pointers are device pointers on the context's GPU, "h_" pointers are host
+ *    pointers; the caller owns every buffer.  Matrices are row-major, leading dimension
+ *    in ELEMENTS.
+ *  - a dlco_ctx is bound to one GPU and one CUDA stream; one ctx per GPU, not
+ *    thread-safe; different ctx may be driven from different host threads.
+ *  - device functions are asynchronous on the ctx stream unless they return a host
+ *    scalar; dlco_sync() waits for the stream.
+ *  - there is no CPU fallback: every compute entry point fails with DLCO_ENODEV when no
+ *    sm_100 device is present.
+ */
+#ifndef DLCO_B200_H
+#define DLCO_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DLCO_OK 0
+#define DLCO_EINVAL (-1)
+#define DLCO_ENODEV (-2)
+#define DLCO_ECUDA (-3)
+#define DLCO_ENOMEM (-4)
+
+#define DLCO_PATCH 64      /* patch side; K = 4096 pixels            */
+#define DLCO_NBINS 8       /* orientation bins (reference -anglebins) */
+
+typedef struct dlco_ctx dlco_ctx;
+typedef struct dlco_bank dlco_bank;
+
+/* ---- context (replaces cuda::setDevice(0): src/comp-fulldists.cpp:278,
+ *      src/pr-learn.cpp:284, src/pj-learn.cpp:267) ----------------------------------- */
+int dlco_init(int device, dlco_ctx **ctx);
+int dlco_shutdown(dlco_ctx *ctx);
+const char *dlco_last_error(void);
+int dlco_device_name(dlco_ctx *ctx, char *buf, int len, int *cc_major, int *cc_minor);
+int dlco_sync(dlco_ctx *ctx);
+/* use an existing stream (e.g. torch's current stream); NULL restores the ctx's own */
+int dlco_set_stream(dlco_ctx *ctx, void *cuda_stream);
+int dlco_malloc(dlco_ctx *ctx, size_t bytes, void **d_ptr);
+int dlco_free(dlco_ctx *ctx, void *d_ptr);
+int dlco_memcpy_h2d(dlco_ctx *ctx, void *d_dst, const void *h_src, size_t bytes);
+int dlco_memcpy_d2h(dlco_ctx *ctx, void *h_dst, const void *d_src, size_t bytes);
+/* number of kernels this library launched on this ctx since init (bench "gpu_launches") */
+int64_t dlco_launch_count(dlco_ctx *ctx);
+
+/* ---- pool-region filter bank (prfilters.upload: src/comp-fulldists.cpp:281) ---------
+ * h_filters: nF x 4096 f32, element index x*64+y as gen-poolregion writes it
+ * (src/gen-poolregion.cpp:68).  The bank keeps the tf32 hi/lo planes the tensor-core
+ * kernel consumes.  nF must be a multiple of 8 (8 members per ring). */
+int dlco_bank_create(dlco_ctx *ctx, const float *h_filters, int nF, dlco_bank **bank);
+int dlco_bank_create_dev(dlco_ctx *ctx, const float *d_filters, int nF, dlco_bank **bank);
+int dlco_bank_destroy(dlco_ctx *ctx, dlco_bank *bank);
+
+/* ---- get_desc (src/vgg-desc.cpp:41-152) on the GPU -----------------------------------
+ * d_patches: P x 64 x 64 u8; d_ids: n patch indices; d_out: n x 4096 x 8 f32
+ * ("PatchTrans", row p = column-major pixel index). */
+int dlco_get_desc(dlco_ctx *ctx, const uint8_t *d_patches, const int32_t *d_ids, int n,
+                  int nAngleBins, float sigma, int bNorm, float *d_out);
+
+/* ---- comp-fulldists loop body (src/comp-fulldists.cpp:294-356) -----------------------
+ * d_indices: N x 4 i32 "Indices" rows (patch1, point1, patch2, point2); computes rows
+ * [lo,hi) of "Distance" into d_out (row r of d_out = pair lo+r), ld_out >= nF/8. */
+int dlco_fulldist_build(dlco_ctx *ctx, const dlco_bank *bank, const uint8_t *d_patches,
+                        const int32_t *d_indices, int64_t lo, int64_t hi, int nAngleBins,
+                        float sigma, int bNorm, float *d_out, int64_t ld_out);
+/* same with host buffers (pinned or pageable): patches/indices are uploaded, rows are
+ * downloaded into h_out -- the end-to-end call the comp-fulldists tool makes per range. */
+int dlco_fulldist_build_host(dlco_ctx *ctx, const dlco_bank *bank, const uint8_t *h_patches,
+                             int64_t nPatches, const int32_t *h_indices, int64_t lo, int64_t hi,
+                             int nAngleBins, float sigma, int bNorm, float *h_out,
+                             int64_t ld_out);
+/* Label = (point1 == point2): src/comp-fulldists.cpp:247-251 */
+int dlco_pair_labels(dlco_ctx *ctx, const int32_t *d_indices, int64_t n, uint8_t *d_label);
+
+/* ---- comp-uprjdists loop body (src/comp-uprjdists.cpp:298-335) ------------------------
+ * bank holds the nSel selected filters (SelectPRFilters output); d_out rows are
+ * [PR0 bin0..7, PR1 bin0..7, ...] = Desc1 - Desc2, ld_out >= 8*nSel. */
+int dlco_uprjdist_build(dlco_ctx *ctx, const dlco_bank *bank, const uint8_t *d_patches,
+                        const int32_t *d_indices, int64_t lo, int64_t hi, int nAngleBins,
+                        float sigma, int bNorm, float *d_out, int64_t ld_out);
+
+/* ---- cv::cuda::dlco::SubtractVectorsByRows + cuda::sum (include/trainer.hpp:60-61,
+ *      src/kernelop-opencv.cu:49-80; callers src/pr-learn.cpp:348-351,
+ *      src/pj-learn.cpp:515-520): sum_i sum_j max(pos_i + margin - neg_j, 0) ----------- */
+int dlco_hinge_pairsum(dlco_ctx *ctx, const float *d_pos, int64_t n1, const float *d_neg,
+                       int64_t n2, float margin, double *h_sum);
+
+/* ---- pr-learn (src/pr-learn.cpp:303-358) ----------------------------------------------
+ * dlco_pr_rda_run: steps t0 .. t0+nSteps-1 of the l1/non-negative RDA.  d_dists: N x F,
+ * d_idx_pos/d_idx_neg: shuffled row indices (train part first), sampler = cv::RNG whose
+ * 64-bit state is *rng_state (updated).  d_w, d_dfavg: F floats, in/out. */
+int dlco_pr_rda_run(dlco_ctx *ctx, const float *d_dists, int64_t ld, int F,
+                    const int32_t *d_idx_pos, int32_t nPosTrn, const int32_t *d_idx_neg,
+                    int32_t nNegTrn, float mu, float gamma, uint64_t t0, uint64_t nSteps,
+                    uint64_t *rng_state, float *d_w, float *d_dfavg);
+/* validation objective: LossVal, Regul (src/pr-learn.cpp:340-358).  d_pos_rows/d_neg_rows
+ * index rows of d_dists (the 20 % hold-out). */
+int dlco_pr_validate(dlco_ctx *ctx, const float *d_dists, int64_t ld, int F,
+                     const int32_t *d_pos_rows, int64_t nPos, const int32_t *d_neg_rows,
+                     int64_t nNeg, const float *d_w, float mu, float *h_loss, float *h_regul);
+
+/* ---- pj-learn inner step (src/pj-learn.cpp:311-432) ------------------------------------
+ * dlco_pj_rda_grad: gather the 2 x szBatch sampled rows, margins ||W d||^2, hinge mask,
+ * dLoss = X^T diag(c) X (tensor-core SYRK, 3xTF32).  d_W: rank x D (ldW = D).
+ * d_rows_pos/neg: szBatch row indices into d_dists. */
+int dlco_pj_rda_grad(dlco_ctx *ctx, const float *d_dists, int64_t ld, int D,
+                     const int32_t *d_rows_pos, const int32_t *d_rows_neg, int szBatch,
+                     const float *d_W, int rank, float *d_dLoss);
+/* dfAvg <- t/(t+1) dfAvg + dLoss/(b*b*(t+1));  A <- sym(-sqrt(t+1)/gamma (dfAvg + mu I))
+ * (src/pj-learn.cpp:422-432) */
+int dlco_pj_rda_update(dlco_ctx *ctx, int D, uint64_t t, int szBatch, float mu, float gamma,
+                       const float *d_dLoss, float *d_dfavg, float *d_A);
+/* A <- V diag(max(e,0)) V^T, W <- rows sqrt(e_k) v_k^T for e_k > 0 (ascending e);
+ * d_evec: D x D, row k = eigenvector k (src/pj-learn.cpp:448-490).  *h_rank = rows of W. */
+int dlco_pj_prox_apply(dlco_ctx *ctx, int D, const float *d_eval, const float *d_evec,
+                       float *d_A, float *d_W, int *h_rank);
+/* symmetric eigen-decomposition used between update and prox_apply (stays library code:
+ * cuSOLVER syevd; the reference uses LAPACKE_ssyevr, src/pj-learn.cpp:440-446) */
+int dlco_pj_eig(dlco_ctx *ctx, int D, const float *d_A, float *d_eval, float *d_evec);
+int dlco_pj_validate(dlco_ctx *ctx, const float *d_dists, int64_t ld, int D,
+                     const int32_t *d_pos_rows, int64_t nPos, const int32_t *d_neg_rows,
+                     int64_t nNeg, const float *d_W, int rank, const float *d_A, float mu,
+                     float *h_loss, float *h_regul);
+
+/* ---- FPR95 evaluation (src/misc.cpp:171-333) --------------------------------------------
+ * pr: PatchDist = Dists . w ; pj: PatchDist = colsum((W Dists^T)^2); then ascending sort,
+ * ROC, FPR at first TPR >= 0.95f, AUC = polygon area.  d_labels: N u8. */
+int dlco_pr_patchdist(dlco_ctx *ctx, const float *d_dists, int64_t N, int64_t ld, int F,
+                      const float *d_w, float *d_pd);
+int dlco_pj_patchdist(dlco_ctx *ctx, const float *d_dists, int64_t N, int64_t ld, int D,
+                      const float *d_W, int rank, float *d_pd);
+int dlco_roc_stats(dlco_ctx *ctx, const float *d_pd, const uint8_t *d_labels, int64_t N,
+                   float *h_fpr95, double *h_auc);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,209 @@
+"""Host-side binding of libdlco_b200.so (the C ABI in include/dlco_b200.h).
+
+The reference (cbalint13/opencv-dlco) is a set of C++ command-line tools with no plugin API;
+the functions here are the Python face of the C entry points that replace the tools' inline hot
+loops (each docstring cites the reference loop).  torch is used only to hold device memory and
+streams.  There is NO CPU fallback: importing works anywhere (so the symbol table can be
+checked), but every compute call raises DlcoError unless the CUDA library initialises on an
+sm_100 device.
+"""
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libdlco_b200.so")
+
+c_void_p, c_int, c_int64, c_float = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_float
+c_size_t, c_uint64, c_double, c_char_p = ctypes.c_size_t, ctypes.c_uint64, ctypes.c_double, ctypes.c_char_p
+P = ctypes.POINTER
+
+# name -> (restype, argtypes); mirrors include/dlco_b200.h one-to-one
+SIGNATURES = {
+    "dlco_init": (c_int, [c_int, P(c_void_p)]),
+    "dlco_shutdown": (c_int, [c_void_p]),
+    "dlco_last_error": (c_char_p, []),
+    "dlco_device_name": (c_int, [c_void_p, c_char_p, c_int, P(c_int), P(c_int)]),
+    "dlco_sync": (c_int, [c_void_p]),
+    "dlco_set_stream": (c_int, [c_void_p, c_void_p]),
+    "dlco_malloc": (c_int, [c_void_p, c_size_t, P(c_void_p)]),
+    "dlco_free": (c_int, [c_void_p, c_void_p]),
+    "dlco_memcpy_h2d": (c_int, [c_void_p, c_void_p, c_void_p, c_size_t]),
+    "dlco_memcpy_d2h": (c_int, [c_void_p, c_void_p, c_void_p, c_size_t]),
+    "dlco_launch_count": (c_int64, [c_void_p]),
+    "dlco_bank_create": (c_int, [c_void_p, c_void_p, c_int, P(c_void_p)]),
+    "dlco_bank_create_dev": (c_int, [c_void_p, c_void_p, c_int, P(c_void_p)]),
+    "dlco_bank_destroy": (c_int, [c_void_p, c_void_p]),
+    "dlco_get_desc": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_int, c_void_p]),
+    "dlco_fulldist_build": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int,
+                                    c_float, c_int, c_void_p, c_int64]),
+    "dlco_fulldist_build_host": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int64,
+                                         c_int64, c_int, c_float, c_int, c_void_p, c_int64]),
+    "dlco_pair_labels": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
+    "dlco_uprjdist_build": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int,
+                                    c_float, c_int, c_void_p, c_int64]),
+    "dlco_hinge_pairsum": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_float, P(c_double)]),
+    "dlco_pr_rda_run": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_void_p, ctypes.c_int32, c_void_p,
+                                ctypes.c_int32, c_float, c_float, c_uint64, c_uint64, P(c_uint64),
+                                c_void_p, c_void_p]),
+    "dlco_pr_validate": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_void_p, c_int64, c_void_p, c_int64,
+                                 c_void_p, c_float, P(c_float), P(c_float)]),
+    "dlco_pj_rda_grad": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_void_p, c_void_p, c_int, c_void_p,
+                                 c_int, c_void_p]),
+    "dlco_pj_rda_update": (c_int, [c_void_p, c_int, c_uint64, c_int, c_float, c_float, c_void_p, c_void_p,
+                                   c_void_p]),
+    "dlco_pj_prox_apply": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, P(c_int)]),
+    "dlco_pj_eig": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
+    "dlco_pj_validate": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_void_p, c_int64, c_void_p, c_int64,
+                                 c_void_p, c_int, c_void_p, c_float, P(c_float), P(c_float)]),
+    "dlco_pr_patchdist": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int, c_void_p, c_void_p]),
+    "dlco_pj_patchdist": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int, c_void_p, c_int, c_void_p]),
+    "dlco_roc_stats": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, P(c_float), P(c_double)]),
+}
+
+
+class DlcoError(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def load_library():
+    """dlopen libdlco_b200.so and bind every entry point; raises if the library is missing
+    (run `python -c 'import __graft_entry__ as g; g.build()'` first)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise DlcoError("CUDA library %s is missing: build it first (no CPU fallback exists)" % LIB_PATH)
+    lib = ctypes.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)          # AttributeError if a declared symbol is not exported
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def _check(rc):
+    if rc != 0:
+        raise DlcoError("libdlco_b200 error %d: %s" % (rc, load_library().dlco_last_error().decode()))
+
+
+def _ptr(t):
+    return c_void_p(t.data_ptr()) if t is not None else c_void_p(0)
+
+
+class Bank:
+    def __init__(self, ctx, handle, n_filters):
+        self.ctx, self.handle, self.n_filters = ctx, handle, n_filters
+
+    def close(self):
+        if self.handle:
+            load_library().dlco_bank_destroy(self.ctx.handle, self.handle)
+            self.handle = None
+
+
+class Context:
+    """One per GPU (reference: cuda::setDevice(0), src/comp-fulldists.cpp:278)."""
+
+    def __init__(self, device=0):
+        import torch
+        self.torch = torch
+        self.lib = load_library()
+        h = c_void_p()
+        _check(self.lib.dlco_init(device, ctypes.byref(h)))
+        self.handle = h
+        self.device = torch.device("cuda", device)
+        self.use_torch_stream()
+
+    def use_torch_stream(self):
+        s = self.torch.cuda.current_stream(self.device)
+        _check(self.lib.dlco_set_stream(self.handle, c_void_p(s.cuda_stream)))
+
+    def close(self):
+        if self.handle:
+            self.lib.dlco_shutdown(self.handle)
+            self.handle = None
+
+    def sync(self):
+        _check(self.lib.dlco_sync(self.handle))
+
+    def launch_count(self):
+        return int(self.lib.dlco_launch_count(self.handle))
+
+    def device_name(self):
+        buf = ctypes.create_string_buffer(256)
+        ma, mi = c_int(), c_int()
+        _check(self.lib.dlco_device_name(self.handle, buf, 256, ctypes.byref(ma), ctypes.byref(mi)))
+        return buf.value.decode(), ma.value, mi.value
+
+    # ---- filter bank -------------------------------------------------------------------
+    def bank(self, filters):
+        """filters: (nF, 4096) float32, numpy (host) or torch cuda tensor."""
+        torch = self.torch
+        h = c_void_p()
+        if isinstance(filters, torch.Tensor) and filters.is_cuda:
+            f = filters.contiguous().float()
+            _check(self.lib.dlco_bank_create_dev(self.handle, _ptr(f), f.shape[0], ctypes.byref(h)))
+            torch.cuda.synchronize(self.device)
+            return Bank(self, h, f.shape[0])
+        import numpy as np
+        f = np.ascontiguousarray(filters, dtype=np.float32).reshape(len(filters), -1)
+        assert f.shape[1] == 4096
+        _check(self.lib.dlco_bank_create(self.handle, f.ctypes.data_as(c_void_p), f.shape[0], ctypes.byref(h)))
+        return Bank(self, h, f.shape[0])
+
+    # ---- get_desc: src/vgg-desc.cpp:41-152 -----------------------------------------------
+    def get_desc(self, patches, ids, n_bins=8, sigma=1.4, b_norm=True):
+        torch = self.torch
+        out = torch.empty((ids.numel(), 4096, 8), dtype=torch.float32, device=self.device)
+        _check(self.lib.dlco_get_desc(self.handle, _ptr(patches), _ptr(ids), ids.numel(), n_bins,
+                                      sigma, int(b_norm), _ptr(out)))
+        return out
+
+    # ---- comp-fulldists: src/comp-fulldists.cpp:294-356 ----------------------------------
+    def fulldist_build(self, bank, patches, indices, lo=0, hi=None, n_bins=8, sigma=1.4, b_norm=True,
+                       out=None):
+        torch = self.torch
+        hi = indices.shape[0] if hi is None else hi
+        rings = bank.n_filters // 8
+        if out is None:
+            out = torch.empty((hi - lo, rings), dtype=torch.float32, device=self.device)
+        _check(self.lib.dlco_fulldist_build(self.handle, bank.handle, _ptr(patches), _ptr(indices), lo, hi,
+                                            n_bins, sigma, int(b_norm), _ptr(out), out.stride(0)))
+        return out
+
+    def fulldist_build_host(self, bank, patches, indices, lo=0, hi=None, n_bins=8, sigma=1.4,
+                            b_norm=True, out=None):
+        """patches / indices / out are HOST tensors (ideally pinned)."""
+        torch = self.torch
+        hi = indices.shape[0] if hi is None else hi
+        rings = bank.n_filters // 8
+        if out is None:
+            out = torch.empty((hi - lo, rings), dtype=torch.float32).pin_memory()
+        _check(self.lib.dlco_fulldist_build_host(self.handle, bank.handle, _ptr(patches), patches.shape[0],
+                                                 _ptr(indices), lo, hi, n_bins, sigma, int(b_norm),
+                                                 _ptr(out), out.stride(0)))
+        return out
+
+    def pair_labels(self, indices):
+        out = self.torch.empty((indices.shape[0],), dtype=self.torch.uint8, device=self.device)
+        _check(self.lib.dlco_pair_labels(self.handle, _ptr(indices), indices.shape[0], _ptr(out)))
+        return out
+
+    # ---- comp-uprjdists: src/comp-uprjdists.cpp:298-335 ----------------------------------
+    def uprjdist_build(self, bank, patches, indices, lo=0, hi=None, n_bins=8, sigma=1.4, b_norm=True):
+        torch = self.torch
+        hi = indices.shape[0] if hi is None else hi
+        out = torch.empty((hi - lo, bank.n_filters * 8), dtype=torch.float32, device=self.device)
+        _check(self.lib.dlco_uprjdist_build(self.handle, bank.handle, _ptr(patches), _ptr(indices), lo, hi,
+                                            n_bins, sigma, int(b_norm), _ptr(out), out.stride(0)))
+        return out
+
+    # ---- SubtractVectorsByRows + sum: src/kernelop-opencv.cu:49-80 -------------------------
+    def hinge_pairsum(self, pos, neg, margin=1.0):
+        s = c_double()
+        _check(self.lib.dlco_hinge_pairsum(self.handle, _ptr(pos), pos.numel(), _ptr(neg), neg.numel(),
+                                           margin, ctypes.byref(s)))
+        return s.value

@@ -1,0 +1,172 @@
+// comp-fulldists / comp-uprjdists loop bodies behind the C ABI: batching, descriptor kernel,
+// pooling kernel.  Reference: src/comp-fulldists.cpp:294-356, src/comp-uprjdists.cpp:298-335.
+#include "common.cuh"
+#include "kernels.h"
+#include <stdlib.h>
+
+static int env_int(const char *name, int dflt)
+{
+    const char *s = getenv(name);
+    if (!s || !*s) return dflt;
+    int v = atoi(s);
+    return v > 0 ? v : dflt;
+}
+
+// pairs per batch: 16 pair-tiles of the tensor-core kernel by default (B operand = 128 MB)
+static int batch_pairs() { return (env_int("DLCO_FULLDIST_BATCH", 256) + 15) / 16 * 16; }
+// DLCO_POOL_IMPL=simt routes the full-distance pooling through the SIMT cross-check kernel
+static bool use_simt()
+{
+    const char *s = getenv("DLCO_POOL_IMPL");
+    return s && strcmp(s, "simt") == 0;
+}
+
+__global__ void k_pair_labels(const int32_t *__restrict__ idx, int64_t n, uint8_t *__restrict__ lab)
+{
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) lab[i] = idx[i * 4 + 1] == idx[i * 4 + 3] ? 1 : 0;
+}
+
+extern "C" int dlco_pair_labels(dlco_ctx *ctx, const int32_t *d_indices, int64_t n, uint8_t *d_label)
+{
+    DLCO_REQUIRE(ctx && d_indices && d_label && n >= 0, "dlco_pair_labels: bad arguments");
+    if (n == 0) return DLCO_OK;
+    k_pair_labels<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(d_indices, n, d_label);
+    DLCO_CHECK_LAUNCH(ctx);
+    return DLCO_OK;
+}
+
+static int check_common(dlco_ctx *ctx, const dlco_bank *bank, const void *patches, const void *idx,
+                        int64_t lo, int64_t hi, int nbins, const void *out, const char *who)
+{
+    DLCO_REQUIRE(ctx && bank && patches && idx && out, "%s: NULL argument", who);
+    DLCO_REQUIRE(lo >= 0 && hi >= lo, "%s: bad pair range [%lld,%lld)", who, (long long)lo, (long long)hi);
+    DLCO_REQUIRE(nbins == DLCO_NBINS, "%s: only %d orientation bins supported (got %d)", who, DLCO_NBINS, nbins);
+    return DLCO_OK;
+}
+
+// one batch, everything on device: pairs [0,n) of d_idx (N x 4 rows) -> d_out rows
+static int fulldist_batch(dlco_ctx *ctx, const dlco_bank *bank, const uint8_t *d_patches,
+                          const int32_t *d_idx, int n, int nbins, float sigma, int bnorm,
+                          float *d_out, int64_t ld_out)
+{
+    const int npad = (n + 15) / 16 * 16;
+    const size_t plane = (size_t)npad * 16 * 4096 * sizeof(float);
+    int r;
+    if (use_simt()) {
+        float *rows = (float *)dlco_scratch(ctx, 0, plane);
+        if (!rows) return DLCO_ENOMEM;
+        r = dlco_launch_desc(ctx, DESC_OUT_ROWS, d_patches, d_idx, 4, 2 * n, 2 * n, nbins, sigma, bnorm, rows, nullptr);
+        if (r != DLCO_OK) return r;
+        return dlco_launch_pool_simt(ctx, 0, bank->d_f32, bank->nF, rows, n, d_out, ld_out);
+    }
+    float *bhi = (float *)dlco_scratch(ctx, 0, plane);
+    float *blo = (float *)dlco_scratch(ctx, 1, plane);
+    if (!bhi || !blo) return DLCO_ENOMEM;
+    r = dlco_launch_desc(ctx, DESC_OUT_SPLIT, d_patches, d_idx, 4, 2 * n, 2 * npad, nbins, sigma, bnorm, bhi, blo);
+    if (r != DLCO_OK) return r;
+    return dlco_launch_pool_tc(ctx, bank, bhi, blo, n, npad, d_out, ld_out);
+}
+
+extern "C" int dlco_fulldist_build(dlco_ctx *ctx, const dlco_bank *bank, const uint8_t *d_patches,
+                                   const int32_t *d_indices, int64_t lo, int64_t hi, int nAngleBins,
+                                   float sigma, int bNorm, float *d_out, int64_t ld_out)
+{
+    int r = check_common(ctx, bank, d_patches, d_indices, lo, hi, nAngleBins, d_out, "dlco_fulldist_build");
+    if (r != DLCO_OK) return r;
+    DLCO_REQUIRE(ld_out >= bank->nF / 8, "dlco_fulldist_build: ld_out=%lld < %d rings", (long long)ld_out, bank->nF / 8);
+    const int nb = batch_pairs();
+    for (int64_t p = lo; p < hi; p += nb) {
+        int n = (int)((hi - p) < nb ? (hi - p) : nb);
+        r = fulldist_batch(ctx, bank, d_patches, d_indices + p * 4, n, nAngleBins, sigma, bNorm,
+                           d_out + (p - lo) * ld_out, ld_out);
+        if (r != DLCO_OK) return r;
+    }
+    return DLCO_OK;
+}
+
+extern "C" int dlco_fulldist_build_host(dlco_ctx *ctx, const dlco_bank *bank, const uint8_t *h_patches,
+                                        int64_t nPatches, const int32_t *h_indices, int64_t lo,
+                                        int64_t hi, int nAngleBins, float sigma, int bNorm,
+                                        float *h_out, int64_t ld_out)
+{
+    int r = check_common(ctx, bank, h_patches, h_indices, lo, hi, nAngleBins, h_out, "dlco_fulldist_build_host");
+    if (r != DLCO_OK) return r;
+    const int rings = bank->nF / 8;
+    DLCO_REQUIRE(ld_out >= rings, "dlco_fulldist_build_host: ld_out too small");
+    DLCO_CUDA(cudaSetDevice(ctx->device));
+    const int nb = batch_pairs();
+    // staging: per slot, 2*nb patches (pair order) + nb index rows rewritten to local ids
+    const size_t pbytes = (size_t)nb * 2 * 4096, ibytes = (size_t)nb * 4 * sizeof(int32_t);
+    uint8_t *h_stage[2];
+    for (int s = 0; s < 2; s++) {
+        h_stage[s] = (uint8_t *)dlco_pinned(ctx, s, pbytes + ibytes);
+        if (!h_stage[s]) return DLCO_ENOMEM;
+    }
+    uint8_t *d_stage = (uint8_t *)dlco_scratch(ctx, 2, 2 * (pbytes + ibytes));
+    float *d_o = (float *)dlco_scratch(ctx, 3, (size_t)nb * rings * sizeof(float));
+    if (!d_stage || !d_o) return DLCO_ENOMEM;
+    cudaEvent_t ev[2];
+    for (int s = 0; s < 2; s++) DLCO_CUDA(cudaEventCreateWithFlags(&ev[s], cudaEventDisableTiming));
+    int rc = DLCO_OK;
+    int64_t bi = 0;
+    for (int64_t p = lo; p < hi && rc == DLCO_OK; p += nb, bi++) {
+        const int s = (int)(bi & 1);
+        const int n = (int)((hi - p) < nb ? (hi - p) : nb);
+        if (bi >= 2) cudaEventSynchronize(ev[s]);     // slot's previous upload has been consumed
+        uint8_t *hp = h_stage[s];
+        int32_t *hi_ = (int32_t *)(h_stage[s] + pbytes);
+        for (int k = 0; k < n; k++) {
+            const int32_t *row = h_indices + (p + k) * 4;
+            if (row[0] < 0 || row[0] >= nPatches || row[2] < 0 || row[2] >= nPatches) {
+                dlco_set_error("dlco_fulldist_build_host: pair %lld references patch outside [0,%lld)",
+                               (long long)(p + k), (long long)nPatches);
+                rc = DLCO_EINVAL;
+                break;
+            }
+            memcpy(hp + (size_t)(2 * k) * 4096, h_patches + (size_t)row[0] * 4096, 4096);
+            memcpy(hp + (size_t)(2 * k + 1) * 4096, h_patches + (size_t)row[2] * 4096, 4096);
+            hi_[4 * k + 0] = 2 * k;
+            hi_[4 * k + 1] = row[1];
+            hi_[4 * k + 2] = 2 * k + 1;
+            hi_[4 * k + 3] = row[3];
+        }
+        if (rc != DLCO_OK) break;
+        uint8_t *dp = d_stage + (size_t)s * (pbytes + ibytes);
+        cudaError_t e = cudaMemcpyAsync(dp, hp, pbytes + ibytes, cudaMemcpyHostToDevice, ctx->stream);
+        if (e == cudaSuccess) e = cudaEventRecord(ev[s], ctx->stream);
+        if (e != cudaSuccess) { dlco_set_error("upload failed: %s", cudaGetErrorString(e)); rc = DLCO_ECUDA; break; }
+        rc = fulldist_batch(ctx, bank, dp, (const int32_t *)(dp + pbytes), n, nAngleBins, sigma, bNorm, d_o, rings);
+        if (rc != DLCO_OK) break;
+        e = cudaMemcpy2DAsync(h_out + (p - lo) * ld_out, (size_t)ld_out * sizeof(float), d_o,
+                              (size_t)rings * sizeof(float), (size_t)rings * sizeof(float), n,
+                              cudaMemcpyDeviceToHost, ctx->stream);
+        if (e != cudaSuccess) { dlco_set_error("download failed: %s", cudaGetErrorString(e)); rc = DLCO_ECUDA; }
+    }
+    cudaError_t e = cudaStreamSynchronize(ctx->stream);
+    if (rc == DLCO_OK && e != cudaSuccess) { dlco_set_error("fulldist_build_host: %s", cudaGetErrorString(e)); rc = DLCO_ECUDA; }
+    for (int s = 0; s < 2; s++) cudaEventDestroy(ev[s]);
+    return rc;
+}
+
+extern "C" int dlco_uprjdist_build(dlco_ctx *ctx, const dlco_bank *bank, const uint8_t *d_patches,
+                                   const int32_t *d_indices, int64_t lo, int64_t hi, int nAngleBins,
+                                   float sigma, int bNorm, float *d_out, int64_t ld_out)
+{
+    int r = check_common(ctx, bank, d_patches, d_indices, lo, hi, nAngleBins, d_out, "dlco_uprjdist_build");
+    if (r != DLCO_OK) return r;
+    DLCO_REQUIRE(ld_out >= (int64_t)bank->nF * 8, "dlco_uprjdist_build: ld_out=%lld < 8*nSel=%d",
+                 (long long)ld_out, bank->nF * 8);
+    const int nb = batch_pairs();
+    for (int64_t p = lo; p < hi; p += nb) {
+        int n = (int)((hi - p) < nb ? (hi - p) : nb);
+        float *rows = (float *)dlco_scratch(ctx, 0, (size_t)n * 16 * 4096 * sizeof(float));
+        if (!rows) return DLCO_ENOMEM;
+        r = dlco_launch_desc(ctx, DESC_OUT_ROWS, d_patches, d_indices + p * 4, 4, 2 * n, 2 * n, nAngleBins,
+                             sigma, bNorm, rows, nullptr);
+        if (r != DLCO_OK) return r;
+        r = dlco_launch_pool_simt(ctx, 1, bank->d_f32, bank->nF, rows, n, d_out + (p - lo) * ld_out, ld_out);
+        if (r != DLCO_OK) return r;
+    }
+    return DLCO_OK;
+}

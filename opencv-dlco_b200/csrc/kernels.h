@@ -1,0 +1,30 @@
+// Internal launch interfaces between the translation units of libdlco_b200.
+#pragma once
+#include "common.cuh"
+
+enum { DESC_OUT_PT = 0, DESC_OUT_ROWS = 1, DESC_OUT_SPLIT = 2 };
+
+// desc.cu: one CTA per slot; slots >= n_slots (padding) are zero-filled in ROWS/SPLIT mode.
+// id_stride 4: d_ids is the N x 4 "Indices" matrix, slot s = (row s/2, column 0 or 2).
+int dlco_launch_desc(dlco_ctx *ctx, int mode, const uint8_t *d_patches, const int32_t *d_ids,
+                     int id_stride, int n_slots, int n_slots_padded, int nbins, float sigma,
+                     int bnorm, float *out0, float *out1);
+
+// api.cu
+int dlco_make_tmap_2d(CUtensorMap *map, const float *base, uint64_t rows, uint64_t cols,
+                      uint32_t box_rows, uint32_t box_cols);
+
+// pool_simt.cu: SIMT pooling over K-major descriptor rows (slot*8+bin) x 4096.
+//   mode 0: full distance  out[pair][ring]   (nF/8 per pair)
+//   mode 1: unprojected    out[pair][f*8+b]  = min(F.T1,1) - min(F.T2,1)
+int dlco_launch_pool_simt(dlco_ctx *ctx, int mode, const float *d_filters, int nF,
+                          const float *d_rows, int n_pairs, float *d_out, int64_t ld_out);
+
+// pool_tc.cu: tcgen05 3xTF32 pooling GEMM + fused full-distance epilogue
+int dlco_launch_pool_tc(dlco_ctx *ctx, const dlco_bank *bank, const float *d_bhi,
+                        const float *d_blo, int n_pairs, int n_pairs_padded, float *d_out,
+                        int64_t ld_out);
+
+// hinge.cu
+int dlco_hinge_pairsum_dev(dlco_ctx *ctx, const float *d_pos, int64_t n1, const float *d_neg,
+                           int64_t n2, float margin, double *d_sum);
