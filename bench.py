@@ -1,0 +1,415 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the DLCO hot path on B200.
+
+Workload (BASELINE.json configs[1]): comp-fulldists full build, 500k synthetic 64x64 patch
+pairs x the full gen-poolregion candidate set (5120 rings / 40960 filters) per GPU.
+One "step" = one pass of the whole 500k-pair build.  N>1: every rank builds its own 500k-pair
+shard of an N x 500k job (pairs are independent: no data-path collective, weak scaling).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--pairs P] [--impl b200|reference]
+
+Prints ONE JSON line (rank 0).  `value` = pairs/s with inputs resident in HBM; `e2e` = the same
+through dlco_fulldist_build_host (pinned host patches/indices in, distances out to pinned host
+memory, copies inside the timed region); `roofline` = the pooling GEMM kernel against the
+measured tensor peak; `cpu_baseline` = the oracle's CPU port on a bounded sample.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+RINGS, NFILT, K = 5120, 40960, 4096
+FLOP_PER_PAIR = 2.0 * 2 * NFILT * K * 8          # dense-equivalent fp32 flops
+GTX970_PAIRS_PER_S = 35.5                        # reference's own GPU path, derived from mtimes
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+# --------------------------------------------------------------------------------------------
+# synthetic inputs (torch, on device): same shapes / layouts as conv-impatches + gen-poolregion
+# --------------------------------------------------------------------------------------------
+def synth_bank(torch, dev):
+    """gen-poolregion-shaped bank (src/gen-poolregion.cpp:51-80,189-213,247-257), float64 math,
+    box-truncated Gaussians normalised to unit sum; an input generator, not the oracle."""
+    import math
+    sig = torch.arange(1, 33, dtype=torch.float64, device=dev) * 0.5
+    phi = torch.arange(0, 5, dtype=torch.float64, device=dev) * (math.pi / 16)
+    r = torch.arange(0, 32, dtype=torch.float64, device=dev)
+    S, Ph, R = torch.meshgrid(sig, phi, r, indexing="ij")
+    S, Ph, R = S.reshape(-1), Ph.reshape(-1), R.reshape(-1)
+    xc, yc = R * torch.cos(Ph), R * torch.sin(Ph)
+    o0 = torch.stack([yc, yc, -yc, -yc, xc, xc, -xc, -xc], 1).reshape(-1)
+    o1 = torch.stack([xc, -xc, xc, -xc, yc, -yc, -yc, yc], 1).reshape(-1)
+    sg = S.repeat_interleave(8)
+    x0, y0 = o1, o0                                   # get_PR_filter(ps, Offsets[:,1], Offsets[:,0], s)
+    grid = torch.arange(64, dtype=torch.float64, device=dev) - 31.5
+    out = torch.empty((NFILT, K), dtype=torch.float32, device=dev)
+    for a in range(0, NFILT, 4096):
+        b = a + 4096
+        dx = grid[None, :] - x0[a:b, None]
+        dy = grid[None, :] - y0[a:b, None]
+        s = sg[a:b, None]
+        mx = dx.abs() <= 3 * s + 1
+        my = dy.abs() <= 3 * s + 1
+        gx = torch.exp(-dx * dx / (2 * s * s)) * mx
+        gy = torch.exp(-dy * dy / (2 * s * s)) * my
+        f = gx[:, :, None] * gy[:, None, :]
+        f = f / f.sum(dim=(1, 2), keepdim=True)
+        out[a:b] = f.reshape(-1, K).float()
+    return out
+
+
+def synth_patches(torch, dev, n_points, per_point=3, seed=20240601):
+    g = torch.Generator(device=dev)
+    g.manual_seed(seed)
+    P = n_points * per_point
+    out = torch.empty((P, 64, 64), dtype=torch.uint8, device=dev)
+    chunk = 8192
+    for a in range(0, n_points, chunk):
+        n = min(chunk, n_points - a)
+        low = torch.randn((n, 1, 8, 8), generator=g, device=dev)
+        base = torch.nn.functional.interpolate(low, size=(64, 64), mode="bicubic", align_corners=False)
+        base = base.repeat_interleave(per_point, dim=0)
+        gain = 0.8 + 0.4 * torch.rand((n * per_point, 1, 1, 1), generator=g, device=dev)
+        img = 128 + 55 * gain * base + 4 * torch.randn(base.shape, generator=g, device=dev)
+        out[a * per_point:(a + n) * per_point] = img.clamp(0, 255).round().to(torch.uint8)[:, 0]
+    return out
+
+
+def synth_pairs(torch, dev, n_points, per_point, n_pairs, seed=20240602):
+    g = torch.Generator(device=dev)
+    g.manual_seed(seed)
+    P = n_points * per_point
+    a = torch.randint(0, P, (n_pairs,), generator=g, device=dev)
+    pos = torch.arange(n_pairs, device=dev) % 2 == 0
+    sib = (a // per_point) * per_point + (a % per_point + torch.randint(1, per_point, (n_pairs,), generator=g, device=dev)) % per_point
+    rnd = torch.randint(0, P, (n_pairs,), generator=g, device=dev)
+    rnd = torch.where(rnd // per_point == a // per_point, (rnd + per_point) % P, rnd)
+    b = torch.where(pos, sib, rnd)
+    idx = torch.stack([a, a // per_point, b, b // per_point], 1).to(torch.int32)
+    return idx.contiguous()
+
+
+# --------------------------------------------------------------------------------------------
+# clocks sampler (nvidia-smi) during the timed region
+# --------------------------------------------------------------------------------------------
+class Clocks:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.p = index, None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                       "--format=csv,noheader,nounits", "-lms", "200"],
+                                      stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            self.p = None
+
+    def stop(self):
+        if not self.p:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.p.terminate()
+        try:
+            out, _ = self.p.communicate(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+            out, _ = self.p.communicate()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in out.splitlines():
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# --------------------------------------------------------------------------------------------
+# CPU arm: the oracle's port of src/comp-fulldists.cpp:320-342 (get_desc on CPU, SGEMM pooling
+# through numpy/OpenBLAS with every host thread, clamp, diff^2, two reductions)
+# --------------------------------------------------------------------------------------------
+def _desc_worker(p):
+    from oracle import dlco_oracle as O
+    return O.get_desc(p)
+
+
+def cpu_fulldist(filters, patches, idx, pool=None, chunk=128):
+    """Per pair: get_desc x2, SGEMM (40960x4096)(4096x8) x2, min, diff^2, two reductions --
+    the reference's per-pair work (no de-duplication of repeated patches), batched over
+    `chunk` pairs per SGEMM call so OpenBLAS can use every core."""
+    from oracle import dlco_oracle as O
+    out = np.empty((len(idx), filters.shape[0] // 8), np.float32)
+    for c0 in range(0, len(idx), chunk):
+        sub = idx[c0:c0 + chunk]
+        slots = [patches[i] for row in sub for i in (row[0], row[2])]
+        if pool is not None:
+            descs = pool.map(_desc_worker, slots, chunksize=8)
+        else:
+            descs = [O.get_desc(p) for p in slots]
+        T = np.concatenate(descs, axis=1)                        # 4096 x (16 * n)
+        Pm = np.minimum(filters @ T, np.float32(1.0))             # SGEMM + clamp
+        Pm = Pm.reshape(filters.shape[0], len(sub), 2, 8)
+        d = Pm[:, :, 1, :] - Pm[:, :, 0, :]
+        l2 = (d * d).sum(axis=2)                                  # 40960 x n
+        out[c0:c0 + len(sub)] = l2.reshape(-1, 8, len(sub)).sum(axis=1).T
+    return out
+
+
+def cpu_arm_setup():
+    import ctypes
+    from oracle import dlco_oracle as O
+    lib_path = os.path.join(ROOT, "oracle", "libdlco_oracle.so")
+    if not os.path.exists(lib_path):
+        subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle")], stdout=subprocess.DEVNULL)
+    lib = ctypes.CDLL(lib_path)
+    rings = O.ring_params()
+    filt = np.zeros((NFILT, K), np.float32)
+    lib.dlco_oracle_pr_bank(64, RINGS, rings.ctypes.data_as(ctypes.c_void_p),
+                            filt.ctypes.data_as(ctypes.c_void_p), None)
+    patches, pid = O.synth_patches(48, per_point=3, seed=5)
+    return filt, patches, pid
+
+
+def cpu_time_sample(filt, patches, pid, n_pairs, pool, seed):
+    from oracle import dlco_oracle as O
+    idx = O.synth_pairs(pid, n_pairs, seed=seed)
+    t = time.perf_counter()
+    cpu_fulldist(filt, patches, idx, pool)
+    return time.perf_counter() - t
+
+
+def run_cpu_baseline(target_s=12.0):
+    import multiprocessing as mp
+    cores = os.cpu_count() or 1
+    filt, patches, pid = cpu_arm_setup()
+    pool = mp.get_context("fork").Pool(min(cores, 32))
+    try:
+        t0 = cpu_time_sample(filt, patches, pid, 16, pool, 1)            # calibrate (+ warm BLAS)
+        n = int(max(16, min(2048, 16 * target_s / max(t0, 1e-3))))
+        dt = cpu_time_sample(filt, patches, pid, n, pool, 2)
+    finally:
+        pool.close()
+    return {"value": n / dt, "unit": "pairs/s", "cores": cores, "kind": "port",
+            "sample": "%d pairs x 5120 rings (get_desc on %d procs + OpenBLAS SGEMM 40960x4096x%d), %.1f s"
+                      % (n, min(cores, 32), 16 * n, dt)}
+
+
+def run_reference_arm(args, rank):
+    """--impl reference: the CPU implementation timed alone (rank 0 only)."""
+    if rank != 0:
+        return
+    import multiprocessing as mp
+    cores = os.cpu_count() or 1
+    filt, patches, pid = cpu_arm_setup()
+    pool = mp.get_context("fork").Pool(min(cores, 32))
+    try:
+        t0 = cpu_time_sample(filt, patches, pid, 16, pool, 1)
+        n = int(max(16, min(1024, 16 * 6.0 / max(t0, 1e-3))))          # ~6 s per step
+        for i in range(args.warmup):
+            cpu_time_sample(filt, patches, pid, n, pool, 10 + i)
+        tt = 0.0
+        for i in range(args.steps):
+            tt += cpu_time_sample(filt, patches, pid, n, pool, 100 + i)
+    finally:
+        pool.close()
+    v = n * args.steps / tt
+    line = {
+        "impl": "reference", "metric": "full-dist pairs/s", "value": v, "unit": "pairs/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": tt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "comp-fulldists full build, 500k pairs x 5120 rings (40960 filters) per GPU; "
+                               "CPU arm timed on a bounded sample of %d pairs per step" % n},
+        "cpu_baseline": {"value": v, "unit": "pairs/s", "cores": cores, "kind": "port",
+                         "sample": "%d pairs/step: oracle get_desc + OpenBLAS SGEMM pooling, all host threads" % n},
+        "e2e": {"value": v, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--pairs", type=int, default=500000)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if args.impl == "reference":
+        run_reference_arm(args, rank)
+        return
+
+    import torch
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the DLCO hot path has no CPU fallback "
+                         "(use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    import dlco_b200
+    ctx = dlco_b200.Context(local)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    n_pairs = args.pairs
+    per_point = 3
+    n_points = max(64, int(n_pairs * 0.9) // per_point)      # ~Liberty: 450k patches for 500k pairs
+    t_setup = time.time()
+    bank_t = synth_bank(torch, dev)
+    bank = ctx.bank(bank_t)
+    del bank_t
+    patches = synth_patches(torch, dev, n_points, per_point, seed=20240601 + rank)
+    idx = synth_pairs(torch, dev, n_points, per_point, n_pairs, seed=20240602 + rank)
+    out = torch.empty((n_pairs, RINGS), dtype=torch.float32, device=dev)
+    torch.cuda.synchronize(dev)
+    log("[bench] rank %d setup %.1fs: %d patches, %d pairs" % (rank, time.time() - t_setup, patches.shape[0], n_pairs))
+
+    def step():
+        ctx.fulldist_build(bank, patches, idx, out=out)
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    clocks = Clocks(local)
+    if rank == 0:
+        clocks.start()
+    ctx.profile(True)
+    l0 = ctx.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        step()
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = ctx.launch_count() - l0
+    pool_ms, pool_n = ctx.profile_read(1)
+    desc_ms, desc_n = ctx.profile_read(0)
+    ctx.profile(False)
+    clk = clocks.stop() if rank == 0 else None
+    checksum = float(out[:: max(1, n_pairs // 1000)].double().sum().item())
+    if not np.isfinite(checksum):
+        raise SystemExit("bench.py: non-finite distances")
+
+    tmax = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+    ms_max = float(tmax.item())
+    value = world * n_pairs * args.steps / (ms_max * 1e-3)
+
+    # ---- end to end through the host-buffer entry point -------------------------------------
+    e2e = None
+    if not args.no_e2e:
+        h_patches = patches.cpu().pin_memory()
+        h_idx = idx.cpu().pin_memory()
+        del out
+        torch.cuda.empty_cache()
+        h_out = torch.empty((n_pairs, RINGS), dtype=torch.float32).pin_memory()
+        e2e_steps = max(1, min(args.steps, 2))
+        ctx.fulldist_build_host(bank, h_patches, h_idx, 0, min(n_pairs, 4096), out=h_out)   # warm-up
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            ctx.fulldist_build_host(bank, h_patches, h_idx, out=h_out)
+        torch.cuda.synchronize(dev)
+        dt = time.perf_counter() - t0
+        te = torch.tensor([dt], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(te, op=dist.ReduceOp.MAX)
+        e2e = {"value": world * n_pairs * e2e_steps / float(te.item()), "unit": "pairs/s",
+               "h2d_bytes_per_step": n_pairs * (2 * 4096 + 16), "d2h_bytes_per_step": n_pairs * RINGS * 4,
+               "steps": e2e_steps, "host_checksum": float(h_out[:: max(1, n_pairs // 1000)].double().sum().item())}
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except (OSError, ValueError):
+        pass
+    bf16 = peaks.get("bf16_tflops_sustained")
+    peak_src = "MEASURED_PEAKS.json bf16_tflops_sustained / 2 (tf32 issues at half the bf16 rate)"
+    if not bf16:
+        bf16, peak_src = 1400.0, "fallback 1.4 PFLOP/s sustained bf16 / 2 (B200_PROFILING.md)"
+    tf32_peak = bf16 / 2.0
+    pairs_per_launch = n_pairs * args.steps / max(pool_n, 1)
+    avg_ms = pool_ms / max(pool_n, 1)
+    issued_tflops = 3.0 * FLOP_PER_PAIR * pairs_per_launch / (avg_ms * 1e-3) / 1e12 if pool_n else None
+    roofline = {
+        "bound": "tensor", "kernel": "k_pool_fulldist (tcgen05 kind::tf32, 3xTF32)",
+        "achieved": issued_tflops, "peak": tf32_peak, "unit": "TFLOP/s",
+        "frac": (issued_tflops / tf32_peak) if issued_tflops else None, "traffic": None,
+        "peak_source": peak_src, "launches": pool_n, "avg_launch_ms": avg_ms,
+        "fp32_equiv_tflops": issued_tflops / 3.0 if issued_tflops else None,
+        "kernel_share_of_step": pool_ms / ms if ms else None,
+        "desc_kernel_ms_total": desc_ms, "desc_launches": desc_n,
+        "out_stream_gbs": n_pairs * args.steps * (RINGS * 4 + 8192) / (ms * 1e-3) / 1e9,
+    }
+    cpu = None
+    if world == 1 and not args.no_cpu:
+        try:
+            cpu = run_cpu_baseline()
+        except Exception as ex:  # the GPU line must still be printed
+            cpu = {"value": None, "unit": "pairs/s", "cores": os.cpu_count(), "kind": "port",
+                   "sample": "failed: %r" % (ex,)}
+    line = {
+        "metric": "full-dist pairs/s", "value": value, "unit": "pairs/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_max / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": "comp-fulldists full build: %d synthetic 64x64 patch pairs x 5120 rings "
+                               "(40960 filters) per GPU, pair-sharded" % n_pairs,
+                   "pairs_per_gpu": n_pairs, "filters": NFILT, "arith": "3xTF32 on tcgen05, fp32 accumulate",
+                   "l2": "inputs larger than L2 (1.34 GB filter planes streamed per 256-pair batch)",
+                   "reference_gtx970_pairs_per_s": GTX970_PAIRS_PER_S},
+        "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
+        "cpu_baseline": cpu, "checksum": checksum,
+    }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

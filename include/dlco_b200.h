@@ -46,14 +46,21 @@ int dlco_shutdown(dlco_ctx *ctx);
 const char *dlco_last_error(void);
 int dlco_device_name(dlco_ctx *ctx, char *buf, int len, int *cc_major, int *cc_minor);
 int dlco_sync(dlco_ctx *ctx);
-/* use an existing stream (e.g. torch's current stream); NULL restores the ctx's own */
+/* run on an existing cudaStream_t (e.g. torch's current stream; NULL = the legacy default
+ * stream); dlco_use_own_stream() goes back to the ctx's private non-blocking stream */
 int dlco_set_stream(dlco_ctx *ctx, void *cuda_stream);
+int dlco_use_own_stream(dlco_ctx *ctx);
 int dlco_malloc(dlco_ctx *ctx, size_t bytes, void **d_ptr);
 int dlco_free(dlco_ctx *ctx, void *d_ptr);
 int dlco_memcpy_h2d(dlco_ctx *ctx, void *d_dst, const void *h_src, size_t bytes);
 int dlco_memcpy_d2h(dlco_ctx *ctx, void *h_dst, const void *d_src, size_t bytes);
 /* number of kernels this library launched on this ctx since init (bench "gpu_launches") */
 int64_t dlco_launch_count(dlco_ctx *ctx);
+/* per-kernel device timing with CUDA events on the launching stream (bench roofline):
+ * enable, run, then read total milliseconds and launch count of kernel class `which`
+ * (0 = get_desc, 1 = pooling GEMM, 2 = pj SYRK, 3 = pr GEMV / patch distances). */
+int dlco_profile_enable(dlco_ctx *ctx, int on);
+int dlco_profile_read(dlco_ctx *ctx, int which, double *h_ms, int64_t *h_count);
 
 /* ---- pool-region filter bank (prfilters.upload: src/comp-fulldists.cpp:281) ---------
  * h_filters: nF x 4096 f32, element index x*64+y as gen-poolregion writes it

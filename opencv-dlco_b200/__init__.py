@@ -25,11 +25,14 @@ SIGNATURES = {
     "dlco_device_name": (c_int, [c_void_p, c_char_p, c_int, P(c_int), P(c_int)]),
     "dlco_sync": (c_int, [c_void_p]),
     "dlco_set_stream": (c_int, [c_void_p, c_void_p]),
+    "dlco_use_own_stream": (c_int, [c_void_p]),
     "dlco_malloc": (c_int, [c_void_p, c_size_t, P(c_void_p)]),
     "dlco_free": (c_int, [c_void_p, c_void_p]),
     "dlco_memcpy_h2d": (c_int, [c_void_p, c_void_p, c_void_p, c_size_t]),
     "dlco_memcpy_d2h": (c_int, [c_void_p, c_void_p, c_void_p, c_size_t]),
     "dlco_launch_count": (c_int64, [c_void_p]),
+    "dlco_profile_enable": (c_int, [c_void_p, c_int]),
+    "dlco_profile_read": (c_int, [c_void_p, c_int, P(c_double), P(c_int64)]),
     "dlco_bank_create": (c_int, [c_void_p, c_void_p, c_int, P(c_void_p)]),
     "dlco_bank_create_dev": (c_int, [c_void_p, c_void_p, c_int, P(c_void_p)]),
     "dlco_bank_destroy": (c_int, [c_void_p, c_void_p]),
@@ -66,6 +69,7 @@ class DlcoError(RuntimeError):
 
 
 _lib = None
+MISSING = []
 
 
 def load_library():
@@ -78,7 +82,11 @@ def load_library():
         raise DlcoError("CUDA library %s is missing: build it first (no CPU fallback exists)" % LIB_PATH)
     lib = ctypes.CDLL(LIB_PATH)
     for name, (res, args) in SIGNATURES.items():
-        fn = getattr(lib, name)          # AttributeError if a declared symbol is not exported
+        try:
+            fn = getattr(lib, name)
+        except AttributeError:           # tests/test_abi.py asserts MISSING stays empty
+            MISSING.append(name)
+            continue
         fn.restype = res
         fn.argtypes = args
     _lib = lib
@@ -131,6 +139,14 @@ class Context:
 
     def launch_count(self):
         return int(self.lib.dlco_launch_count(self.handle))
+
+    def profile(self, on):
+        _check(self.lib.dlco_profile_enable(self.handle, int(on)))
+
+    def profile_read(self, which):
+        ms, cnt = c_double(), c_int64()
+        _check(self.lib.dlco_profile_read(self.handle, which, ctypes.byref(ms), ctypes.byref(cnt)))
+        return ms.value, cnt.value
 
     def device_name(self):
         buf = ctypes.create_string_buffer(256)

@@ -94,6 +94,11 @@ extern "C" int dlco_shutdown(dlco_ctx *ctx)
         if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
     for (int i = 0; i < 4; i++)
         if (ctx->pinned[i]) cudaFreeHost(ctx->pinned[i]);
+    if (ctx->prof_ev) {
+        for (int i = 0; i < 2 * ctx->prof_cap; i++) cudaEventDestroy(ctx->prof_ev[i]);
+        free(ctx->prof_ev);
+        free(ctx->prof_class);
+    }
     cudaStreamDestroy(ctx->own_stream);
     free(ctx);
     return DLCO_OK;
@@ -120,7 +125,14 @@ extern "C" int dlco_sync(dlco_ctx *ctx)
 extern "C" int dlco_set_stream(dlco_ctx *ctx, void *s)
 {
     DLCO_REQUIRE(ctx, "dlco_set_stream: ctx is NULL");
-    ctx->stream = s ? (cudaStream_t)s : ctx->own_stream;
+    ctx->stream = (cudaStream_t)s;
+    return DLCO_OK;
+}
+
+extern "C" int dlco_use_own_stream(dlco_ctx *ctx)
+{
+    DLCO_REQUIRE(ctx, "dlco_use_own_stream: ctx is NULL");
+    ctx->stream = ctx->own_stream;
     return DLCO_OK;
 }
 
@@ -161,6 +173,64 @@ extern "C" int dlco_memcpy_d2h(dlco_ctx *ctx, void *h, const void *d, size_t byt
 }
 
 extern "C" int64_t dlco_launch_count(dlco_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+// ---- event timing ----------------------------------------------------------------------
+static void prof_flush(dlco_ctx *ctx)
+{
+    if (ctx->prof_n == 0) return;
+    cudaStreamSynchronize(ctx->stream);
+    for (int i = 0; i < ctx->prof_n; i++) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, ctx->prof_ev[2 * i], ctx->prof_ev[2 * i + 1]) == cudaSuccess) {
+            ctx->prof_ms[ctx->prof_class[i]] += ms;
+            ctx->prof_cnt[ctx->prof_class[i]]++;
+        }
+    }
+    ctx->prof_n = 0;
+}
+
+void dlco_prof_begin(dlco_ctx *ctx, int which)
+{
+    if (!ctx->profile_on) return;
+    if (ctx->prof_n == ctx->prof_cap) prof_flush(ctx);
+    ctx->prof_class[ctx->prof_n] = which;
+    cudaEventRecord(ctx->prof_ev[2 * ctx->prof_n], ctx->stream);
+}
+
+void dlco_prof_end(dlco_ctx *ctx)
+{
+    if (!ctx->profile_on) return;
+    cudaEventRecord(ctx->prof_ev[2 * ctx->prof_n + 1], ctx->stream);
+    ctx->prof_n++;
+}
+
+extern "C" int dlco_profile_enable(dlco_ctx *ctx, int on)
+{
+    DLCO_REQUIRE(ctx, "dlco_profile_enable: ctx is NULL");
+    if (on && !ctx->prof_ev) {
+        ctx->prof_cap = 1024;
+        ctx->prof_ev = (cudaEvent_t *)calloc(2 * ctx->prof_cap, sizeof(cudaEvent_t));
+        ctx->prof_class = (int *)calloc(ctx->prof_cap, sizeof(int));
+        for (int i = 0; i < 2 * ctx->prof_cap; i++) DLCO_CUDA(cudaEventCreate(&ctx->prof_ev[i]));
+    }
+    if (!on) prof_flush(ctx);
+    if (on) {
+        memset(ctx->prof_ms, 0, sizeof(ctx->prof_ms));
+        memset(ctx->prof_cnt, 0, sizeof(ctx->prof_cnt));
+        ctx->prof_n = 0;
+    }
+    ctx->profile_on = on;
+    return DLCO_OK;
+}
+
+extern "C" int dlco_profile_read(dlco_ctx *ctx, int which, double *ms, int64_t *cnt)
+{
+    DLCO_REQUIRE(ctx && which >= 0 && which < 8, "dlco_profile_read: bad arguments");
+    prof_flush(ctx);
+    if (ms) *ms = ctx->prof_ms[which];
+    if (cnt) *cnt = ctx->prof_cnt[which];
+    return DLCO_OK;
+}
 
 // ---------------------------------------------------------------------------------------
 // filter bank

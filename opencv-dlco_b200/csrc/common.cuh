@@ -25,6 +25,13 @@ struct dlco_ctx {
     // pinned staging
     void *pinned[4];
     size_t pinned_bytes[4];
+    // optional per-kernel-class event timing (dlco_profile_*)
+    int profile_on;
+    cudaEvent_t *prof_ev;     // pairs (start, stop)
+    int *prof_class;
+    int prof_n, prof_cap;
+    double prof_ms[8];
+    int64_t prof_cnt[8];
     void *cusolver;       // cusolverDnHandle_t (lazy)
     void *cusolver_lib;   // dlopen handle
 };
@@ -41,6 +48,8 @@ struct dlco_bank {
 void dlco_set_error(const char *fmt, ...);
 void *dlco_scratch(dlco_ctx *ctx, int slot, size_t bytes);
 void *dlco_pinned(dlco_ctx *ctx, int slot, size_t bytes);
+void dlco_prof_begin(dlco_ctx *ctx, int which);
+void dlco_prof_end(dlco_ctx *ctx);
 
 #define DLCO_CUDA(call)                                                                     \
     do {                                                                                    \

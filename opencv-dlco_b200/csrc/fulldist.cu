@@ -63,9 +63,14 @@ static int fulldist_batch(dlco_ctx *ctx, const dlco_bank *bank, const uint8_t *d
     float *bhi = (float *)dlco_scratch(ctx, 0, plane);
     float *blo = (float *)dlco_scratch(ctx, 1, plane);
     if (!bhi || !blo) return DLCO_ENOMEM;
+    dlco_prof_begin(ctx, 0);
     r = dlco_launch_desc(ctx, DESC_OUT_SPLIT, d_patches, d_idx, 4, 2 * n, 2 * npad, nbins, sigma, bnorm, bhi, blo);
+    dlco_prof_end(ctx);
     if (r != DLCO_OK) return r;
-    return dlco_launch_pool_tc(ctx, bank, bhi, blo, n, npad, d_out, ld_out);
+    dlco_prof_begin(ctx, 1);
+    r = dlco_launch_pool_tc(ctx, bank, bhi, blo, n, npad, d_out, ld_out);
+    dlco_prof_end(ctx);
+    return r;
 }
 
 extern "C" int dlco_fulldist_build(dlco_ctx *ctx, const dlco_bank *bank, const uint8_t *d_patches,

@@ -75,7 +75,7 @@ def main():
     t = time.time()
     bank = ctx.bank(filt)
     print("full bank upload+split %.2fs" % (time.time() - t))
-    npairs = 512
+    npairs = int(os.environ.get('DIAG_PAIRS', '2048'))
     P2, pid2 = O.synth_patches(64, per_point=3, seed=11)
     idx2 = O.synth_pairs(pid2, npairs, seed=12)
     dP2 = torch.from_numpy(P2).to(dev)
@@ -95,7 +95,7 @@ def main():
     pt2 = ctx.get_desc(dP2, torch.arange(P2.shape[0], dtype=torch.int32, device=dev)).cpu().numpy()
     o = out.cpu().numpy()
     worst = 0
-    for k in (0, 100, 511):
+    for k in (0, 100, npairs - 1):
         w = O.full_distance(filt, pt2[idx2[k, 0]], pt2[idx2[k, 2]])
         worst = max(worst, np.abs(o[k] - w).max() / w.max())
     print("full bank sample row-rel err %.3e" % worst)
