@@ -58,14 +58,16 @@ int dlco_memcpy_d2h(dlco_ctx *ctx, void *h_dst, const void *d_src, size_t bytes)
 int64_t dlco_launch_count(dlco_ctx *ctx);
 /* per-kernel device timing with CUDA events on the launching stream (bench roofline):
  * enable, run, then read total milliseconds and launch count of kernel class `which`
- * (0 = get_desc, 1 = pooling GEMM, 2 = pj SYRK, 3 = pr GEMV / patch distances). */
+ * (0 = get_desc, 1 = pooling GEMM, 2 = pj SYRK, 3 = pr GEMV, 4 = pr RDA chain,
+ * 5 = pj margins / patch distances). */
 int dlco_profile_enable(dlco_ctx *ctx, int on);
 int dlco_profile_read(dlco_ctx *ctx, int which, double *h_ms, int64_t *h_count);
 
 /* ---- pool-region filter bank (prfilters.upload: src/comp-fulldists.cpp:281) ---------
  * h_filters: nF x 4096 f32, element index x*64+y as gen-poolregion writes it
  * (src/gen-poolregion.cpp:68).  The bank keeps the tf32 hi/lo planes the tensor-core
- * kernel consumes.  nF must be a multiple of 8 (8 members per ring). */
+ * kernel consumes.  The full-distance builder needs nF % 8 == 0 (8 members per ring);
+ * the unprojected builder takes any nF (SelectPRFilters output, 60 / 68 in practice). */
 int dlco_bank_create(dlco_ctx *ctx, const float *h_filters, int nF, dlco_bank **bank);
 int dlco_bank_create_dev(dlco_ctx *ctx, const float *d_filters, int nF, dlco_bank **bank);
 int dlco_bank_destroy(dlco_ctx *ctx, dlco_bank *bank);
@@ -112,6 +114,14 @@ int dlco_pr_rda_run(dlco_ctx *ctx, const float *d_dists, int64_t ld, int F,
                     const int32_t *d_idx_pos, int32_t nPosTrn, const int32_t *d_idx_neg,
                     int32_t nNegTrn, float mu, float gamma, uint64_t t0, uint64_t nSteps,
                     uint64_t *rng_state, float *d_w, float *d_dfavg);
+/* the same chain for nCfg (mu, gamma) configurations at once (one CTA each): every run of the
+ * reference's grid (workspace/04-prlearn.sh) draws the same RNG(2215) sample stream, so the
+ * sampled rows are shared.  d_w / d_dfavg: nCfg x F. */
+int dlco_pr_rda_run_grid(dlco_ctx *ctx, const float *d_dists, int64_t ld, int F,
+                         const int32_t *d_idx_pos, int32_t nPosTrn, const int32_t *d_idx_neg,
+                         int32_t nNegTrn, int nCfg, const float *h_mu, const float *h_gamma,
+                         uint64_t t0, uint64_t nSteps, uint64_t *rng_state, float *d_w,
+                         float *d_dfavg);
 /* validation objective: LossVal, Regul (src/pr-learn.cpp:340-358).  d_pos_rows/d_neg_rows
  * index rows of d_dists (the 20 % hold-out). */
 int dlco_pr_validate(dlco_ctx *ctx, const float *d_dists, int64_t ld, int F,
@@ -125,6 +135,13 @@ int dlco_pr_validate(dlco_ctx *ctx, const float *d_dists, int64_t ld, int F,
 int dlco_pj_rda_grad(dlco_ctx *ctx, const float *d_dists, int64_t ld, int D,
                      const int32_t *d_rows_pos, const int32_t *d_rows_neg, int szBatch,
                      const float *d_W, int rank, float *d_dLoss);
+/* nCfg configurations sharing one sampled batch (workspace/08-pjlearn.sh: same seed for every
+ * run): W of config g at d_W + g*w_stride with h_rank[g] rows, dLoss of config g at
+ * d_dLoss + g*D*D; one grouped SYRK launch. */
+int dlco_pj_rda_grad_grid(dlco_ctx *ctx, const float *d_dists, int64_t ld, int D,
+                          const int32_t *d_rows_pos, const int32_t *d_rows_neg, int szBatch,
+                          int nCfg, const float *d_W, int64_t w_stride, const int *h_rank,
+                          float *d_dLoss);
 /* dfAvg <- t/(t+1) dfAvg + dLoss/(b*b*(t+1));  A <- sym(-sqrt(t+1)/gamma (dfAvg + mu I))
  * (src/pj-learn.cpp:422-432) */
 int dlco_pj_rda_update(dlco_ctx *ctx, int D, uint64_t t, int szBatch, float mu, float gamma,
@@ -150,6 +167,12 @@ int dlco_pj_patchdist(dlco_ctx *ctx, const float *d_dists, int64_t N, int64_t ld
                       const float *d_W, int rank, float *d_pd);
 int dlco_roc_stats(dlco_ctx *ctx, const float *d_pd, const uint8_t *d_labels, int64_t N,
                    float *h_fpr95, double *h_auc);
+
+/* ---- utility: C (M x N) = A (M x K) . B (N x K)^T through the same tcgen05 3xTF32 kernel the
+ * pj-learn SYRK uses (fp32 row-major in and out); exported so the tensor-core path can be
+ * checked in isolation against an fp64 product. */
+int dlco_gemm3x_nt_f32(dlco_ctx *ctx, const float *d_A, int M, const float *d_B, int N, int K,
+                       float *d_C);
 
 #ifdef __cplusplus
 }

@@ -48,10 +48,15 @@ SIGNATURES = {
     "dlco_pr_rda_run": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_void_p, ctypes.c_int32, c_void_p,
                                 ctypes.c_int32, c_float, c_float, c_uint64, c_uint64, P(c_uint64),
                                 c_void_p, c_void_p]),
+    "dlco_pr_rda_run_grid": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_void_p, ctypes.c_int32, c_void_p,
+                                     ctypes.c_int32, c_int, c_void_p, c_void_p, c_uint64, c_uint64,
+                                     P(c_uint64), c_void_p, c_void_p]),
     "dlco_pr_validate": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_void_p, c_int64, c_void_p, c_int64,
                                  c_void_p, c_float, P(c_float), P(c_float)]),
     "dlco_pj_rda_grad": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_void_p, c_void_p, c_int, c_void_p,
                                  c_int, c_void_p]),
+    "dlco_pj_rda_grad_grid": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_void_p, c_void_p, c_int, c_int,
+                                      c_void_p, c_int64, c_void_p, c_void_p]),
     "dlco_pj_rda_update": (c_int, [c_void_p, c_int, c_uint64, c_int, c_float, c_float, c_void_p, c_void_p,
                                    c_void_p]),
     "dlco_pj_prox_apply": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, P(c_int)]),
@@ -60,6 +65,7 @@ SIGNATURES = {
                                  c_void_p, c_int, c_void_p, c_float, P(c_float), P(c_float)]),
     "dlco_pr_patchdist": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int, c_void_p, c_void_p]),
     "dlco_pj_patchdist": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int, c_void_p, c_int, c_void_p]),
+    "dlco_gemm3x_nt_f32": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_int, c_void_p]),
     "dlco_roc_stats": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, P(c_float), P(c_double)]),
 }
 
@@ -223,3 +229,101 @@ class Context:
         _check(self.lib.dlco_hinge_pairsum(self.handle, _ptr(pos), pos.numel(), _ptr(neg), neg.numel(),
                                            margin, ctypes.byref(s)))
         return s.value
+
+    # ---- pr-learn: src/pr-learn.cpp:303-358 ----------------------------------------------
+    def pr_rda_run(self, dists, idx_pos, n_pos_trn, idx_neg, n_neg_trn, mu, gamma, t0, n_steps,
+                   rng_state, w, dfavg):
+        """Steps t0..t0+n_steps-1 of the l1/non-negative RDA; w, dfavg (F,) or (nCfg, F) float32
+        cuda tensors updated in place; mu/gamma scalars or sequences (one per config).
+        Returns the new cv::RNG state."""
+        import numpy as np
+        mus = np.atleast_1d(np.asarray(mu, np.float32))
+        gammas = np.atleast_1d(np.asarray(gamma, np.float32))
+        n_cfg = len(mus)
+        assert len(gammas) == n_cfg and w.numel() == n_cfg * dists.shape[1] == dfavg.numel()
+        st = c_uint64(rng_state)
+        _check(self.lib.dlco_pr_rda_run_grid(
+            self.handle, _ptr(dists), dists.stride(0), dists.shape[1], _ptr(idx_pos), n_pos_trn,
+            _ptr(idx_neg), n_neg_trn, n_cfg, mus.ctypes.data_as(c_void_p), gammas.ctypes.data_as(c_void_p),
+            t0, n_steps, ctypes.byref(st), _ptr(w), _ptr(dfavg)))
+        return st.value
+
+    def pr_validate(self, dists, pos_rows, neg_rows, w, mu):
+        loss, regul = c_float(), c_float()
+        _check(self.lib.dlco_pr_validate(self.handle, _ptr(dists), dists.stride(0), dists.shape[1],
+                                         _ptr(pos_rows), pos_rows.numel(), _ptr(neg_rows), neg_rows.numel(),
+                                         _ptr(w), mu, ctypes.byref(loss), ctypes.byref(regul)))
+        return loss.value, regul.value
+
+    # ---- pj-learn: src/pj-learn.cpp:311-527 ----------------------------------------------
+    def pj_rda_grad(self, dists, rows_pos, rows_neg, W, rank, out=None):
+        D = dists.shape[1]
+        if out is None:
+            out = self.torch.empty((D, D), dtype=self.torch.float32, device=self.device)
+        _check(self.lib.dlco_pj_rda_grad(self.handle, _ptr(dists), dists.stride(0), D, _ptr(rows_pos),
+                                         _ptr(rows_neg), rows_pos.numel(), _ptr(W), rank, _ptr(out)))
+        return out
+
+    def pj_rda_grad_grid(self, dists, rows_pos, rows_neg, W, ranks, out=None):
+        """W: (nCfg, Rmax, D) cuda tensor, ranks: list of ints; -> (nCfg, D, D)."""
+        D = dists.shape[1]
+        n_cfg = len(ranks)
+        if out is None:
+            out = self.torch.empty((n_cfg, D, D), dtype=self.torch.float32, device=self.device)
+        rk = (c_int * n_cfg)(*[int(r) for r in ranks])
+        _check(self.lib.dlco_pj_rda_grad_grid(self.handle, _ptr(dists), dists.stride(0), D, _ptr(rows_pos),
+                                              _ptr(rows_neg), rows_pos.numel(), n_cfg, _ptr(W),
+                                              W.stride(0) if W is not None else 0, rk, _ptr(out)))
+        return out
+
+    def pj_rda_update(self, t, sz_batch, mu, gamma, d_loss, dfavg, A):
+        _check(self.lib.dlco_pj_rda_update(self.handle, A.shape[0], t, sz_batch, mu, gamma, _ptr(d_loss),
+                                           _ptr(dfavg), _ptr(A)))
+
+    def pj_eig(self, A, evals=None, evecs=None):
+        torch = self.torch
+        D = A.shape[0]
+        evals = torch.empty((D,), dtype=torch.float32, device=self.device) if evals is None else evals
+        evecs = torch.empty((D, D), dtype=torch.float32, device=self.device) if evecs is None else evecs
+        _check(self.lib.dlco_pj_eig(self.handle, D, _ptr(A), _ptr(evals), _ptr(evecs)))
+        return evals, evecs
+
+    def pj_prox_apply(self, evals, evecs, A, W):
+        rank = c_int()
+        _check(self.lib.dlco_pj_prox_apply(self.handle, A.shape[0], _ptr(evals), _ptr(evecs), _ptr(A), _ptr(W),
+                                           ctypes.byref(rank)))
+        return rank.value
+
+    def pj_validate(self, dists, pos_rows, neg_rows, W, rank, A, mu):
+        loss, regul = c_float(), c_float()
+        _check(self.lib.dlco_pj_validate(self.handle, _ptr(dists), dists.stride(0), dists.shape[1],
+                                         _ptr(pos_rows), pos_rows.numel(), _ptr(neg_rows), neg_rows.numel(),
+                                         _ptr(W), rank, _ptr(A), mu, ctypes.byref(loss), ctypes.byref(regul)))
+        return loss.value, regul.value
+
+    # ---- FPR95 evaluation: src/misc.cpp:171-333 --------------------------------------------
+    def pr_patchdist(self, dists, w):
+        out = self.torch.empty((dists.shape[0],), dtype=self.torch.float32, device=self.device)
+        _check(self.lib.dlco_pr_patchdist(self.handle, _ptr(dists), dists.shape[0], dists.stride(0),
+                                          dists.shape[1], _ptr(w), _ptr(out)))
+        return out
+
+    def pj_patchdist(self, dists, W, rank):
+        out = self.torch.empty((dists.shape[0],), dtype=self.torch.float32, device=self.device)
+        _check(self.lib.dlco_pj_patchdist(self.handle, _ptr(dists), dists.shape[0], dists.stride(0),
+                                          dists.shape[1], _ptr(W), rank, _ptr(out)))
+        return out
+
+    def roc_stats(self, patch_dist, labels):
+        """-> (FPR95 float32, AUC float64)"""
+        f, a = c_float(), c_double()
+        _check(self.lib.dlco_roc_stats(self.handle, _ptr(patch_dist), _ptr(labels), patch_dist.numel(),
+                                       ctypes.byref(f), ctypes.byref(a)))
+        return f.value, a.value
+
+    def gemm3x_nt(self, A, B):
+        """A (M,K) . B (N,K)^T on tcgen05 with the 3xTF32 split (diagnostic entry point)."""
+        out = self.torch.empty((A.shape[0], B.shape[0]), dtype=self.torch.float32, device=self.device)
+        _check(self.lib.dlco_gemm3x_nt_f32(self.handle, _ptr(A.contiguous()), A.shape[0], _ptr(B.contiguous()),
+                                           B.shape[0], A.shape[1], _ptr(out)))
+        return out

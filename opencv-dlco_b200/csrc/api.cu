@@ -90,9 +90,9 @@ extern "C" int dlco_shutdown(dlco_ctx *ctx)
     if (!ctx) return DLCO_OK;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
-    for (int i = 0; i < 8; i++)
+    for (int i = 0; i < 24; i++)
         if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
-    for (int i = 0; i < 4; i++)
+    for (int i = 0; i < 8; i++)
         if (ctx->pinned[i]) cudaFreeHost(ctx->pinned[i]);
     if (ctx->prof_ev) {
         for (int i = 0; i < 2 * ctx->prof_cap; i++) cudaEventDestroy(ctx->prof_ev[i]);
@@ -225,7 +225,7 @@ extern "C" int dlco_profile_enable(dlco_ctx *ctx, int on)
 
 extern "C" int dlco_profile_read(dlco_ctx *ctx, int which, double *ms, int64_t *cnt)
 {
-    DLCO_REQUIRE(ctx && which >= 0 && which < 8, "dlco_profile_read: bad arguments");
+    DLCO_REQUIRE(ctx && which >= 0 && which < 16, "dlco_profile_read: bad arguments");
     prof_flush(ctx);
     if (ms) *ms = ctx->prof_ms[which];
     if (cnt) *cnt = ctx->prof_cnt[which];
@@ -284,7 +284,7 @@ __global__ void k_bank_split(const float *__restrict__ src, float *__restrict__ 
 extern "C" int dlco_bank_create_dev(dlco_ctx *ctx, const float *d_filters, int nF, dlco_bank **out)
 {
     DLCO_REQUIRE(ctx && d_filters && out, "dlco_bank_create: bad arguments");
-    DLCO_REQUIRE(nF > 0 && nF % 8 == 0, "dlco_bank_create: nF=%d must be a positive multiple of 8", nF);
+    DLCO_REQUIRE(nF > 0, "dlco_bank_create: nF=%d must be positive", nF);
     DLCO_CUDA(cudaSetDevice(ctx->device));
     dlco_bank *b = (dlco_bank *)calloc(1, sizeof(dlco_bank));
     if (!b) return DLCO_ENOMEM;
@@ -313,7 +313,7 @@ extern "C" int dlco_bank_create_dev(dlco_ctx *ctx, const float *d_filters, int n
 extern "C" int dlco_bank_create(dlco_ctx *ctx, const float *h_filters, int nF, dlco_bank **out)
 {
     DLCO_REQUIRE(ctx && h_filters && out, "dlco_bank_create: bad arguments");
-    DLCO_REQUIRE(nF > 0 && nF % 8 == 0, "dlco_bank_create: nF=%d must be a positive multiple of 8", nF);
+    DLCO_REQUIRE(nF > 0, "dlco_bank_create: nF=%d must be positive", nF);
     DLCO_CUDA(cudaSetDevice(ctx->device));
     size_t bytes = (size_t)nF * DLCO_PATCH * DLCO_PATCH * 4;
     float *tmp = nullptr;

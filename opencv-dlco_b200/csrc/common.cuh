@@ -20,18 +20,18 @@ struct dlco_ctx {
     cudaStream_t stream;
     int64_t launches;
     // scratch buffers, grown on demand
-    void *scratch[8];
-    size_t scratch_bytes[8];
+    void *scratch[24];
+    size_t scratch_bytes[24];
     // pinned staging
-    void *pinned[4];
-    size_t pinned_bytes[4];
+    void *pinned[8];
+    size_t pinned_bytes[8];
     // optional per-kernel-class event timing (dlco_profile_*)
     int profile_on;
     cudaEvent_t *prof_ev;     // pairs (start, stop)
     int *prof_class;
     int prof_n, prof_cap;
-    double prof_ms[8];
-    int64_t prof_cnt[8];
+    double prof_ms[16];
+    int64_t prof_cnt[16];
     void *cusolver;       // cusolverDnHandle_t (lazy)
     void *cusolver_lib;   // dlopen handle
 };

@@ -39,7 +39,7 @@ extern "C" int dlco_pair_labels(dlco_ctx *ctx, const int32_t *d_indices, int64_t
 static int check_common(dlco_ctx *ctx, const dlco_bank *bank, const void *patches, const void *idx,
                         int64_t lo, int64_t hi, int nbins, const void *out, const char *who)
 {
-    DLCO_REQUIRE(ctx && bank && patches && idx && out, "%s: NULL argument", who);
+    DLCO_REQUIRE(ctx && bank && patches && idx && (out || hi == lo), "%s: NULL argument", who);
     DLCO_REQUIRE(lo >= 0 && hi >= lo, "%s: bad pair range [%lld,%lld)", who, (long long)lo, (long long)hi);
     DLCO_REQUIRE(nbins == DLCO_NBINS, "%s: only %d orientation bins supported (got %d)", who, DLCO_NBINS, nbins);
     return DLCO_OK;
@@ -79,6 +79,7 @@ extern "C" int dlco_fulldist_build(dlco_ctx *ctx, const dlco_bank *bank, const u
 {
     int r = check_common(ctx, bank, d_patches, d_indices, lo, hi, nAngleBins, d_out, "dlco_fulldist_build");
     if (r != DLCO_OK) return r;
+    DLCO_REQUIRE(bank->nF % 8 == 0, "dlco_fulldist_build: bank has %d filters, need 8 per ring", bank->nF);
     DLCO_REQUIRE(ld_out >= bank->nF / 8, "dlco_fulldist_build: ld_out=%lld < %d rings", (long long)ld_out, bank->nF / 8);
     const int nb = batch_pairs();
     for (int64_t p = lo; p < hi; p += nb) {
@@ -98,6 +99,7 @@ extern "C" int dlco_fulldist_build_host(dlco_ctx *ctx, const dlco_bank *bank, co
     int r = check_common(ctx, bank, h_patches, h_indices, lo, hi, nAngleBins, h_out, "dlco_fulldist_build_host");
     if (r != DLCO_OK) return r;
     const int rings = bank->nF / 8;
+    DLCO_REQUIRE(bank->nF % 8 == 0, "dlco_fulldist_build_host: bank has %d filters, need 8 per ring", bank->nF);
     DLCO_REQUIRE(ld_out >= rings, "dlco_fulldist_build_host: ld_out too small");
     DLCO_CUDA(cudaSetDevice(ctx->device));
     const int nb = batch_pairs();

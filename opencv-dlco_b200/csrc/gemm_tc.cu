@@ -1,0 +1,191 @@
+// K_gemm3x_nt: C[g][m, n] = sum_k A[g][m, k] * B[g][n, k] in fp32-equivalent accuracy on the
+// tensor cores (tcgen05.mma kind::tf32, 3xTF32: hi*hi + hi*lo + lo*hi into one fp32 TMEM
+// accumulator).  Both operands are K-major tf32 hi / lo planes (rows padded to the tile, K
+// padded to 32, padding zero), fetched by TMA with the 128-byte swizzle.  One 128 x 64 output
+// tile per CTA, grid = (n tiles, m tiles, batch): the pj-learn weighted SYRK is 5 x 9 tiles
+// per (mu, gamma) configuration and the configurations of a sweep are the batch dimension.
+// Roles: warp 0 = TMA producer, warp 1 = MMA issuer + TMEM owner, warps 2..5 = epilogue.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace {
+
+constexpr int BM = 128;
+constexpr int BN = 64;
+constexpr int BK = 32;
+constexpr int STAGES = 4;
+constexpr int A_BYTES = BM * BK * 4;
+constexpr int B_BYTES = BN * BK * 4;
+constexpr int STAGE_BYTES = 2 * A_BYTES + 2 * B_BYTES;
+constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256;
+constexpr int NTHREADS = 192;
+constexpr int TMEM_COLS = 64;
+
+struct __align__(64) GemmMaps {
+    CUtensorMap a_hi, a_lo, b_hi, b_lo;
+};
+
+__global__ void __launch_bounds__(NTHREADS, 1)
+k_gemm3x_nt(const __grid_constant__ GemmMaps maps, int k_chunks, int a_batch_rows, int b_batch_rows,
+            int M, int N, float *__restrict__ C, int64_t ldc, int64_t c_batch_stride)
+{
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem + STAGES * STAGE_BYTES);
+    uint64_t *full = bars;
+    uint64_t *empty = bars + STAGES;
+    uint64_t *tfull = bars + 2 * STAGES;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * STAGES + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nt = blockIdx.x, mt = blockIdx.y, g = blockIdx.z;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&maps.a_hi);
+        tma_prefetch_desc(&maps.a_lo);
+        tma_prefetch_desc(&maps.b_hi);
+        tma_prefetch_desc(&maps.b_lo);
+        for (int s = 0; s < STAGES; s++) {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], 1);
+        }
+        mbar_init(tfull, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc<TMEM_COLS>(tmem_slot);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            const int arow = g * a_batch_rows + mt * BM, brow = g * b_batch_rows + nt * BN;
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int kc = 0; kc < k_chunks; kc++) {
+                mbar_wait(&empty[stage], phase ^ 1);
+                uint8_t *st = smem + stage * STAGE_BYTES;
+                mbar_expect_tx(&full[stage], STAGE_BYTES);
+                tma_load_2d(st, &maps.a_hi, &full[stage], kc * BK, arow);
+                tma_load_2d(st + A_BYTES, &maps.a_lo, &full[stage], kc * BK, arow);
+                tma_load_2d(st + 2 * A_BYTES, &maps.b_hi, &full[stage], kc * BK, brow);
+                tma_load_2d(st + 2 * A_BYTES + B_BYTES, &maps.b_lo, &full[stage], kc * BK, brow);
+                if (++stage == STAGES) { stage = 0; phase ^= 1; }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_tf32(BM, BN);
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int kc = 0; kc < k_chunks; kc++) {
+                mbar_wait(&full[stage], phase);
+                tc_fence_after();
+                const uint32_t sa = smem_u32(smem + stage * STAGE_BYTES);
+                const uint64_t d_ahi = umma_desc_sw128(sa);
+                const uint64_t d_alo = umma_desc_sw128(sa + A_BYTES);
+                const uint64_t d_bhi = umma_desc_sw128(sa + 2 * A_BYTES);
+                const uint64_t d_blo = umma_desc_sw128(sa + 2 * A_BYTES + B_BYTES);
+#pragma unroll
+                for (int k = 0; k < BK / 8; k++) {
+                    const uint64_t ko = (uint64_t)(k * 2);
+                    umma_tf32(tmem_base, d_alo + ko, d_bhi + ko, idesc, (kc | k) != 0);
+                    umma_tf32(tmem_base, d_ahi + ko, d_blo + ko, idesc, 1);
+                    umma_tf32(tmem_base, d_ahi + ko, d_bhi + ko, idesc, 1);
+                }
+                umma_commit(&empty[stage]);
+                if (++stage == STAGES) { stage = 0; phase ^= 1; }
+            }
+            umma_commit(tfull);
+        }
+    } else {
+        const int q = warp & 3;
+        mbar_wait(tfull, 0);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
+        const int row = mt * BM + q * 32 + lane;
+        float *crow = C + (size_t)g * c_batch_stride + (size_t)row * ldc;
+#pragma unroll
+        for (int j = 0; j < BN / 16; j++) {
+            float v[16];
+            tmem_ld16(taddr + j * 16, v);
+            const int col0 = nt * BN + j * 16;
+            if (row < M) {
+#pragma unroll
+                for (int e = 0; e < 16; e++)
+                    if (col0 + e < N) crow[col0 + e] = v[e];
+            }
+        }
+        tc_fence_before();
+    }
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc<TMEM_COLS>(tmem_base);
+    }
+}
+
+}  // namespace
+
+// A planes: (batch * a_rows_pad) x k_pad, B planes: (b_batch ? batch : 1) * b_rows_pad x k_pad.
+int dlco_launch_gemm3x_nt(dlco_ctx *ctx, const float *a_hi, const float *a_lo, int a_rows_pad,
+                          const float *b_hi, const float *b_lo, int b_rows_pad, int b_batched,
+                          int k_pad, int batch, int M, int N, float *d_C, int64_t ldc,
+                          int64_t c_batch_stride)
+{
+    DLCO_REQUIRE(a_rows_pad % BM == 0 && b_rows_pad % BN == 0 && k_pad % BK == 0 && k_pad > 0,
+                 "gemm3x_nt: operands must be padded to %d x %d x %d", BM, BN, BK);
+    DLCO_REQUIRE(M <= a_rows_pad && N <= b_rows_pad && batch > 0, "gemm3x_nt: bad shapes");
+    GemmMaps maps;
+    int r = dlco_make_tmap_2d(&maps.a_hi, a_hi, (uint64_t)batch * a_rows_pad, k_pad, BM, BK);
+    if (r == DLCO_OK) r = dlco_make_tmap_2d(&maps.a_lo, a_lo, (uint64_t)batch * a_rows_pad, k_pad, BM, BK);
+    const uint64_t brows = (uint64_t)(b_batched ? batch : 1) * b_rows_pad;
+    if (r == DLCO_OK) r = dlco_make_tmap_2d(&maps.b_hi, b_hi, brows, k_pad, BN, BK);
+    if (r == DLCO_OK) r = dlco_make_tmap_2d(&maps.b_lo, b_lo, brows, k_pad, BN, BK);
+    if (r != DLCO_OK) return r;
+    static bool attr = false;
+    if (!attr) {
+        DLCO_CUDA(cudaFuncSetAttribute(k_gemm3x_nt, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+        attr = true;
+    }
+    dim3 grid((N + BN - 1) / BN, (M + BM - 1) / BM, batch);
+    dlco_prof_begin(ctx, 2);
+    k_gemm3x_nt<<<grid, NTHREADS, SMEM_BYTES, ctx->stream>>>(maps, k_pad / BK, a_rows_pad,
+                                                           b_batched ? b_rows_pad : 0, M, N, d_C, ldc,
+                                                           c_batch_stride);
+    dlco_prof_end(ctx);
+    DLCO_CHECK_LAUNCH(ctx);
+    return DLCO_OK;
+}
+
+// ---- fp32 front end: split row-major A (M x K) and B (N x K) into padded tf32 planes ----------
+__global__ void __launch_bounds__(256)
+k_split_pad(const float *__restrict__ src, int rows, int cols, int64_t ld, int rows_pad, int cols_pad,
+            float *__restrict__ hi, float *__restrict__ lo)
+{
+    const size_t total = (size_t)rows_pad * cols_pad;
+    for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < total; i += (size_t)gridDim.x * 256) {
+        const int r = (int)(i / cols_pad), c = (int)(i % cols_pad);
+        float h = 0.f, l = 0.f;
+        if (r < rows && c < cols) tf32_split(src[(size_t)r * ld + c], h, l);
+        hi[i] = h;
+        lo[i] = l;
+    }
+}
+
+extern "C" int dlco_gemm3x_nt_f32(dlco_ctx *ctx, const float *d_A, int M, const float *d_B, int N, int K,
+                                  float *d_C)
+{
+    DLCO_REQUIRE(ctx && d_A && d_B && d_C && M > 0 && N > 0 && K > 0, "dlco_gemm3x_nt_f32: bad arguments");
+    const int mp = (M + BM - 1) / BM * BM, np = (N + BN - 1) / BN * BN, kp = (K + BK - 1) / BK * BK;
+    float *pa = (float *)dlco_scratch(ctx, 21, (size_t)2 * mp * kp * sizeof(float));
+    float *pb = (float *)dlco_scratch(ctx, 22, (size_t)2 * np * kp * sizeof(float));
+    if (!pa || !pb) return DLCO_ENOMEM;
+    k_split_pad<<<ctx->sm_count * 4, 256, 0, ctx->stream>>>(d_A, M, K, K, mp, kp, pa, pa + (size_t)mp * kp);
+    DLCO_CHECK_LAUNCH(ctx);
+    k_split_pad<<<ctx->sm_count * 4, 256, 0, ctx->stream>>>(d_B, N, K, K, np, kp, pb, pb + (size_t)np * kp);
+    DLCO_CHECK_LAUNCH(ctx);
+    return dlco_launch_gemm3x_nt(ctx, pa, pa + (size_t)mp * kp, mp, pb, pb + (size_t)np * kp, np, 0, kp, 1, M, N,
+                                 d_C, N, 0);
+}

@@ -28,3 +28,17 @@ int dlco_launch_pool_tc(dlco_ctx *ctx, const dlco_bank *bank, const float *d_bhi
 // hinge.cu
 int dlco_hinge_pairsum_dev(dlco_ctx *ctx, const float *d_pos, int64_t n1, const float *d_neg,
                            int64_t n2, float margin, double *d_sum);
+
+// pr_learn.cu: out[i] = Dists[row(i), :] . w  (rows == NULL: row(i) = i)
+int dlco_gemv_rows(dlco_ctx *ctx, const float *d_dists, int64_t ld, int F, const int32_t *d_rows,
+                   int64_t n, const float *d_w, float *d_out);
+
+// pj_learn.cu: out[n] = || W x_row(n) ||^2
+int dlco_sqnorm_proj(dlco_ctx *ctx, const float *d_X, int64_t ld, const int32_t *d_rows, int64_t n,
+                     const float *d_W, int64_t ldw, int rank, int D, float *d_out);
+
+// gemm_tc.cu: batched C = A * B^T on tcgen05 (3xTF32) from K-major tf32 hi/lo planes
+int dlco_launch_gemm3x_nt(dlco_ctx *ctx, const float *a_hi, const float *a_lo, int a_rows_pad,
+                          const float *b_hi, const float *b_lo, int b_rows_pad, int b_batched,
+                          int k_pad, int batch, int M, int N, float *d_C, int64_t ldc,
+                          int64_t c_batch_stride);

@@ -1,0 +1,453 @@
+// pj-learn inner step on the GPU (reference src/pj-learn.cpp:311-527).
+//
+//   margins   m_k = || W x_k ||^2                      K_sqnorm_proj   (:332-365, :501-511)
+//   hinge     c+_i = #{k : m+_i + 1 > m-_k},  c-_k = -#{i : m+_i + 1 > m-_k}     (:373-378)
+//   gradient  dLoss = sum_i [ c+_i p_i p_i^T ] + sum_k [ c-_k n_k n_k^T ] = X^T diag(c) X
+//             one weighted SYRK on the tensor cores (tcgen05, 3xTF32) instead of the
+//             reference's up-to-200 per-positive SGEMMs (:394-416)             K_gemm3x_nt
+//   update    dfAvg, A, symmetrise                      K_pj_update               (:422-432)
+//   prox      A = V diag(e+) V^T,  W = rows sqrt(e+) v  K_pj_prox_*               (:448-490)
+#include "common.cuh"
+#include "kernels.h"
+#include <dlfcn.h>
+#include <math.h>
+
+// ---------------------------------------------------------------------------------------
+// K_sqnorm_proj: out[n] = sum_r ( sum_d W[r, d] X[row(n), d] )^2     (SIMT fp32, 64x64 tiles)
+// ---------------------------------------------------------------------------------------
+#define SP_BM 64
+#define SP_BR 64
+#define SP_BK 16
+
+__global__ void __launch_bounds__(256)
+k_sqnorm_proj(const float *__restrict__ X, int64_t ld, const int32_t *__restrict__ rows, int64_t n,
+              const float *__restrict__ W, int64_t ldw, int rank, int D, float *__restrict__ out)
+{
+    __shared__ float Xs[SP_BK][SP_BM + 4];
+    __shared__ float Ws[SP_BK][SP_BR + 4];
+    const int tid = threadIdx.x;
+    const int tx = tid & 15, ty = tid >> 4;
+    const int64_t m0 = (int64_t)blockIdx.x * SP_BM;
+    const int lr = tid >> 2, lk = (tid & 3) * 4;          // loader: row lr, k offset lk..lk+3
+    const int64_t xm = m0 + lr;
+    const float *xrow = nullptr;
+    if (xm < n) xrow = X + (rows ? (int64_t)rows[xm] : xm) * ld;
+    const bool vec_ok = ((ld | ldw | D) & 3) == 0;
+    float ssq[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int r0 = 0; r0 < rank; r0 += SP_BR) {
+        float acc[4][4];
+#pragma unroll
+        for (int i = 0; i < 4; i++)
+#pragma unroll
+            for (int j = 0; j < 4; j++) acc[i][j] = 0.f;
+        const float *wrow = (r0 + lr < rank) ? W + (int64_t)(r0 + lr) * ldw : nullptr;
+        for (int k0 = 0; k0 < D; k0 += SP_BK) {
+            float xv[4] = {0.f, 0.f, 0.f, 0.f}, wv[4] = {0.f, 0.f, 0.f, 0.f};
+            const int k = k0 + lk;
+            if (vec_ok && k + 3 < D) {
+                if (xrow) { float4 t = *reinterpret_cast<const float4 *>(xrow + k); xv[0] = t.x; xv[1] = t.y; xv[2] = t.z; xv[3] = t.w; }
+                if (wrow) { float4 t = *reinterpret_cast<const float4 *>(wrow + k); wv[0] = t.x; wv[1] = t.y; wv[2] = t.z; wv[3] = t.w; }
+            } else {
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    if (k + j < D) {
+                        if (xrow) xv[j] = xrow[k + j];
+                        if (wrow) wv[j] = wrow[k + j];
+                    }
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < 4; j++) { Xs[lk + j][lr] = xv[j]; Ws[lk + j][lr] = wv[j]; }
+            __syncthreads();
+#pragma unroll
+            for (int kk = 0; kk < SP_BK; kk++) {
+                const float4 a = *reinterpret_cast<const float4 *>(&Xs[kk][ty * 4]);
+                const float4 b = *reinterpret_cast<const float4 *>(&Ws[kk][tx * 4]);
+                const float av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+                for (int i = 0; i < 4; i++)
+#pragma unroll
+                    for (int j = 0; j < 4; j++) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+            }
+            __syncthreads();
+        }
+#pragma unroll
+        for (int i = 0; i < 4; i++)
+#pragma unroll
+            for (int j = 0; j < 4; j++) ssq[i] = fmaf(acc[i][j], acc[i][j], ssq[i]);
+    }
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        float v = ssq[i];
+        v += __shfl_xor_sync(0xffffffffu, v, 1);
+        v += __shfl_xor_sync(0xffffffffu, v, 2);
+        v += __shfl_xor_sync(0xffffffffu, v, 4);
+        v += __shfl_xor_sync(0xffffffffu, v, 8);
+        const int64_t m = m0 + ty * 4 + i;
+        if (tx == 0 && m < n) out[m] = v;
+    }
+}
+
+int dlco_sqnorm_proj(dlco_ctx *ctx, const float *d_X, int64_t ld, const int32_t *d_rows, int64_t n,
+                     const float *d_W, int64_t ldw, int rank, int D, float *d_out)
+{
+    if (n <= 0) return DLCO_OK;
+    DLCO_REQUIRE(D > 0 && rank >= 0 && ld >= D && ldw >= D, "sqnorm_proj: bad shapes");
+    if (rank == 0) {
+        DLCO_CUDA(cudaMemsetAsync(d_out, 0, (size_t)n * sizeof(float), ctx->stream));
+        return DLCO_OK;
+    }
+    dlco_prof_begin(ctx, 5);
+    k_sqnorm_proj<<<(unsigned)((n + SP_BM - 1) / SP_BM), 256, 0, ctx->stream>>>(d_X, ld, d_rows, n, d_W, ldw, rank, D, d_out);
+    dlco_prof_end(ctx);
+    DLCO_CHECK_LAUNCH(ctx);
+    return DLCO_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// hinge weights: c[i] = #{k : m[i] + 1 > m[b + k]}  (i < b),  c[b + k] = -#{i : m[i] + 1 > m[b + k]}
+// (IdxNegViol = (PosDist(iPos) + 1.0f) > NegDist, src/pj-learn.cpp:373-378).  One CTA per config.
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+k_pj_hinge(const float *__restrict__ m, int b, float *__restrict__ c)
+{
+    extern __shared__ float s_m[];
+    const float *mg = m + (size_t)blockIdx.x * 2 * b;
+    float *cg = c + (size_t)blockIdx.x * 2 * b;
+    for (int i = threadIdx.x; i < 2 * b; i += 256) s_m[i] = mg[i];
+    __syncthreads();
+    for (int i = threadIdx.x; i < 2 * b; i += 256) {
+        int cnt = 0;
+        if (i < b) {
+            const float p = __fadd_rn(s_m[i], 1.0f);
+            for (int k = 0; k < b; k++) cnt += p > s_m[b + k];
+        } else {
+            const float nk = s_m[i];
+            for (int k = 0; k < b; k++) cnt -= __fadd_rn(s_m[k], 1.0f) > nk;
+        }
+        cg[i] = (float)cnt;
+    }
+}
+
+// K-major operand planes of the SYRK: Xt[d][k] = x_k[d] (shared by all configs) and, per config g,
+// Yt[g][d][k] = c_g[k] * x_k[d]; tf32 hi / lo split, zero padding up to (d_pad, k_pad).
+// grid (k_pad/32, d_pad/32, 1 + nCfg): z == 0 writes Xt, z = g + 1 writes Yt[g].
+__global__ void __launch_bounds__(256)
+k_pj_planes(const float *__restrict__ dists, int64_t ld, int D, const int32_t *__restrict__ rows, int nk,
+            const float *__restrict__ c, int d_pad, int k_pad, float *__restrict__ xt_hi,
+            float *__restrict__ xt_lo, float *__restrict__ yt_hi, float *__restrict__ yt_lo)
+{
+    __shared__ float tile[32][33];
+    const int k0 = blockIdx.x * 32, d0 = blockIdx.y * 32, z = blockIdx.z;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    for (int r = ty; r < 32; r += 8) {                    // r: sample within tile, tx: feature
+        const int k = k0 + r, d = d0 + tx;
+        float v = 0.f;
+        if (k < nk && d < D) {
+            v = dists[(int64_t)rows[k] * ld + d];
+            if (z > 0) v = __fmul_rn(v, c[(size_t)(z - 1) * nk + k]);
+        }
+        tile[r][tx] = v;
+    }
+    __syncthreads();
+    float *hi = z == 0 ? xt_hi : yt_hi + (size_t)(z - 1) * d_pad * k_pad;
+    float *lo = z == 0 ? xt_lo : yt_lo + (size_t)(z - 1) * d_pad * k_pad;
+    for (int r = ty; r < 32; r += 8) {                    // r: feature within tile, tx: sample
+        float h, l;
+        tf32_split(tile[tx][r], h, l);
+        const size_t o = (size_t)(d0 + r) * k_pad + k0 + tx;
+        hi[o] = h;
+        lo[o] = l;
+    }
+}
+
+// dLoss for nCfg configurations that share one sampled batch (rows) but have their own W.
+// d_W: config g at d_W + g * w_stride, ranks h_rank[g]; d_dLoss: config g at d_dLoss + g * D * D.
+extern "C" int dlco_pj_rda_grad_grid(dlco_ctx *ctx, const float *d_dists, int64_t ld, int D,
+                                     const int32_t *d_rows_pos, const int32_t *d_rows_neg, int szBatch,
+                                     int nCfg, const float *d_W, int64_t w_stride, const int *h_rank,
+                                     float *d_dLoss)
+{
+    DLCO_REQUIRE(ctx && d_dists && d_rows_pos && d_rows_neg && d_dLoss && h_rank, "dlco_pj_rda_grad: NULL argument");
+    DLCO_REQUIRE(D > 0 && szBatch > 0 && szBatch <= 4096 && nCfg > 0 && ld >= D, "dlco_pj_rda_grad: bad shapes");
+    const int nk = 2 * szBatch;
+    const int d_pad = (D + 127) / 128 * 128, k_pad = (nk + 31) / 32 * 32;
+    const size_t plane = (size_t)d_pad * k_pad;
+    int32_t *rows = (int32_t *)dlco_scratch(ctx, 16, (size_t)nk * sizeof(int32_t));
+    float *m = (float *)dlco_scratch(ctx, 17, (size_t)nCfg * nk * 2 * sizeof(float));
+    float *planes = (float *)dlco_scratch(ctx, 18, plane * 2 * (1 + (size_t)nCfg) * sizeof(float));
+    if (!rows || !m || !planes) return DLCO_ENOMEM;
+    float *c = m + (size_t)nCfg * nk;
+    float *xt_hi = planes, *xt_lo = planes + plane;
+    float *yt_hi = planes + 2 * plane, *yt_lo = yt_hi + plane * nCfg;
+    DLCO_CUDA(cudaMemcpyAsync(rows, d_rows_pos, szBatch * sizeof(int32_t), cudaMemcpyDeviceToDevice, ctx->stream));
+    DLCO_CUDA(cudaMemcpyAsync(rows + szBatch, d_rows_neg, szBatch * sizeof(int32_t), cudaMemcpyDeviceToDevice, ctx->stream));
+    for (int g = 0; g < nCfg; g++) {
+        DLCO_REQUIRE(h_rank[g] >= 0 && (h_rank[g] == 0 || d_W), "dlco_pj_rda_grad: bad rank / W");
+        int r = dlco_sqnorm_proj(ctx, d_dists, ld, rows, nk, d_W ? d_W + (size_t)g * w_stride : nullptr, D,
+                                 h_rank[g], D, m + (size_t)g * nk);
+        if (r != DLCO_OK) return r;
+    }
+    k_pj_hinge<<<nCfg, 256, (size_t)nk * sizeof(float), ctx->stream>>>(m, szBatch, c);
+    DLCO_CHECK_LAUNCH(ctx);
+    dim3 pg(k_pad / 32, d_pad / 32, 1 + nCfg);
+    k_pj_planes<<<pg, 256, 0, ctx->stream>>>(d_dists, ld, D, rows, nk, c, d_pad, k_pad, xt_hi, xt_lo, yt_hi, yt_lo);
+    DLCO_CHECK_LAUNCH(ctx);
+    return dlco_launch_gemm3x_nt(ctx, yt_hi, yt_lo, d_pad, xt_hi, xt_lo, d_pad, 0, k_pad, nCfg, D, D, d_dLoss, D,
+                                 (int64_t)D * D);
+}
+
+extern "C" int dlco_pj_rda_grad(dlco_ctx *ctx, const float *d_dists, int64_t ld, int D,
+                                const int32_t *d_rows_pos, const int32_t *d_rows_neg, int szBatch,
+                                const float *d_W, int rank, float *d_dLoss)
+{
+    return dlco_pj_rda_grad_grid(ctx, d_dists, ld, D, d_rows_pos, d_rows_neg, szBatch, 1, d_W, 0, &rank, d_dLoss);
+}
+
+// ---------------------------------------------------------------------------------------
+// K_pj_update (src/pj-learn.cpp:422-432), one pass:
+//   dfAvg <- dfAvg * float(t/(t+1)) + dLoss * (1.0f / (b*b*(t+1)))          addWeighted
+//   A     <- (dfAvg + mu I) * float(-sqrt(t+1)/gamma);  A <- 0.5f * (A + A^T)
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+k_pj_update(int D, float a_avg, float beta, float mu, float div, const float *__restrict__ dLoss,
+            float *__restrict__ dfavg, float *__restrict__ A)
+{
+    const int j = blockIdx.x * 32 + (threadIdx.x & 31);
+    const int i = blockIdx.y * 8 + (threadIdx.x >> 5);
+    if (i >= D || j >= D || i > j) return;          // the thread of (i, j), i <= j, owns both entries
+    const size_t ij = (size_t)i * D + j, ji = (size_t)j * D + i;
+    const float d_ij = __fadd_rn(__fmul_rn(dfavg[ij], a_avg), __fmul_rn(dLoss[ij], beta));
+    const float d_ji = __fadd_rn(__fmul_rn(dfavg[ji], a_avg), __fmul_rn(dLoss[ji], beta));
+    const float m = (i == j) ? mu : 0.0f;
+    const float a_ij = __fmul_rn(__fadd_rn(d_ij, m), div);
+    const float a_ji = __fmul_rn(__fadd_rn(d_ji, m), div);
+    const float s = __fmul_rn(0.5f, __fadd_rn(a_ij, a_ji));
+    dfavg[ij] = d_ij;
+    dfavg[ji] = d_ji;
+    A[ij] = s;
+    A[ji] = s;
+}
+
+extern "C" int dlco_pj_rda_update(dlco_ctx *ctx, int D, uint64_t t, int szBatch, float mu, float gamma,
+                                  const float *d_dLoss, float *d_dfavg, float *d_A)
+{
+    DLCO_REQUIRE(ctx && d_dLoss && d_dfavg && d_A && D > 0 && szBatch > 0, "dlco_pj_rda_update: bad arguments");
+    const float a_avg = (float)((double)t / (double)(t + 1));
+    const unsigned int den = (unsigned int)szBatch * (unsigned int)szBatch * (unsigned int)(t + 1);
+    const float beta = 1.0f / (float)den;
+    const float div = (float)(-sqrt((double)t + 1.0) / (double)gamma);
+    dim3 grid((D + 31) / 32, (D + 7) / 8);
+    k_pj_update<<<grid, 256, 0, ctx->stream>>>(D, a_avg, beta, mu, div, d_dLoss, d_dfavg, d_A);
+    DLCO_CHECK_LAUNCH(ctx);
+    return DLCO_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// prox (src/pj-learn.cpp:448-490).  evec row k = eigenvector k, eval ascending, so the positive
+// part is the last `rank` rows.   W[r] = sqrt(e) v ;  A = sum_r v_r (e_r v_r)^T  (Evec * Bmul).
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+k_pj_prox_w(int D, int first, int rank, const float *__restrict__ eval, const float *__restrict__ evec,
+            float *__restrict__ W)
+{
+    const int r = blockIdx.x;
+    if (r < rank) {
+        const float sq = sqrtf(fmaxf(eval[first + r], 0.0f));
+        for (int c = threadIdx.x; c < D; c += 256) W[(size_t)r * D + c] = __fmul_rn(sq, evec[(size_t)(first + r) * D + c]);
+    } else {
+        for (int c = threadIdx.x; c < D; c += 256) W[(size_t)r * D + c] = 0.0f;     // rows beyond the rank
+    }
+}
+
+// C[i][j] = sum_{r < R} P[r][i] * (e[r] * P[r][j]),  P row-major R x D  (64 x 64 tiles, SIMT fp32)
+__global__ void __launch_bounds__(256)
+k_pj_prox_a(int D, int R, const float *__restrict__ e, const float *__restrict__ P, float *__restrict__ C)
+{
+    __shared__ float Ps[16][64 + 4];
+    __shared__ float Qs[16][64 + 4];
+    const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+    const int i0 = blockIdx.y * 64, j0 = blockIdx.x * 64;
+    const int lr = tid >> 4, lc = (tid & 15) * 4;
+    float acc[4][4];
+#pragma unroll
+    for (int a = 0; a < 4; a++)
+#pragma unroll
+        for (int b = 0; b < 4; b++) acc[a][b] = 0.f;
+    for (int r0 = 0; r0 < R; r0 += 16) {
+        const int r = r0 + lr;
+        const float er = r < R ? fmaxf(e[r], 0.0f) : 0.0f;
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int ci = i0 + lc + u, cj = j0 + lc + u;
+            Ps[lr][lc + u] = (r < R && ci < D) ? P[(size_t)r * D + ci] : 0.0f;
+            Qs[lr][lc + u] = (r < R && cj < D) ? __fmul_rn(er, P[(size_t)r * D + cj]) : 0.0f;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int kk = 0; kk < 16; kk++) {
+            const float4 a = *reinterpret_cast<const float4 *>(&Ps[kk][ty * 4]);
+            const float4 b = *reinterpret_cast<const float4 *>(&Qs[kk][tx * 4]);
+            const float av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+            for (int x = 0; x < 4; x++)
+#pragma unroll
+                for (int y = 0; y < 4; y++) acc[x][y] = fmaf(av[x], bv[y], acc[x][y]);
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int x = 0; x < 4; x++)
+#pragma unroll
+        for (int y = 0; y < 4; y++) {
+            const int i = i0 + ty * 4 + x, j = j0 + tx * 4 + y;
+            if (i < D && j < D) C[(size_t)i * D + j] = acc[x][y];
+        }
+}
+
+extern "C" int dlco_pj_prox_apply(dlco_ctx *ctx, int D, const float *d_eval, const float *d_evec,
+                                  float *d_A, float *d_W, int *h_rank)
+{
+    DLCO_REQUIRE(ctx && d_eval && d_evec && d_A && d_W && h_rank && D > 0 && D <= 8192, "dlco_pj_prox_apply: bad arguments");
+    float *h_e = (float *)dlco_pinned(ctx, 4, (size_t)D * sizeof(float));
+    if (!h_e) return DLCO_ENOMEM;
+    DLCO_CUDA(cudaMemcpyAsync(h_e, d_eval, (size_t)D * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    DLCO_CUDA(cudaStreamSynchronize(ctx->stream));
+    int first = D;
+    for (int k = D - 1; k >= 0 && h_e[k] > 0.0f; k--) first = k;       // positive suffix (ascending order)
+    for (int k = 0; k < first; k++)
+        DLCO_REQUIRE(!(h_e[k] > 0.0f), "dlco_pj_prox_apply: eigenvalues are not ascending");
+    const int rank = D - first;
+    *h_rank = rank;
+    k_pj_prox_w<<<D, 256, 0, ctx->stream>>>(D, first, rank, d_eval, d_evec, d_W);
+    DLCO_CHECK_LAUNCH(ctx);
+    if (rank == 0) {
+        DLCO_CUDA(cudaMemsetAsync(d_A, 0, (size_t)D * D * sizeof(float), ctx->stream));
+        return DLCO_OK;
+    }
+    dim3 grid((D + 63) / 64, (D + 63) / 64);
+    k_pj_prox_a<<<grid, 256, 0, ctx->stream>>>(D, rank, d_eval + first, d_evec + (size_t)first * D, d_A);
+    DLCO_CHECK_LAUNCH(ctx);
+    return DLCO_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// symmetric eigen-decomposition: library code (cuSOLVER syevd), loaded lazily so that the
+// rest of the ABI does not depend on libcusolver.  The reference calls LAPACKE_ssyevr
+// (src/pj-learn.cpp:440-446); north_star keeps the eigen-prox outside the named hot path.
+// cuSOLVER is column-major: the row-major symmetric A is its own transpose, and the returned
+// eigenvector columns are the rows of our row-major d_evec.
+// ---------------------------------------------------------------------------------------
+typedef int (*fn_create)(void **);
+typedef int (*fn_setstream)(void *, cudaStream_t);
+typedef int (*fn_bufsize)(void *, int, int, int, const float *, int, const float *, int *);
+typedef int (*fn_syevd)(void *, int, int, int, float *, int, float *, float *, int, int *);
+static struct {
+    void *lib;
+    fn_create create;
+    fn_setstream setstream;
+    fn_bufsize bufsize;
+    fn_syevd syevd;
+} g_cs;
+
+static int cusolver_load()
+{
+    if (g_cs.lib) return DLCO_OK;
+    const char *names[] = {"libcusolver.so.11", "libcusolver.so", "/usr/local/cuda/lib64/libcusolver.so.11", "libcusolver.so.12"};
+    void *h = nullptr;
+    for (const char *n : names)
+        if ((h = dlopen(n, RTLD_NOW | RTLD_GLOBAL))) break;
+    if (!h) { dlco_set_error("dlco_pj_eig: cannot load libcusolver (%s)", dlerror()); return DLCO_ECUDA; }
+    g_cs.create = (fn_create)dlsym(h, "cusolverDnCreate");
+    g_cs.setstream = (fn_setstream)dlsym(h, "cusolverDnSetStream");
+    g_cs.bufsize = (fn_bufsize)dlsym(h, "cusolverDnSsyevd_bufferSize");
+    g_cs.syevd = (fn_syevd)dlsym(h, "cusolverDnSsyevd");
+    if (!g_cs.create || !g_cs.setstream || !g_cs.bufsize || !g_cs.syevd) {
+        dlco_set_error("dlco_pj_eig: libcusolver lacks the syevd entry points");
+        return DLCO_ECUDA;
+    }
+    g_cs.lib = h;
+    return DLCO_OK;
+}
+
+extern "C" int dlco_pj_eig(dlco_ctx *ctx, int D, const float *d_A, float *d_eval, float *d_evec)
+{
+    DLCO_REQUIRE(ctx && d_A && d_eval && d_evec && D > 0, "dlco_pj_eig: bad arguments");
+    int r = cusolver_load();
+    if (r != DLCO_OK) return r;
+    if (!ctx->cusolver) {
+        void *h = nullptr;
+        if (g_cs.create(&h) != 0 || !h) { dlco_set_error("cusolverDnCreate failed"); return DLCO_ECUDA; }
+        ctx->cusolver = h;
+    }
+    if (g_cs.setstream(ctx->cusolver, ctx->stream) != 0) { dlco_set_error("cusolverDnSetStream failed"); return DLCO_ECUDA; }
+    if (d_evec != d_A)
+        DLCO_CUDA(cudaMemcpyAsync(d_evec, d_A, (size_t)D * D * sizeof(float), cudaMemcpyDeviceToDevice, ctx->stream));
+    const int JOBZ_VECTOR = 1, FILL_UPPER = 1;     // CUSOLVER_EIG_MODE_VECTOR, CUBLAS_FILL_MODE_UPPER
+    int lwork = 0;
+    if (g_cs.bufsize(ctx->cusolver, JOBZ_VECTOR, FILL_UPPER, D, d_evec, D, d_eval, &lwork) != 0) {
+        dlco_set_error("cusolverDnSsyevd_bufferSize failed");
+        return DLCO_ECUDA;
+    }
+    float *work = (float *)dlco_scratch(ctx, 19, (size_t)lwork * sizeof(float) + 64);
+    int *info = (int *)dlco_scratch(ctx, 20, 64);
+    if (!work || !info) return DLCO_ENOMEM;
+    int st = g_cs.syevd(ctx->cusolver, JOBZ_VECTOR, FILL_UPPER, D, d_evec, D, d_eval, work, lwork, info);
+    ctx->launches++;
+    if (st != 0) { dlco_set_error("cusolverDnSsyevd failed: status %d", st); return DLCO_ECUDA; }
+    int h_info = 0;
+    DLCO_CUDA(cudaMemcpyAsync(&h_info, info, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    DLCO_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (h_info != 0) { dlco_set_error("cusolverDnSsyevd: info = %d", h_info); return DLCO_ECUDA; }
+    return DLCO_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// validation objective (src/pj-learn.cpp:501-527) and ComputePJStats distances (src/misc.cpp:283-290)
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_trace(const float *__restrict__ A, int D, double *out)
+{
+    __shared__ double s_red[8];
+    double s = 0.0;
+    for (int i = threadIdx.x; i < D; i += 256) s += (double)A[(size_t)i * D + i];
+    s = warp_sum_d(s);
+    if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int i = 0; i < 8; i++) t += s_red[i];
+        *out = t;
+    }
+}
+
+extern "C" int dlco_pj_validate(dlco_ctx *ctx, const float *d_dists, int64_t ld, int D,
+                                const int32_t *d_pos_rows, int64_t nPos, const int32_t *d_neg_rows,
+                                int64_t nNeg, const float *d_W, int rank, const float *d_A, float mu,
+                                float *h_loss, float *h_regul)
+{
+    DLCO_REQUIRE(ctx && d_dists && d_pos_rows && d_neg_rows && d_A && h_loss && h_regul, "dlco_pj_validate: NULL argument");
+    DLCO_REQUIRE(nPos > 0 && nNeg > 0 && rank >= 0 && (rank == 0 || d_W), "dlco_pj_validate: bad arguments");
+    float *pd = (float *)dlco_scratch(ctx, 9, (size_t)nPos * sizeof(float));
+    float *nd = (float *)dlco_scratch(ctx, 10, (size_t)nNeg * sizeof(float));
+    double *d_res = (double *)dlco_scratch(ctx, 11, 64);
+    if (!pd || !nd || !d_res) return DLCO_ENOMEM;
+    int r = dlco_sqnorm_proj(ctx, d_dists, ld, d_pos_rows, nPos, d_W, D, rank, D, pd);
+    if (r == DLCO_OK) r = dlco_sqnorm_proj(ctx, d_dists, ld, d_neg_rows, nNeg, d_W, D, rank, D, nd);
+    if (r == DLCO_OK) r = dlco_hinge_pairsum_dev(ctx, pd, nPos, nd, nNeg, 1.0f, d_res);
+    if (r != DLCO_OK) return r;
+    k_trace<<<1, 256, 0, ctx->stream>>>(d_A, D, d_res + 1);
+    DLCO_CHECK_LAUNCH(ctx);
+    double h[2];
+    DLCO_CUDA(cudaMemcpyAsync(h, d_res, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream));
+    DLCO_CUDA(cudaStreamSynchronize(ctx->stream));
+    *h_loss = (float)h[0] / (float)nPos / (float)nNeg;               // Loss / nPosVal / nNegVal  (:524)
+    *h_regul = (float)((double)mu * h[1]);                           // mu * trace(A)             (:527)
+    return DLCO_OK;
+}
+
+extern "C" int dlco_pj_patchdist(dlco_ctx *ctx, const float *d_dists, int64_t N, int64_t ld, int D,
+                                 const float *d_W, int rank, float *d_pd)
+{
+    DLCO_REQUIRE(ctx && d_dists && d_pd && N >= 0 && rank >= 0 && (rank == 0 || d_W), "dlco_pj_patchdist: bad arguments");
+    return dlco_sqnorm_proj(ctx, d_dists, ld, nullptr, N, d_W, D, rank, D, d_pd);
+}

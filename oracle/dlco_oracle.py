@@ -496,9 +496,11 @@ def pj_prox(A, dt=f32):
     from scipy.linalg import lapack
     A = np.asarray(A)
     if np.dtype(dt) == np.float32:
-        ev, evec, *_ = lapack.ssyevr(A.astype(f32), jobz="V", range="A", lower=0)
+        ev, evec, _m, _isuppz, info = lapack.ssyevr(A.astype(f32), compute_v=1, range="A", lower=0)
+        assert info == 0
     else:
-        ev, evec, *_ = lapack.dsyevr(A.astype(np.float64), jobz="V", range="A", lower=0)
+        ev, evec, _m, _isuppz, info = lapack.dsyevr(A.astype(np.float64), compute_v=1, range="A", lower=0)
+        assert info == 0
     e = np.maximum(ev, 0)
     A_new = (evec * e) @ evec.T
     keep = e != 0

@@ -1,0 +1,155 @@
+"""GPU parity tests: every call goes through the C ABI (libdlco_b200.so via ctypes) and is
+compared with the CPU oracle (oracle/dlco_oracle.py, restating the reference file:line cited
+in each oracle function).  Tolerances follow BASELINE.json's north_star: distances 1e-5
+relative (to the row's largest distance -- SURVEY.md H3), learnt w / A 1e-4 relative, FPR95
+0.1 percentage points; integer / index results are exact."""
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+from conftest import make_bank  # noqa: E402
+from oracle import dlco_oracle as O  # noqa: E402
+
+DIST_RTOL = 1e-5
+
+
+def dev_t(ctx, a):
+    return torch.from_numpy(np.ascontiguousarray(a)).to(ctx.device)
+
+
+# ------------------------------------------------------------------------------------------
+# get_desc: src/vgg-desc.cpp:41-152
+# ------------------------------------------------------------------------------------------
+def test_get_desc_matches_oracle(gpu_ctx, synth):
+    patches, _, _ = synth
+    ids = torch.arange(patches.shape[0], dtype=torch.int32, device=gpu_ctx.device)
+    pt = gpu_ctx.get_desc(dev_t(gpu_ctx, patches), ids).cpu().numpy()
+    ref64 = np.stack([O.get_desc(p, dt=np.float64) for p in patches])
+    ref32 = np.stack([O.get_desc(p) for p in patches])
+    assert pt.shape == ref64.shape == (patches.shape[0], 4096, 8)
+    # at most two non-zero bins per pixel, non-negative
+    assert (np.count_nonzero(pt, axis=2) <= 2).all() and (pt >= 0).all()
+    # the fp32 evaluation of the reference differs from exact arithmetic by the conditioning of
+    # atan2 / the soft-bin offset: the GPU must be as close to fp64 as the fp32 oracle is
+    scale = ref64.max()
+    err_gpu = np.abs(pt - ref64).max() / scale
+    err_o32 = np.abs(ref32 - ref64).max() / scale
+    assert err_gpu <= max(2.0 * err_o32, 2e-5), (err_gpu, err_o32)
+    # quantile normalisation: the 0.8-quantile of the magnitude maps to n_bins = 8
+    mag = pt.sum(axis=2)
+    q = np.array([O.quantile_threshold(m.astype(np.float32)) for m in mag])
+    np.testing.assert_allclose(q, 8.0, rtol=1e-5)
+
+
+def test_get_desc_subset_and_repeat_ids(gpu_ctx, synth):
+    patches, _, _ = synth
+    ids = torch.tensor([5, 0, 5, 17], dtype=torch.int32, device=gpu_ctx.device)
+    pt = gpu_ctx.get_desc(dev_t(gpu_ctx, patches), ids).cpu().numpy()
+    assert np.array_equal(pt[0], pt[2])
+    ref = O.get_desc(patches[17], dt=np.float64)
+    assert np.abs(pt[3] - ref).max() <= 5e-5 * ref.max()
+
+
+def test_get_desc_constant_patch_is_zero(gpu_ctx):
+    """T == 0 branch of src/vgg-desc.cpp:131: a flat patch has zero gradient everywhere."""
+    patches = np.full((1, 64, 64), 77, np.uint8)
+    ids = torch.zeros(1, dtype=torch.int32, device=gpu_ctx.device)
+    pt = gpu_ctx.get_desc(dev_t(gpu_ctx, patches), ids).cpu().numpy()
+    assert np.isfinite(pt).all() and np.abs(pt).max() == 0.0
+
+
+# ------------------------------------------------------------------------------------------
+# comp-fulldists: src/comp-fulldists.cpp:294-356
+# ------------------------------------------------------------------------------------------
+@pytest.fixture(scope="module")
+def small_bank(oracle_lib):
+    rings = O.ring_params()
+    sel = np.r_[0:8, 700:708, 2500:2508, 5112:5120]          # 32 rings = 256 filters = 2 M tiles
+    filt, prp = make_bank(oracle_lib, rings[sel])
+    return filt, prp
+
+
+def _want_fulldist(filt, pt, idx):
+    want = np.zeros((len(idx), filt.shape[0] // 8))
+    for k, row in enumerate(idx):
+        want[k] = O.full_distance(filt, pt[row[0]], pt[row[2]])
+    return want
+
+
+@pytest.mark.parametrize("impl", ["tc", "simt"])
+def test_fulldist_matches_oracle(gpu_ctx, synth, small_bank, impl):
+    patches, _, idx = synth
+    filt, _ = small_bank
+    d_p, d_i = dev_t(gpu_ctx, patches), dev_t(gpu_ctx, idx)
+    ids = torch.arange(patches.shape[0], dtype=torch.int32, device=gpu_ctx.device)
+    pt = gpu_ctx.get_desc(d_p, ids).cpu().numpy()
+    want = _want_fulldist(filt, pt, idx)                       # fp64 pooling of the GPU descriptors
+    bank = gpu_ctx.bank(filt)
+    os.environ["DLCO_POOL_IMPL"] = impl
+    try:
+        got = gpu_ctx.fulldist_build(bank, d_p, d_i).cpu().numpy()
+    finally:
+        os.environ.pop("DLCO_POOL_IMPL", None)
+        bank.close()
+    assert np.isfinite(got).all()
+    rel = np.abs(got - want).max(axis=1) / want.max(axis=1)
+    assert rel.max() <= DIST_RTOL, rel.max()
+    # end to end against the oracle's own fp32 descriptors (looser: descriptor conditioning)
+    want_e2e = O.full_distances(filt, patches, idx)
+    rel = np.abs(got - want_e2e).max(axis=1) / want_e2e.max(axis=1)
+    assert rel.max() <= 2e-4, rel.max()
+
+
+@pytest.mark.parametrize("n", [0, 1, 15, 16, 17, 33])
+def test_fulldist_ragged_ranges(gpu_ctx, synth, small_bank, n):
+    patches, _, idx = synth
+    filt, _ = small_bank
+    d_p, d_i = dev_t(gpu_ctx, patches), dev_t(gpu_ctx, idx)
+    bank = gpu_ctx.bank(filt)
+    full = gpu_ctx.fulldist_build(bank, d_p, d_i).cpu().numpy()
+    lo = 3
+    got = gpu_ctx.fulldist_build(bank, d_p, d_i, lo, lo + n).cpu().numpy()
+    bank.close()
+    assert got.shape == (n, filt.shape[0] // 8)
+    assert np.array_equal(got, full[lo:lo + n])               # batching must not change a single bit
+
+
+def test_fulldist_host_entry_point(gpu_ctx, synth, small_bank):
+    patches, _, idx = synth
+    filt, _ = small_bank
+    bank = gpu_ctx.bank(filt)
+    dev = gpu_ctx.fulldist_build(bank, dev_t(gpu_ctx, patches), dev_t(gpu_ctx, idx)).cpu().numpy()
+    host = gpu_ctx.fulldist_build_host(bank, torch.from_numpy(patches), torch.from_numpy(idx)).numpy()
+    bank.close()
+    assert np.array_equal(dev, host)
+
+
+def test_fulldist_identical_patches_give_zero(gpu_ctx, synth, small_bank):
+    patches, pid, _ = synth
+    filt, _ = small_bank
+    idx = np.array([[4, pid[4], 4, pid[4]], [9, pid[9], 9, pid[9]]], np.int32)
+    bank = gpu_ctx.bank(filt)
+    got = gpu_ctx.fulldist_build(bank, dev_t(gpu_ctx, patches), dev_t(gpu_ctx, idx)).cpu().numpy()
+    bank.close()
+    assert np.abs(got).max() == 0.0
+
+
+def test_fulldist_symmetric_in_the_pair(gpu_ctx, synth, small_bank):
+    patches, _, idx = synth
+    filt, _ = small_bank
+    swapped = idx[:, [2, 3, 0, 1]].copy()
+    bank = gpu_ctx.bank(filt)
+    a = gpu_ctx.fulldist_build(bank, dev_t(gpu_ctx, patches), dev_t(gpu_ctx, idx)).cpu().numpy()
+    b = gpu_ctx.fulldist_build(bank, dev_t(gpu_ctx, patches), dev_t(gpu_ctx, swapped)).cpu().numpy()
+    bank.close()
+    assert np.array_equal(a, b)                               # (p2 - p1)^2 == (p1 - p2)^2 bit for bit
+
+
+def test_pair_labels(gpu_ctx, synth):
+    _, _, idx = synth
+    got = gpu_ctx.pair_labels(dev_t(gpu_ctx, idx)).cpu().numpy()
+    assert np.array_equal(got, O.pair_labels(idx))

@@ -1,0 +1,287 @@
+"""GPU parity tests for the unprojected-distance builder, the hinge pair-sum, the pr-learn and
+pj-learn steps and the FPR95 evaluation -- all through the C ABI, against the CPU oracle."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+from conftest import make_bank  # noqa: E402
+from oracle import dlco_oracle as O  # noqa: E402
+
+
+def dev_t(ctx, a):
+    return torch.from_numpy(np.ascontiguousarray(a)).to(ctx.device)
+
+
+# ------------------------------------------------------------------------------------------
+# comp-uprjdists: src/comp-uprjdists.cpp:298-335
+# ------------------------------------------------------------------------------------------
+def test_uprjdist_matches_oracle(gpu_ctx, synth, oracle_lib):
+    patches, _, idx = synth
+    rings = O.ring_params()
+    w = np.zeros(len(rings), np.float32)
+    sel_rings = [3, 40, 900, 2600, 4100]
+    w[sel_rings] = 1.0
+    filt, _ = make_bank(oracle_lib, rings[sel_rings])
+    full = np.zeros((len(rings) * 8, 4096), np.float32)
+    for k, r in enumerate(sel_rings):
+        full[8 * r:8 * r + 8] = filt[8 * k:8 * k + 8]
+    sel = O.select_pr_filters(full, w)                         # SelectPRFilters: unique + sortrows
+    assert 0 < sel.shape[0] <= 40
+    d_p, d_i = dev_t(gpu_ctx, patches), dev_t(gpu_ctx, idx)
+    ids = torch.arange(patches.shape[0], dtype=torch.int32, device=gpu_ctx.device)
+    pt = gpu_ctx.get_desc(d_p, ids).cpu().numpy()
+    n_sel = sel.shape[0]
+    bank = gpu_ctx.bank(sel)
+    got = gpu_ctx.uprjdist_build(bank, d_p, d_i).cpu().numpy()
+    bank.close()
+    want = np.stack([O.uprj_distance(sel, pt[r[0]], pt[r[2]]) for r in idx])
+    assert got.shape == want.shape
+    # signed differences of values clamped to [0, 1]: absolute tolerance on that scale
+    assert np.abs(got - want).max() <= 2e-6, np.abs(got - want).max()
+
+
+# ------------------------------------------------------------------------------------------
+# SubtractVectorsByRows + sum: src/kernelop-opencv.cu:49-80
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("n1,n2", [(1, 1), (5000, 7001), (257, 4096), (4097, 3)])
+def test_hinge_pairsum(gpu_ctx, n1, n2):
+    rng = np.random.default_rng(n1 * 7 + n2)
+    pos = rng.normal(0, 1, n1).astype(np.float32)
+    neg = rng.normal(0.5, 1, n2).astype(np.float32)
+    got = gpu_ctx.hinge_pairsum(dev_t(gpu_ctx, pos), dev_t(gpu_ctx, neg))
+    want = O.hinge_pairsum(pos, neg)
+    assert abs(got - want) <= 1e-6 * max(abs(want), 1.0)
+
+
+def test_hinge_pairsum_all_inactive(gpu_ctx):
+    pos = np.full(100, -5.0, np.float32)
+    neg = np.full(333, 5.0, np.float32)
+    assert gpu_ctx.hinge_pairsum(dev_t(gpu_ctx, pos), dev_t(gpu_ctx, neg)) == 0.0
+
+
+def test_hinge_pairsum_reference_size(gpu_ctx, oracle_lib):
+    """50 000 x 50 000 (the reference's validation size) against the C brute force."""
+    import ctypes
+    rng = np.random.default_rng(3)
+    pos = rng.gamma(2.0, 1.0, 50000).astype(np.float32)
+    neg = rng.gamma(3.0, 1.5, 50000).astype(np.float32)
+    got = gpu_ctx.hinge_pairsum(dev_t(gpu_ctx, pos), dev_t(gpu_ctx, neg))
+    want = oracle_lib.dlco_oracle_hinge_pairsum(pos.ctypes.data_as(ctypes.c_void_p), 50000,
+                                                neg.ctypes.data_as(ctypes.c_void_p), 50000, 1.0)
+    assert abs(got - want) <= 1e-6 * want
+    assert abs(O.hinge_pairsum(pos, neg) - want) <= 1e-9 * want
+
+
+# ------------------------------------------------------------------------------------------
+# synthetic "Distance" matrices for the learners
+# ------------------------------------------------------------------------------------------
+def synth_fulldist(n, f, seed):
+    rng = np.random.default_rng(seed)
+    lab = (rng.random(n) < 0.5).astype(np.uint8)
+    base = rng.gamma(2.0, 0.5, (n, f)).astype(np.float32)
+    informative = rng.random(f) < 0.3
+    scale = np.where(lab[:, None] == 1, np.where(informative, 0.35, 1.0), 1.0).astype(np.float32)
+    return (base * scale).astype(np.float32), lab
+
+
+def synth_uprj(n, d, seed):
+    rng = np.random.default_rng(seed)
+    lab = (rng.random(n) < 0.5).astype(np.uint8)
+    x = rng.normal(0, 0.25, (n, d)).astype(np.float32)
+    x[lab == 1, : d // 2] *= 0.6
+    return x, lab
+
+
+# ------------------------------------------------------------------------------------------
+# pr-learn: src/pr-learn.cpp:303-358
+# ------------------------------------------------------------------------------------------
+def test_pr_rda_matches_oracle(gpu_ctx):
+    import dlco_b200
+    dists, lab = synth_fulldist(3000, 64, 1)
+    d_d = dev_t(gpu_ctx, dists)
+    L = dlco_b200.learn.PrLearner(gpu_ctx, d_d, lab, 0.035, 0.25)
+    ip, ineg, npt, nnt = O.split_train_val(lab)
+    assert np.array_equal(ip, L.idx_pos.cpu().numpy()) and np.array_equal(ineg, L.idx_neg.cpu().numpy())
+    assert (npt, nnt) == (L.n_pos_trn, L.n_neg_trn)
+    n1, n2 = 700, 1300                                   # two calls: state and RNG carry over
+    L.run_steps(n1)
+    L.run_steps(n2)
+    w_o, df_o, rng, gap = O.pr_rda_steps(dists, ip, ineg, npt, nnt, 0.035, 0.25, n1 + n2)
+    assert L.rng_state == rng.state                       # identical sample stream consumed
+    w_g, df_g = L.w[0].cpu().numpy(), L.dfavg[0].cpu().numpy()
+    assert gap > 1e-6, "oracle run has a near-tie hinge decision; pick another seed"
+    assert np.abs(df_g - df_o).max() <= 1e-4 * np.abs(df_o).max()
+    assert np.abs(w_g - w_o).max() <= 1e-4 * max(np.abs(w_o).max(), 1e-12)
+    assert np.array_equal(w_g > 0, w_o > 0)               # same support
+    # validation objective
+    loss, regul = L.validate(0)
+    lo, ro = O.pr_validate(dists[ip[npt:]], dists[ineg[nnt:]], w_g, 0.035)
+    assert abs(loss - lo) <= 1e-5 * max(lo, 1e-6) and abs(regul - ro) <= 1e-6 * max(ro, 1e-6)
+
+
+def test_pr_rda_grid_equals_single_runs(gpu_ctx):
+    """one CTA per (mu, gamma): the grid launch must reproduce the single-config runs bit for bit"""
+    import dlco_b200
+    dists, lab = synth_fulldist(2000, 128, 2)
+    d_d = dev_t(gpu_ctx, dists)
+    mus, gammas = [0.01, 0.035, 0.05], [0.1, 0.25, 1.0]
+    G = dlco_b200.learn.PrLearner(gpu_ctx, d_d, lab, mus, gammas)
+    G.run_steps(1500)
+    for c in range(3):
+        S = dlco_b200.learn.PrLearner(gpu_ctx, d_d, lab, mus[c], gammas[c])
+        S.run_steps(1500)
+        assert torch.equal(S.w[0], G.w[c]) and torch.equal(S.dfavg[0], G.dfavg[c])
+
+
+def test_pr_train_log_format(gpu_ctx):
+    import re
+    import dlco_b200
+    dists, lab = synth_fulldist(2000, 64, 5)
+    lines = []
+    L = dlco_b200.learn.PrLearner(gpu_ctx, dev_t(gpu_ctx, dists), lab, 0.035, 0.25, log_step=500,
+                                  emit=lines.append)
+    L.train(1500)
+    heads = [ln.split(":")[0] for ln in lines]
+    assert heads[0] == "Best" and heads[1] == "Stat"
+    steps = [int(re.match(r"(Best|Step): (\d+)  Loss", ln).group(2)) for ln in lines if ln[:4] in ("Best", "Step")]
+    assert steps == [500, 1000, 1500]
+    pat = r"^(Best|Step): \d+  Loss: \d+\.\d{6} Regul: \d+\.\d{6} Obj: \d+\.\d{6} \(\d+\.\d{6}\)  NNZ: \d+ \(\d+\)  Ttime: \d+\.\d{4} Vtime: \d+\.\d{4}$"
+    assert all(re.match(pat, ln) for ln in lines if ln[:4] in ("Best", "Step"))
+
+
+# ------------------------------------------------------------------------------------------
+# FPR95 evaluation: src/misc.cpp:171-333
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("n", [1000, 4097, 100000])
+def test_roc_stats(gpu_ctx, n):
+    rng = np.random.default_rng(n)
+    lab = (rng.random(n) < 0.4).astype(np.uint8)
+    pd = (rng.gamma(2.0, 1.0, n) * np.where(lab == 1, 0.5, 1.0)).astype(np.float32)
+    pd[::7] = pd[3]                                           # ties: stable order by index
+    f, a = gpu_ctx.roc_stats(dev_t(gpu_ctx, pd), dev_t(gpu_ctx, lab))
+    fo, ao = O.roc_stats(pd, lab)
+    assert f == float(fo)                                     # same float counters: bit-exact
+    assert abs(a - ao) <= 1e-12
+
+
+def test_pr_patchdist_and_stats(gpu_ctx):
+    dists, lab = synth_fulldist(5000, 256, 9)
+    rng = np.random.default_rng(1)
+    w = np.where(rng.random(256) < 0.1, rng.random(256), 0).astype(np.float32)
+    pd = gpu_ctx.pr_patchdist(dev_t(gpu_ctx, dists), dev_t(gpu_ctx, w)).cpu().numpy()
+    want = dists.astype(np.float64) @ w.astype(np.float64)
+    assert np.abs(pd - want).max() <= 1e-6 * np.abs(want).max()
+    f, a = gpu_ctx.roc_stats(dev_t(gpu_ctx, pd), dev_t(gpu_ctx, lab))
+    fo, ao = O.roc_stats(want.astype(np.float32), lab)
+    assert abs(f - float(fo)) <= 1e-3 and abs(a - ao) <= 1e-5   # FPR95 within 0.1 pp
+
+
+# ------------------------------------------------------------------------------------------
+# tcgen05 3xTF32 GEMM used by the pj-learn SYRK
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("m,n,k", [(128, 64, 32), (544, 544, 400), (100, 70, 50), (640, 65, 1000)])
+def test_gemm3x_nt_fp32_accuracy(gpu_ctx, m, n, k):
+    rng = np.random.default_rng(m + n + k)
+    a = rng.normal(0, 1, (m, k)).astype(np.float32)
+    b = rng.normal(0, 1, (n, k)).astype(np.float32)
+    got = gpu_ctx.gemm3x_nt(dev_t(gpu_ctx, a), dev_t(gpu_ctx, b)).cpu().numpy()
+    want = a.astype(np.float64) @ b.astype(np.float64).T
+    scale = np.sqrt(k)                                        # typical magnitude of an entry
+    assert np.abs(got - want).max() <= 2e-6 * scale * 4, np.abs(got - want).max()
+
+
+# ------------------------------------------------------------------------------------------
+# pj-learn: src/pj-learn.cpp:311-527
+# ------------------------------------------------------------------------------------------
+def test_pj_grad_matches_oracle(gpu_ctx):
+    x, lab = synth_uprj(3000, 48, 11)
+    rng = np.random.default_rng(0)
+    b = 50
+    rp = rng.integers(0, 3000, b).astype(np.int32)
+    rn = rng.integers(0, 3000, b).astype(np.int32)
+    W = rng.normal(0, 1.0, (20, 48)).astype(np.float32)
+    got = gpu_ctx.pj_rda_grad(dev_t(gpu_ctx, x), dev_t(gpu_ctx, rp), dev_t(gpu_ctx, rn), dev_t(gpu_ctx, W), 20)
+    got = got.cpu().numpy()
+    pd = O.pj_margins(W, x[rp]).astype(np.float32)
+    nd = O.pj_margins(W, x[rn]).astype(np.float32)
+    gap = np.abs((pd[:, None] + np.float32(1.0)) - nd[None, :]).min()
+    assert gap > 1e-5, "near-tie hinge in the test data; change the seed"
+    want, c_pos, c_neg = O.pj_grad(x[rp], x[rn], pd, nd)
+    assert c_pos.sum() > 0 and c_pos.sum() < b * b            # hinge partly active
+    assert np.abs(got - want).max() <= 1e-5 * np.abs(want).max()
+    # rank 0 (t = 0: W is all zeros -> every pair violates)
+    got0 = gpu_ctx.pj_rda_grad(dev_t(gpu_ctx, x), dev_t(gpu_ctx, rp), dev_t(gpu_ctx, rn), None, 0).cpu().numpy()
+    z = np.zeros(b, np.float32)
+    want0, _, _ = O.pj_grad(x[rp], x[rn], z, z)
+    assert np.abs(got0 - want0).max() <= 1e-5 * np.abs(want0).max()
+
+
+def test_pj_update_eig_prox(gpu_ctx):
+    rng = np.random.default_rng(5)
+    D = 40
+    dl = rng.normal(0, 100, (D, D)).astype(np.float32)
+    dl = (dl + dl.T).astype(np.float32)
+    df = rng.normal(0, 0.01, (D, D)).astype(np.float32)
+    t, b, mu, gamma = 7, 200, 0.001, 0.1
+    d_df, d_A = dev_t(gpu_ctx, df), torch.zeros((D, D), device=gpu_ctx.device)
+    gpu_ctx.pj_rda_update(t, b, mu, gamma, dev_t(gpu_ctx, dl), d_df, d_A)
+    f32 = np.float32
+    beta = f32(1.0) / f32(b * b * (t + 1))
+    df_o = (df * f32(t / (t + 1)) + dl * beta).astype(f32)
+    A_o = ((df_o + f32(mu) * np.eye(D, dtype=f32)) * f32(-np.sqrt(t + 1.0) / float(f32(gamma)))).astype(f32)
+    A_o = (f32(0.5) * (A_o + A_o.T)).astype(f32)
+    assert np.array_equal(d_df.cpu().numpy(), df_o)           # same fp32 operation order: exact
+    assert np.array_equal(d_A.cpu().numpy(), A_o)
+    ev, evec = gpu_ctx.pj_eig(d_A)
+    W = torch.zeros((D, D), device=gpu_ctx.device)
+    rank = gpu_ctx.pj_prox_apply(ev, evec, d_A, W)
+    A_ref, W_ref, e = O.pj_prox(A_o.astype(np.float64), np.float64)
+    assert rank == W_ref.shape[0] and 0 < rank < D
+    A_g, W_g = d_A.cpu().numpy(), W.cpu().numpy()
+    assert np.abs(A_g - A_ref).max() <= 1e-5 * np.abs(A_ref).max()
+    assert np.abs(W_g[:rank].T @ W_g[:rank] - A_ref).max() <= 1e-5 * np.abs(A_ref).max()
+    assert np.abs(W_g[rank:]).max() == 0.0
+    # rows ordered by ascending eigenvalue
+    norms = (W_g[:rank] ** 2).sum(axis=1)
+    assert np.all(np.diff(norms) >= -1e-6 * norms.max())
+
+
+def test_pj_rda_matches_oracle(gpu_ctx):
+    import dlco_b200
+    x, lab = synth_uprj(3000, 32, 4)
+    mu, gamma, b, steps = 0.001, 0.1, 50, 40
+    L = dlco_b200.learn.PjLearner(gpu_ctx, dev_t(gpu_ctx, x), lab, mu, gamma, sz_batch=b)
+    for _ in range(steps):
+        L.step()
+    ip, ineg, npt, nnt = O.split_train_val(lab)
+    st = O.pj_rda_steps(x, ip, ineg, npt, nnt, mu, gamma, steps, sz_batch=b, dt=np.float64)
+    assert L.rng.state == st["rng"].state
+    A_g = L.A.cpu().numpy()
+    assert np.abs(A_g - st["A"]).max() <= 1e-4 * np.abs(st["A"]).max()      # north_star: A within 1e-4
+    assert L.rank == st["W"].shape[0]
+    W_g = L.W.cpu().numpy()[:L.rank]
+    assert np.abs(W_g.T @ W_g - A_g).max() <= 1e-5 * np.abs(A_g).max()      # A = W^T W
+    loss, regul = L.validate()
+    lo, ro = O.pj_validate(x[ip[npt:]], x[ineg[nnt:]], st["W"], st["A"], mu)
+    assert abs(loss - lo) <= 1e-4 * lo and abs(regul - ro) <= 1e-4 * ro
+    f, a = L.stats()
+    dim, fo, ao = O.pj_stats(st["W"], x, lab)
+    assert dim == L.rank and abs(f - float(fo)) <= 1e-3 and abs(a - ao) <= 1e-4
+
+
+def test_pj_grad_grid_equals_single(gpu_ctx):
+    x, lab = synth_uprj(2000, 64, 12)
+    rng = np.random.default_rng(1)
+    b = 40
+    rp = dev_t(gpu_ctx, rng.integers(0, 2000, b).astype(np.int32))
+    rn = dev_t(gpu_ctx, rng.integers(0, 2000, b).astype(np.int32))
+    d_x = dev_t(gpu_ctx, x)
+    Ws = rng.normal(0, 0.8, (3, 64, 64)).astype(np.float32)
+    ranks = [10, 64, 0]
+    d_W = dev_t(gpu_ctx, Ws)
+    grid = gpu_ctx.pj_rda_grad_grid(d_x, rp, rn, d_W, ranks)
+    for g in range(3):
+        single = gpu_ctx.pj_rda_grad(d_x, rp, rn, d_W[g], ranks[g])
+        assert torch.equal(single, grid[g])
