@@ -2,6 +2,8 @@
 #include "common.cuh"
 #include <stdlib.h>
 #include <vector>
+#include <algorithm>
+#include <cuda_fp16.h>
 
 static thread_local char g_err[1024] = "";
 
@@ -90,7 +92,7 @@ extern "C" int dlco_shutdown(dlco_ctx *ctx)
     if (!ctx) return DLCO_OK;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
-    for (int i = 0; i < 24; i++)
+    for (int i = 0; i < 32; i++)
         if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
     for (int i = 0; i < 8; i++)
         if (ctx->pinned[i]) cudaFreeHost(ctx->pinned[i]);
@@ -240,8 +242,8 @@ typedef CUresult (*PFN_encodeTiled)(CUtensorMap *, CUtensorMapDataType, cuuint32
                                     const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
                                     CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
-int dlco_make_tmap_2d(CUtensorMap *map, const float *base, uint64_t rows, uint64_t cols,
-                      uint32_t box_rows, uint32_t box_cols)
+int dlco_make_tmap_2d_ex(CUtensorMap *map, const void *base, int elem_bytes, uint64_t rows, uint64_t cols,
+                         uint32_t box_rows, uint32_t box_cols)
 {
     static PFN_encodeTiled fn = nullptr;
     if (!fn) {
@@ -255,12 +257,13 @@ int dlco_make_tmap_2d(CUtensorMap *map, const float *base, uint64_t rows, uint64
         fn = (PFN_encodeTiled)p;
     }
     cuuint64_t gdim[2] = {cols, rows};
-    cuuint64_t gstride[1] = {cols * sizeof(float)};
+    cuuint64_t gstride[1] = {cols * (cuuint64_t)elem_bytes};
     cuuint32_t box[2] = {box_cols, box_rows};
     cuuint32_t estr[2] = {1, 1};
-    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void *)base, gdim, gstride, box, estr,
-                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    CUresult r = fn(map, elem_bytes == 2 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
+                    (void *)base, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
         dlco_set_error("cuTensorMapEncodeTiled failed: CUresult %d", (int)r);
         return DLCO_ECUDA;
@@ -268,46 +271,146 @@ int dlco_make_tmap_2d(CUtensorMap *map, const float *base, uint64_t rows, uint64
     return DLCO_OK;
 }
 
-__global__ void k_bank_split(const float *__restrict__ src, float *__restrict__ hi,
-                             float *__restrict__ lo, size_t n_valid, size_t n_total)
+int dlco_make_tmap_2d(CUtensorMap *map, const float *base, uint64_t rows, uint64_t cols,
+                      uint32_t box_rows, uint32_t box_cols)
 {
-    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    size_t stride = (size_t)gridDim.x * blockDim.x;
-    for (; i < n_total; i += stride) {
-        float h = 0.f, l = 0.f;
-        if (i < n_valid) tf32_split(src[i], h, l);
-        hi[i] = h;
-        lo[i] = l;
+    return dlco_make_tmap_2d_ex(map, base, 4, rows, cols, box_rows, box_cols);
+}
+
+// ---- bank construction -------------------------------------------------------------------
+// The GEMM A operand is not the bank as given: identical filters are computed once (the default
+// gen-poolregion bank has 31 776 distinct rows among 40 960: rings at phi = 0, pi/4 and r = 0
+// repeat members), rows are sorted by their K support so that a 128-row tile touches few
+// 64-wide K chunks (K index = x*64 + y, so chunk c is image row x = c; a Gaussian of width
+// sigma covers rows x0 +- 3 sigma only), and each row is scaled by a power of two so that its
+// largest entry lies in [2^14, 2^15): then hi = rn16(v) and lo = rn16(v - hi) are both normal
+// fp16 numbers and hi + lo carries 22 mantissa bits of v.
+__global__ void k_bank_planes(const float *__restrict__ src, const int32_t *__restrict__ row_src, int n_rows,
+                              int n_rows_pad, __half *__restrict__ hi, __half *__restrict__ lo,
+                              float *__restrict__ inv_scale)
+{
+    const int r = blockIdx.x;
+    __shared__ float s_max[8];
+    __shared__ float s_scale;
+    const int K = DLCO_PATCH * DLCO_PATCH;
+    __half *h = hi + (size_t)r * K, *l = lo + (size_t)r * K;
+    if (r >= n_rows) {
+        for (int k = threadIdx.x; k < K; k += 256) { h[k] = __float2half_rn(0.f); l[k] = __float2half_rn(0.f); }
+        if (threadIdx.x == 0) inv_scale[r] = 1.0f;
+        return;
+    }
+    const float *f = src + (size_t)row_src[r] * K;
+    float m = 0.f;
+    for (int k = threadIdx.x; k < K; k += 256) m = fmaxf(m, fabsf(f[k]));
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0) s_max[threadIdx.x >> 5] = m;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float mm = 0.f;
+        for (int i = 0; i < 8; i++) mm = fmaxf(mm, s_max[i]);
+        float sc = 1.0f;
+        if (mm > 0.f && isfinite(mm)) sc = exp2f((float)(14 - ilogbf(mm)));
+        s_scale = sc;
+        inv_scale[r] = 1.0f / sc;
+    }
+    __syncthreads();
+    const float sc = s_scale;
+    for (int k = threadIdx.x; k < K; k += 256) {
+        const float v = f[k] * sc;
+        const __half a = __float2half_rn(v);
+        h[k] = a;
+        l[k] = __float2half_rn(v - __half2float(a));
     }
 }
 
-extern "C" int dlco_bank_create_dev(dlco_ctx *ctx, const float *d_filters, int nF, dlco_bank **out)
+static inline uint64_t mix64(uint64_t h, uint64_t v)
 {
-    DLCO_REQUIRE(ctx && d_filters && out, "dlco_bank_create: bad arguments");
-    DLCO_REQUIRE(nF > 0, "dlco_bank_create: nF=%d must be positive", nF);
-    DLCO_CUDA(cudaSetDevice(ctx->device));
-    dlco_bank *b = (dlco_bank *)calloc(1, sizeof(dlco_bank));
-    if (!b) return DLCO_ENOMEM;
-    const int K = DLCO_PATCH * DLCO_PATCH;
-    b->nF = nF;
-    b->nFpad = (nF + 127) / 128 * 128;
-    size_t n_valid = (size_t)nF * K, n_total = (size_t)b->nFpad * K;
-    if (cudaMalloc(&b->d_hi, n_total * 4) != cudaSuccess ||
-        cudaMalloc(&b->d_lo, n_total * 4) != cudaSuccess ||
-        cudaMalloc(&b->d_f32, n_valid * 4) != cudaSuccess) {
+    h ^= v + 0x9e3779b97f4a7c15ULL + (h << 6) + (h >> 2);
+    return h * 0xff51afd7ed558ccdULL;
+}
+
+struct BankKey {
+    uint64_t mask, hash;
+    int lo, hi, idx;
+};
+
+static int bank_finish(dlco_ctx *ctx, dlco_bank *b, const float *h_filters)
+{
+    const int K = DLCO_PATCH * DLCO_PATCH, nF = b->nF;
+    std::vector<BankKey> keys(nF);
+    for (int i = 0; i < nF; i++) {
+        const uint32_t *p = (const uint32_t *)(h_filters + (size_t)i * K);
+        uint64_t mask = 0, hash = 0x1234567ULL;
+        for (int x = 0; x < 64; x++) {
+            uint32_t any = 0;
+            for (int y = 0; y < 64; y++) {
+                const uint32_t v = p[x * 64 + y];
+                any |= (v << 1);                          // -0.0f counts as zero
+                hash = mix64(hash, v);
+            }
+            if (any) mask |= 1ULL << x;
+        }
+        keys[i].mask = mask;
+        keys[i].hash = hash;
+        keys[i].idx = i;
+        keys[i].lo = mask ? __builtin_ctzll(mask) : 64;
+        keys[i].hi = mask ? 63 - __builtin_clzll(mask) : 64;
+    }
+    std::vector<int> order(nF);
+    for (int i = 0; i < nF; i++) order[i] = i;
+    std::sort(order.begin(), order.end(), [&](int a, int c) {
+        const BankKey &x = keys[a], &y = keys[c];
+        if (x.lo != y.lo) return x.lo < y.lo;
+        if (x.hi != y.hi) return x.hi < y.hi;
+        if (x.hash != y.hash) return x.hash < y.hash;
+        return x.idx < y.idx;
+    });
+    std::vector<int32_t> row_src, map(nF);
+    row_src.reserve(nF);
+    for (int o = 0; o < nF; o++) {
+        const int i = order[o];
+        bool dup = false;
+        if (o > 0) {
+            const int j = order[o - 1];
+            dup = keys[i].hash == keys[j].hash && keys[i].mask == keys[j].mask &&
+                  memcmp(h_filters + (size_t)i * K, h_filters + (size_t)j * K, (size_t)K * 4) == 0;
+        }
+        if (!dup) row_src.push_back(i);
+        map[i] = (int32_t)row_src.size() - 1;
+    }
+    b->nRows = (int)row_src.size();
+    b->nRowsPad = (b->nRows + 127) / 128 * 128;
+    const int tiles = b->nRowsPad / 128;
+    std::vector<uint64_t> kmask(tiles, 0);
+    b->chunks_total = 0;
+    for (int r = 0; r < b->nRows; r++) kmask[r / 128] |= keys[row_src[r]].mask;
+    for (int t = 0; t < tiles; t++) b->chunks_total += __builtin_popcountll(kmask[t]);
+
+    const size_t plane = (size_t)b->nRowsPad * K * sizeof(__half);
+    int32_t *d_row_src = nullptr;
+    if (cudaMalloc(&b->d_hi, plane) != cudaSuccess || cudaMalloc(&b->d_lo, plane) != cudaSuccess ||
+        cudaMalloc(&b->d_inv_scale, (size_t)b->nRowsPad * 4) != cudaSuccess ||
+        cudaMalloc(&b->d_kmask, (size_t)tiles * 8) != cudaSuccess ||
+        cudaMalloc(&b->d_map, (size_t)nF * 4) != cudaSuccess ||
+        cudaMalloc(&d_row_src, (size_t)b->nRows * 4) != cudaSuccess) {
         dlco_set_error("dlco_bank_create: out of device memory for %d filters", nF);
-        cudaFree(b->d_hi); cudaFree(b->d_lo); cudaFree(b->d_f32); free(b);
+        cudaFree(d_row_src);
         return DLCO_ENOMEM;
     }
-    DLCO_CUDA(cudaMemcpyAsync(b->d_f32, d_filters, n_valid * 4, cudaMemcpyDeviceToDevice, ctx->stream));
-    k_bank_split<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(b->d_f32, b->d_hi, b->d_lo, n_valid, n_total);
-    DLCO_CHECK_LAUNCH(ctx);
-    int r = dlco_make_tmap_2d(&b->map_hi, b->d_hi, b->nFpad, K, 128, 32);
-    if (r == DLCO_OK) r = dlco_make_tmap_2d(&b->map_lo, b->d_lo, b->nFpad, K, 128, 32);
-    if (r != DLCO_OK) { dlco_bank_destroy(ctx, b); return r; }
-    DLCO_CUDA(cudaStreamSynchronize(ctx->stream));
-    *out = b;
-    return DLCO_OK;
+    DLCO_CUDA(cudaMemcpyAsync(d_row_src, row_src.data(), (size_t)b->nRows * 4, cudaMemcpyHostToDevice, ctx->stream));
+    DLCO_CUDA(cudaMemcpyAsync(b->d_map, map.data(), (size_t)nF * 4, cudaMemcpyHostToDevice, ctx->stream));
+    DLCO_CUDA(cudaMemcpyAsync(b->d_kmask, kmask.data(), (size_t)tiles * 8, cudaMemcpyHostToDevice, ctx->stream));
+    k_bank_planes<<<b->nRowsPad, 256, 0, ctx->stream>>>(b->d_f32, d_row_src, b->nRows, b->nRowsPad,
+                                                         (__half *)b->d_hi, (__half *)b->d_lo, b->d_inv_scale);
+    ctx->launches++;
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(d_row_src);
+    if (e != cudaSuccess) { dlco_set_error("dlco_bank_create: %s", cudaGetErrorString(e)); return DLCO_ECUDA; }
+    int r = dlco_make_tmap_2d_ex(&b->map_hi, b->d_hi, 2, b->nRowsPad, K, 128, 64);
+    if (r == DLCO_OK) r = dlco_make_tmap_2d_ex(&b->map_lo, b->d_lo, 2, b->nRowsPad, K, 128, 64);
+    return r;
 }
 
 extern "C" int dlco_bank_create(dlco_ctx *ctx, const float *h_filters, int nF, dlco_bank **out)
@@ -315,21 +418,43 @@ extern "C" int dlco_bank_create(dlco_ctx *ctx, const float *h_filters, int nF, d
     DLCO_REQUIRE(ctx && h_filters && out, "dlco_bank_create: bad arguments");
     DLCO_REQUIRE(nF > 0, "dlco_bank_create: nF=%d must be positive", nF);
     DLCO_CUDA(cudaSetDevice(ctx->device));
-    size_t bytes = (size_t)nF * DLCO_PATCH * DLCO_PATCH * 4;
-    float *tmp = nullptr;
-    if (cudaMalloc(&tmp, bytes) != cudaSuccess) {
+    dlco_bank *b = (dlco_bank *)calloc(1, sizeof(dlco_bank));
+    if (!b) return DLCO_ENOMEM;
+    b->nF = nF;
+    const size_t bytes = (size_t)nF * DLCO_PATCH * DLCO_PATCH * 4;
+    if (cudaMalloc(&b->d_f32, bytes) != cudaSuccess) {
+        free(b);
         dlco_set_error("dlco_bank_create: out of device memory");
         return DLCO_ENOMEM;
     }
-    cudaError_t e = cudaMemcpyAsync(tmp, h_filters, bytes, cudaMemcpyHostToDevice, ctx->stream);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaError_t e = cudaMemcpyAsync(b->d_f32, h_filters, bytes, cudaMemcpyHostToDevice, ctx->stream);
     if (e != cudaSuccess) {
-        cudaFree(tmp);
+        dlco_bank_destroy(ctx, b);
         dlco_set_error("dlco_bank_create: upload failed: %s", cudaGetErrorString(e));
         return DLCO_ECUDA;
     }
-    int r = dlco_bank_create_dev(ctx, tmp, nF, out);
-    cudaFree(tmp);
+    int r = bank_finish(ctx, b, h_filters);
+    if (r != DLCO_OK) { dlco_bank_destroy(ctx, b); return r; }
+    *out = b;
+    return DLCO_OK;
+}
+
+extern "C" int dlco_bank_create_dev(dlco_ctx *ctx, const float *d_filters, int nF, dlco_bank **out)
+{
+    DLCO_REQUIRE(ctx && d_filters && out, "dlco_bank_create: bad arguments");
+    DLCO_REQUIRE(nF > 0, "dlco_bank_create: nF=%d must be positive", nF);
+    // the de-duplication / support analysis runs on the host: bring the bank over once
+    const size_t bytes = (size_t)nF * DLCO_PATCH * DLCO_PATCH * 4;
+    float *h = (float *)malloc(bytes);
+    if (!h) { dlco_set_error("dlco_bank_create_dev: out of host memory"); return DLCO_ENOMEM; }
+    cudaError_t e = cudaMemcpy(h, d_filters, bytes, cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) {
+        free(h);
+        dlco_set_error("dlco_bank_create_dev: download failed: %s", cudaGetErrorString(e));
+        return DLCO_ECUDA;
+    }
+    int r = dlco_bank_create(ctx, h, nF, out);
+    free(h);
     return r;
 }
 
@@ -339,7 +464,21 @@ extern "C" int dlco_bank_destroy(dlco_ctx *ctx, dlco_bank *b)
     if (ctx) cudaStreamSynchronize(ctx->stream);
     cudaFree(b->d_hi);
     cudaFree(b->d_lo);
+    cudaFree(b->d_inv_scale);
+    cudaFree(b->d_kmask);
+    cudaFree(b->d_map);
     cudaFree(b->d_f32);
     free(b);
+    return DLCO_OK;
+}
+
+// rows / tiles / K chunks of the GEMM operand built from a bank (bench roofline accounting)
+extern "C" int dlco_bank_info(const dlco_bank *b, int *n_filters, int *n_rows, int *n_tiles, int64_t *k_chunks)
+{
+    DLCO_REQUIRE(b, "dlco_bank_info: bank is NULL");
+    if (n_filters) *n_filters = b->nF;
+    if (n_rows) *n_rows = b->nRows;
+    if (n_tiles) *n_tiles = b->nRowsPad / 128;
+    if (k_chunks) *k_chunks = b->chunks_total;
     return DLCO_OK;
 }

@@ -20,8 +20,8 @@ struct dlco_ctx {
     cudaStream_t stream;
     int64_t launches;
     // scratch buffers, grown on demand
-    void *scratch[24];
-    size_t scratch_bytes[24];
+    void *scratch[32];
+    size_t scratch_bytes[32];
     // pinned staging
     void *pinned[8];
     size_t pinned_bytes[8];
@@ -37,12 +37,17 @@ struct dlco_ctx {
 };
 
 struct dlco_bank {
-    int nF;          // filters (rows), multiple of 8
-    int nFpad;       // rows padded to a multiple of 128 (zero rows)
-    float *d_hi;     // nFpad x 4096, tf32-rounded
-    float *d_lo;     // nFpad x 4096, tf32-rounded residual
-    float *d_f32;    // nF x 4096 original (SIMT check path, uprj)
-    CUtensorMap map_hi, map_lo;   // box 32 x 128, 128B swizzle
+    int nF;              // filters as given by the caller
+    int nRows;           // distinct filters, sorted by K support (rows of the GEMM A operand)
+    int nRowsPad;        // rows padded to a multiple of 128 (zero rows)
+    void *d_hi;          // nRowsPad x 4096 fp16: hi = rn16(f * scale_row)
+    void *d_lo;          // nRowsPad x 4096 fp16: lo = rn16(f * scale_row - hi)
+    float *d_inv_scale;  // nRowsPad: 1 / scale_row (powers of two)
+    uint64_t *d_kmask;   // nRowsPad / 128: bit x set <=> some filter of the tile is non-zero in K chunk x
+    int32_t *d_map;      // nF: filter -> distinct row
+    float *d_f32;        // nF x 4096 original (SIMT cross-check path, comp-uprjdists)
+    int64_t chunks_total;   // sum over M tiles of popcount(kmask)  (vs 64 * tiles when dense)
+    CUtensorMap map_hi, map_lo;   // box 64 (K) x 128 (rows), 128B swizzle
 };
 
 void dlco_set_error(const char *fmt, ...);
@@ -210,6 +215,20 @@ __device__ __forceinline__ void umma_commit(uint64_t *bar)
                  : "memory");
 }
 
+// D[tmem] (+)= A[smem desc] * B[smem desc], kind::f16 (fp16 x fp16 -> fp32), single CTA
+__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,
+                                         uint32_t idesc, uint32_t accumulate)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+
 // K-major, 128B-swizzled operand tile: rows of 128 bytes, 8-row groups 1024 B apart.
 __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr)
 {
@@ -231,6 +250,26 @@ __host__ __device__ constexpr uint32_t umma_idesc_tf32(int M, int N)
            | ((uint32_t)(N >> 3) << 17) // n_dim
            | ((uint32_t)(M >> 4) << 24);// m_dim
 }
+
+// instruction descriptor: fp16 x fp16 -> f32, K-major A and B (a_format = b_format = 0 = F16)
+__host__ __device__ constexpr uint32_t umma_idesc_f16(int M, int N)
+{
+    return (1u << 4)                    // c_format = F32
+           | ((uint32_t)(N >> 3) << 17) // n_dim
+           | ((uint32_t)(M >> 4) << 24);// m_dim
+}
+
+// 32 lanes x 16 columns, no wait: pair with tmem_ld_wait() before using the registers
+__device__ __forceinline__ void tmem_ld16_nowait(uint32_t taddr, uint32_t *r)
+{
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]),
+          "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]),
+          "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // 32 lanes x 16 consecutive columns -> 16 registers per thread
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float *v)

@@ -8,10 +8,13 @@
 // Three output layouts:
 //   DESC_OUT_PT    : n x 4096 x 8 f32                     (the reference's PatchTrans)
 //   DESC_OUT_ROWS  : (slot*8 + bin) x 4096 f32             (K-major rows, SIMT pooling)
-//   DESC_OUT_SPLIT : same rows, tf32 hi / lo planes        (tensor-core pooling, 3xTF32)
+//   DESC_OUT_SPLIT : same rows as fp16 hi / lo planes scaled per patch by a power of two
+//                    (largest entry in [2^14, 2^15)), plus 1/scale per slot
+//                    (tensor-core pooling, 3 x fp16 products = fp32-equivalent accuracy)
 #include "common.cuh"
 #include "kernels.h"
 #include <math.h>
+#include <cuda_fp16.h>
 
 #define DESC_THREADS 256
 #define PS DLCO_PATCH
@@ -78,7 +81,8 @@ __device__ uint32_t radix_select(const uint32_t *vals, int rank, uint32_t *hist,
 template <int MODE>
 __global__ void __launch_bounds__(DESC_THREADS)
 k_desc(const uint8_t *__restrict__ patches, const int32_t *__restrict__ ids, int id_stride,
-       int n_slots, DescParams prm, float *__restrict__ out0, float *__restrict__ out1)
+       int n_slots, DescParams prm, float *__restrict__ out0, float *__restrict__ out1,
+       float *__restrict__ inv_scale)
 {
     __shared__ float s_a[PS * SROW];
     __shared__ float s_b[PS * SROW];
@@ -91,12 +95,13 @@ k_desc(const uint8_t *__restrict__ patches, const int32_t *__restrict__ ids, int
     // slots beyond n_slots are padding rows of the GEMM operand: write zeros
     const bool valid = slot < n_slots;
     if (!valid) {
-        if (MODE != DESC_OUT_PT) {
-            for (int i = tid; i < NPIX * 8; i += DESC_THREADS) {
-                size_t o = (size_t)slot * 8 * NPIX + i;
-                out0[o] = 0.f;
-                if (MODE == DESC_OUT_SPLIT) out1[o] = 0.f;
-            }
+        if (MODE == DESC_OUT_ROWS) {
+            for (int i = tid; i < NPIX * 8; i += DESC_THREADS) out0[(size_t)slot * 8 * NPIX + i] = 0.f;
+        } else if (MODE == DESC_OUT_SPLIT) {
+            uint32_t *h = reinterpret_cast<uint32_t *>(reinterpret_cast<__half *>(out0) + (size_t)slot * 8 * NPIX);
+            uint32_t *l = reinterpret_cast<uint32_t *>(reinterpret_cast<__half *>(out1) + (size_t)slot * 8 * NPIX);
+            for (int i = tid; i < NPIX * 4; i += DESC_THREADS) { h[i] = 0u; l[i] = 0u; }
+            if (tid == 0) inv_scale[slot] = 1.0f;
         }
         return;
     }
@@ -186,6 +191,23 @@ k_desc(const uint8_t *__restrict__ patches, const int32_t *__restrict__ ids, int
         if (T != 0.0f) scale = (float)(1.0 / (double)(T / (float)nb));   // Mat /= s
     }
 
+    float pscale = 1.0f;       // fp16 planes: power-of-two scale of this patch
+    if (MODE == DESC_OUT_SPLIT) {
+        __syncthreads();
+        if (tid == 0) s_bc[0] = 0u;
+        __syncthreads();
+        float mx = 0.f;
+#pragma unroll
+        for (int i = 0; i < NPIX / DESC_THREADS; i++) mx = fmaxf(mx, prm.bnorm ? mag[i] * scale : mag[i]);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        if ((tid & 31) == 0) atomicMax(&s_bc[0], __float_as_uint(mx));     // non-negative floats order as uints
+        __syncthreads();
+        mx = __uint_as_float(s_bc[0]);
+        if (mx > 0.f && isfinite(mx)) pscale = exp2f((float)(14 - ilogbf(mx)));
+        if (tid == 0) inv_scale[slot] = 1.0f / pscale;
+    }
+
 #pragma unroll
     for (int i = 0; i < NPIX / DESC_THREADS; i++) {
         int p = tid + DESC_THREADS * i;
@@ -213,10 +235,10 @@ k_desc(const uint8_t *__restrict__ patches, const int32_t *__restrict__ ids, int
                 if (MODE == DESC_OUT_ROWS) {
                     out0[o] = v[b];
                 } else {
-                    float hi, lo;
-                    tf32_split(v[b], hi, lo);
-                    out0[o] = hi;
-                    out1[o] = lo;
+                    const float sv = v[b] * pscale;
+                    const __half hi = __float2half_rn(sv);
+                    reinterpret_cast<__half *>(out0)[o] = hi;
+                    reinterpret_cast<__half *>(out1)[o] = __float2half_rn(sv - __half2float(hi));
                 }
             }
         }
@@ -249,7 +271,7 @@ static int make_params(int nbins, float sigma, int bnorm, DescParams *prm)
 
 int dlco_launch_desc(dlco_ctx *ctx, int mode, const uint8_t *d_patches, const int32_t *d_ids,
                      int id_stride, int n_slots, int n_slots_padded, int nbins, float sigma,
-                     int bnorm, float *out0, float *out1)
+                     int bnorm, float *out0, float *out1, float *inv_scale)
 {
     DescParams prm;
     int r = make_params(nbins, sigma, bnorm, &prm);
@@ -257,11 +279,11 @@ int dlco_launch_desc(dlco_ctx *ctx, int mode, const uint8_t *d_patches, const in
     if (n_slots_padded <= 0) return DLCO_OK;
     dim3 grid(n_slots_padded), block(DESC_THREADS);
     if (mode == DESC_OUT_PT)
-        k_desc<DESC_OUT_PT><<<grid, block, 0, ctx->stream>>>(d_patches, d_ids, id_stride, n_slots, prm, out0, out1);
+        k_desc<DESC_OUT_PT><<<grid, block, 0, ctx->stream>>>(d_patches, d_ids, id_stride, n_slots, prm, out0, out1, inv_scale);
     else if (mode == DESC_OUT_ROWS)
-        k_desc<DESC_OUT_ROWS><<<grid, block, 0, ctx->stream>>>(d_patches, d_ids, id_stride, n_slots, prm, out0, out1);
+        k_desc<DESC_OUT_ROWS><<<grid, block, 0, ctx->stream>>>(d_patches, d_ids, id_stride, n_slots, prm, out0, out1, inv_scale);
     else
-        k_desc<DESC_OUT_SPLIT><<<grid, block, 0, ctx->stream>>>(d_patches, d_ids, id_stride, n_slots, prm, out0, out1);
+        k_desc<DESC_OUT_SPLIT><<<grid, block, 0, ctx->stream>>>(d_patches, d_ids, id_stride, n_slots, prm, out0, out1, inv_scale);
     DLCO_CHECK_LAUNCH(ctx);
     return DLCO_OK;
 }
@@ -272,5 +294,5 @@ extern "C" int dlco_get_desc(dlco_ctx *ctx, const uint8_t *d_patches, const int3
     DLCO_REQUIRE(ctx && d_patches && d_ids && d_out, "dlco_get_desc: NULL argument");
     DLCO_REQUIRE(n >= 0, "dlco_get_desc: n < 0");
     DLCO_REQUIRE(nAngleBins == 8, "dlco_get_desc: output layout is fixed at 8 bins (got %d)", nAngleBins);
-    return dlco_launch_desc(ctx, DESC_OUT_PT, d_patches, d_ids, 1, n, n, nAngleBins, sigma, bNorm, d_out, nullptr);
+    return dlco_launch_desc(ctx, DESC_OUT_PT, d_patches, d_ids, 1, n, n, nAngleBins, sigma, bNorm, d_out, nullptr, nullptr);
 }

@@ -51,26 +51,27 @@ static int fulldist_batch(dlco_ctx *ctx, const dlco_bank *bank, const uint8_t *d
                           float *d_out, int64_t ld_out)
 {
     const int npad = (n + 15) / 16 * 16;
-    const size_t plane = (size_t)npad * 16 * 4096 * sizeof(float);
     int r;
     if (use_simt()) {
-        float *rows = (float *)dlco_scratch(ctx, 0, plane);
+        float *rows = (float *)dlco_scratch(ctx, 0, (size_t)n * 16 * 4096 * sizeof(float));
         if (!rows) return DLCO_ENOMEM;
-        r = dlco_launch_desc(ctx, DESC_OUT_ROWS, d_patches, d_idx, 4, 2 * n, 2 * n, nbins, sigma, bnorm, rows, nullptr);
+        r = dlco_launch_desc(ctx, DESC_OUT_ROWS, d_patches, d_idx, 4, 2 * n, 2 * n, nbins, sigma, bnorm, rows, nullptr, nullptr);
         if (r != DLCO_OK) return r;
         return dlco_launch_pool_simt(ctx, 0, bank->d_f32, bank->nF, rows, n, d_out, ld_out);
     }
-    float *bhi = (float *)dlco_scratch(ctx, 0, plane);
-    float *blo = (float *)dlco_scratch(ctx, 1, plane);
-    if (!bhi || !blo) return DLCO_ENOMEM;
+    // fp16 hi / lo planes of the B operand, 1/scale per slot, per-filter squared differences
+    const size_t plane = (size_t)npad * 16 * 4096 * 2;
+    uint8_t *bhi = (uint8_t *)dlco_scratch(ctx, 0, plane);
+    uint8_t *blo = (uint8_t *)dlco_scratch(ctx, 1, plane);
+    float *binv = (float *)dlco_scratch(ctx, 2, (size_t)npad * 2 * sizeof(float));
+    float *S = (float *)dlco_scratch(ctx, 3, (size_t)n * bank->nRowsPad * sizeof(float));
+    if (!bhi || !blo || !binv || !S) return DLCO_ENOMEM;
     dlco_prof_begin(ctx, 0);
-    r = dlco_launch_desc(ctx, DESC_OUT_SPLIT, d_patches, d_idx, 4, 2 * n, 2 * npad, nbins, sigma, bnorm, bhi, blo);
+    r = dlco_launch_desc(ctx, DESC_OUT_SPLIT, d_patches, d_idx, 4, 2 * n, 2 * npad, nbins, sigma, bnorm,
+                         (float *)bhi, (float *)blo, binv);
     dlco_prof_end(ctx);
     if (r != DLCO_OK) return r;
-    dlco_prof_begin(ctx, 1);
-    r = dlco_launch_pool_tc(ctx, bank, bhi, blo, n, npad, d_out, ld_out);
-    dlco_prof_end(ctx);
-    return r;
+    return dlco_launch_pool_tc(ctx, bank, bhi, blo, binv, n, npad, S, d_out, ld_out);
 }
 
 extern "C" int dlco_fulldist_build(dlco_ctx *ctx, const dlco_bank *bank, const uint8_t *d_patches,
@@ -110,8 +111,8 @@ extern "C" int dlco_fulldist_build_host(dlco_ctx *ctx, const dlco_bank *bank, co
         h_stage[s] = (uint8_t *)dlco_pinned(ctx, s, pbytes + ibytes);
         if (!h_stage[s]) return DLCO_ENOMEM;
     }
-    uint8_t *d_stage = (uint8_t *)dlco_scratch(ctx, 2, 2 * (pbytes + ibytes));
-    float *d_o = (float *)dlco_scratch(ctx, 3, (size_t)nb * rings * sizeof(float));
+    uint8_t *d_stage = (uint8_t *)dlco_scratch(ctx, 23, 2 * (pbytes + ibytes));
+    float *d_o = (float *)dlco_scratch(ctx, 24, (size_t)nb * rings * sizeof(float));
     if (!d_stage || !d_o) return DLCO_ENOMEM;
     cudaEvent_t ev[2];
     for (int s = 0; s < 2; s++) DLCO_CUDA(cudaEventCreateWithFlags(&ev[s], cudaEventDisableTiming));
@@ -170,7 +171,7 @@ extern "C" int dlco_uprjdist_build(dlco_ctx *ctx, const dlco_bank *bank, const u
         float *rows = (float *)dlco_scratch(ctx, 0, (size_t)n * 16 * 4096 * sizeof(float));
         if (!rows) return DLCO_ENOMEM;
         r = dlco_launch_desc(ctx, DESC_OUT_ROWS, d_patches, d_indices + p * 4, 4, 2 * n, 2 * n, nAngleBins,
-                             sigma, bNorm, rows, nullptr);
+                             sigma, bNorm, rows, nullptr, nullptr);
         if (r != DLCO_OK) return r;
         r = dlco_launch_pool_simt(ctx, 1, bank->d_f32, bank->nF, rows, n, d_out + (p - lo) * ld_out, ld_out);
         if (r != DLCO_OK) return r;

@@ -8,9 +8,11 @@ enum { DESC_OUT_PT = 0, DESC_OUT_ROWS = 1, DESC_OUT_SPLIT = 2 };
 // id_stride 4: d_ids is the N x 4 "Indices" matrix, slot s = (row s/2, column 0 or 2).
 int dlco_launch_desc(dlco_ctx *ctx, int mode, const uint8_t *d_patches, const int32_t *d_ids,
                      int id_stride, int n_slots, int n_slots_padded, int nbins, float sigma,
-                     int bnorm, float *out0, float *out1);
+                     int bnorm, float *out0, float *out1, float *inv_scale);
 
 // api.cu
+int dlco_make_tmap_2d_ex(CUtensorMap *map, const void *base, int elem_bytes, uint64_t rows, uint64_t cols,
+                         uint32_t box_rows, uint32_t box_cols);
 int dlco_make_tmap_2d(CUtensorMap *map, const float *base, uint64_t rows, uint64_t cols,
                       uint32_t box_rows, uint32_t box_cols);
 
@@ -20,10 +22,13 @@ int dlco_make_tmap_2d(CUtensorMap *map, const float *base, uint64_t rows, uint64
 int dlco_launch_pool_simt(dlco_ctx *ctx, int mode, const float *d_filters, int nF,
                           const float *d_rows, int n_pairs, float *d_out, int64_t ld_out);
 
-// pool_tc.cu: tcgen05 3xTF32 pooling GEMM + fused full-distance epilogue
-int dlco_launch_pool_tc(dlco_ctx *ctx, const dlco_bank *bank, const float *d_bhi,
-                        const float *d_blo, int n_pairs, int n_pairs_padded, float *d_out,
-                        int64_t ld_out);
+// pool_tc.cu: tcgen05 pooling GEMM (3 x fp16 products, fp32 accumulate) + fused epilogue.
+// d_bhi / d_blo: fp16 planes (n_pairs_padded * 16) x 4096, d_binv: 1/scale per slot;
+// d_S: n_pairs x bank->nRowsPad per-filter squared differences (scratch), then the ring
+// reduction writes d_out.
+int dlco_launch_pool_tc(dlco_ctx *ctx, const dlco_bank *bank, const void *d_bhi, const void *d_blo,
+                        const float *d_binv, int n_pairs, int n_pairs_padded, float *d_S,
+                        float *d_out, int64_t ld_out);
 
 // hinge.cu
 int dlco_hinge_pairsum_dev(dlco_ctx *ctx, const float *d_pos, int64_t n1, const float *d_neg,

@@ -1,39 +1,52 @@
 // K_pool_fulldist: the comp-fulldists hot loop (reference src/comp-fulldists.cpp:328-342) as ONE
-// persistent, warp-specialised tcgen05 GEMM with a fused epilogue.
+// persistent, warp-specialised tcgen05 GEMM with a fused epilogue, plus the ring reduction.
 //
-//   D[f, (pair, patch, bin)] = sum_k F[f, k] * T[(pair, patch, bin), k]          (K = 4096)
-//   Dist[pair, ring] = sum_{j<8} sum_{b<8} ( min(D[8 ring + j, pair, 1, b], 1)
-//                                          - min(D[8 ring + j, pair, 0, b], 1) )^2
+//   P[r, (pair, patch, bin)] = sum_k F[r, k] * T[(pair, patch, bin), k]            (K = 4096)
+//   S[pair, r]    = sum_{b<8} ( min(P[r, pair, 1, b], 1) - min(P[r, pair, 0, b], 1) )^2
+//   Dist[pair, g] = sum_{j<8} S[pair, map[8 g + j]]                (K_ring_reduce, below)
 //
-// fp32 accuracy on the tensor pipe: 3xTF32.  Both operands are pre-split into tf32 planes
-// (hi = rna(x), lo = rna(x - hi)); each K step issues  hi*hi + hi*lo + lo*hi  into the same
-// fp32 TMEM accumulator (the dropped lo*lo term is ~2^-22 relative).
+// fp32 accuracy on the tensor pipe.  Both operands are split into two fp16 planes after a
+// power-of-two scaling that keeps every hi AND lo value a normal fp16 number (filters per row,
+// descriptors per patch): v * s = hi + lo + O(2^-22 v s).  Each K step issues lo*hi + hi*lo +
+// hi*hi (kind::f16, fp32 accumulate); the products are exact in fp32.  This carries the same 22
+// mantissa bits as a 3xTF32 split at twice the tensor rate and half the operand bytes.
 //
-// CTA tile 128 filters (TMEM lanes) x 256 columns (16 pairs x 2 patches x 8 bins), K step 32
-// floats = one 128-byte swizzle row.  Roles: warp 0 = TMA producer, warp 1 = MMA issuer (one
-// lane) + TMEM owner, warps 2..5 = epilogue (TMEM -> registers -> clamp/diff/square ->
-// 8-lane ring reduction -> global).  Two TMEM accumulators (2 x 256 columns) let the epilogue
-// of tile i overlap the MMAs of tile i+1.
+// The tensor core adds into its fp32 accumulator with truncation (measured: the bias grows
+// linearly with the number of accumulated MMAs, -2e-5 relative at K = 4096 for non-negative
+// operands).  The accumulation is therefore cut every FLUSH K-chunks: the epilogue warps drain
+// the partial sums from TMEM and add them in round-to-nearest fp32 registers, which bounds the
+// truncation bias by that of a K = 256 product (< 1e-6).
+//
+// Sparsity: rows of the A operand are the DISTINCT filters of the bank sorted by K support
+// (api.cu), and kmask[m] says which 64-wide K chunks contain a non-zero of M tile m; producer
+// and MMA issuer walk only those chunks (56 % of the dense work for the gen-poolregion bank).
+//
+// CTA tile 128 rows (TMEM lanes) x 256 columns (16 pairs x 2 patches x 8 bins), K chunk 64 fp16 =
+// one 128-byte swizzle row.  Roles: warp 0 = TMA producer, warp 1 = MMA issuer (one lane) + TMEM
+// owner, warps 2..9 = epilogue (two warps per TMEM lane quarter, 128 columns each).  Two TMEM
+// accumulators (2 x 256 columns): the drain of one overlaps the MMAs into the other.
 //
 // Tile order: n (pair block) fastest, so the CTAs resident at one time share a few filter
-// tiles and all pair tiles of the batch and walk K in step: the live working set in L2 is a
-// window of K chunks, and each operand byte is fetched from HBM about once per batch.
+// tiles and all pair tiles of the batch: the B planes of a 256-pair batch (64 MB) stay in L2 and
+// the A planes stream from HBM once per batch.
 #include "common.cuh"
 #include "kernels.h"
+#include <cuda_fp16.h>
 
 namespace {
 
 constexpr int BM = 128;
 constexpr int BN = 256;
-constexpr int BK = 32;
+constexpr int BK = 64;                       // fp16 elements per K chunk (128 bytes)
 constexpr int KTOT = DLCO_PATCH * DLCO_PATCH;
-constexpr int KCHUNKS = KTOT / BK;
 constexpr int STAGES = 2;
-constexpr int A_BYTES = BM * BK * 4;
-constexpr int B_BYTES = BN * BK * 4;
+constexpr int FLUSH = 4;                     // K chunks accumulated in TMEM between drains
+constexpr int A_BYTES = BM * BK * 2;
+constexpr int B_BYTES = BN * BK * 2;
 constexpr int STAGE_BYTES = 2 * A_BYTES + 2 * B_BYTES;
 constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256;
-constexpr int NTHREADS = 192;
+constexpr int EPI_WARPS = 8;
+constexpr int NTHREADS = 64 + EPI_WARPS * 32;
 constexpr int TMEM_COLS = 512;
 
 struct __align__(64) TMaps {
@@ -41,8 +54,9 @@ struct __align__(64) TMaps {
 };
 
 __global__ void __launch_bounds__(NTHREADS, 1)
-k_pool_fulldist(const __grid_constant__ TMaps maps, int m_tiles, int n_tiles, int n_pairs,
-                int n_rings, float *__restrict__ out, int64_t ld_out)
+k_pool_fulldist(const __grid_constant__ TMaps maps, const uint64_t *__restrict__ kmask,
+                const float *__restrict__ a_inv, const float *__restrict__ b_inv, int m_tiles,
+                int n_tiles, int n_pairs, int n_rows, float *__restrict__ S, int64_t ld_s)
 {
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -67,7 +81,7 @@ k_pool_fulldist(const __grid_constant__ TMaps maps, int m_tiles, int n_tiles, in
         }
         for (int a = 0; a < 2; a++) {
             mbar_init(&tfull[a], 1);
-            mbar_init(&tempty[a], 4);
+            mbar_init(&tempty[a], EPI_WARPS);
         }
         fence_barrier_init();
     }
@@ -84,7 +98,10 @@ k_pool_fulldist(const __grid_constant__ TMaps maps, int m_tiles, int n_tiles, in
             uint32_t phase = 0;
             for (int t = blockIdx.x; t < total; t += gridDim.x) {
                 const int m = t / n_tiles, n = t % n_tiles;
-                for (int kc = 0; kc < KCHUNKS; kc++) {
+                uint64_t mask = kmask[m];
+                while (mask) {
+                    const int kc = __ffsll((long long)mask) - 1;
+                    mask &= mask - 1;
                     mbar_wait(&empty[stage], phase ^ 1);
                     uint8_t *st = smem + stage * STAGE_BYTES;
                     mbar_expect_tx(&full[stage], STAGE_BYTES);
@@ -99,16 +116,20 @@ k_pool_fulldist(const __grid_constant__ TMaps maps, int m_tiles, int n_tiles, in
     } else if (warp == 1) {
         // ===== MMA issuer =====
         if (lane == 0) {
-            constexpr uint32_t idesc = umma_idesc_tf32(BM, BN);
+            constexpr uint32_t idesc = umma_idesc_f16(BM, BN);
             int stage = 0;
             uint32_t phase = 0;
-            int it = 0;
-            for (int t = blockIdx.x; t < total; t += gridDim.x, it++) {
-                const int acc = it & 1;
-                mbar_wait(&tempty[acc], ((it >> 1) & 1) ^ 1);
-                tc_fence_after();
-                const uint32_t d_tmem = tmem_base + acc * BN;
-                for (int kc = 0; kc < KCHUNKS; kc++) {
+            uint32_t it = 0;                       // drains so far (accumulator = it & 1)
+            for (int t = blockIdx.x; t < total; t += gridDim.x) {
+                uint64_t mask = kmask[t / n_tiles];
+                int in_flush = 0;
+                while (mask) {
+                    mask &= mask - 1;
+                    const uint32_t d_tmem = tmem_base + (it & 1) * BN;
+                    if (in_flush == 0) {
+                        mbar_wait(&tempty[it & 1], ((it >> 1) & 1) ^ 1);
+                        tc_fence_after();
+                    }
                     mbar_wait(&full[stage], phase);
                     tc_fence_after();
                     const uint32_t sa = smem_u32(smem + stage * STAGE_BYTES);
@@ -117,49 +138,67 @@ k_pool_fulldist(const __grid_constant__ TMaps maps, int m_tiles, int n_tiles, in
                     const uint64_t d_bhi = umma_desc_sw128(sa + 2 * A_BYTES);
                     const uint64_t d_blo = umma_desc_sw128(sa + 2 * A_BYTES + B_BYTES);
 #pragma unroll
-                    for (int k = 0; k < BK / 8; k++) {
-                        const uint64_t ko = (uint64_t)(k * 2);   // 8 tf32 = 32 B = 2 x 16 B
-                        umma_tf32(d_tmem, d_alo + ko, d_bhi + ko, idesc, (kc | k) != 0);
-                        umma_tf32(d_tmem, d_ahi + ko, d_blo + ko, idesc, 1);
-                        umma_tf32(d_tmem, d_ahi + ko, d_bhi + ko, idesc, 1);
+                    for (int k = 0; k < BK / 16; k++) {
+                        const uint64_t ko = (uint64_t)(k * 2);   // 16 fp16 = 32 B = 2 x 16 B
+                        umma_f16(d_tmem, d_alo + ko, d_bhi + ko, idesc, (in_flush | k) != 0);
+                        umma_f16(d_tmem, d_ahi + ko, d_blo + ko, idesc, 1);
+                        umma_f16(d_tmem, d_ahi + ko, d_bhi + ko, idesc, 1);
                     }
                     umma_commit(&empty[stage]);
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                    if (++in_flush == FLUSH || mask == 0) {
+                        umma_commit(&tfull[it & 1]);
+                        it++;
+                        in_flush = 0;
+                    }
                 }
-                umma_commit(&tfull[acc]);
             }
         }
     } else {
-        // ===== epilogue: warps 2..5, TMEM lane quarter = warp % 4 =====
-        const int q = warp & 3;
-        int it = 0;
-        for (int t = blockIdx.x; t < total; t += gridDim.x, it++) {
+        // ===== epilogue: warps 2..9; TMEM lane quarter = warp % 4, column half = (warp - 2) / 4 =====
+        const int q = warp & 3, half = (warp - 2) >> 2;
+        uint32_t it = 0;
+        for (int t = blockIdx.x; t < total; t += gridDim.x) {
             const int m = t / n_tiles, n = t % n_tiles;
-            const int acc = it & 1;
-            mbar_wait(&tfull[acc], (it >> 1) & 1);
-            tc_fence_after();
-            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN;
-            const int ring = m * (BM / 8) + q * 4 + (lane >> 3);
-#pragma unroll 4
-            for (int j = 0; j < BN / 16; j++) {
-                float v[16];
-                tmem_ld16(taddr + j * 16, v);
+            const int n_flush = (__popcll(kmask[m]) + FLUSH - 1) / FLUSH;
+            float acc[BN / 2];
+#pragma unroll
+            for (int i = 0; i < BN / 2; i++) acc[i] = 0.f;
+            for (int f = 0; f < n_flush; f++, it++) {
+                mbar_wait(&tfull[it & 1], (it >> 1) & 1);
+                tc_fence_after();
+                const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (it & 1) * BN + half * (BN / 2);
+#pragma unroll
+                for (int j = 0; j < BN / 32; j += 2) {
+                    uint32_t r0[16], r1[16];
+                    tmem_ld16_nowait(taddr + j * 16, r0);
+                    tmem_ld16_nowait(taddr + (j + 1) * 16, r1);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int e = 0; e < 16; e++) {
+                        acc[j * 16 + e] += __uint_as_float(r0[e]);
+                        acc[(j + 1) * 16 + e] += __uint_as_float(r1[e]);
+                    }
+                }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&tempty[it & 1]);
+            }
+            // clamp, difference, square, sum over the 8 bins -> S[pair][row]
+            const int row = m * BM + q * 32 + lane;
+            const float ra = a_inv[row];
+#pragma unroll
+            for (int j = 0; j < BN / 32; j++) {
+                const int pair = n * (BN / 16) + half * (BN / 32) + j;
+                const float s1 = ra * __ldg(b_inv + 2 * pair), s2 = ra * __ldg(b_inv + 2 * pair + 1);
                 float d = 0.f;
 #pragma unroll
                 for (int b = 0; b < 8; b++) {
-                    float l = fminf(v[8 + b], 1.f) - fminf(v[b], 1.f);
+                    const float l = fminf(acc[j * 16 + 8 + b] * s2, 1.f) - fminf(acc[j * 16 + b] * s1, 1.f);
                     d = fmaf(l, l, d);
                 }
-                d += __shfl_xor_sync(0xffffffffu, d, 1);
-                d += __shfl_xor_sync(0xffffffffu, d, 2);
-                d += __shfl_xor_sync(0xffffffffu, d, 4);
-                const int pair = n * (BN / 16) + j;
-                if ((lane & 7) == 0 && pair < n_pairs && ring < n_rings)
-                    out[(size_t)pair * ld_out + ring] = d;
+                if (pair < n_pairs && row < n_rows) S[(size_t)pair * ld_s + row] = d;
             }
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&tempty[acc]);
         }
     }
 
@@ -171,31 +210,58 @@ k_pool_fulldist(const __grid_constant__ TMaps maps, int m_tiles, int n_tiles, in
     }
 }
 
+// Dist[pair][g] = sum_{j<8} S[pair][map[8 g + j]] in the fixed order j = 0..7
+// (cuda::reduce over the 8 members of a ring, src/comp-fulldists.cpp:341-342)
+__global__ void __launch_bounds__(256)
+k_ring_reduce(const float *__restrict__ S, int64_t ld_s, const int32_t *__restrict__ map, int n_rings,
+              float *__restrict__ out, int64_t ld_out)
+{
+    const int pair = blockIdx.y;
+    const float *s = S + (size_t)pair * ld_s;
+    for (int g = blockIdx.x * 256 + threadIdx.x; g < n_rings; g += gridDim.x * 256) {
+        const int4 m0 = reinterpret_cast<const int4 *>(map)[2 * g], m1 = reinterpret_cast<const int4 *>(map)[2 * g + 1];
+        float d = s[m0.x];
+        d += s[m0.y]; d += s[m0.z]; d += s[m0.w];
+        d += s[m1.x]; d += s[m1.y]; d += s[m1.z]; d += s[m1.w];
+        __stcs(out + (size_t)pair * ld_out + g, d);
+    }
+}
+
 }  // namespace
 
-int dlco_launch_pool_tc(dlco_ctx *ctx, const dlco_bank *bank, const float *d_bhi,
-                        const float *d_blo, int n_pairs, int n_pairs_padded, float *d_out,
-                        int64_t ld_out)
+int dlco_launch_pool_tc(dlco_ctx *ctx, const dlco_bank *bank, const void *d_bhi, const void *d_blo,
+                        const float *d_binv, int n_pairs, int n_pairs_padded, float *d_S,
+                        float *d_out, int64_t ld_out)
 {
     if (n_pairs <= 0) return DLCO_OK;
     DLCO_REQUIRE(n_pairs_padded % 16 == 0 && n_pairs_padded >= n_pairs, "pool_tc: bad padding");
+    DLCO_REQUIRE(n_pairs <= 65535, "pool_tc: at most 65535 pairs per launch");
     TMaps maps;
     maps.a_hi = bank->map_hi;
     maps.a_lo = bank->map_lo;
-    int r = dlco_make_tmap_2d(&maps.b_hi, d_bhi, (uint64_t)n_pairs_padded * 16, KTOT, BN, BK);
+    int r = dlco_make_tmap_2d_ex(&maps.b_hi, d_bhi, 2, (uint64_t)n_pairs_padded * 16, KTOT, BN, BK);
     if (r != DLCO_OK) return r;
-    r = dlco_make_tmap_2d(&maps.b_lo, d_blo, (uint64_t)n_pairs_padded * 16, KTOT, BN, BK);
+    r = dlco_make_tmap_2d_ex(&maps.b_lo, d_blo, 2, (uint64_t)n_pairs_padded * 16, KTOT, BN, BK);
     if (r != DLCO_OK) return r;
     static bool attr_set = false;
     if (!attr_set) {
         DLCO_CUDA(cudaFuncSetAttribute(k_pool_fulldist, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
         attr_set = true;
     }
-    const int m_tiles = bank->nFpad / BM, n_tiles = n_pairs_padded / 16;
+    const int m_tiles = bank->nRowsPad / BM, n_tiles = n_pairs_padded / 16;
     const int total = m_tiles * n_tiles;
     const int grid = total < ctx->sm_count ? total : ctx->sm_count;
-    k_pool_fulldist<<<grid, NTHREADS, SMEM_BYTES, ctx->stream>>>(maps, m_tiles, n_tiles, n_pairs,
-                                                                bank->nF / 8, d_out, ld_out);
+    dlco_prof_begin(ctx, 1);
+    k_pool_fulldist<<<grid, NTHREADS, SMEM_BYTES, ctx->stream>>>(maps, bank->d_kmask, bank->d_inv_scale, d_binv,
+                                                                m_tiles, n_tiles, n_pairs, bank->nRows, d_S,
+                                                                bank->nRowsPad);
+    dlco_prof_end(ctx);
+    DLCO_CHECK_LAUNCH(ctx);
+    const int n_rings = bank->nF / 8;
+    dim3 rg((n_rings + 255) / 256 < 8 ? (n_rings + 255) / 256 : 8, n_pairs);
+    dlco_prof_begin(ctx, 6);
+    k_ring_reduce<<<rg, 256, 0, ctx->stream>>>(d_S, bank->nRowsPad, bank->d_map, n_rings, d_out, ld_out);
+    dlco_prof_end(ctx);
     DLCO_CHECK_LAUNCH(ctx);
     return DLCO_OK;
 }

@@ -64,6 +64,8 @@ def gpu_ctx():
     import torch
     if not torch.cuda.is_available():
         pytest.skip("no CUDA device")
+    import __graft_entry__
+    __graft_entry__.build()            # no-op when libdlco_b200.so is newer than its sources
     import dlco_b200
     ctx = dlco_b200.Context(0)
     yield ctx
