@@ -323,6 +323,7 @@ def main():
     launches = ctx.launch_count() - l0
     pool_ms, pool_n = ctx.profile_read(1)
     desc_ms, desc_n = ctx.profile_read(0)
+    red_ms, red_n = ctx.profile_read(6)
     ctx.profile(False)
     clk = clocks.stop() if rank == 0 else None
     checksum = float(out[:: max(1, n_pairs // 1000)].double().sum().item())
@@ -369,21 +370,35 @@ def main():
     except (OSError, ValueError):
         pass
     bf16 = peaks.get("bf16_tflops_sustained")
-    peak_src = "MEASURED_PEAKS.json bf16_tflops_sustained / 2 (tf32 issues at half the bf16 rate)"
+    peak_src = "of measured: MEASURED_PEAKS.json bf16_tflops_sustained (kernel timed inside a long step)"
     if not bf16:
-        bf16, peak_src = 1400.0, "fallback 1.4 PFLOP/s sustained bf16 / 2 (B200_PROFILING.md)"
-    tf32_peak = bf16 / 2.0
-    pairs_per_launch = n_pairs * args.steps / max(pool_n, 1)
+        bf16, peak_src = 1400.0, "of fallback: 1.4 PFLOP/s sustained bf16 (B200_PROFILING.md)"
+    # what one launch of k_pool_fulldist does: every non-empty (128-row tile, 64-wide K chunk) block of
+    # the bank against every 256-column pair tile, 3 fp16 MMA passes (lo*hi + hi*lo + hi*hi)
+    info = bank.info()
+    batch = int(os.environ.get("DLCO_FULLDIST_BATCH", "256"))
+    launches_per_step = -(-n_pairs // batch)
+    pairs_issued = 0
+    for b0 in range(0, n_pairs, batch):
+        pairs_issued += -(-min(batch, n_pairs - b0) // 16) * 16
+    issued_flop_per_pair_slot = 2.0 * 3 * info["k_chunks"] * 128 * 64 * 16
+    issued_per_step = issued_flop_per_pair_slot * pairs_issued
     avg_ms = pool_ms / max(pool_n, 1)
-    issued_tflops = 3.0 * FLOP_PER_PAIR * pairs_per_launch / (avg_ms * 1e-3) / 1e12 if pool_n else None
+    issued_tflops = issued_per_step * args.steps / (pool_ms * 1e-3) / 1e12 if pool_n else None
+    dense_equiv_tflops = FLOP_PER_PAIR * n_pairs * args.steps / (pool_ms * 1e-3) / 1e12 if pool_n else None
     roofline = {
-        "bound": "tensor", "kernel": "k_pool_fulldist (tcgen05 kind::tf32, 3xTF32)",
-        "achieved": issued_tflops, "peak": tf32_peak, "unit": "TFLOP/s",
-        "frac": (issued_tflops / tf32_peak) if issued_tflops else None, "traffic": None,
+        "bound": "tensor", "kernel": "k_pool_fulldist (tcgen05 kind::f16, 3 fp16 passes = fp32-equivalent)",
+        "achieved": issued_tflops, "peak": bf16, "unit": "TFLOP/s",
+        "frac": (issued_tflops / bf16) if issued_tflops else None, "traffic": None,
         "peak_source": peak_src, "launches": pool_n, "avg_launch_ms": avg_ms,
-        "fp32_equiv_tflops": issued_tflops / 3.0 if issued_tflops else None,
+        "achieved_is": "fp16 tensor flops the kernel issues (non-empty tile x K-chunk blocks x 3 passes)",
+        "issued_gflop_per_pair": issued_flop_per_pair_slot / 1e9,
+        "algorithmic_gflop_per_pair_dense_fp32": FLOP_PER_PAIR / 1e9,
+        "algorithmic_tflops_dense_equiv": dense_equiv_tflops,
+        "bank": info, "launches_per_step": launches_per_step,
         "kernel_share_of_step": pool_ms / ms if ms else None,
         "desc_kernel_ms_total": desc_ms, "desc_launches": desc_n,
+        "reduce_kernel_ms_total": red_ms, "reduce_launches": red_n,
         "out_stream_gbs": n_pairs * args.steps * (RINGS * 4 + 8192) / (ms * 1e-3) / 1e9,
     }
     cpu = None
@@ -400,8 +415,8 @@ def main():
         "data": "synthetic",
         "config": {"workload": "comp-fulldists full build: %d synthetic 64x64 patch pairs x 5120 rings "
                                "(40960 filters) per GPU, pair-sharded" % n_pairs,
-                   "pairs_per_gpu": n_pairs, "filters": NFILT, "arith": "3xTF32 on tcgen05, fp32 accumulate",
-                   "l2": "inputs larger than L2 (1.34 GB filter planes streamed per 256-pair batch)",
+                   "pairs_per_gpu": n_pairs, "filters": NFILT, "arith": "3 fp16 products per fp32 product on tcgen05 (22 mantissa bits), fp32 accumulate",
+                   "l2": "inputs larger than L2 (1.04 GB of filter planes streamed per 256-pair batch, 10 GB of output per step)",
                    "reference_gtx970_pairs_per_s": GTX970_PAIRS_PER_S},
         "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
         "cpu_baseline": cpu, "checksum": checksum,

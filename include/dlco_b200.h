@@ -59,18 +59,21 @@ int64_t dlco_launch_count(dlco_ctx *ctx);
 /* per-kernel device timing with CUDA events on the launching stream (bench roofline):
  * enable, run, then read total milliseconds and launch count of kernel class `which`
  * (0 = get_desc, 1 = pooling GEMM, 2 = pj SYRK, 3 = pr GEMV, 4 = pr RDA chain,
- * 5 = pj margins / patch distances). */
+ * 5 = pj margins / patch distances, 6 = ring reduce). */
 int dlco_profile_enable(dlco_ctx *ctx, int on);
 int dlco_profile_read(dlco_ctx *ctx, int which, double *h_ms, int64_t *h_count);
 
 /* ---- pool-region filter bank (prfilters.upload: src/comp-fulldists.cpp:281) ---------
  * h_filters: nF x 4096 f32, element index x*64+y as gen-poolregion writes it
- * (src/gen-poolregion.cpp:68).  The bank keeps the tf32 hi/lo planes the tensor-core
- * kernel consumes.  The full-distance builder needs nF % 8 == 0 (8 members per ring);
+ * (src/gen-poolregion.cpp:68).  The bank keeps the de-duplicated, support-sorted fp16 hi/lo
+ * planes the tensor-core kernel consumes.  The full-distance builder needs nF % 8 == 0 (8 members per ring);
  * the unprojected builder takes any nF (SelectPRFilters output, 60 / 68 in practice). */
 int dlco_bank_create(dlco_ctx *ctx, const float *h_filters, int nF, dlco_bank **bank);
 int dlco_bank_create_dev(dlco_ctx *ctx, const float *d_filters, int nF, dlco_bank **bank);
 int dlco_bank_destroy(dlco_ctx *ctx, dlco_bank *bank);
+/* what the tensor-core kernel actually multiplies: distinct filters (rows), 128-row tiles and the
+ * number of non-empty (tile, 64-wide K chunk) blocks -- 64 per tile when dense */
+int dlco_bank_info(const dlco_bank *bank, int *n_filters, int *n_rows, int *n_tiles, int64_t *k_chunks);
 
 /* ---- get_desc (src/vgg-desc.cpp:41-152) on the GPU -----------------------------------
  * d_patches: P x 64 x 64 u8; d_ids: n patch indices; d_out: n x 4096 x 8 f32

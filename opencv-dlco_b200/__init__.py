@@ -36,6 +36,7 @@ SIGNATURES = {
     "dlco_bank_create": (c_int, [c_void_p, c_void_p, c_int, P(c_void_p)]),
     "dlco_bank_create_dev": (c_int, [c_void_p, c_void_p, c_int, P(c_void_p)]),
     "dlco_bank_destroy": (c_int, [c_void_p, c_void_p]),
+    "dlco_bank_info": (c_int, [c_void_p, P(c_int), P(c_int), P(c_int), P(c_int64)]),
     "dlco_get_desc": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_int, c_void_p]),
     "dlco_fulldist_build": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int,
                                     c_float, c_int, c_void_p, c_int64]),
@@ -116,6 +117,13 @@ class Bank:
         if self.handle:
             load_library().dlco_bank_destroy(self.ctx.handle, self.handle)
             self.handle = None
+
+    def info(self):
+        """-> dict(filters, rows (distinct), tiles (128 rows), k_chunks (non-empty 64-wide chunks))"""
+        nf, nr, nt, kc = c_int(), c_int(), c_int(), c_int64()
+        _check(load_library().dlco_bank_info(self.handle, ctypes.byref(nf), ctypes.byref(nr), ctypes.byref(nt),
+                                            ctypes.byref(kc)))
+        return {"filters": nf.value, "rows": nr.value, "tiles": nt.value, "k_chunks": kc.value}
 
 
 class Context:
