@@ -1,0 +1,201 @@
+#!/usr/bin/env python
+"""bench_paths.py -- device timings of the hot-path rows other than the full-distance build
+(SURVEY 8 rows b, c, d): one JSON object per sub-path with its roofline fraction.
+
+  python bench_paths.py [--n-train 500000] [--n-test 100000] [--quick]
+
+Used by bench.py (`secondary` block) and on its own for the ncu captures under profiles/.
+All inputs are synthetic and resident in HBM; timings are CUDA events on the launching stream,
+after warm-up.  Nothing here touches oracle/.
+"""
+import argparse
+import json
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+
+def _peaks():
+    try:
+        p = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return float(p["hbm_gbs"]), float(p["bf16_tflops_sustained"]), "measured"
+    except (OSError, ValueError, KeyError):
+        return 6500.0, 1400.0, "fallback (B200_PROFILING.md)"
+
+
+def timeit(torch, fn, warm=3, rep=10):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ts = []
+    for _ in range(rep):
+        e0.record()
+        fn()
+        e1.record()
+        torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1))
+    return float(np.mean(ts)), float(np.min(ts))
+
+
+def synth_dists(torch, dev, n, f, seed, sep=0.3):
+    """Distance-like matrix: non-negative, positives (even rows) smaller on average."""
+    g = torch.Generator(device=dev)
+    g.manual_seed(seed)
+    out = torch.empty((n, f), dtype=torch.float32, device=dev)
+    step = 65536
+    for a in range(0, n, step):
+        b = min(n, a + step)
+        x = torch.rand((b - a, f), generator=g, device=dev)
+        lab = ((torch.arange(a, b, device=dev) % 2) == 0).float()[:, None]
+        out[a:b] = x * (1.0 + sep * (1.0 - lab))
+    labels = ((np.arange(n) % 2) == 0).astype(np.uint8)
+    return out, labels
+
+
+def synth_uprj(torch, dev, n, d, seed, sep=0.6):
+    g = torch.Generator(device=dev)
+    g.manual_seed(seed)
+    lab = ((torch.arange(n, device=dev) % 2) == 0).float()[:, None]
+    x = torch.randn((n, d), generator=g, device=dev) * (0.08 + 0.08 * sep * (1.0 - lab))
+    labels = ((np.arange(n) % 2) == 0).astype(np.uint8)
+    return x.contiguous(), labels
+
+
+def run(ctx, n_train=500000, n_test=100000, quick=False, D=544, n_pj_cfg=45, n_pr_cfg=256):
+    import torch
+    import dlco_b200
+    from dlco_b200 import learn
+    dev = ctx.device
+    hbm, bf16, src = _peaks()
+    tf32x3 = bf16 / 2.0 / 3.0                    # fp32-equivalent rate of a 3xTF32 product
+    res = {"peaks": {"hbm_gbs": hbm, "bf16_tflops_sustained": bf16, "source": src}}
+    F = 5120
+
+    # ---- (c)/(d1): GEMV over the full-distance matrix (ComputePRStats, src/misc.cpp:226) -----
+    dists, labels = synth_dists(torch, dev, n_train, F, 11)
+    w = torch.zeros(F, dtype=torch.float32, device=dev)
+    w[torch.randperm(F, device=dev)[:12]] = 0.05
+    mean_ms, best_ms = timeit(torch, lambda: ctx.pr_patchdist(dists, w), rep=5 if quick else 10)
+    gb = n_train * F * 4 / 1e9
+    res["pr_patchdist_gemv"] = {"rows": n_train, "cols": F, "ms": mean_ms, "best_ms": best_ms,
+                                "achieved_gbs": gb / (mean_ms * 1e-3), "frac_hbm": gb / (mean_ms * 1e-3) / hbm,
+                                "bytes": n_train * F * 4}
+
+    # ---- (d1) ROC / FPR95 on n_test pairs -----------------------------------------------
+    pd = ctx.pr_patchdist(dists[:n_test], w)
+    d_lab = torch.from_numpy(labels[:n_test]).to(dev)
+    mean_ms, best_ms = timeit(torch, lambda: ctx.roc_stats(pd, d_lab))
+    res["roc_stats"] = {"n": n_test, "ms": mean_ms, "best_ms": best_ms}
+
+    # ---- (c1) pr-learn RDA chain -----------------------------------------------------------
+    ip, ineg, npt, nnt = learn.split_train_val(labels)
+    d_ip, d_in = torch.from_numpy(ip).to(dev), torch.from_numpy(ineg).to(dev)
+    for n_cfg in (1, n_pr_cfg):
+        mus = np.full(n_cfg, 0.035, np.float32)
+        gammas = np.linspace(0.05, 1.0, n_cfg).astype(np.float32) if n_cfg > 1 else np.array([0.25], np.float32)
+        wv = torch.zeros((n_cfg, F), dtype=torch.float32, device=dev)
+        df = torch.zeros_like(wv)
+        steps = 20000 if quick else 200000
+        st = {"s": 2215, "t": 0}
+
+        def chain():
+            st["s"] = ctx.pr_rda_run(dists, d_ip, npt, d_in, nnt, mus, gammas, st["t"], steps, st["s"], wv, df)
+            st["t"] += steps
+        mean_ms, best_ms = timeit(torch, chain, warm=1, rep=3)
+        res["pr_rda_%dcfg" % n_cfg] = {"steps": steps, "ms": mean_ms,
+                                       "steps_per_s_per_cfg": steps / (mean_ms * 1e-3),
+                                       "cfg_steps_per_s": n_cfg * steps / (mean_ms * 1e-3),
+                                       "algorithmic_bytes_per_step": 2 * F * 4,
+                                       "achieved_gbs": n_cfg * steps * 2 * F * 4 / (mean_ms * 1e-3) / 1e9,
+                                       "nnz": int((wv[0] != 0).sum().item())}
+
+    # ---- (c2) pr validation: 2 gathered GEMVs + 50k x 50k hinge ------------------------------
+    pos_val, neg_val = d_ip[npt:].contiguous(), d_in[nnt:].contiguous()
+    mean_ms, best_ms = timeit(torch, lambda: ctx.pr_validate(dists, pos_val, neg_val, w, 0.035))
+    vb = (pos_val.numel() + neg_val.numel()) * F * 4
+    res["pr_validate"] = {"n_pos": pos_val.numel(), "n_neg": neg_val.numel(), "ms": mean_ms,
+                          "achieved_gbs": vb / (mean_ms * 1e-3) / 1e9, "frac_hbm": vb / (mean_ms * 1e-3) / 1e9 / hbm}
+    a = torch.rand(50000, device=dev)
+    b = torch.rand(50000, device=dev) + 0.3
+    mean_ms, best_ms = timeit(torch, lambda: ctx.hinge_pairsum(a, b))
+    res["hinge_pairsum_50k_x_50k"] = {"ms": mean_ms, "gterms_per_s": 2.5e9 / (mean_ms * 1e-3) / 1e9}
+    del dists, wv, df
+    torch.cuda.empty_cache()
+
+    # ---- (b) pj-learn inner step at D ---------------------------------------------------------
+    ud, ulabels = synth_uprj(torch, dev, n_train, D, 12)
+    split = learn.split_train_val(ulabels)
+    L = learn.PjLearner(ctx, ud, ulabels, 0.001, 0.1, split=split)
+    for _ in range(30):
+        L.step()                                 # let the rank settle
+    torch.cuda.synchronize()
+    rp, rn = L.sample_batch()
+    d_rp, d_rn = torch.from_numpy(rp).to(dev), torch.from_numpy(rn).to(dev)
+    parts = {}
+    parts["grad_ms"] = timeit(torch, lambda: ctx.pj_rda_grad(ud, d_rp, d_rn, L.W, L.rank, out=L.dLoss))[0]
+    dfa = L.dfavg.clone()
+    parts["update_ms"] = timeit(torch, lambda: ctx.pj_rda_update(40, 200, 0.001, 0.1, L.dLoss, dfa, L.A))[0]
+    A0 = L.A.clone()
+    parts["eig_ms"] = timeit(torch, lambda: ctx.pj_eig(A0, L.evals, L.evec), rep=5)[0]
+    Ax, Wx = L.A.clone(), L.W.clone()
+    parts["prox_ms"] = timeit(torch, lambda: ctx.pj_prox_apply(L.evals, L.evec, Ax, Wx))[0]
+    n_it = 20 if quick else 100
+    mean_ms, best_ms = timeit(torch, lambda: [L.step() for _ in range(n_it)], warm=1, rep=3)
+    ctx.profile(True)
+    for _ in range(20):
+        ctx.pj_rda_grad(ud, d_rp, d_rn, L.W, L.rank, out=L.dLoss)
+    torch.cuda.synchronize()
+    syrk_ms, syrk_n = ctx.profile_read(2)
+    ctx.profile(False)
+    syrk_flop = 2.0 * 400 * D * D
+    syrk_avg = syrk_ms / max(syrk_n, 1)
+    res["pj_step"] = dict(parts, D=D, rank=L.rank, iters_per_s=n_it / (mean_ms * 1e-3),
+                          syrk_ms=syrk_avg, syrk_tflops_fp32_equiv=syrk_flop / (syrk_avg * 1e-3) / 1e12 if syrk_n else None,
+                          syrk_frac_of_3xtf32_peak=(syrk_flop / (syrk_avg * 1e-3) / 1e12 / tf32x3) if syrk_n else None)
+
+    # grouped SYRK over the configurations of a sweep sharing one batch
+    Wg = L.W[None, :max(L.rank, 1)].repeat(n_pj_cfg, 1, 1).contiguous()
+    ranks = [L.rank] * n_pj_cfg
+    outg = torch.empty((n_pj_cfg, D, D), dtype=torch.float32, device=dev)
+    ctx.profile(True)
+    mean_ms, _ = timeit(torch, lambda: ctx.pj_rda_grad_grid(ud, d_rp, d_rn, Wg, ranks, out=outg))
+    syrk_ms, syrk_n = ctx.profile_read(2)
+    ctx.profile(False)
+    syrk_avg = syrk_ms / max(syrk_n, 1)
+    res["pj_grad_grid"] = {"n_cfg": n_pj_cfg, "ms": mean_ms, "syrk_ms": syrk_avg,
+                           "syrk_tflops_fp32_equiv": n_pj_cfg * syrk_flop / (syrk_avg * 1e-3) / 1e12 if syrk_n else None,
+                           "syrk_frac_of_3xtf32_peak": (n_pj_cfg * syrk_flop / (syrk_avg * 1e-3) / 1e12 / tf32x3) if syrk_n else None,
+                           "cfg_grads_per_s": n_pj_cfg / (mean_ms * 1e-3)}
+
+    # ---- (d2) ComputePJStats distances + (b6) pj validation -----------------------------------
+    mean_ms, best_ms = timeit(torch, lambda: ctx.pj_patchdist(ud, L.W, L.rank))
+    res["pj_patchdist"] = {"rows": n_train, "D": D, "rank": L.rank, "ms": mean_ms,
+                           "achieved_gbs": n_train * D * 4 / (mean_ms * 1e-3) / 1e9,
+                           "frac_hbm": n_train * D * 4 / (mean_ms * 1e-3) / 1e9 / hbm,
+                           "tflops": 2.0 * n_train * D * max(L.rank, 1) / (mean_ms * 1e-3) / 1e12}
+    mean_ms, best_ms = timeit(torch, lambda: L.validate(), rep=5)
+    res["pj_validate"] = {"ms": mean_ms, "n_pos": L.pos_val.numel(), "n_neg": L.neg_val.numel()}
+    return res
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--n-train", type=int, default=500000)
+    ap.add_argument("--n-test", type=int, default=100000)
+    ap.add_argument("--dim", type=int, default=544)
+    ap.add_argument("--quick", action="store_true")
+    args = ap.parse_args()
+    import torch
+    import dlco_b200
+    ctx = dlco_b200.Context(0)
+    res = run(ctx, args.n_train, args.n_test, args.quick, D=args.dim)
+    print(json.dumps(res))
+
+
+if __name__ == "__main__":
+    main()
