@@ -14,3 +14,4 @@ if "opencv_dlco_b200" not in sys.modules:
 from opencv_dlco_b200 import *  # noqa: F401,F403,E402
 from opencv_dlco_b200 import Context, Bank, DlcoError, load_library, LIB_PATH, SIGNATURES  # noqa: F401,E402
 import opencv_dlco_b200.learn as learn  # noqa: F401,E402
+import opencv_dlco_b200.shard as shard  # noqa: F401,E402

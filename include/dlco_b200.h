@@ -145,6 +145,15 @@ int dlco_pj_rda_grad_grid(dlco_ctx *ctx, const float *d_dists, int64_t ld, int D
                           const int32_t *d_rows_pos, const int32_t *d_rows_neg, int szBatch,
                           int nCfg, const float *d_W, int64_t w_stride, const int *h_rank,
                           float *d_dLoss);
+/* The three stages of dlco_pj_rda_grad as separate calls, for pair-sharded runs (each GPU holds a
+ * row range of "Distance"): margins of the sampled rows a rank owns -> exchange -> hinge weights
+ * c (2*szBatch floats: +nViol_i for positives, -count for negatives, src/pj-learn.cpp:373-410) ->
+ * partial dLoss = sum_k c[k] x_k x_k^T over the owned rows -> all-reduce of the D x D matrix. */
+int dlco_pj_margins(dlco_ctx *ctx, const float *d_dists, int64_t ld, int D, const int32_t *d_rows,
+                    int64_t n, const float *d_W, int rank, float *d_out);
+int dlco_pj_hinge_weights(dlco_ctx *ctx, const float *d_margins, int szBatch, float *d_c);
+int dlco_pj_wsyrk(dlco_ctx *ctx, const float *d_dists, int64_t ld, int D, const int32_t *d_rows,
+                  int nk, const float *d_c, float *d_dLoss);
 /* dfAvg <- t/(t+1) dfAvg + dLoss/(b*b*(t+1));  A <- sym(-sqrt(t+1)/gamma (dfAvg + mu I))
  * (src/pj-learn.cpp:422-432) */
 int dlco_pj_rda_update(dlco_ctx *ctx, int D, uint64_t t, int szBatch, float mu, float gamma,
@@ -166,6 +175,9 @@ int dlco_pj_validate(dlco_ctx *ctx, const float *d_dists, int64_t ld, int D,
  * ROC, FPR at first TPR >= 0.95f, AUC = polygon area.  d_labels: N u8. */
 int dlco_pr_patchdist(dlco_ctx *ctx, const float *d_dists, int64_t N, int64_t ld, int F,
                       const float *d_w, float *d_pd);
+/* Dists[rows, :] . w for an explicit row list (d_rows == NULL: rows 0..n-1) */
+int dlco_pr_margins(dlco_ctx *ctx, const float *d_dists, int64_t ld, int F, const int32_t *d_rows,
+                    int64_t n, const float *d_w, float *d_out);
 int dlco_pj_patchdist(dlco_ctx *ctx, const float *d_dists, int64_t N, int64_t ld, int D,
                       const float *d_W, int rank, float *d_pd);
 int dlco_roc_stats(dlco_ctx *ctx, const float *d_pd, const uint8_t *d_labels, int64_t N,

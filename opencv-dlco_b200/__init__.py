@@ -58,6 +58,10 @@ SIGNATURES = {
                                  c_int, c_void_p]),
     "dlco_pj_rda_grad_grid": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_void_p, c_void_p, c_int, c_int,
                                       c_void_p, c_int64, c_void_p, c_void_p]),
+    "dlco_pj_margins": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_void_p, c_int64, c_void_p, c_int, c_void_p]),
+    "dlco_pj_hinge_weights": (c_int, [c_void_p, c_void_p, c_int, c_void_p]),
+    "dlco_pj_wsyrk": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_void_p, c_int, c_void_p, c_void_p]),
+    "dlco_pr_margins": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_void_p, c_int64, c_void_p, c_void_p]),
     "dlco_pj_rda_update": (c_int, [c_void_p, c_int, c_uint64, c_int, c_float, c_float, c_void_p, c_void_p,
                                    c_void_p]),
     "dlco_pj_prox_apply": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, P(c_int)]),
@@ -282,6 +286,38 @@ class Context:
         _check(self.lib.dlco_pj_rda_grad_grid(self.handle, _ptr(dists), dists.stride(0), D, _ptr(rows_pos),
                                               _ptr(rows_neg), rows_pos.numel(), n_cfg, _ptr(W),
                                               W.stride(0) if W is not None else 0, rk, _ptr(out)))
+        return out
+
+    # staged gradient (pair-sharded runs, shard.py)
+    def pj_margins(self, dists, rows, W, rank):
+        n = dists.shape[0] if rows is None else rows.numel()
+        out = self.torch.empty((n,), dtype=self.torch.float32, device=self.device)
+        if n == 0:
+            return out
+        _check(self.lib.dlco_pj_margins(self.handle, _ptr(dists), dists.stride(0), dists.shape[1], _ptr(rows), n,
+                                        _ptr(W), rank, _ptr(out)))
+        return out
+
+    def pj_hinge_weights(self, margins):
+        c = self.torch.empty_like(margins)
+        _check(self.lib.dlco_pj_hinge_weights(self.handle, _ptr(margins), margins.numel() // 2, _ptr(c)))
+        return c
+
+    def pj_wsyrk(self, dists, rows, c, out=None):
+        D = dists.shape[1]
+        if out is None:
+            out = self.torch.empty((D, D), dtype=self.torch.float32, device=self.device)
+        _check(self.lib.dlco_pj_wsyrk(self.handle, _ptr(dists), dists.stride(0), D, _ptr(rows), rows.numel(),
+                                      _ptr(c), _ptr(out)))
+        return out
+
+    def pr_margins(self, dists, rows, w):
+        n = dists.shape[0] if rows is None else rows.numel()
+        out = self.torch.empty((n,), dtype=self.torch.float32, device=self.device)
+        if n == 0:
+            return out
+        _check(self.lib.dlco_pr_margins(self.handle, _ptr(dists), dists.stride(0), dists.shape[1], _ptr(rows), n,
+                                        _ptr(w), _ptr(out)))
         return out
 
     def pj_rda_update(self, t, sz_batch, mu, gamma, d_loss, dfavg, A):

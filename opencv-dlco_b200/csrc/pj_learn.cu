@@ -204,6 +204,45 @@ extern "C" int dlco_pj_rda_grad(dlco_ctx *ctx, const float *d_dists, int64_t ld,
     return dlco_pj_rda_grad_grid(ctx, d_dists, ld, D, d_rows_pos, d_rows_neg, szBatch, 1, d_W, 0, &rank, d_dLoss);
 }
 
+// ---- the three stages of the gradient as separate entry points: a pair-sharded run computes the
+// margins of the sampled rows it owns, exchanges them, derives the hinge weights redundantly and
+// all-reduces the partial X^T diag(c) X of its rows --------------------------------
+extern "C" int dlco_pj_margins(dlco_ctx *ctx, const float *d_dists, int64_t ld, int D, const int32_t *d_rows,
+                               int64_t n, const float *d_W, int rank, float *d_out)
+{
+    DLCO_REQUIRE(ctx && d_dists && d_out && n >= 0 && rank >= 0 && (rank == 0 || d_W), "dlco_pj_margins: bad arguments");
+    return dlco_sqnorm_proj(ctx, d_dists, ld, d_rows, n, d_W, D, rank, D, d_out);
+}
+
+extern "C" int dlco_pj_hinge_weights(dlco_ctx *ctx, const float *d_margins, int szBatch, float *d_c)
+{
+    DLCO_REQUIRE(ctx && d_margins && d_c && szBatch > 0 && szBatch <= 4096, "dlco_pj_hinge_weights: bad arguments");
+    k_pj_hinge<<<1, 256, (size_t)2 * szBatch * sizeof(float), ctx->stream>>>(d_margins, szBatch, d_c);
+    DLCO_CHECK_LAUNCH(ctx);
+    return DLCO_OK;
+}
+
+extern "C" int dlco_pj_wsyrk(dlco_ctx *ctx, const float *d_dists, int64_t ld, int D, const int32_t *d_rows,
+                             int nk, const float *d_c, float *d_dLoss)
+{
+    DLCO_REQUIRE(ctx && d_dists && d_dLoss && D > 0 && nk >= 0 && nk <= 8192 && ld >= D, "dlco_pj_wsyrk: bad arguments");
+    if (nk == 0) {
+        DLCO_CUDA(cudaMemsetAsync(d_dLoss, 0, (size_t)D * D * sizeof(float), ctx->stream));
+        return DLCO_OK;
+    }
+    DLCO_REQUIRE(d_rows && d_c, "dlco_pj_wsyrk: NULL rows / weights");
+    const int d_pad = (D + 127) / 128 * 128, k_pad = (nk + 31) / 32 * 32;
+    const size_t plane = (size_t)d_pad * k_pad;
+    float *planes = (float *)dlco_scratch(ctx, 18, plane * 4 * sizeof(float));
+    if (!planes) return DLCO_ENOMEM;
+    dim3 pg(k_pad / 32, d_pad / 32, 2);
+    k_pj_planes<<<pg, 256, 0, ctx->stream>>>(d_dists, ld, D, d_rows, nk, d_c, d_pad, k_pad, planes, planes + plane,
+                                             planes + 2 * plane, planes + 3 * plane);
+    DLCO_CHECK_LAUNCH(ctx);
+    return dlco_launch_gemm3x_nt(ctx, planes + 2 * plane, planes + 3 * plane, d_pad, planes, planes + plane, d_pad, 0,
+                                 k_pad, 1, D, D, d_dLoss, D, (int64_t)D * D);
+}
+
 // ---------------------------------------------------------------------------------------
 // K_pj_update (src/pj-learn.cpp:422-432), one pass:
 //   dfAvg <- dfAvg * float(t/(t+1)) + dLoss * (1.0f / (b*b*(t+1)))          addWeighted

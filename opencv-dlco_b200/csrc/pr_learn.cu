@@ -319,6 +319,14 @@ extern "C" int dlco_pr_patchdist(dlco_ctx *ctx, const float *d_dists, int64_t N,
     return dlco_gemv_rows(ctx, d_dists, ld, F, nullptr, N, d_w, d_pd);
 }
 
+// margins of an explicit row list (validation hold-out, or the rows a pair-sharded rank owns)
+extern "C" int dlco_pr_margins(dlco_ctx *ctx, const float *d_dists, int64_t ld, int F, const int32_t *d_rows,
+                               int64_t n, const float *d_w, float *d_out)
+{
+    DLCO_REQUIRE(ctx && d_dists && d_w && d_out && n >= 0, "dlco_pr_margins: bad arguments");
+    return dlco_gemv_rows(ctx, d_dists, ld, F, d_rows, n, d_w, d_out);
+}
+
 // sum |w| in double (cv::sum accumulates in double): Regul = mu * sum(abs(w)), src/pr-learn.cpp:358
 __global__ void __launch_bounds__(256) k_abs_sum(const float *__restrict__ w, int n, double *out)
 {

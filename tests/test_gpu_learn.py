@@ -286,3 +286,54 @@ def test_pj_grad_grid_equals_single(gpu_ctx):
     for g in range(3):
         single = gpu_ctx.pj_rda_grad(d_x, rp, rn, d_W[g], ranks[g])
         assert torch.equal(single, grid[g])
+
+
+# ------------------------------------------------------------------------------------------
+# staged gradient entry points + shard.py driven by the real Context (world of 1)
+# ------------------------------------------------------------------------------------------
+def test_pj_staged_grad_equals_fused(gpu_ctx):
+    x, lab = synth_uprj(3000, 72, 21)
+    rng = np.random.default_rng(3)
+    b = 64
+    rp = rng.integers(0, 3000, b).astype(np.int32)
+    rn = rng.integers(0, 3000, b).astype(np.int32)
+    W = rng.normal(0, 0.8, (30, 72)).astype(np.float32)
+    d_x, d_W = dev_t(gpu_ctx, x), dev_t(gpu_ctx, W)
+    fused = gpu_ctx.pj_rda_grad(d_x, dev_t(gpu_ctx, rp), dev_t(gpu_ctx, rn), d_W, 30).cpu().numpy()
+    rows = dev_t(gpu_ctx, np.concatenate([rp, rn]))
+    m = gpu_ctx.pj_margins(d_x, rows, d_W, 30)
+    c = gpu_ctx.pj_hinge_weights(m)
+    staged = gpu_ctx.pj_wsyrk(d_x, rows, c).cpu().numpy()
+    assert np.array_equal(fused, staged)
+    # split the batch rows in two "ranks": partial SYRKs add up to the whole
+    half = rows.numel() // 3
+    part = gpu_ctx.pj_wsyrk(d_x, rows[:half].contiguous(), c[:half].contiguous()) + \
+        gpu_ctx.pj_wsyrk(d_x, rows[half:].contiguous(), c[half:].contiguous())
+    assert np.abs(part.cpu().numpy() - fused).max() <= 2e-6 * np.abs(fused).max()
+    # empty share
+    z = gpu_ctx.pj_wsyrk(d_x, rows[:0].contiguous(), c[:0].contiguous())
+    assert float(z.abs().max()) == 0.0
+
+
+def test_sharded_driver_world1_matches_direct(gpu_ctx):
+    import dlco_b200
+    from dlco_b200 import shard
+    x, lab = synth_uprj(4000, 48, 5)
+    d_x, d_lab = dev_t(gpu_ctx, x), dev_t(gpu_ctx, lab)
+    rng = np.random.default_rng(8)
+    W = rng.normal(0, 1.0, (16, 48)).astype(np.float32)
+    d_W = dev_t(gpu_ctx, W)
+    A = dev_t(gpu_ctx, (W.T @ W).astype(np.float32))
+    ip, ineg, npt, nnt = dlco_b200.learn.split_train_val(lab)
+    coll = shard.Collective()
+    sp = shard.ShardedPj(gpu_ctx, coll, d_x, d_lab, 0, 4000)
+    rp, rn = ip[:40], ineg[:40]
+    g = sp.grad(rp, rn, d_W, 16).cpu().numpy()
+    want = gpu_ctx.pj_rda_grad(d_x, dev_t(gpu_ctx, rp), dev_t(gpu_ctx, rn), d_W, 16).cpu().numpy()
+    assert np.array_equal(g, want)
+    loss, regul = sp.validate(ip[npt:], ineg[nnt:], d_W, 16, A, 0.001)
+    l2, r2 = gpu_ctx.pj_validate(d_x, dev_t(gpu_ctx, ip[npt:]), dev_t(gpu_ctx, ineg[nnt:]), d_W, 16, A, 0.001)
+    assert abs(loss - l2) <= 1e-6 * abs(l2) and abs(regul - r2) <= 1e-6 * abs(r2)
+    f, a = sp.stats(d_W, 16)
+    f2, a2 = gpu_ctx.roc_stats(gpu_ctx.pj_patchdist(d_x, d_W, 16), d_lab)
+    assert (f, a) == (f2, a2)
