@@ -30,7 +30,7 @@ def main():
     g = torch.Generator(device="cpu").manual_seed(1)
     lab = (torch.arange(n) % 2 == 0).to(torch.uint8)
     x = torch.randn((n, D), generator=g) * 0.1 * (1.0 + (1 - lab.float())[:, None])
-    W = torch.randn((r, D), generator=g) * 0.3
+    W = torch.randn((r, D), generator=g) * 0.03
     ip, ineg, npt, nnt = dlco_b200.learn.split_train_val(lab.numpy())
     rng = dlco_b200.learn.CvRNG(2215)
     b = 200
@@ -57,7 +57,8 @@ def main():
         g1 = ctx.pj_rda_grad(xa, torch.from_numpy(rp).to(dev), torch.from_numpy(rn).to(dev), d_W, r)
         l1, r1 = ctx.pj_validate(xa, torch.from_numpy(ip[npt:]).to(dev), torch.from_numpy(ineg[nnt:]).to(dev), d_W, r, A, 0.001)
         f1, a1 = ctx.roc_stats(ctx.pj_patchdist(xa, d_W, r), la)
-        err = float((grad - g1).abs().max() / g1.abs().max())
+        err = float((grad - g1).abs().max() / g1.abs().max().clamp_min(1e-30))
+        assert float(g1.abs().max()) > 0, "hinge inactive: test data too separable"
         ok = err <= 2e-6 and abs(loss - l1) <= 1e-6 * abs(l1) and abs(f - f1) <= 1e-6 and abs(a - a1) <= 1e-9
         print(json.dumps({"world": world, "grad_rel_err": err, "loss": [loss, l1], "fpr95": [f, f1], "auc": [a, a1],
                           "sharded_grad_ms": float(ms.item()), "ok": bool(ok)}))

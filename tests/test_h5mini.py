@@ -1,0 +1,187 @@
+"""tools/h5mini.hpp (the C++ HDF5 subset the drop-in tools use) against the committed reference
+model file and against an independent reader (oracle/h5lite.py); CPU only."""
+import os
+import struct
+import subprocess
+import sys
+import zlib
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+from oracle.h5lite import H5File  # noqa: E402
+
+GOLDEN = os.path.join(ROOT, "tests", "golden", "liberty-0.035-0.250-pr.h5")
+UNDEF = 0xFFFFFFFFFFFFFFFF
+
+
+@pytest.fixture(scope="module")
+def h5tool(tmp_path_factory):
+    exe = str(tmp_path_factory.mktemp("h5") / "h5tool")
+    subprocess.check_call(["g++", "-O2", "-std=c++17", "-Wall", "-o", exe,
+                           os.path.join(ROOT, "tools", "h5tool.cpp"), "-lz", "-lpthread"])
+    return exe
+
+
+def raw(h5tool, path, name, dtype, tmp, lo=None, hi=None):
+    out = os.path.join(tmp, "raw.bin")
+    cmd = [h5tool, "raw", path, name, out] + ([str(lo), str(hi)] if lo is not None else [])
+    subprocess.check_call(cmd)
+    return np.fromfile(out, dtype)
+
+
+def test_reads_reference_model_file(h5tool, tmp_path):
+    """`w` as pr-learn wrote it (unlimited rows, chunk 1 x 5120, gzip 9: src/pr-learn.cpp:397-407)"""
+    ls = subprocess.check_output([h5tool, "ls", GOLDEN]).decode().split()
+    assert ls == ["w", "f32", "9", "5120", "chunk", "1", "5120", "deflate", "unlimited"]
+    want = H5File(GOLDEN).read("w")
+    got = raw(h5tool, GOLDEN, "w", np.float32, str(tmp_path)).reshape(9, 5120)
+    assert np.array_equal(got, want)
+    part = raw(h5tool, GOLDEN, "w", np.float32, str(tmp_path), 3, 8).reshape(5, 5120)
+    assert np.array_equal(part, want[3:8])
+
+
+@pytest.mark.parametrize("chunk_rows,level", [(0, 0), (1, 9), (4, 0), (128, 1)])
+def test_copy_round_trip(h5tool, tmp_path, chunk_rows, level):
+    out = str(tmp_path / "copy.h5")
+    subprocess.check_call([h5tool, "copy", GOLDEN, out, str(chunk_rows), str(level), "3"])
+    a, b = H5File(GOLDEN), H5File(out)
+    assert np.array_equal(a.read("w"), b.read("w"))
+    info = b.info("w")
+    if chunk_rows:
+        assert info["chunk"] == (chunk_rows, 5120) and info["maxshape"][0] == UNDEF
+        assert bool(info["filters"]) == (level > 0)
+    # and our own reader reads what our writer wrote
+    got = raw(h5tool, out, "w", np.float32, str(tmp_path)).reshape(9, 5120)
+    assert np.array_equal(got, a.read("w"))
+
+
+@pytest.mark.parametrize("rows,chunk_rows,level", [(1000, 1, 1), (5000, 128, 0), (77, 128, 9), (4160, 1, 0)])
+def test_pipeline_shapes_and_deep_btrees(h5tool, tmp_path, rows, chunk_rows, level):
+    """every dataset shape of the pipeline; 1000+ chunks need a 2- or 3-level chunk B-tree"""
+    out = str(tmp_path / "gen.h5")
+    subprocess.check_call([h5tool, "gen", out, str(rows), str(chunk_rows), str(level)])
+    f = H5File(out)
+    assert sorted(f.keys()) == ["Distance", "Indices", "Label", "Patches", "RingParams"]
+    r = np.arange(rows, dtype=np.float32)[:, None] * np.float32(0.5) + np.arange(40, dtype=np.float32)[None, :] * np.float32(0.001)
+    assert np.array_equal(f.read("Distance"), r)
+    assert np.array_equal(f.read("Label").ravel(), (np.arange(rows) % 3 == 0).astype(np.uint8))
+    k = np.arange(rows)
+    assert np.array_equal(f.read("Indices"), np.stack([k, k // 2, k + 7, k // 3], 1).astype(np.int32))
+    p = np.arange(rows // 8)[:, None]
+    i = np.arange(4096)[None, :]
+    assert np.array_equal(f.read("Patches").reshape(rows // 8, 4096), ((p * 31 + i * 7 + (i >> 6)) & 255).astype(np.uint8))
+    assert np.array_equal(f.read("RingParams").ravel(), 0.125 * np.arange(21) - 1.0 / 3.0)
+    assert f.info("Distance")["dtype"] == np.float32 and f.info("RingParams")["dtype"] == np.float64
+    # row windows through the C++ reader (crossing chunk and B-tree node boundaries)
+    for lo, hi in [(0, rows), (rows // 3, rows // 3 + 1), (rows // 2 - 5, min(rows, rows // 2 + 140))]:
+        got = raw(h5tool, out, "Distance", np.float32, str(tmp_path), lo, hi).reshape(hi - lo, 40)
+        assert np.array_equal(got, r[lo:hi])
+    got = raw(h5tool, out, "Patches", np.uint8, str(tmp_path), 2, 5).reshape(3, 4096)
+    assert np.array_equal(got, ((p * 31 + i * 7 + (i >> 6)) & 255).astype(np.uint8)[2:5])
+
+
+def test_append_and_flush_per_row(h5tool, tmp_path):
+    out = str(tmp_path / "w.h5")
+    subprocess.check_call([h5tool, "append-test", out])
+    f = H5File(out)
+    w = f.read("w")
+    assert w.shape == (5, 5120) and f.info("w")["maxshape"][0] == UNDEF and f.info("w")["chunk"] == (1, 5120)
+    for k in range(5):
+        want = np.where(np.arange(5120) % 97 == k, np.float32((k + 1) * 0.25), np.float32(0))
+        assert np.array_equal(w[k], want)
+
+
+def _colchunk_file(path, data, crow, deflate, leaf_entries=3):
+    """A file laid out like the reference's comp-uprjdists output: `Distance` f32 N x D with
+    {crow, 1} COLUMN chunks (src/comp-uprjdists.cpp:289-290), gzip, multi-level chunk B-tree."""
+    n, d = data.shape
+    buf = bytearray(4096)
+    chunks = []
+    for r0 in range(0, n, crow):
+        for c in range(d):
+            blk = np.zeros((crow, 1), np.float32)
+            part = data[r0:r0 + crow, c:c + 1]
+            blk[:part.shape[0]] = part
+            raw = blk.tobytes()
+            z = zlib.compress(raw, 6) if deflate else raw
+            chunks.append((len(buf), len(z), r0, c))
+            buf += z
+            buf += b"\0" * (-len(buf) % 8)
+
+    def key(sz, r0, c):
+        return struct.pack("<IIQQQ", sz, 0, r0, c, 0)
+
+    level, depth = [(a, sz, r0, c) for a, sz, r0, c in chunks], 0
+    while True:
+        nodes = [level[i:i + leaf_entries] for i in range(0, len(level), leaf_entries)]
+        up = []
+        for k, ent in enumerate(nodes):
+            addr = len(buf)
+            node = b"TREE" + struct.pack("<BBHQQ", 1, depth, len(ent), UNDEF, UNDEF)
+            for a, sz, r0, c in ent:
+                node += key(sz, r0, c) + struct.pack("<Q", a)
+            nxt = nodes[k + 1][0] if k + 1 < len(nodes) else None
+            node += key(0, nxt[2], nxt[3]) if nxt else key(0, chunks[-1][2] + crow, d)
+            buf += node
+            up.append((addr, ent[0][1], ent[0][2], ent[0][3]))
+        if len(nodes) == 1:
+            root = up[0][0]
+            break
+        level, depth = up, depth + 1
+
+    def msg(t, body, flags=0):
+        body += b"\0" * (-len(body) % 8)
+        return struct.pack("<HHB3x", t, len(body), flags) + body
+
+    msgs = [msg(1, struct.pack("<BBB5xQQQQ", 1, 2, 1, n, d, n, d)),
+            msg(3, bytes([0x11, 0x20, 0x1f, 0, 4, 0, 0, 0, 0, 0, 32, 0, 23, 8, 0, 23, 127, 0, 0, 0]), 1),
+            msg(5, bytes([2, 3, 2, 1, 0, 0, 0, 0]))]
+    if deflate:
+        msgs.append(msg(0xb, bytes([1, 1, 0, 0, 0, 0, 0, 0, 1, 0, 8, 0, 1, 0, 1, 0]) + b"deflate\0" + struct.pack("<II", 6, 0)))
+    msgs.append(msg(8, struct.pack("<BBBQIII", 3, 2, 3, root, crow, 1, 4)))
+    body = b"".join(msgs)
+    hdr = struct.pack("<BBHII4x", 1, 0, len(msgs), 1, len(body)) + body
+    ROOT_, BTREE, HEAP, HDATA, OHDR = 96, 136, 680, 712, 800
+    snod = OHDR + len(hdr) + (-len(hdr) % 8)
+    buf[0:8] = b"\x89HDF\r\n\x1a\n"
+    buf[13], buf[14] = 8, 8
+    struct.pack_into("<HH", buf, 16, 4, 16)
+    struct.pack_into("<QQQQ", buf, 24, 0, UNDEF, len(buf), UNDEF)
+    struct.pack_into("<QQI4xQQ", buf, 56, 0, ROOT_, 1, BTREE, HEAP)
+    struct.pack_into("<BBHII4xHHB3xQQ", buf, ROOT_, 1, 0, 1, 1, 24, 0x11, 16, 0, BTREE, HEAP)
+    buf[BTREE:BTREE + 4] = b"TREE"
+    struct.pack_into("<BBHQQQQQ", buf, BTREE + 4, 0, 0, 1, UNDEF, UNDEF, 0, snod, 8)
+    buf[HEAP:HEAP + 4] = b"HEAP"
+    struct.pack_into("<QQQ", buf, HEAP + 8, 88, 24, HDATA)
+    buf[HDATA + 8:HDATA + 16] = b"Distance"
+    struct.pack_into("<QQ", buf, HDATA + 24, 1, 64)
+    buf[OHDR:OHDR + len(hdr)] = hdr
+    buf[snod:snod + 4] = b"SNOD"
+    struct.pack_into("<BBHQQ", buf, snod + 4, 1, 0, 1, 8, OHDR)
+    with open(path, "wb") as f:
+        f.write(buf)
+
+
+@pytest.mark.parametrize("deflate", [False, True])
+def test_reads_column_chunked_distance(h5tool, tmp_path, deflate):
+    rng = np.random.default_rng(3)
+    data = rng.normal(0, 1, (300, 7)).astype(np.float32)
+    path = str(tmp_path / "colchunk.h5")
+    _colchunk_file(path, data, 128, deflate)
+    assert np.array_equal(H5File(path).read("Distance"), data)          # the fixture itself is well-formed
+    got = raw(h5tool, path, "Distance", np.float32, str(tmp_path)).reshape(300, 7)
+    assert np.array_equal(got, data)
+    for lo, hi in [(0, 1), (127, 129), (250, 300), (128, 256)]:
+        got = raw(h5tool, path, "Distance", np.float32, str(tmp_path), lo, hi).reshape(hi - lo, 7)
+        assert np.array_equal(got, data[lo:hi])
+
+
+def test_missing_dataset_and_bad_file_fail_loudly(h5tool, tmp_path):
+    bad = tmp_path / "bad.h5"
+    bad.write_bytes(b"not hdf5" * 100)
+    assert subprocess.call([h5tool, "ls", str(bad)], stderr=subprocess.DEVNULL) == 2
+    assert subprocess.call([h5tool, "raw", GOLDEN, "nope", str(tmp_path / "x.bin")], stderr=subprocess.DEVNULL) == 2
