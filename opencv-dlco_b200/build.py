@@ -53,3 +53,39 @@ def build(force=False, verbose=False):
 
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv, verbose=True))
+
+
+TOOLS = ["comp-fulldists", "comp-uprjdists", "pr-learn", "pj-learn", "pr-stats", "pj-stats", "h5tool"]
+
+
+def build_tools(force=False, verbose=False):
+    """The drop-in command-line tools (tools/*.cpp, C++ host code over the C ABI) -> bin/."""
+    root = os.path.abspath(os.path.join(HERE, ".."))
+    src_dir, bin_dir = os.path.join(root, "tools"), os.path.join(root, "bin")
+    os.makedirs(bin_dir, exist_ok=True)
+    cuda = os.environ.get("CUDA_HOME", "/usr/local/cuda")
+    headers = [os.path.join(src_dir, f) for f in os.listdir(src_dir) if f.endswith(".hpp")]
+    headers.append(os.path.join(root, "include", "dlco_b200.h"))
+    procs = []
+    for t in TOOLS:
+        src = os.path.join(src_dir, t + ".cpp")
+        exe = os.path.join(bin_dir, t)
+        if not os.path.exists(src):
+            continue
+        if not (force or _stale(exe, [src] + headers)):
+            continue
+        cmd = ["g++", "-O2", "-std=c++17", "-Wall", "-I", os.path.join(cuda, "include"), src, "-o", exe]
+        if t != "h5tool":
+            cmd += ["-L", HERE, "-ldlco_b200", "-L", os.path.join(cuda, "lib64"), "-lcudart",
+                    "-Wl,-rpath,$ORIGIN/../opencv-dlco_b200", "-Wl,-rpath," + os.path.join(cuda, "lib64")]
+        cmd += ["-lz", "-lpthread"]
+        if verbose:
+            print(" ".join(cmd))
+        procs.append((t, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)))
+    for t, p in procs:
+        out, _ = p.communicate()
+        if p.returncode != 0:
+            raise RuntimeError("g++ failed on tools/%s.cpp:\n%s" % (t, out.decode()))
+        if verbose and out:
+            print(out.decode())
+    return bin_dir

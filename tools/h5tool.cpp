@@ -4,6 +4,7 @@
 //   h5tool ls   <file>                      one line per dataset: name dtype dims [chunk] [deflate]
 //   h5tool raw  <file> <dataset> <out.bin> [lo hi]   rows [lo, hi) as raw little-endian bytes
 //   h5tool copy <in> <out> [chunk_rows] [deflate] [threads]   every dataset, through Reader -> Writer
+//   h5tool pack <out> {<name> <dtype> <ndims> <dims..> <file.bin> <chunk_rows|0> <deflate>}...
 //   h5tool gen  <out> <rows> <chunk_rows> <deflate>   formula data in the pipeline's dataset shapes
 //   h5tool append-test <out>                the pr-learn `w` pattern: unlimited rows, flush per row
 #include "h5mini.hpp"
@@ -84,6 +85,37 @@ int main(int argc, char **argv)
             w.close();
             return 0;
         }
+        if (argc >= 3 && !strcmp(argv[1], "pack")) {
+            // pack <out> {<name> <u8|i32|f32|f64> <ndims> <d0> .. <file.bin> <chunk_rows|0> <deflate>}...
+            Writer w(argv[2]);
+            int i = 3;
+            while (i + 2 < argc) {
+                const std::string name = argv[i++], tn = argv[i++];
+                const DType t = tn == "u8" ? U8 : tn == "i32" ? I32 : tn == "f64" ? F64 : F32;
+                const int nd = atoi(argv[i++]);
+                if (nd < 1 || nd > 4 || i + nd + 3 > argc) throw Error("pack: bad dataset spec for " + name);
+                std::vector<uint64_t> dims;
+                for (int k = 0; k < nd; k++) dims.push_back(strtoull(argv[i++], 0, 10));
+                const char *bin = argv[i++];
+                const uint32_t cr = (uint32_t)atoi(argv[i++]);
+                const int level = atoi(argv[i++]);
+                uint64_t bytes = dtype_size(t);
+                for (auto d : dims) bytes *= d;
+                std::vector<uint8_t> buf(bytes);
+                FILE *f = fopen(bin, "rb");
+                if (!f || fread(buf.data(), 1, bytes, f) != bytes) throw Error(std::string("pack: cannot read ") + bin);
+                fclose(f);
+                if (!cr) {
+                    w.write_contiguous(name, t, dims, buf.data());
+                } else {
+                    std::vector<uint64_t> trailing(dims.begin() + 1, dims.end());
+                    const int h = w.create_chunked(name, t, trailing, cr, level, false);
+                    w.append_rows(h, buf.data(), dims[0], 4);
+                }
+            }
+            w.close();
+            return 0;
+        }
         if (argc >= 6 && !strcmp(argv[1], "gen")) {
             // gen <out> <rows> <chunk_rows> <deflate>: the dataset shapes of the DLCO pipeline with
             // formula data (tests/test_h5mini.py recomputes them): Distance f32 rows x 40,
@@ -116,7 +148,7 @@ int main(int argc, char **argv)
             w.close();
             return 0;
         }
-        fprintf(stderr, "usage: h5tool ls|raw|copy|append-test|gen ...\n");
+        fprintf(stderr, "usage: h5tool ls|raw|copy|pack|append-test|gen ...\n");
         return 1;
     } catch (const std::exception &e) {
         fprintf(stderr, "h5tool: %s\n", e.what());
