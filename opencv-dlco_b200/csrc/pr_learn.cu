@@ -11,6 +11,7 @@
 // seeds every run with RNG(2215)), so a grid launch runs one CTA per configuration and the rows
 // are served from L2 after the first CTA touched them.
 #include "common.cuh"
+#include <stdlib.h>
 #include "kernels.h"
 #include <math.h>
 #include <vector>
@@ -255,17 +256,72 @@ extern "C" int dlco_pr_rda_run(dlco_ctx *ctx, const float *d_dists, int64_t ld, 
 // Reference: cuda::gemm(POSVal, W) src/pr-learn.cpp:343-344; w * Dists.t() src/misc.cpp:226.
 // ---------------------------------------------------------------------------------------
 #define GEMV_THREADS 512
+#define GEMV_SPARSE_CAP 768      // non-zeros of w kept in shared memory for the sparse path
+
+// w learnt by the l1 RDA is sparse (4-21 non-zeros of 5120 in the reference's logs): when at most
+// F/16 entries are non-zero the warp gathers just those columns of its row -- one 32-byte sector per
+// non-zero instead of the whole 4 F byte row -- in ascending column order (deterministic).
 __global__ void __launch_bounds__(GEMV_THREADS)
 k_gemv_rows(const float *__restrict__ dists, int64_t ld, int F, const int32_t *__restrict__ rows,
-            int64_t n, const float *__restrict__ w, float *__restrict__ out)
+            int64_t n, const float *__restrict__ w, float *__restrict__ out, int allow_sparse)
 {
     extern __shared__ float4 s_w[];
+    __shared__ int s_idx[GEMV_SPARSE_CAP];
+    __shared__ float s_val[GEMV_SPARSE_CAP];
+    __shared__ int s_warp_tot[GEMV_THREADS / 32];
+    __shared__ int s_nnz;
     const int nvec = F >> 2;
     for (int v = threadIdx.x; v < nvec; v += GEMV_THREADS) s_w[v] = reinterpret_cast<const float4 *>(w)[v];
     __syncthreads();
-    const int lane = threadIdx.x & 31;
-    const int64_t warp0 = (int64_t)blockIdx.x * (GEMV_THREADS / 32) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    // ordered compaction of the non-zeros: thread t owns elements [t * per, (t + 1) * per)
+    const float *sw = reinterpret_cast<const float *>(s_w);
+    const int per = (F + GEMV_THREADS - 1) / GEMV_THREADS;
+    const int e0 = threadIdx.x * per, e1 = min(F, e0 + per);
+    int cnt = 0;
+    for (int e = e0; e < e1; e++) cnt += sw[e] != 0.0f;
+    int incl = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+    }
+    if (lane == 31) s_warp_tot[wid] = incl;
+    __syncthreads();
+    int base = 0;
+    for (int k = 0; k < wid; k++) base += s_warp_tot[k];
+    if (threadIdx.x == GEMV_THREADS - 1) s_nnz = base + incl;
+    __syncthreads();
+    const int nnz = s_nnz;
+    const bool sparse = allow_sparse && nnz <= GEMV_SPARSE_CAP && nnz * 16 <= F;
+    if (sparse) {
+        int o = base + incl - cnt;
+        for (int e = e0; e < e1; e++)
+            if (sw[e] != 0.0f) { s_idx[o] = e; s_val[o] = sw[e]; o++; }
+    }
+    __syncthreads();
+    const int64_t warp0 = (int64_t)blockIdx.x * (GEMV_THREADS / 32) + wid;
     const int64_t nwarp = (int64_t)gridDim.x * (GEMV_THREADS / 32);
+    if (sparse) {
+        // one row per thread, the gathers of 8 non-zeros in flight at a time, fixed summation order
+        const int64_t t0 = (int64_t)blockIdx.x * GEMV_THREADS + threadIdx.x;
+        for (int64_t i = t0; i < n; i += (int64_t)gridDim.x * GEMV_THREADS) {
+            const int64_t r = rows ? (int64_t)rows[i] : i;
+            const float *src = dists + r * ld;
+            float a = 0.f;
+            int j = 0;
+            for (; j + 8 <= nnz; j += 8) {
+                float x[8];
+#pragma unroll
+                for (int u = 0; u < 8; u++) x[u] = __ldg(src + s_idx[j + u]);
+#pragma unroll
+                for (int u = 0; u < 8; u++) a = fmaf(x[u], s_val[j + u], a);
+            }
+            for (; j < nnz; j++) a = fmaf(__ldg(src + s_idx[j]), s_val[j], a);
+            out[i] = a;
+        }
+        return;
+    }
     for (int64_t i = warp0; i < n; i += nwarp) {
         const int64_t r = rows ? (int64_t)rows[i] : i;
         const float4 *src = reinterpret_cast<const float4 *>(dists + r * ld);
@@ -290,6 +346,12 @@ k_gemv_rows(const float *__restrict__ dists, int64_t ld, int F, const int32_t *_
     }
 }
 
+static bool gemv_sparse_enabled()
+{
+    const char *e = getenv("DLCO_GEMV_SPARSE");       // 0 forces the dense streaming path (bench, tests)
+    return !(e && e[0] == '0');
+}
+
 int dlco_gemv_rows(dlco_ctx *ctx, const float *d_dists, int64_t ld, int F, const int32_t *d_rows,
                    int64_t n, const float *d_w, float *d_out)
 {
@@ -306,7 +368,8 @@ int dlco_gemv_rows(dlco_ctx *ctx, const float *d_dists, int64_t ld, int F, const
         attr = true;
     }
     dlco_prof_begin(ctx, 3);
-    k_gemv_rows<<<grid, GEMV_THREADS, (size_t)F * sizeof(float), ctx->stream>>>(d_dists, ld, F, d_rows, n, d_w, d_out);
+    k_gemv_rows<<<grid, GEMV_THREADS, (size_t)F * sizeof(float), ctx->stream>>>(d_dists, ld, F, d_rows, n, d_w, d_out,
+                                                                               gemv_sparse_enabled() ? 1 : 0);
     dlco_prof_end(ctx);
     DLCO_CHECK_LAUNCH(ctx);
     return DLCO_OK;

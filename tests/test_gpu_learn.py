@@ -337,3 +337,26 @@ def test_sharded_driver_world1_matches_direct(gpu_ctx):
     f, a = sp.stats(d_W, 16)
     f2, a2 = gpu_ctx.roc_stats(gpu_ctx.pj_patchdist(d_x, d_W, 16), d_lab)
     assert (f, a) == (f2, a2)
+
+
+@pytest.mark.parametrize("nnz", [1, 12, 300, 400])
+def test_pr_patchdist_sparse_and_dense_paths(gpu_ctx, nnz):
+    """the gather path (few non-zeros in w) and the streaming path give the same distances"""
+    import os
+    dists, lab = synth_fulldist(3000, 5120, 4)
+    rng = np.random.default_rng(nnz)
+    w = np.zeros(5120, np.float32)
+    w[rng.choice(5120, nnz, replace=False)] = rng.random(nnz).astype(np.float32) + 0.01
+    d_d, d_w = dev_t(gpu_ctx, dists), dev_t(gpu_ctx, w)
+    want = dists.astype(np.float64) @ w.astype(np.float64)
+    got = gpu_ctx.pr_patchdist(d_d, d_w).cpu().numpy()           # sparse when nnz <= 5120 / 16
+    os.environ["DLCO_GEMV_SPARSE"] = "0"
+    try:
+        dense = gpu_ctx.pr_patchdist(d_d, d_w).cpu().numpy()
+    finally:
+        os.environ.pop("DLCO_GEMV_SPARSE")
+    assert np.abs(got - want).max() <= 1e-6 * np.abs(want).max()
+    assert np.abs(dense - want).max() <= 1e-6 * np.abs(want).max()
+    rows = dev_t(gpu_ctx, rng.integers(0, 3000, 777).astype(np.int32))
+    m = gpu_ctx.pr_margins(d_d, rows, d_w).cpu().numpy()
+    assert np.abs(m - want[rows.cpu().numpy()]).max() <= 1e-6 * np.abs(want).max()
