@@ -6,7 +6,8 @@
 
 Used by bench.py (`secondary` block) and on its own for the ncu captures under profiles/.
 All inputs are synthetic and resident in HBM; timings are CUDA events on the launching stream,
-after warm-up.  Nothing here touches oracle/.
+after warm-up.  The GPU legs never touch oracle/; `cpu_leg` (the `cpu_baseline` of these rows,
+--cpu) times the oracle's CPU port of each row on a bounded sample, on the box's host cores.
 """
 import argparse
 import json
@@ -192,17 +193,107 @@ def run(ctx, n_train=500000, n_test=100000, quick=False, D=544, n_pj_cfg=45, n_p
     return res
 
 
+def cpu_leg(D=544, quick=False):
+    """CPU baselines of rows b, c, d: the oracle's port of the reference's host path
+    (src/pr-learn.cpp:303-358, src/pj-learn.cpp:311-527, src/misc.cpp:171-333) on bounded samples.
+    numpy -> OpenBLAS with every host thread where the reference calls cv::gemm / cblas_sgemm; the
+    serial pr-learn chain is the C restatement (one core, as the reference's `ordered` section)."""
+    import ctypes
+    import subprocess
+    import time
+    from oracle import dlco_oracle as O
+    lib_path = os.path.join(ROOT, "oracle", "libdlco_oracle.so")
+    if not os.path.exists(lib_path):
+        subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle")], stdout=subprocess.DEVNULL)
+    lib = ctypes.CDLL(lib_path)
+    cores = os.cpu_count() or 1
+    rng = np.random.default_rng(3)
+    res = {"cores": cores, "kind": "port"}
+    F, n = 5120, 20000 if quick else 40000
+    labels = (np.arange(n) % 2 == 0).astype(np.uint8)
+    dists = rng.random((n, F), dtype=np.float32) * (1.0 + 0.3 * (1 - labels[:, None])).astype(np.float32)
+    w = np.zeros(F, np.float32)
+    w[rng.permutation(F)[:12]] = 0.05
+
+    def best(fn, rep=3):
+        ts = []
+        for _ in range(rep):
+            t = time.perf_counter()
+            fn()
+            ts.append(time.perf_counter() - t)
+        return min(ts)
+    # (c2)/(d1) w * Dists^T (src/misc.cpp:226, src/pr-learn.cpp:343-344): SGEMV over the matrix
+    dt = best(lambda: dists @ w)
+    res["pr_patchdist_gemv"] = {"rows": n, "ms": dt * 1e3, "achieved_gbs": n * F * 4 / dt / 1e9,
+                                "sample": "%d x %d f32 rows, numpy/OpenBLAS sgemv, %d threads" % (n, F, cores)}
+    pd = (dists @ w).astype(np.float32)
+    dt = best(lambda: O.roc_stats(pd, labels))
+    res["roc_stats"] = {"n": n, "ms": dt * 1e3, "sample": "sort + ROC + polygon area on %d pairs (numpy)" % n}
+    # (c1) the serial RDA chain
+    ip, ineg, npt, nnt = O.split_train_val(labels)
+    ip, ineg = np.asarray(ip, np.int32), np.asarray(ineg, np.int32)
+    vp = ctypes.c_void_p
+    lib.dlco_oracle_pr_rda.restype = None
+    lib.dlco_oracle_pr_rda.argtypes = [vp, ctypes.c_long, ctypes.c_int, vp, ctypes.c_int, vp, ctypes.c_int,
+                                       ctypes.c_float, ctypes.c_float, ctypes.c_ulonglong, ctypes.c_ulonglong,
+                                       ctypes.POINTER(ctypes.c_ulonglong), vp, vp]
+    steps = 50000 if quick else 200000
+    wv, df, st = np.zeros(F, np.float32), np.zeros(F, np.float32), ctypes.c_ulonglong(2215)
+    t = time.perf_counter()
+    lib.dlco_oracle_pr_rda(dists.ctypes.data, F, F, ip.ctypes.data, npt, ineg.ctypes.data, nnt, 0.035, 0.25, 0,
+                           steps, ctypes.byref(st), wv.ctypes.data, df.ctypes.data)
+    dt = time.perf_counter() - t
+    res["pr_rda_1cfg"] = {"steps": steps, "ms": dt * 1e3, "steps_per_s_per_cfg": steps / dt, "cores_used": 1,
+                          "sample": "%d steps over a %d-row matrix, C restatement, 1 core (serial chain)" % (steps, n)}
+    # (c3) all-pairs hinge, as the reference's kernel computes it (brute force), OpenMP over host cores
+    a = rng.random(50000, dtype=np.float32)
+    b = rng.random(50000, dtype=np.float32) + np.float32(0.3)
+    lib.dlco_oracle_hinge_pairsum.restype = ctypes.c_double
+    lib.dlco_oracle_hinge_pairsum.argtypes = [vp, ctypes.c_int, vp, ctypes.c_int, ctypes.c_double]
+    nh = 10000 if quick else 50000
+    dt = best(lambda: lib.dlco_oracle_hinge_pairsum(a.ctypes.data, nh, b.ctypes.data, 50000, 1.0), rep=2)
+    res["hinge_pairsum_50k_x_50k"] = {"ms": dt * 1e3 * (50000 / nh), "gterms_per_s": nh * 50000 / dt / 1e9,
+                                      "sample": "%d x 50000 terms, C brute force, OpenMP %d threads" % (nh, cores)}
+    del dists
+    # (b) pj-learn: whole RDA iterations (margins, hinge, sum of outer products, update, ssyevr prox)
+    nu = 20000
+    ulab = (np.arange(nu) % 2 == 0).astype(np.uint8)
+    ud = (rng.standard_normal((nu, D)) * (0.08 + 0.048 * (1 - ulab[:, None]))).astype(np.float32)
+    up, un, upt, unt = O.split_train_val(ulab)
+    state = O.pj_rda_steps(ud, up, un, upt, unt, 0.001, 0.1, 3)
+    n_it = 5 if quick else 20
+    t = time.perf_counter()
+    state = O.pj_rda_steps(ud, up, un, upt, unt, 0.001, 0.1, n_it, state=state)
+    dt = time.perf_counter() - t
+    res["pj_step"] = {"D": D, "iters_per_s": n_it / dt, "ms_per_iter": dt / n_it * 1e3, "rank": int(state["W"].shape[0]),
+                      "sample": "%d iterations at D=%d, numpy/OpenBLAS sgemm + LAPACK ssyevr, %d threads" % (n_it, D, cores)}
+    # (d2) ComputePJStats distances
+    Wm = state["W"].astype(np.float32)
+    dt = best(lambda: O.pj_patch_dist(Wm, ud, np.float32))
+    res["pj_patchdist"] = {"rows": nu, "D": D, "rank": int(Wm.shape[0]), "ms": dt * 1e3,
+                           "achieved_gbs": nu * D * 4 / dt / 1e9,
+                           "sample": "%d x %d rows, numpy/OpenBLAS sgemm, %d threads" % (nu, D, cores)}
+    return res
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--n-train", type=int, default=500000)
     ap.add_argument("--n-test", type=int, default=100000)
     ap.add_argument("--dim", type=int, default=544)
     ap.add_argument("--quick", action="store_true")
+    ap.add_argument("--cpu", action="store_true", help="also time the oracle's CPU port of each row")
+    ap.add_argument("--cpu-only", action="store_true")
     args = ap.parse_args()
+    if args.cpu_only:
+        print(json.dumps({"cpu_baseline": cpu_leg(args.dim, args.quick)}))
+        return
     import torch
     import dlco_b200
     ctx = dlco_b200.Context(0)
     res = run(ctx, args.n_train, args.n_test, args.quick, D=args.dim)
+    if args.cpu:
+        res["cpu_baseline"] = cpu_leg(args.dim, args.quick)
     print(json.dumps(res))
 
 

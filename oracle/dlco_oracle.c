@@ -109,3 +109,43 @@ double dlco_oracle_hinge_pairsum(const float *pos, int n1, const float *neg, int
     }
     return tot;
 }
+
+/* pr-learn RDA chain, fp32 "reference order" (src/pr-learn.cpp:303-329, single-thread draw
+ * order): same arithmetic as dlco_oracle.py:pr_rda_steps(dt=f32).  rng_state: cv::RNG state
+ * (multiply-with-carry, uniform(0,n) = next() % n), updated.  The CPU baseline of row c1. */
+void dlco_oracle_pr_rda(const float *dists, long ld, int F, const int *idx_pos, int n_pos_trn,
+                        const int *idx_neg, int n_neg_trn, float mu, float gamma,
+                        unsigned long long t0, unsigned long long n_steps,
+                        unsigned long long *rng_state, float *w, float *df_avg)
+{
+    unsigned long long s = *rng_state;
+    float *diff = (float *)malloc(sizeof(float) * (size_t)F);
+    for (unsigned long long k = 0; k < n_steps; k++) {
+        const unsigned long long t = t0 + k;
+        s = (unsigned long long)(unsigned)s * 4164903690ULL + (s >> 32);
+        const int ip = (int)((unsigned)s % (unsigned)n_pos_trn);
+        s = (unsigned long long)(unsigned)s * 4164903690ULL + (s >> 32);
+        const int in = (int)((unsigned)s % (unsigned)n_neg_trn);
+        const float *a = dists + (size_t)idx_pos[ip] * ld, *b = dists + (size_t)idx_neg[in] * ld;
+        double acc = 0.0;
+        for (int j = 0; j < F; j++) {
+            diff[j] = a[j] - b[j];
+            acc += (double)w[j] * (double)diff[j];
+        }
+        const float f = (float)acc;
+        const float decay = (float)((double)t * (1.0 / (double)(t + 1)));
+        const float inv = (float)(1.0 / (double)(t + 1));
+        const double alpha = -sqrt((double)(t + 1)) / (double)gamma;
+        const float fa = (float)alpha, fb = (float)(alpha * (double)mu);
+        const int active = f > -1.0f;
+        for (int j = 0; j < F; j++) {
+            float d = df_avg[j] * decay;
+            if (active) d = diff[j] * inv + d;
+            df_avg[j] = d;
+            const float v = d * fa + fb;
+            w[j] = v > 0.0f ? v : 0.0f;
+        }
+    }
+    free(diff);
+    *rng_state = s;
+}

@@ -172,3 +172,29 @@ def test_full_distance_c_and_numpy_agree(oracle_lib, synth):
                                      np.ascontiguousarray(t2).ctypes.data_as(ctypes.c_void_p),
                                      got.ctypes.data_as(ctypes.c_void_p))
     np.testing.assert_allclose(got, want, rtol=1e-12)
+
+
+def test_c_pr_rda_chain_equals_numpy_restatement(oracle_lib):
+    """oracle/dlco_oracle.c:dlco_oracle_pr_rda (the timed CPU baseline of row c1) follows the
+    numpy restatement of src/pr-learn.cpp:303-329 bit for bit."""
+    import ctypes
+    rng = np.random.default_rng(5)
+    n, F = 400, 96
+    labels = (np.arange(n) % 2 == 0).astype(np.uint8)
+    dists = (rng.random((n, F)) * (1.0 + 0.4 * (1 - labels[:, None]))).astype(np.float32)
+    ip, ineg, npt, nnt = O.split_train_val(labels)
+    ip, ineg = np.asarray(ip, np.int32), np.asarray(ineg, np.int32)
+    w_ref, df_ref, r_ref, _ = O.pr_rda_steps(dists, ip, ineg, npt, nnt, 0.035, 0.25, 300)
+    w = np.zeros(F, np.float32)
+    df = np.zeros(F, np.float32)
+    st = ctypes.c_ulonglong(2215)
+    vp = ctypes.c_void_p
+    oracle_lib.dlco_oracle_pr_rda.restype = None
+    oracle_lib.dlco_oracle_pr_rda.argtypes = [vp, ctypes.c_long, ctypes.c_int, vp, ctypes.c_int, vp, ctypes.c_int,
+                                              ctypes.c_float, ctypes.c_float, ctypes.c_ulonglong,
+                                              ctypes.c_ulonglong, ctypes.POINTER(ctypes.c_ulonglong), vp, vp]
+    oracle_lib.dlco_oracle_pr_rda(dists.ctypes.data, F, F, ip.ctypes.data, npt, ineg.ctypes.data, nnt,
+                                  0.035, 0.25, 0, 300, ctypes.byref(st), w.ctypes.data, df.ctypes.data)
+    assert st.value == r_ref.state
+    np.testing.assert_array_equal(df, df_ref)
+    np.testing.assert_array_equal(w, w_ref)
