@@ -182,6 +182,23 @@ def run(ctx, n_train=500000, n_test=100000, quick=False, D=544, n_pj_cfg=45, n_p
                            "syrk_frac_of_3xtf32_peak": (n_pj_cfg * syrk_flop / (syrk_avg * 1e-3) / 1e12 / tf32x3) if syrk_n else None,
                            "cfg_grads_per_s": n_pj_cfg / (mean_ms * 1e-3)}
 
+    # ---- (b) the whole lock-step sweep iteration: 45 (mu, gamma) configurations of one data set ----
+    mus = np.repeat(np.array([0.0001, 0.0005, 0.001, 0.002, 0.003], np.float32), 9)[:n_pj_cfg]
+    gms = np.tile(np.array([0.025, 0.05, 0.1, 0.15, 0.2, 0.25, 0.5, 0.75, 1.0], np.float32), 5)[:n_pj_cfg]
+    S = learn.PjSweep(ctx, ud, ulabels, mus, gms, split=split)
+    for _ in range(10):
+        S.step()
+    S.ranks()
+    n_it = 10 if quick else 40
+    mean_ms, best_ms = timeit(torch, lambda: [S.step() for _ in range(n_it)], warm=1, rep=3)
+    rk = S.ranks()
+    res["pj_sweep_step"] = {"n_cfg": int(len(mus)), "D": D, "ms_per_iter": mean_ms / n_it,
+                            "cfg_iters_per_s": len(mus) * n_it / (mean_ms * 1e-3),
+                            "rank_min": int(rk.min()), "rank_max": int(rk.max()),
+                            "note": "sample + margins + hinge + grouped SYRK + update + batched eig + prox, no host sync"}
+    del S
+    torch.cuda.empty_cache()
+
     # ---- (d2) ComputePJStats distances + (b6) pj validation -----------------------------------
     mean_ms, best_ms = timeit(torch, lambda: ctx.pj_patchdist(ud, L.W, L.rank))
     res["pj_patchdist"] = {"rows": n_train, "D": D, "rank": L.rank, "ms": mean_ms,

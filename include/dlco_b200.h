@@ -170,6 +170,43 @@ int dlco_pj_validate(dlco_ctx *ctx, const float *d_dists, int64_t ld, int D,
                      int64_t nNeg, const float *d_W, int rank, const float *d_A, float mu,
                      float *h_loss, float *h_regul);
 
+/* ---- pj-learn sweep: nCfg (mu, gamma) configurations in lock step on one GPU ----------------
+ * workspace/08-pjlearn.sh runs pj-learn once per (mu, gamma); every run shuffles with the default
+ * theRNG() and samples with RNG(2215) (src/pj-learn.cpp:214-227), so all runs on one data set draw
+ * identical batches.  The entry points below advance nCfg runs together: one gather, one grouped
+ * SYRK launch, one batched eigen-decomposition per iteration.  Per-configuration state is device
+ * resident (d_W, d_A, d_dfavg: nCfg x D x D; d_rank: nCfg i32; d_mu, d_gamma: nCfg f32; RNG state
+ * u64), an iteration never synchronises with the host. */
+/* the batch draw of src/pj-learn.cpp:311-316 on the device (cv::RNG state read and updated) */
+int dlco_pj_sample_batch(dlco_ctx *ctx, const int32_t *d_idx_pos, int32_t nPosTrn,
+                         const int32_t *d_idx_neg, int32_t nNegTrn, int szBatch,
+                         uint64_t *d_rng_state, int32_t *d_rows_pos, int32_t *d_rows_neg);
+/* dlco_pj_rda_grad_grid with the ranks read from device memory */
+int dlco_pj_rda_grad_grid_dev(dlco_ctx *ctx, const float *d_dists, int64_t ld, int D,
+                              const int32_t *d_rows_pos, const int32_t *d_rows_neg, int szBatch,
+                              int nCfg, const float *d_W, int64_t w_stride, const int32_t *d_rank,
+                              float *d_dLoss);
+int dlco_pj_rda_update_grid(dlco_ctx *ctx, int D, uint64_t t, int szBatch, int nCfg,
+                            const float *d_mu, const float *d_gamma, const float *d_dLoss,
+                            float *d_dfavg, float *d_A);
+/* nCfg symmetric eigen-decompositions in one library call (cusolverDnXsyevBatched); d_eval nCfg x D
+ * ascending, d_evec nCfg x D x D with row k = eigenvector k.  Synchronises and checks info. */
+int dlco_pj_eig_batched(dlco_ctx *ctx, int D, int nCfg, const float *d_A, float *d_eval,
+                        float *d_evec);
+/* dlco_pj_prox_apply for nCfg configurations; ranks are written to d_rank (device) */
+int dlco_pj_prox_apply_grid(dlco_ctx *ctx, int D, int nCfg, const float *d_eval,
+                            const float *d_evec, float *d_A, float *d_W, int64_t w_stride,
+                            int32_t *d_rank);
+/* iteration t of all configurations: sample, gradient, dual average, batched eig, prox
+ * (src/pj-learn.cpp:305-490).  d_work: nCfg * (2 D D + D) floats.  Asynchronous. */
+int dlco_pj_rda_step_grid(dlco_ctx *ctx, const float *d_dists, int64_t ld, int D,
+                          const int32_t *d_idx_pos, int32_t nPosTrn, const int32_t *d_idx_neg,
+                          int32_t nNegTrn, int szBatch, uint64_t *d_rng_state, int nCfg,
+                          const float *d_mu, const float *d_gamma, uint64_t t, float *d_W,
+                          float *d_A, float *d_dfavg, int32_t *d_rank, float *d_work);
+/* synchronise and report a failed eigen-decomposition of the steps issued so far */
+int dlco_pj_grid_check(dlco_ctx *ctx, int nCfg);
+
 /* ---- FPR95 evaluation (src/misc.cpp:171-333) --------------------------------------------
  * pr: PatchDist = Dists . w ; pj: PatchDist = colsum((W Dists^T)^2); then ascending sort,
  * ROC, FPR at first TPR >= 0.95f, AUC = polygon area.  d_labels: N u8. */

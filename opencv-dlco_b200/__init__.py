@@ -66,6 +66,19 @@ SIGNATURES = {
                                    c_void_p]),
     "dlco_pj_prox_apply": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, P(c_int)]),
     "dlco_pj_eig": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
+    "dlco_pj_sample_batch": (c_int, [c_void_p, c_void_p, ctypes.c_int32, c_void_p, ctypes.c_int32, c_int, c_void_p,
+                                     c_void_p, c_void_p]),
+    "dlco_pj_rda_grad_grid_dev": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_void_p, c_void_p, c_int, c_int,
+                                          c_void_p, c_int64, c_void_p, c_void_p]),
+    "dlco_pj_rda_update_grid": (c_int, [c_void_p, c_int, c_uint64, c_int, c_int, c_void_p, c_void_p, c_void_p,
+                                        c_void_p, c_void_p]),
+    "dlco_pj_eig_batched": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "dlco_pj_prox_apply_grid": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int64,
+                                        c_void_p]),
+    "dlco_pj_rda_step_grid": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_void_p, ctypes.c_int32, c_void_p,
+                                      ctypes.c_int32, c_int, c_void_p, c_int, c_void_p, c_void_p, c_uint64,
+                                      c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "dlco_pj_grid_check": (c_int, [c_void_p, c_int]),
     "dlco_pj_validate": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_void_p, c_int64, c_void_p, c_int64,
                                  c_void_p, c_int, c_void_p, c_float, P(c_float), P(c_float)]),
     "dlco_pr_patchdist": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int, c_void_p, c_void_p]),
@@ -337,6 +350,44 @@ class Context:
         _check(self.lib.dlco_pj_prox_apply(self.handle, A.shape[0], _ptr(evals), _ptr(evecs), _ptr(A), _ptr(W),
                                            ctypes.byref(rank)))
         return rank.value
+
+    # ---- pj-learn sweep (nCfg configurations in lock step; state device resident) -------------
+    def pj_sample_batch(self, idx_pos, n_pos_trn, idx_neg, n_neg_trn, sz_batch, rng_state, rows_pos, rows_neg):
+        _check(self.lib.dlco_pj_sample_batch(self.handle, _ptr(idx_pos), n_pos_trn, _ptr(idx_neg), n_neg_trn,
+                                             sz_batch, _ptr(rng_state), _ptr(rows_pos), _ptr(rows_neg)))
+
+    def pj_rda_grad_grid_dev(self, dists, rows_pos, rows_neg, W, d_rank, out):
+        n_cfg, D = W.shape[0], dists.shape[1]
+        _check(self.lib.dlco_pj_rda_grad_grid_dev(self.handle, _ptr(dists), dists.stride(0), D, _ptr(rows_pos),
+                                                  _ptr(rows_neg), rows_pos.numel(), n_cfg, _ptr(W), W.stride(0),
+                                                  _ptr(d_rank), _ptr(out)))
+        return out
+
+    def pj_rda_update_grid(self, t, sz_batch, d_mu, d_gamma, d_loss, dfavg, A):
+        _check(self.lib.dlco_pj_rda_update_grid(self.handle, A.shape[-1], t, sz_batch, A.shape[0], _ptr(d_mu),
+                                                _ptr(d_gamma), _ptr(d_loss), _ptr(dfavg), _ptr(A)))
+
+    def pj_eig_batched(self, A, evals=None, evecs=None):
+        torch = self.torch
+        n_cfg, D = A.shape[0], A.shape[-1]
+        evals = torch.empty((n_cfg, D), dtype=torch.float32, device=self.device) if evals is None else evals
+        evecs = torch.empty((n_cfg, D, D), dtype=torch.float32, device=self.device) if evecs is None else evecs
+        _check(self.lib.dlco_pj_eig_batched(self.handle, D, n_cfg, _ptr(A), _ptr(evals), _ptr(evecs)))
+        return evals, evecs
+
+    def pj_prox_apply_grid(self, evals, evecs, A, W, d_rank):
+        _check(self.lib.dlco_pj_prox_apply_grid(self.handle, A.shape[-1], A.shape[0], _ptr(evals), _ptr(evecs),
+                                                _ptr(A), _ptr(W), W.stride(0), _ptr(d_rank)))
+
+    def pj_rda_step_grid(self, dists, idx_pos, n_pos_trn, idx_neg, n_neg_trn, sz_batch, rng_state, d_mu, d_gamma,
+                         t, W, A, dfavg, d_rank, work):
+        _check(self.lib.dlco_pj_rda_step_grid(self.handle, _ptr(dists), dists.stride(0), dists.shape[1],
+                                              _ptr(idx_pos), n_pos_trn, _ptr(idx_neg), n_neg_trn, sz_batch,
+                                              _ptr(rng_state), W.shape[0], _ptr(d_mu), _ptr(d_gamma), t, _ptr(W),
+                                              _ptr(A), _ptr(dfavg), _ptr(d_rank), _ptr(work)))
+
+    def pj_grid_check(self, n_cfg):
+        _check(self.lib.dlco_pj_grid_check(self.handle, n_cfg))
 
     def pj_validate(self, dists, pos_rows, neg_rows, W, rank, A, mu):
         loss, regul = c_float(), c_float()

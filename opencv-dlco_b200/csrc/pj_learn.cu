@@ -19,12 +19,20 @@
 #define SP_BR 64
 #define SP_BK 16
 
+// blockIdx.y = configuration g of a sweep: W_g = W + g * w_stride, rank_g = d_rank[g] (device-resident
+// ranks keep the lock-step sweep free of host round trips), out_g = out + g * n.
 __global__ void __launch_bounds__(256)
 k_sqnorm_proj(const float *__restrict__ X, int64_t ld, const int32_t *__restrict__ rows, int64_t n,
-              const float *__restrict__ W, int64_t ldw, int rank, int D, float *__restrict__ out)
+              const float *__restrict__ W, int64_t ldw, int rank, int D, float *__restrict__ out,
+              const int32_t *__restrict__ d_rank, int64_t w_stride)
 {
     __shared__ float Xs[SP_BK][SP_BM + 4];
     __shared__ float Ws[SP_BK][SP_BR + 4];
+    if (d_rank) {
+        rank = d_rank[blockIdx.y];
+        W += (int64_t)blockIdx.y * w_stride;
+        out += (int64_t)blockIdx.y * n;
+    }
     const int tid = threadIdx.x;
     const int tx = tid & 15, ty = tid >> 4;
     const int64_t m0 = (int64_t)blockIdx.x * SP_BM;
@@ -98,7 +106,22 @@ int dlco_sqnorm_proj(dlco_ctx *ctx, const float *d_X, int64_t ld, const int32_t 
         return DLCO_OK;
     }
     dlco_prof_begin(ctx, 5);
-    k_sqnorm_proj<<<(unsigned)((n + SP_BM - 1) / SP_BM), 256, 0, ctx->stream>>>(d_X, ld, d_rows, n, d_W, ldw, rank, D, d_out);
+    k_sqnorm_proj<<<(unsigned)((n + SP_BM - 1) / SP_BM), 256, 0, ctx->stream>>>(d_X, ld, d_rows, n, d_W, ldw, rank, D, d_out,
+                                                                                nullptr, 0);
+    dlco_prof_end(ctx);
+    DLCO_CHECK_LAUNCH(ctx);
+    return DLCO_OK;
+}
+
+// nCfg configurations in one launch, ranks read on the device
+static int dlco_sqnorm_proj_grid(dlco_ctx *ctx, const float *d_X, int64_t ld, const int32_t *d_rows, int64_t n,
+                                 const float *d_W, int64_t w_stride, const int32_t *d_rank, int nCfg, int D,
+                                 float *d_out)
+{
+    if (n <= 0 || nCfg <= 0) return DLCO_OK;
+    dim3 grid((unsigned)((n + SP_BM - 1) / SP_BM), nCfg);
+    dlco_prof_begin(ctx, 5);
+    k_sqnorm_proj<<<grid, 256, 0, ctx->stream>>>(d_X, ld, d_rows, n, d_W, D, 0, D, d_out, d_rank, w_stride);
     dlco_prof_end(ctx);
     DLCO_CHECK_LAUNCH(ctx);
     return DLCO_OK;
@@ -162,14 +185,12 @@ k_pj_planes(const float *__restrict__ dists, int64_t ld, int D, const int32_t *_
 }
 
 // dLoss for nCfg configurations that share one sampled batch (rows) but have their own W.
-// d_W: config g at d_W + g * w_stride, ranks h_rank[g]; d_dLoss: config g at d_dLoss + g * D * D.
-extern "C" int dlco_pj_rda_grad_grid(dlco_ctx *ctx, const float *d_dists, int64_t ld, int D,
-                                     const int32_t *d_rows_pos, const int32_t *d_rows_neg, int szBatch,
-                                     int nCfg, const float *d_W, int64_t w_stride, const int *h_rank,
-                                     float *d_dLoss)
+// d_W: config g at d_W + g * w_stride, ranks h_rank[g] (host) or d_rank[g] (device);
+// d_dLoss: config g at d_dLoss + g * D * D.
+static int pj_grad_core(dlco_ctx *ctx, const float *d_dists, int64_t ld, int D, const int32_t *d_rows_pos,
+                        const int32_t *d_rows_neg, int szBatch, int nCfg, const float *d_W, int64_t w_stride,
+                        const int *h_rank, const int32_t *d_rank, float *d_dLoss)
 {
-    DLCO_REQUIRE(ctx && d_dists && d_rows_pos && d_rows_neg && d_dLoss && h_rank, "dlco_pj_rda_grad: NULL argument");
-    DLCO_REQUIRE(D > 0 && szBatch > 0 && szBatch <= 4096 && nCfg > 0 && ld >= D, "dlco_pj_rda_grad: bad shapes");
     const int nk = 2 * szBatch;
     const int d_pad = (D + 127) / 128 * 128, k_pad = (nk + 31) / 32 * 32;
     const size_t plane = (size_t)d_pad * k_pad;
@@ -182,11 +203,16 @@ extern "C" int dlco_pj_rda_grad_grid(dlco_ctx *ctx, const float *d_dists, int64_
     float *yt_hi = planes + 2 * plane, *yt_lo = yt_hi + plane * nCfg;
     DLCO_CUDA(cudaMemcpyAsync(rows, d_rows_pos, szBatch * sizeof(int32_t), cudaMemcpyDeviceToDevice, ctx->stream));
     DLCO_CUDA(cudaMemcpyAsync(rows + szBatch, d_rows_neg, szBatch * sizeof(int32_t), cudaMemcpyDeviceToDevice, ctx->stream));
-    for (int g = 0; g < nCfg; g++) {
-        DLCO_REQUIRE(h_rank[g] >= 0 && (h_rank[g] == 0 || d_W), "dlco_pj_rda_grad: bad rank / W");
-        int r = dlco_sqnorm_proj(ctx, d_dists, ld, rows, nk, d_W ? d_W + (size_t)g * w_stride : nullptr, D,
-                                 h_rank[g], D, m + (size_t)g * nk);
+    if (d_rank) {
+        int r = dlco_sqnorm_proj_grid(ctx, d_dists, ld, rows, nk, d_W, w_stride, d_rank, nCfg, D, m);
         if (r != DLCO_OK) return r;
+    } else {
+        for (int g = 0; g < nCfg; g++) {
+            DLCO_REQUIRE(h_rank[g] >= 0 && (h_rank[g] == 0 || d_W), "dlco_pj_rda_grad: bad rank / W");
+            int r = dlco_sqnorm_proj(ctx, d_dists, ld, rows, nk, d_W ? d_W + (size_t)g * w_stride : nullptr, D,
+                                     h_rank[g], D, m + (size_t)g * nk);
+            if (r != DLCO_OK) return r;
+        }
     }
     k_pj_hinge<<<nCfg, 256, (size_t)nk * sizeof(float), ctx->stream>>>(m, szBatch, c);
     DLCO_CHECK_LAUNCH(ctx);
@@ -195,6 +221,17 @@ extern "C" int dlco_pj_rda_grad_grid(dlco_ctx *ctx, const float *d_dists, int64_
     DLCO_CHECK_LAUNCH(ctx);
     return dlco_launch_gemm3x_nt(ctx, yt_hi, yt_lo, d_pad, xt_hi, xt_lo, d_pad, 0, k_pad, nCfg, D, D, d_dLoss, D,
                                  (int64_t)D * D);
+}
+
+extern "C" int dlco_pj_rda_grad_grid(dlco_ctx *ctx, const float *d_dists, int64_t ld, int D,
+                                     const int32_t *d_rows_pos, const int32_t *d_rows_neg, int szBatch,
+                                     int nCfg, const float *d_W, int64_t w_stride, const int *h_rank,
+                                     float *d_dLoss)
+{
+    DLCO_REQUIRE(ctx && d_dists && d_rows_pos && d_rows_neg && d_dLoss && h_rank, "dlco_pj_rda_grad: NULL argument");
+    DLCO_REQUIRE(D > 0 && szBatch > 0 && szBatch <= 4096 && nCfg > 0 && ld >= D, "dlco_pj_rda_grad: bad shapes");
+    return pj_grad_core(ctx, d_dists, ld, D, d_rows_pos, d_rows_neg, szBatch, nCfg, d_W, w_stride, h_rank, nullptr,
+                        d_dLoss);
 }
 
 extern "C" int dlco_pj_rda_grad(dlco_ctx *ctx, const float *d_dists, int64_t ld, int D,
@@ -489,4 +526,305 @@ extern "C" int dlco_pj_patchdist(dlco_ctx *ctx, const float *d_dists, int64_t N,
 {
     DLCO_REQUIRE(ctx && d_dists && d_pd && N >= 0 && rank >= 0 && (rank == 0 || d_W), "dlco_pj_patchdist: bad arguments");
     return dlco_sqnorm_proj(ctx, d_dists, ld, nullptr, N, d_W, D, rank, D, d_pd);
+}
+
+// =======================================================================================
+// Lock-step sweep: nCfg (mu, gamma) configurations of workspace/08-pjlearn.sh on one GPU.  Every
+// run of the reference's grid seeds RNG(2215) and shuffles with the default theRNG(), so all
+// configurations of one data set draw the SAME batches: one gather, one grouped SYRK launch,
+// one batched eigen-decomposition per iteration.  Ranks, RNG state, mu, gamma live on the device:
+// an iteration issues no host synchronisation, iterations queue back to back on the stream.
+// =======================================================================================
+
+// interleaved pos, neg draws from cv::RNG (src/pj-learn.cpp:311-316): uniform(0, n) = next() % n
+__global__ void k_pj_sample(const int32_t *__restrict__ idx_pos, uint32_t n_pos_trn,
+                            const int32_t *__restrict__ idx_neg, uint32_t n_neg_trn, int b,
+                            uint64_t *__restrict__ state, int32_t *__restrict__ rows_pos,
+                            int32_t *__restrict__ rows_neg)
+{
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    uint64_t s = *state;
+    for (int k = 0; k < b; k++) {
+        s = (uint64_t)(uint32_t)s * 4164903690ULL + (s >> 32);
+        rows_pos[k] = idx_pos[(uint32_t)s % n_pos_trn];
+        s = (uint64_t)(uint32_t)s * 4164903690ULL + (s >> 32);
+        rows_neg[k] = idx_neg[(uint32_t)s % n_neg_trn];
+    }
+    *state = s;
+}
+
+extern "C" int dlco_pj_sample_batch(dlco_ctx *ctx, const int32_t *d_idx_pos, int32_t nPosTrn,
+                                    const int32_t *d_idx_neg, int32_t nNegTrn, int szBatch,
+                                    uint64_t *d_rng_state, int32_t *d_rows_pos, int32_t *d_rows_neg)
+{
+    DLCO_REQUIRE(ctx && d_idx_pos && d_idx_neg && d_rng_state && d_rows_pos && d_rows_neg, "dlco_pj_sample_batch: NULL argument");
+    DLCO_REQUIRE(nPosTrn > 0 && nNegTrn > 0 && szBatch > 0, "dlco_pj_sample_batch: bad sizes");
+    k_pj_sample<<<1, 32, 0, ctx->stream>>>(d_idx_pos, (uint32_t)nPosTrn, d_idx_neg, (uint32_t)nNegTrn, szBatch,
+                                           d_rng_state, d_rows_pos, d_rows_neg);
+    DLCO_CHECK_LAUNCH(ctx);
+    return DLCO_OK;
+}
+
+extern "C" int dlco_pj_rda_grad_grid_dev(dlco_ctx *ctx, const float *d_dists, int64_t ld, int D,
+                                         const int32_t *d_rows_pos, const int32_t *d_rows_neg, int szBatch,
+                                         int nCfg, const float *d_W, int64_t w_stride, const int32_t *d_rank,
+                                         float *d_dLoss)
+{
+    DLCO_REQUIRE(ctx && d_dists && d_rows_pos && d_rows_neg && d_dLoss && d_rank && d_W, "dlco_pj_rda_grad_grid_dev: NULL argument");
+    DLCO_REQUIRE(D > 0 && szBatch > 0 && szBatch <= 4096 && nCfg > 0 && ld >= D, "dlco_pj_rda_grad_grid_dev: bad shapes");
+    return pj_grad_core(ctx, d_dists, ld, D, d_rows_pos, d_rows_neg, szBatch, nCfg, d_W, w_stride, nullptr, d_rank,
+                        d_dLoss);
+}
+
+// K_pj_update for configuration blockIdx.z: same arithmetic as k_pj_update, the per-configuration
+// scalar -sqrt(t+1)/gamma is formed in double and rounded once, as the host version does.
+__global__ void __launch_bounds__(256)
+k_pj_update_grid(int D, double t1, float a_avg, float beta, const float *__restrict__ mu,
+                 const float *__restrict__ gamma, const float *__restrict__ dLoss,
+                 float *__restrict__ dfavg, float *__restrict__ A)
+{
+    const int j = blockIdx.x * 32 + (threadIdx.x & 31);
+    const int i = blockIdx.y * 8 + (threadIdx.x >> 5);
+    if (i >= D || j >= D || i > j) return;
+    const int g = blockIdx.z;
+    const size_t off = (size_t)g * D * D;
+    const float div = (float)(-sqrt(t1) / (double)gamma[g]);
+    const size_t ij = off + (size_t)i * D + j, ji = off + (size_t)j * D + i;
+    const float d_ij = __fadd_rn(__fmul_rn(dfavg[ij], a_avg), __fmul_rn(dLoss[ij], beta));
+    const float d_ji = __fadd_rn(__fmul_rn(dfavg[ji], a_avg), __fmul_rn(dLoss[ji], beta));
+    const float m = (i == j) ? mu[g] : 0.0f;
+    const float a_ij = __fmul_rn(__fadd_rn(d_ij, m), div);
+    const float a_ji = __fmul_rn(__fadd_rn(d_ji, m), div);
+    const float s = __fmul_rn(0.5f, __fadd_rn(a_ij, a_ji));
+    dfavg[ij] = d_ij;
+    dfavg[ji] = d_ji;
+    A[ij] = s;
+    A[ji] = s;
+}
+
+extern "C" int dlco_pj_rda_update_grid(dlco_ctx *ctx, int D, uint64_t t, int szBatch, int nCfg,
+                                       const float *d_mu, const float *d_gamma, const float *d_dLoss,
+                                       float *d_dfavg, float *d_A)
+{
+    DLCO_REQUIRE(ctx && d_mu && d_gamma && d_dLoss && d_dfavg && d_A && D > 0 && szBatch > 0 && nCfg > 0,
+                 "dlco_pj_rda_update_grid: bad arguments");
+    const float a_avg = (float)((double)t / (double)(t + 1));
+    const unsigned int den = (unsigned int)szBatch * (unsigned int)szBatch * (unsigned int)(t + 1);
+    const float beta = 1.0f / (float)den;
+    dim3 grid((D + 31) / 32, (D + 7) / 8, nCfg);
+    k_pj_update_grid<<<grid, 256, 0, ctx->stream>>>(D, (double)t + 1.0, a_avg, beta, d_mu, d_gamma, d_dLoss, d_dfavg, d_A);
+    DLCO_CHECK_LAUNCH(ctx);
+    return DLCO_OK;
+}
+
+// ---- batched eigen-decomposition: library code (cusolverDnXsyevBatched), like dlco_pj_eig ------
+typedef int (*fn_createparams)(void **);
+typedef int (*fn_xsyevb_bufsize)(void *, void *, int, int, int64_t, int, const void *, int64_t, int, const void *, int,
+                                 size_t *, size_t *, int64_t);
+typedef int (*fn_xsyevb)(void *, void *, int, int, int64_t, int, void *, int64_t, int, void *, int, void *, size_t,
+                         void *, size_t, int *, int64_t);
+static struct {
+    fn_createparams createparams;
+    fn_xsyevb_bufsize bufsize;
+    fn_xsyevb run;
+    void *params;
+} g_csb;
+
+static int cusolver_batched_load(dlco_ctx *ctx)
+{
+    int r = cusolver_load();
+    if (r != DLCO_OK) return r;
+    if (!g_csb.run) {
+        g_csb.createparams = (fn_createparams)dlsym(g_cs.lib, "cusolverDnCreateParams");
+        g_csb.bufsize = (fn_xsyevb_bufsize)dlsym(g_cs.lib, "cusolverDnXsyevBatched_bufferSize");
+        g_csb.run = (fn_xsyevb)dlsym(g_cs.lib, "cusolverDnXsyevBatched");
+        if (!g_csb.createparams || !g_csb.bufsize || !g_csb.run) {
+            g_csb.run = nullptr;
+            dlco_set_error("dlco_pj_eig_batched: libcusolver lacks cusolverDnXsyevBatched (needs CUDA >= 12.6)");
+            return DLCO_ECUDA;
+        }
+        if (g_csb.createparams(&g_csb.params) != 0) { g_csb.run = nullptr; dlco_set_error("cusolverDnCreateParams failed"); return DLCO_ECUDA; }
+    }
+    if (!ctx->cusolver) {
+        void *h = nullptr;
+        if (g_cs.create(&h) != 0 || !h) { dlco_set_error("cusolverDnCreate failed"); return DLCO_ECUDA; }
+        ctx->cusolver = h;
+    }
+    if (g_cs.setstream(ctx->cusolver, ctx->stream) != 0) { dlco_set_error("cusolverDnSetStream failed"); return DLCO_ECUDA; }
+    return DLCO_OK;
+}
+
+// d_evec (nCfg x D x D) receives A and is overwritten by the eigenvectors (row k = eigenvector k),
+// d_eval: nCfg x D ascending.  Asynchronous; the per-matrix info words stay in scratch slot 27.
+static int pj_eig_batched_async(dlco_ctx *ctx, int D, int nCfg, const float *d_A, float *d_eval, float *d_evec)
+{
+    int r = cusolver_batched_load(ctx);
+    if (r != DLCO_OK) return r;
+    if (d_evec != d_A)
+        DLCO_CUDA(cudaMemcpyAsync(d_evec, d_A, (size_t)nCfg * D * D * sizeof(float), cudaMemcpyDeviceToDevice, ctx->stream));
+    const int JOBZ_VECTOR = 1, FILL_UPPER = 1, R_32F = 0;
+    size_t wd = 0, wh = 0;
+    if (g_csb.bufsize(ctx->cusolver, g_csb.params, JOBZ_VECTOR, FILL_UPPER, D, R_32F, d_evec, D, R_32F, d_eval, R_32F,
+                      &wd, &wh, nCfg) != 0) {
+        dlco_set_error("cusolverDnXsyevBatched_bufferSize failed");
+        return DLCO_ECUDA;
+    }
+    void *work = dlco_scratch(ctx, 26, wd + 256);
+    int *info = (int *)dlco_scratch(ctx, 27, (size_t)nCfg * sizeof(int) + 64);
+    void *hwork = wh ? dlco_pinned(ctx, 6, wh) : nullptr;
+    if (!work || !info || (wh && !hwork)) return DLCO_ENOMEM;
+    int st = g_csb.run(ctx->cusolver, g_csb.params, JOBZ_VECTOR, FILL_UPPER, D, R_32F, d_evec, D, R_32F, d_eval, R_32F,
+                       work, wd, hwork, wh, info, nCfg);
+    ctx->launches++;
+    if (st != 0) { dlco_set_error("cusolverDnXsyevBatched failed: status %d", st); return DLCO_ECUDA; }
+    return DLCO_OK;
+}
+
+static int pj_eig_batched_check(dlco_ctx *ctx, int nCfg)
+{
+    int *info = (int *)dlco_scratch(ctx, 27, (size_t)nCfg * sizeof(int) + 64);
+    int *h = (int *)dlco_pinned(ctx, 7, (size_t)nCfg * sizeof(int));
+    if (!info || !h) return DLCO_ENOMEM;
+    DLCO_CUDA(cudaMemcpyAsync(h, info, (size_t)nCfg * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    DLCO_CUDA(cudaStreamSynchronize(ctx->stream));
+    for (int g = 0; g < nCfg; g++)
+        if (h[g] != 0) { dlco_set_error("cusolverDnXsyevBatched: info[%d] = %d", g, h[g]); return DLCO_ECUDA; }
+    return DLCO_OK;
+}
+
+extern "C" int dlco_pj_eig_batched(dlco_ctx *ctx, int D, int nCfg, const float *d_A, float *d_eval, float *d_evec)
+{
+    DLCO_REQUIRE(ctx && d_A && d_eval && d_evec && D > 0 && nCfg > 0, "dlco_pj_eig_batched: bad arguments");
+    int r = pj_eig_batched_async(ctx, D, nCfg, d_A, d_eval, d_evec);
+    if (r != DLCO_OK) return r;
+    return pj_eig_batched_check(ctx, nCfg);
+}
+
+// ---- prox for the sweep: ranks stay on the device ----------------------------------------------
+__global__ void __launch_bounds__(256) k_pj_rank(int D, const float *__restrict__ eval, int32_t *__restrict__ rank)
+{
+    __shared__ int s_cnt[8];
+    const float *e = eval + (size_t)blockIdx.x * D;
+    int c = 0;
+    for (int k = threadIdx.x; k < D; k += 256) c += e[k] > 0.0f;
+    for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+    if ((threadIdx.x & 31) == 0) s_cnt[threadIdx.x >> 5] = c;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int t = 0;
+        for (int i = 0; i < 8; i++) t += s_cnt[i];
+        rank[blockIdx.x] = t;          // eigenvalues ascend: the positive ones are the last t
+    }
+}
+
+__global__ void __launch_bounds__(256)
+k_pj_prox_w_grid(int D, const int32_t *__restrict__ d_rank, const float *__restrict__ eval,
+                 const float *__restrict__ evec, float *__restrict__ W, int64_t w_stride)
+{
+    const int r = blockIdx.x, g = blockIdx.y;
+    const int rank = d_rank[g], first = D - rank;
+    float *Wg = W + (size_t)g * w_stride;
+    if (r < rank) {
+        const float sq = sqrtf(fmaxf(eval[(size_t)g * D + first + r], 0.0f));
+        const float *v = evec + (size_t)g * D * D + (size_t)(first + r) * D;
+        for (int c = threadIdx.x; c < D; c += 256) Wg[(size_t)r * D + c] = __fmul_rn(sq, v[c]);
+    } else {
+        for (int c = threadIdx.x; c < D; c += 256) Wg[(size_t)r * D + c] = 0.0f;
+    }
+}
+
+__global__ void __launch_bounds__(256)
+k_pj_prox_a_grid(int D, const int32_t *__restrict__ d_rank, const float *__restrict__ eval,
+                 const float *__restrict__ evec, float *__restrict__ A)
+{
+    __shared__ float Ps[16][64 + 4];
+    __shared__ float Qs[16][64 + 4];
+    const int g = blockIdx.z;
+    const int R = d_rank[g], first = D - R;
+    const float *e = eval + (size_t)g * D + first;
+    const float *P = evec + (size_t)g * D * D + (size_t)first * D;
+    float *C = A + (size_t)g * D * D;
+    const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+    const int i0 = blockIdx.y * 64, j0 = blockIdx.x * 64;
+    const int lr = tid >> 4, lc = (tid & 15) * 4;
+    float acc[4][4];
+#pragma unroll
+    for (int a = 0; a < 4; a++)
+#pragma unroll
+        for (int b = 0; b < 4; b++) acc[a][b] = 0.f;
+    for (int r0 = 0; r0 < R; r0 += 16) {
+        const int r = r0 + lr;
+        const float er = r < R ? fmaxf(e[r], 0.0f) : 0.0f;
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int ci = i0 + lc + u, cj = j0 + lc + u;
+            Ps[lr][lc + u] = (r < R && ci < D) ? P[(size_t)r * D + ci] : 0.0f;
+            Qs[lr][lc + u] = (r < R && cj < D) ? __fmul_rn(er, P[(size_t)r * D + cj]) : 0.0f;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int kk = 0; kk < 16; kk++) {
+            const float4 a = *reinterpret_cast<const float4 *>(&Ps[kk][ty * 4]);
+            const float4 b = *reinterpret_cast<const float4 *>(&Qs[kk][tx * 4]);
+            const float av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+            for (int x = 0; x < 4; x++)
+#pragma unroll
+                for (int y = 0; y < 4; y++) acc[x][y] = fmaf(av[x], bv[y], acc[x][y]);
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int x = 0; x < 4; x++)
+#pragma unroll
+        for (int y = 0; y < 4; y++) {
+            const int i = i0 + ty * 4 + x, j = j0 + tx * 4 + y;
+            if (i < D && j < D) C[(size_t)i * D + j] = acc[x][y];
+        }
+}
+
+extern "C" int dlco_pj_prox_apply_grid(dlco_ctx *ctx, int D, int nCfg, const float *d_eval, const float *d_evec,
+                                       float *d_A, float *d_W, int64_t w_stride, int32_t *d_rank)
+{
+    DLCO_REQUIRE(ctx && d_eval && d_evec && d_A && d_W && d_rank && D > 0 && D <= 8192 && nCfg > 0 &&
+                 w_stride >= (int64_t)D * D, "dlco_pj_prox_apply_grid: bad arguments");
+    k_pj_rank<<<nCfg, 256, 0, ctx->stream>>>(D, d_eval, d_rank);
+    DLCO_CHECK_LAUNCH(ctx);
+    k_pj_prox_w_grid<<<dim3(D, nCfg), 256, 0, ctx->stream>>>(D, d_rank, d_eval, d_evec, d_W, w_stride);
+    DLCO_CHECK_LAUNCH(ctx);
+    dim3 grid((D + 63) / 64, (D + 63) / 64, nCfg);
+    k_pj_prox_a_grid<<<grid, 256, 0, ctx->stream>>>(D, d_rank, d_eval, d_evec, d_A);
+    DLCO_CHECK_LAUNCH(ctx);
+    return DLCO_OK;
+}
+
+// One whole RDA iteration t of every configuration: sample -> margins / hinge / grouped SYRK ->
+// dual average -> batched eig -> prox.  d_W / d_A / d_dfavg: nCfg x D x D; d_rank: nCfg;
+// work: d_work >= nCfg * (2 D D + D) floats (dLoss, eigenvectors, eigenvalues).  No host sync.
+extern "C" int dlco_pj_rda_step_grid(dlco_ctx *ctx, const float *d_dists, int64_t ld, int D,
+                                     const int32_t *d_idx_pos, int32_t nPosTrn, const int32_t *d_idx_neg,
+                                     int32_t nNegTrn, int szBatch, uint64_t *d_rng_state, int nCfg,
+                                     const float *d_mu, const float *d_gamma, uint64_t t, float *d_W,
+                                     float *d_A, float *d_dfavg, int32_t *d_rank, float *d_work)
+{
+    DLCO_REQUIRE(ctx && d_dists && d_idx_pos && d_idx_neg && d_rng_state && d_mu && d_gamma && d_W && d_A &&
+                 d_dfavg && d_rank && d_work, "dlco_pj_rda_step_grid: NULL argument");
+    DLCO_REQUIRE(D > 0 && szBatch > 0 && szBatch <= 4096 && nCfg > 0 && ld >= D, "dlco_pj_rda_step_grid: bad shapes");
+    const size_t dd = (size_t)D * D;
+    float *dLoss = d_work, *evec = d_work + nCfg * dd, *eval = evec + nCfg * dd;
+    int32_t *rows = (int32_t *)dlco_scratch(ctx, 25, (size_t)2 * szBatch * sizeof(int32_t));
+    if (!rows) return DLCO_ENOMEM;
+    int r = dlco_pj_sample_batch(ctx, d_idx_pos, nPosTrn, d_idx_neg, nNegTrn, szBatch, d_rng_state, rows, rows + szBatch);
+    if (r == DLCO_OK) r = pj_grad_core(ctx, d_dists, ld, D, rows, rows + szBatch, szBatch, nCfg, d_W, (int64_t)dd, nullptr, d_rank, dLoss);
+    if (r == DLCO_OK) r = dlco_pj_rda_update_grid(ctx, D, t, szBatch, nCfg, d_mu, d_gamma, dLoss, d_dfavg, d_A);
+    if (r == DLCO_OK) r = pj_eig_batched_async(ctx, D, nCfg, d_A, eval, evec);
+    if (r == DLCO_OK) r = dlco_pj_prox_apply_grid(ctx, D, nCfg, eval, evec, d_A, d_W, (int64_t)dd, d_rank);
+    return r;
+}
+
+// info words of the batched eigen-decompositions issued so far (synchronises)
+extern "C" int dlco_pj_grid_check(dlco_ctx *ctx, int nCfg)
+{
+    DLCO_REQUIRE(ctx && nCfg > 0, "dlco_pj_grid_check: bad arguments");
+    return pj_eig_batched_check(ctx, nCfg);
 }

@@ -255,3 +255,103 @@ class PjLearner:
         else:
             self.emit("Step: %i  Loss: %.6f Regul: %.6f Obj: %.6f (%.6f) Rank: %i (%i) Ttime: %.4f Vtime: %.4f"
                       % (t, loss, regul, obj, self.obj_best, rows, self.rank_best, ttime, vtime))
+
+
+class PjSweep:
+    """The (mu, gamma) grid of workspace/08-pjlearn.sh on one data set, in lock step on one GPU.
+
+    Every run of the reference's grid shuffles with the default theRNG() and samples with
+    RNG(2215) (src/pj-learn.cpp:214-227), so all configurations draw the same batches: the sweep
+    gathers each batch once, evaluates all gradients with one grouped SYRK launch and all
+    eigen-decompositions with one batched call (dlco_pj_rda_step_grid).  State is device resident;
+    an iteration never synchronises with the host.  Logs are the reference's lines, prefixed
+    with "[mu/gamma] " as PrLearner does for its grid."""
+
+    def __init__(self, ctx, dists, labels, mus, gammas, sz_batch=200, log_step=100, emit=None, split=None):
+        import torch
+        self.ctx, self.dists, self.torch = ctx, dists, torch
+        self.labels = np.asarray(labels).reshape(-1).astype(np.uint8)
+        self.mu = np.atleast_1d(np.asarray(mus, np.float32))
+        self.gamma = np.atleast_1d(np.asarray(gammas, np.float32))
+        assert len(self.mu) == len(self.gamma)
+        self.n_cfg = len(self.mu)
+        self.sz_batch, self.log_step = sz_batch, log_step
+        self.emit = emit or (lambda s: None)
+        ip, ineg, self.n_pos_trn, self.n_neg_trn = split or split_train_val(self.labels)
+        dev = ctx.device
+        self.idx_pos = torch.from_numpy(np.ascontiguousarray(ip, np.int32)).to(dev)
+        self.idx_neg = torch.from_numpy(np.ascontiguousarray(ineg, np.int32)).to(dev)
+        self.pos_val = self.idx_pos[self.n_pos_trn:].contiguous()
+        self.neg_val = self.idx_neg[self.n_neg_trn:].contiguous()
+        D, n = dists.shape[1], self.n_cfg
+        z = lambda: torch.zeros((n, D, D), dtype=torch.float32, device=dev)     # noqa: E731
+        self.W, self.A, self.dfavg = z(), z(), z()
+        self.work = torch.empty((n * (2 * D * D + D),), dtype=torch.float32, device=dev)
+        self.d_rank = torch.zeros((n,), dtype=torch.int32, device=dev)
+        self.d_mu = torch.from_numpy(self.mu).to(dev)
+        self.d_gamma = torch.from_numpy(self.gamma).to(dev)
+        self.rng_state = torch.tensor([2215], dtype=torch.int64, device=dev)    # RNG rng(2215)
+        self.t = 0
+        self.d_labels = torch.from_numpy(self.labels).to(dev)
+        big = float(np.finfo(np.float32).max)
+        self.obj_best = [big] * n
+        self.auc_best, self.fpr95_best = [0.0] * n, [1.0] * n
+        self.rank_best = [0] * n
+        self.W_save, self.A_save = [None] * n, [None] * n
+
+    def step(self):
+        self.ctx.pj_rda_step_grid(self.dists, self.idx_pos, self.n_pos_trn, self.idx_neg, self.n_neg_trn,
+                                  self.sz_batch, self.rng_state, self.d_mu, self.d_gamma, self.t, self.W, self.A,
+                                  self.dfavg, self.d_rank, self.work)
+        self.t += 1
+
+    def ranks(self):
+        self.ctx.pj_grid_check(self.n_cfg)                       # synchronises; raises on a failed eig
+        return self.d_rank.cpu().numpy().astype(int)
+
+    def validate(self, c, rank):
+        return self.ctx.pj_validate(self.dists, self.pos_val, self.neg_val, self.W[c], int(rank), self.A[c],
+                                    float(self.mu[c]))
+
+    def stats(self, c, rank):
+        pd = self.ctx.pj_patchdist(self.dists, self.W[c], int(rank))
+        return self.ctx.roc_stats(pd, self.d_labels)
+
+    def train(self, n_iter):
+        t_train = time.perf_counter()
+        step = 0
+        while self.t <= n_iter:
+            self.step()
+            if step == self.log_step:
+                ranks = self.ranks()
+                ttime = time.perf_counter() - t_train
+                for c in range(self.n_cfg):
+                    self._log(c, self.t - 1, ttime, ranks[c])
+                step = 0
+                t_train = time.perf_counter()
+            step += 1
+
+    def _log(self, c, t, ttime, rank):
+        tag = "[%g/%g] " % (self.mu[c], self.gamma[c])
+        tv = time.perf_counter()
+        loss, regul = self.validate(c, rank)
+        vtime = time.perf_counter() - tv
+        obj = float(np.float32(loss) + np.float32(regul))
+        rows = rank if rank > 0 else self.dists.shape[1]
+        if obj < self.obj_best[c]:
+            self.obj_best[c] = obj
+            self.rank_best[c] = rows
+            self.emit("%sBest: %i  Loss: %.6f Regul: %.6f Obj: %.6f (%.6f) Rank: %i (%i) Ttime: %.4f Vtime: %.4f"
+                      % (tag, t, loss, regul, obj, self.obj_best[c], rows, rows, ttime, vtime))
+            fpr95, auc = self.stats(c, rank)
+            keep = self.auc_best[c] <= auc and self.fpr95_best[c] >= fpr95
+            if keep:
+                self.auc_best[c], self.fpr95_best[c] = auc, fpr95
+                self.W_save[c] = self.W[c, :rank].clone() if rank > 0 else self.W[c].clone()
+                self.A_save[c] = self.A[c].clone()
+            self.emit("%sStat: Dim [%i] AUC: %.6f (%.6f) FPR95: %.2f (%.2f)%s"
+                      % (tag, rank, auc, self.auc_best[c], fpr95 * 100, self.fpr95_best[c] * 100,
+                         " [saved]" if keep else ""))
+        else:
+            self.emit("%sStep: %i  Loss: %.6f Regul: %.6f Obj: %.6f (%.6f) Rank: %i (%i) Ttime: %.4f Vtime: %.4f"
+                      % (tag, t, loss, regul, obj, self.obj_best[c], rows, self.rank_best[c], ttime, vtime))

@@ -360,3 +360,82 @@ def test_pr_patchdist_sparse_and_dense_paths(gpu_ctx, nnz):
     rows = dev_t(gpu_ctx, rng.integers(0, 3000, 777).astype(np.int32))
     m = gpu_ctx.pr_margins(d_d, rows, d_w).cpu().numpy()
     assert np.abs(m - want[rows.cpu().numpy()]).max() <= 1e-6 * np.abs(want).max()
+
+
+# ------------------------------------------------------------------------------------------
+# lock-step (mu, gamma) sweep: device-resident ranks / RNG, batched eigen-decomposition
+# ------------------------------------------------------------------------------------------
+def test_pj_sample_batch_matches_host_rng(gpu_ctx):
+    import dlco_b200
+    x, lab = synth_uprj(3000, 16, 4)
+    L = dlco_b200.learn.PjLearner(gpu_ctx, dev_t(gpu_ctx, x), lab, 0.001, 0.1, sz_batch=50)
+    S = dlco_b200.learn.PjSweep(gpu_ctx, dev_t(gpu_ctx, x), lab, [0.001], [0.1], sz_batch=50)
+    rp_d = torch.empty(50, dtype=torch.int32, device=gpu_ctx.device)
+    rn_d = torch.empty_like(rp_d)
+    for _ in range(3):
+        rp, rn = L.sample_batch()
+        gpu_ctx.pj_sample_batch(S.idx_pos, S.n_pos_trn, S.idx_neg, S.n_neg_trn, 50, S.rng_state, rp_d, rn_d)
+        gpu_ctx.sync()
+        np.testing.assert_array_equal(rp_d.cpu().numpy(), rp)
+        np.testing.assert_array_equal(rn_d.cpu().numpy(), rn)
+    assert int(S.rng_state.cpu().numpy().view(np.uint64)[0]) == L.rng.state
+
+
+def test_pj_eig_batched_reconstructs(gpu_ctx):
+    rng = np.random.default_rng(2)
+    n, D = 5, 96
+    M = rng.normal(0, 1, (n, D, D)).astype(np.float32)
+    A = ((M + M.transpose(0, 2, 1)) * 0.5).astype(np.float32)
+    ev, evec = gpu_ctx.pj_eig_batched(dev_t(gpu_ctx, A))
+    ev, evec = ev.cpu().numpy().astype(np.float64), evec.cpu().numpy().astype(np.float64)
+    for g in range(n):
+        assert np.all(np.diff(ev[g]) >= 0)
+        want = np.linalg.eigvalsh(A[g].astype(np.float64))
+        assert np.abs(ev[g] - want).max() <= 2e-5 * np.abs(want).max()
+        rec = evec[g].T @ np.diag(ev[g]) @ evec[g]              # row k = eigenvector k
+        assert np.abs(rec - A[g]).max() <= 2e-5 * np.abs(A[g]).max()
+
+
+def test_pj_sweep_matches_single_runs_and_oracle(gpu_ctx):
+    import dlco_b200
+    x, lab = synth_uprj(3000, 32, 4)
+    b, steps = 50, 40
+    mus, gammas = [0.001, 0.0005, 0.002], [0.1, 0.05, 0.2]
+    d_x = dev_t(gpu_ctx, x)
+    S = dlco_b200.learn.PjSweep(gpu_ctx, d_x, lab, mus, gammas, sz_batch=b)
+    for _ in range(steps):
+        S.step()
+    ranks = S.ranks()
+    ip, ineg, npt, nnt = O.split_train_val(lab)
+    for c in range(3):
+        st = O.pj_rda_steps(x, ip, ineg, npt, nnt, mus[c], gammas[c], steps, sz_batch=b, dt=np.float64)
+        A_g = S.A[c].cpu().numpy()
+        assert np.abs(A_g - st["A"]).max() <= 1e-4 * np.abs(st["A"]).max()      # north_star: A within 1e-4
+        assert ranks[c] == st["W"].shape[0]
+        W_g = S.W[c].cpu().numpy()[:ranks[c]]
+        assert np.abs(W_g.T @ W_g - A_g).max() <= 1e-5 * np.abs(A_g).max()
+        assert not S.W[c, ranks[c]:].any().item()
+        L = dlco_b200.learn.PjLearner(gpu_ctx, d_x, lab, mus[c], gammas[c], sz_batch=b)
+        for _ in range(steps):
+            L.step()
+        assert L.rank == ranks[c]
+        assert (L.A - S.A[c]).abs().max().item() <= 2e-5 * L.A.abs().max().item()
+        loss, regul = S.validate(c, ranks[c])
+        lo, ro = O.pj_validate(x[ip[npt:]], x[ineg[nnt:]], st["W"], st["A"], mus[c])
+        assert abs(loss - lo) <= 1e-4 * lo and abs(regul - ro) <= 1e-4 * ro
+    assert int(S.rng_state.cpu().numpy().view(np.uint64)[0]) == st["rng"].state
+
+
+def test_pj_sweep_log_format(gpu_ctx):
+    import dlco_b200
+    import re
+    x, lab = synth_uprj(3000, 32, 9)
+    lines = []
+    S = dlco_b200.learn.PjSweep(gpu_ctx, dev_t(gpu_ctx, x), lab, [0.001, 0.002], [0.1, 0.2], sz_batch=40,
+                                log_step=10, emit=lines.append)
+    S.train(25)
+    assert sum(s.startswith("[0.001/0.1] Best: ") for s in lines) >= 1
+    pat = re.compile(r"^\[[0-9.e-]+/[0-9.e-]+\] (Best|Step): \d+  Loss: [0-9.]+ Regul: [0-9.]+ Obj: [0-9.]+ "
+                     r"\([0-9.]+\) Rank: \d+ \(\d+\) Ttime: [0-9.]+ Vtime: [0-9.]+$")
+    assert all(pat.match(s) for s in lines if " Best: " in s or " Step: " in s)
+    assert S.W_save[0] is not None and S.A_save[0] is not None
