@@ -205,6 +205,15 @@ def run(ctx, n_train=500000, n_test=100000, quick=False, D=544, n_pj_cfg=45, n_p
                            "achieved_gbs": n_train * D * 4 / (mean_ms * 1e-3) / 1e9,
                            "frac_hbm": n_train * D * 4 / (mean_ms * 1e-3) / 1e9 / hbm,
                            "tflops": 2.0 * n_train * D * max(L.rank, 1) / (mean_ms * 1e-3) / 1e12}
+    # the ranks the reference's exported models have (48 / 64 / 80 / 120, workspace/11-opencv-export.sh:3-6)
+    for r in (48, 80, 128, 256):
+        r = min(r, max(L.rank, 1))
+        Wr = L.W[L.rank - r:L.rank].contiguous() if L.rank >= r else L.W
+        mean_ms, best_ms = timeit(torch, lambda: ctx.pj_patchdist(ud, Wr, r))
+        res["pj_patchdist_rank%d" % r] = {"rows": n_train, "D": D, "rank": r, "ms": mean_ms, "best_ms": best_ms,
+                                           "achieved_gbs": n_train * D * 4 / (mean_ms * 1e-3) / 1e9,
+                                           "frac_hbm": n_train * D * 4 / (mean_ms * 1e-3) / 1e9 / hbm,
+                                           "tflops": 2.0 * n_train * D * r / (mean_ms * 1e-3) / 1e12}
     mean_ms, best_ms = timeit(torch, lambda: L.validate(), rep=5)
     res["pj_validate"] = {"ms": mean_ms, "n_pos": L.pos_val.numel(), "n_neg": L.neg_val.numel()}
     return res

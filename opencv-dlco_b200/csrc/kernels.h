@@ -42,6 +42,10 @@ int dlco_gemv_rows(dlco_ctx *ctx, const float *d_dists, int64_t ld, int F, const
 int dlco_sqnorm_proj(dlco_ctx *ctx, const float *d_X, int64_t ld, const int32_t *d_rows, int64_t n,
                      const float *d_W, int64_t ldw, int rank, int D, float *d_out);
 
+// sqnorm_tc.cu: the same on tcgen05 (fp16 hi/lo split of both operands, X converted on the fly)
+int dlco_sqnorm_tc(dlco_ctx *ctx, const float *d_X, int64_t ld, const int32_t *d_rows, int64_t n,
+                   const float *d_W, int64_t ldw, int rank, int D, float *d_out);
+
 // gemm_tc.cu: batched C = A * B^T on tcgen05 (3xTF32) from K-major tf32 hi/lo planes
 int dlco_launch_gemm3x_nt(dlco_ctx *ctx, const float *a_hi, const float *a_lo, int a_rows_pad,
                           const float *b_hi, const float *b_lo, int b_rows_pad, int b_batched,

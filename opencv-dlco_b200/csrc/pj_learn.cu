@@ -11,6 +11,7 @@
 #include "kernels.h"
 #include <dlfcn.h>
 #include <math.h>
+#include <stdlib.h>
 
 // ---------------------------------------------------------------------------------------
 // K_sqnorm_proj: out[n] = sum_r ( sum_d W[r, d] X[row(n), d] )^2     (SIMT fp32, 64x64 tiles)
@@ -105,6 +106,12 @@ int dlco_sqnorm_proj(dlco_ctx *ctx, const float *d_X, int64_t ld, const int32_t 
         DLCO_CUDA(cudaMemsetAsync(d_out, 0, (size_t)n * sizeof(float), ctx->stream));
         return DLCO_OK;
     }
+    // tensor-core path (sqnorm_tc.cu) whenever the layout allows 128-bit row loads; DLCO_SQNORM_SIMT=1
+    // forces the SIMT kernel (the on-device cross-check of the tensor path, tests/test_gpu_learn.py)
+    const char *env = getenv("DLCO_SQNORM_SIMT");
+    const bool simt = env && atoi(env) != 0;
+    if (!simt && (D & 3) == 0 && (ld & 3) == 0 && ((uintptr_t)d_X & 15) == 0 && rank <= 960)
+        return dlco_sqnorm_tc(ctx, d_X, ld, d_rows, n, d_W, ldw, rank, D, d_out);
     dlco_prof_begin(ctx, 5);
     k_sqnorm_proj<<<(unsigned)((n + SP_BM - 1) / SP_BM), 256, 0, ctx->stream>>>(d_X, ld, d_rows, n, d_W, ldw, rank, D, d_out,
                                                                                 nullptr, 0);

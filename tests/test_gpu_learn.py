@@ -439,3 +439,48 @@ def test_pj_sweep_log_format(gpu_ctx):
                      r"\([0-9.]+\) Rank: \d+ \(\d+\) Ttime: [0-9.]+ Vtime: [0-9.]+$")
     assert all(pat.match(s) for s in lines if " Best: " in s or " Step: " in s)
     assert S.W_save[0] is not None and S.A_save[0] is not None
+
+
+# ------------------------------------------------------------------------------------------
+# tensor-core margins / ComputePJStats distances (sqnorm_tc.cu) against fp64 and the SIMT kernel
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("n,D,rank,gather", [
+    (1000, 544, 80, False), (4097, 480, 120, True), (400, 544, 544, True), (129, 64, 3, False),
+    (70000, 544, 48, False), (300, 36, 36, False), (2500, 544, 300, True), (128, 256, 256, False)])
+def test_sqnorm_tc_matches_fp64_and_simt(gpu_ctx, n, D, rank, gather):
+    import os
+    rng = np.random.default_rng(n + D + rank)
+    nx = n * 2 if gather else n
+    x = rng.uniform(-1, 1, (nx, D)).astype(np.float32) * rng.uniform(0.01, 1, (nx, 1)).astype(np.float32)
+    x[rng.random((nx, D)) < 0.1] = 0
+    W = np.zeros((D, D), np.float32)
+    W[:rank] = rng.normal(0, 1, (rank, D)).astype(np.float32) * np.geomspace(1e-3, 3.0, rank)[:, None].astype(np.float32)
+    rows = rng.permutation(nx)[:n].astype(np.int32) if gather else None
+    d_x, d_W = dev_t(gpu_ctx, x), dev_t(gpu_ctx, W)
+    d_rows = dev_t(gpu_ctx, rows) if gather else None
+    xs = x[rows] if gather else x
+    want = ((xs.astype(np.float64) @ W[:rank].astype(np.float64).T) ** 2).sum(axis=1)
+    got = {}
+    for mode in ("0", "1"):
+        os.environ["DLCO_SQNORM_SIMT"] = mode
+        try:
+            if gather:
+                out = gpu_ctx.pj_margins(d_x, d_rows, d_W, rank)
+            else:
+                out = gpu_ctx.pj_patchdist(d_x, d_W, rank)
+            gpu_ctx.sync()
+        finally:
+            os.environ.pop("DLCO_SQNORM_SIMT")
+        got[mode] = out.cpu().numpy().astype(np.float64)
+        assert np.abs(got[mode] - want).max() <= 1e-5 * np.abs(want).max(), mode
+    # element-wise, relative to each row's own value
+    nz = want > 1e-6 * want.max()
+    assert (np.abs(got["0"][nz] - want[nz]) / want[nz]).max() <= 2e-5
+
+
+def test_sqnorm_tc_saturates_out_of_contract_inputs(gpu_ctx):
+    """|x| > 127 is outside the contract of the tensor path: it must stay finite (saturation)."""
+    x = np.full((256, 64), 1000.0, np.float32)
+    W = np.eye(64, dtype=np.float32)
+    out = gpu_ctx.pj_patchdist(dev_t(gpu_ctx, x), dev_t(gpu_ctx, W), 64)
+    assert torch.isfinite(out).all().item()

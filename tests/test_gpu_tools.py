@@ -63,7 +63,7 @@ def workspace(tmp_path_factory, gpu_ctx, oracle_lib):
 
 
 def test_usage_and_exit_codes():
-    for tool in ["comp-fulldists", "comp-uprjdists", "pr-learn", "pj-learn", "pr-stats", "pj-stats"]:
+    for tool in ["comp-fulldists", "comp-uprjdists", "pr-learn", "pj-learn", "pj-sweep", "pr-stats", "pj-stats"]:
         rc, out, _ = run(tool, "-help")
         assert rc == 1 and "Usage:" in out
     rc, out, _ = run("pr-learn", "-bogus", "a", "b", "c")
@@ -187,6 +187,42 @@ def test_pipeline(workspace, gpu_ctx):
     assert np.abs(A - A_py).max() <= 1e-4 * np.abs(A_py).max()
     assert np.abs(W.T @ W - W_py.T @ W_py).max() <= 1e-4 * np.abs(A_py).max()
     assert np.abs(W.T.astype(np.float64) @ W - A).max() <= 1e-5 * max(np.abs(A).max(), 1e-30)
+
+    # ---- pj-sweep: the 08-pjlearn.sh loop in lock step; files and logs as the loop would leave them ----
+    sw = os.path.join(tmp, "sweep")
+    rc, so2, se = run("pj-sweep", os.path.join(tmp, "train-unproj.h5"), sw, "-mu", "0.001,0.0020", "-gamma", "0.1",
+                      "-iters", 300)
+    assert rc == 0, se
+    assert "2 grid points" in so2 and "config-iterations/s" in so2
+    log = open(os.path.join(sw, "logging", "train-0.001-0.1-pj.log")).read()
+    assert log.startswith("mu: 0.001 gamma: 0.1 nIters: 300\nLoad Labels: 700\nLoad Distances: 700 x %d\n" % D)
+    assert os.path.exists(os.path.join(sw, "logging", "train-0.0020-0.1-pj.log"))
+
+    def toks(text):
+        out = []
+        for ln in text.splitlines():
+            if ln[:5] in ("Best:", "Step:", "Stat:"):
+                out.append(re.sub(r" Ttime: .*$", "", ln).replace("(", " ").replace(")", " ").replace("[", " ").replace("]", " ").split())
+        return out
+    a, b = toks(so), toks(log)
+    assert len(a) == len(b) and len(a) >= 3
+    for la, lb in zip(a, b):
+        assert len(la) == len(lb)
+        for x, y in zip(la, lb):
+            if re.fullmatch(r"-?\d+\.\d+", x):
+                assert abs(float(x) - float(y)) <= 3e-6 + 0.0101 * ("." in x and len(x.split(".")[1]) == 2), (la, lb)
+            else:
+                assert x == y, (la, lb)
+    fs = H5File(os.path.join(sw, "train-0.001-0.1-pj.h5"))
+    A_s, W_s = fs.read("A"), fs.read("W")
+    assert W_s.shape == W.shape and np.abs(A_s - A).max() <= 1e-4 * np.abs(A).max()
+    assert np.abs(W_s.T.astype(np.float64) @ W_s - A_s).max() <= 1e-5 * max(np.abs(A_s).max(), 1e-30)
+    f2 = H5File(os.path.join(sw, "train-0.0020-0.1-pj.h5"))
+    assert f2.read("A").shape == (D, D)
+    # -shard r/n partitions the grid
+    rc, so3, se = run("pj-sweep", os.path.join(tmp, "train-unproj.h5"), os.path.join(tmp, "sweep1"), "-mu", "0.001,0.0020",
+                      "-gamma", "0.1", "-iters", 20, "-shard", "1/2")
+    assert rc == 0 and "1 grid points" in so3 and os.listdir(os.path.join(tmp, "sweep1", "logging")) == ["train-0.0020-0.1-pj.log"]
 
     # ---- pj-stats (defined by us, see tools/pj-stats.cpp) ----------------------------------------
     rc, so, se = run("pj-stats", flt, "-maxdim", D, "-dst", os.path.join(tmp, "test-unproj.h5"), "-prg", prm, "-prj", pjm)
