@@ -271,6 +271,33 @@ int dlco_make_tmap_2d_ex(CUtensorMap *map, const void *base, int elem_bytes, uin
     return DLCO_OK;
 }
 
+// fp32 row-major matrix with an explicit leading dimension, no swizzle (raw staging tiles)
+int dlco_make_tmap_2d_raw(CUtensorMap *map, const float *base, uint64_t rows, uint64_t cols, uint64_t ld,
+                          uint32_t box_rows, uint32_t box_cols)
+{
+    CUtensorMap tmp;
+    int r = dlco_make_tmap_2d_ex(&tmp, base, 4, 16, 64, 8, 32);      // resolves the driver entry point
+    if (r != DLCO_OK) return r;
+    void *p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || !p) {
+        dlco_set_error("cuTensorMapEncodeTiled not available from the driver");
+        return DLCO_ECUDA;
+    }
+    cuuint64_t gdim[2] = {cols, rows};
+    cuuint64_t gstride[1] = {ld * 4};
+    cuuint32_t box[2] = {box_cols, box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult cr = ((PFN_encodeTiled)p)(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void *)base, gdim, gstride, box, estr,
+                                       CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                       CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (cr != CUDA_SUCCESS) {
+        dlco_set_error("cuTensorMapEncodeTiled (raw) failed: CUresult %d", (int)cr);
+        return DLCO_ECUDA;
+    }
+    return DLCO_OK;
+}
+
 int dlco_make_tmap_2d(CUtensorMap *map, const float *base, uint64_t rows, uint64_t cols,
                       uint32_t box_rows, uint32_t box_cols)
 {

@@ -15,6 +15,8 @@ int dlco_make_tmap_2d_ex(CUtensorMap *map, const void *base, int elem_bytes, uin
                          uint32_t box_rows, uint32_t box_cols);
 int dlco_make_tmap_2d(CUtensorMap *map, const float *base, uint64_t rows, uint64_t cols,
                       uint32_t box_rows, uint32_t box_cols);
+int dlco_make_tmap_2d_raw(CUtensorMap *map, const float *base, uint64_t rows, uint64_t cols, uint64_t ld,
+                          uint32_t box_rows, uint32_t box_cols);
 
 // pool_simt.cu: SIMT pooling over K-major descriptor rows (slot*8+bin) x 4096.
 //   mode 0: full distance  out[pair][ring]   (nF/8 per pair)

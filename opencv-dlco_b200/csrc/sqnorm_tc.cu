@@ -10,17 +10,20 @@
 // fp32 accuracy: as in K_pool_fulldist, each operand is split into two fp16 planes after a
 // power-of-two scaling, v s = hi + lo (22 mantissa bits), and every K step issues lo*hi + hi*lo +
 // hi*hi (kind::f16, fp32 accumulate).  W is split once per call (k_w_planes: one scale per row,
-// since row k = sqrt(e_k) v_k spans orders of magnitude).  X is split ON THE FLY by the loader
-// warps: 128-bit global loads of the fp32 rows (through the row-index list when the caller
-// gathers), two cvt.rn.f16 per value, stores into the 128-byte-swizzled K-major tile layout the
-// UMMA descriptors expect -- no fp16 copy of X ever exists in HBM.  X uses the fixed scale 2^9:
-// unprojected distances are differences of values clamped to [0, 1] (src/comp-uprjdists.cpp:
-// 322-327), |x| <= 1; inputs are saturated at |x| = 127 (documented contract of this path).
+// since row k = sqrt(e_k) v_k spans orders of magnitude).  X is split ON THE FLY: a producer warp
+// streams the raw fp32 rows into a shared-memory staging ring with 1-D bulk copies (one 256-byte
+// copy per row and K chunk, through the row-index list when the caller gathers; the ring depth is
+// the memory-level parallelism of the stream), converter warps turn each chunk into fp16 hi / lo
+// planes in the 128-byte-swizzled K-major layout the UMMA descriptors expect -- no fp16 copy of X
+// ever exists in HBM.  X uses the fixed scale 2^9: unprojected distances are differences of values
+// clamped to [0, 1] (src/comp-uprjdists.cpp:322-327), |x| <= 1; inputs are saturated at |x| = 127
+// (documented contract of this path).
 //
-// CTA = 128 rows of X (TMEM lanes) x NPB <= 256 rank columns; rank > 256 runs ceil(rank / 256)
+// CTA = 128 rows of X (TMEM lanes) x NPB <= 128 rank columns; rank > 128 runs ceil(rank / 128)
 // passes over the tile (X re-read from L2, not HBM).  Persistent, warp-specialised:
-//   warps 0..7  loaders / converters of X     warp 8  TMA producer of the W planes
-//   warp 9      MMA issuer + TMEM owner        warps 10..13  epilogue (sum of squares per row)
+//   warps 0..7  converters          warp 8  bulk-copy producer of raw X rows
+//   warp 9      TMA producer of W   warp 10 MMA issuer + TMEM owner
+//   warps 11..14  epilogue (sum of squares per row, straight out of TMEM)
 // Two TMEM accumulators: the epilogue of one tile overlaps the MMAs of the next.
 #include "common.cuh"
 #include "kernels.h"
@@ -32,15 +35,21 @@ namespace {
 constexpr int BM = 128;
 constexpr int BK = 64;                        // fp16 elements per K chunk = one 128-byte swizzle row
 constexpr int X_BYTES = BM * BK * 2;          // one fp16 plane of the X tile
-constexpr int LOAD_WARPS = 8;
-constexpr int NTHREADS = (LOAD_WARPS + 2 + 4) * 32;
-constexpr int TMEM_COLS = 512;
+constexpr int RAW_BYTES = BM * BK * 4;        // the same chunk as raw fp32 rows (staging)
+constexpr int CONV_WARPS = 8;
+constexpr int W_COPY = CONV_WARPS, W_TMA = CONV_WARPS + 1, W_MMA = CONV_WARPS + 2;   // warp roles
+constexpr int NTHREADS = (CONV_WARPS + 3 + 4) * 32;
+constexpr int NPB_MAX = 128;                  // rank columns per pass (TMEM accumulator width)
+constexpr int ACC_COLS = 128;
+constexpr int TMEM_COLS = 256;
+constexpr int OP_STAGES = 2;
+constexpr int MAX_STAGING = 5;
 constexpr int MAX_RPAD = 1024;
 constexpr float X_SCALE = 512.0f;             // 2^9
 constexpr float X_INV2 = 1.0f / (512.0f * 512.0f);
 
 struct __align__(64) WMaps {
-    CUtensorMap hi, lo;
+    CUtensorMap hi, lo, x;      // x: the fp32 matrix itself (contiguous-row case), box 128 rows x 64 floats
 };
 
 // W (rank x D fp32) -> fp16 hi / lo planes r_pad x d_pad (zero padded), one power-of-two scale per
@@ -83,42 +92,60 @@ k_w_planes(const float *__restrict__ W, int64_t ldw, int rank, int D, int d_pad,
     if (threadIdx.x == 0) inv[r] = 1.0f / scale;
 }
 
+// 1-D bulk copy global -> shared, completion counted in bytes on an mbarrier
+__device__ __forceinline__ void bulk_g2s(void *smem_dst, const void *gsrc, uint32_t bytes, uint64_t *bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(smem_dst)),
+                 "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+
 __device__ __forceinline__ uint32_t pack_h2(__half a, __half b)
 {
     return (uint32_t)__half_as_ushort(a) | ((uint32_t)__half_as_ushort(b) << 16);
 }
 
-// split 4 scaled floats into hi / lo fp16 quads (8 bytes each)
+__device__ __forceinline__ uint32_t h2_bits(__half2 h)
+{
+    return *reinterpret_cast<uint32_t *>(&h);
+}
+
+// split 4 scaled floats into hi / lo fp16 quads (8 bytes each).  hi = the value rounded to fp16's 11
+// significant bits by integer arithmetic on its bit pattern (exactly representable, so the packed
+// convert is exact), lo = the exact remainder rounded to fp16: hi + lo = v s (1 + O(2^-22)).  Packed cvt.rn.f16x2.f32 only: the
+// scalar f32 <-> f16 converts run at a quarter of the rate and were the bottleneck of this kernel.
 __device__ __forceinline__ void split4(const float4 v, uint2 &hi, uint2 &lo)
 {
-    float x[4] = {v.x, v.y, v.z, v.w};
-    __half h[4], l[4];
+    float s[4] = {v.x, v.y, v.z, v.w}, h[4];
 #pragma unroll
     for (int i = 0; i < 4; i++) {
-        const float s = fminf(fmaxf(x[i] * X_SCALE, -65024.f), 65024.f);
-        h[i] = __float2half_rn(s);
-        l[i] = __float2half_rn(s - __half2float(h[i]));
+        s[i] = fminf(fmaxf(s[i] * X_SCALE, -65024.f), 65024.f);
+        h[i] = __uint_as_float((__float_as_uint(s[i]) + 0x1000u) & 0xFFFFE000u);   // round to 11 bits
     }
-    hi = make_uint2(pack_h2(h[0], h[1]), pack_h2(h[2], h[3]));
-    lo = make_uint2(pack_h2(l[0], l[1]), pack_h2(l[2], l[3]));
+    hi = make_uint2(h2_bits(__floats2half2_rn(h[0], h[1])), h2_bits(__floats2half2_rn(h[2], h[3])));
+    lo = make_uint2(h2_bits(__floats2half2_rn(s[0] - h[0], s[1] - h[1])),
+                    h2_bits(__floats2half2_rn(s[2] - h[2], s[3] - h[3])));
 }
 
 __global__ void __launch_bounds__(NTHREADS, 1)
 k_sqnorm_tc(const __grid_constant__ WMaps maps, const float *__restrict__ X, int64_t ld,
-            const int32_t *__restrict__ rows, int64_t n, int D, int kc_total, int npb, int passes, int stages,
+            const int32_t *__restrict__ rows, int64_t n, int D, int kc_total, int npb, int passes, int n_stage,
             const float *__restrict__ w_inv, float *__restrict__ out)
 {
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     const int w_bytes = npb * 128;                       // one fp16 plane of the W tile
-    const int stage_bytes = 2 * X_BYTES + 2 * w_bytes;
-    uint64_t *bars = reinterpret_cast<uint64_t *>(smem + stages * stage_bytes);
-    uint64_t *full = bars;                    // [4]
-    uint64_t *empty = bars + 4;               // [4]
-    uint64_t *tfull = bars + 8;               // [2]
-    uint64_t *tempty = bars + 10;             // [2]
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 12);
-    float *s_inv = reinterpret_cast<float *>(bars + 32);          // [passes * npb] <= MAX_RPAD
+    const int op_bytes = 2 * X_BYTES + 2 * w_bytes;      // operand stage: X hi, X lo, W hi, W lo
+    uint8_t *staging = smem + OP_STAGES * op_bytes;      // n_stage x (128 rows x 64 fp32), raw rows of X
+    uint64_t *bars = reinterpret_cast<uint64_t *>(staging + n_stage * RAW_BYTES);
+    uint64_t *full = bars;                    // [OP_STAGES]   converters (8) + W TMA (1) -> MMA
+    uint64_t *empty = bars + 2;               // [OP_STAGES]   MMA commit -> converters, W TMA
+    uint64_t *sfull = bars + 4;               // [MAX_STAGING] bulk copies landed -> converters
+    uint64_t *sempty = bars + 4 + MAX_STAGING;   // [MAX_STAGING] converters done -> copy producer
+    uint64_t *tfull = bars + 4 + 2 * MAX_STAGING;
+    uint64_t *tempty = tfull + 2;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tempty + 2);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n_tiles = (int)((n + BM - 1) / BM);
@@ -131,9 +158,14 @@ k_sqnorm_tc(const __grid_constant__ WMaps maps, const float *__restrict__ X, int
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&maps.hi);
         tma_prefetch_desc(&maps.lo);
-        for (int s = 0; s < stages; s++) {
-            mbar_init(&full[s], LOAD_WARPS + 1);
+        if (!rows) tma_prefetch_desc(&maps.x);
+        for (int s = 0; s < OP_STAGES; s++) {
+            mbar_init(&full[s], CONV_WARPS + 1);
             mbar_init(&empty[s], 1);
+        }
+        for (int s = 0; s < n_stage; s++) {
+            mbar_init(&sfull[s], 32);
+            mbar_init(&sempty[s], CONV_WARPS);
         }
         for (int a = 0; a < 2; a++) {
             mbar_init(&tfull[a], 1);
@@ -141,89 +173,126 @@ k_sqnorm_tc(const __grid_constant__ WMaps maps, const float *__restrict__ X, int
         }
         fence_barrier_init();
     }
-    for (int i = threadIdx.x; i < passes * npb; i += NTHREADS) s_inv[i] = w_inv[i];
-    if (warp == LOAD_WARPS + 1) tmem_alloc<TMEM_COLS>(tmem_slot);
+    if (warp == W_MMA) tmem_alloc<TMEM_COLS>(tmem_slot);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
-    if (warp < LOAD_WARPS) {
-        // ===== X loaders: fp32 rows -> fp16 hi / lo swizzled tiles, one K chunk prefetched ahead =====
+    if (warp < CONV_WARPS) {
+        // ===== converters: raw fp32 rows in staging -> fp16 hi / lo planes in the swizzled K-major layout =====
         const int q = threadIdx.x & 15, rsub = threadIdx.x >> 4;
-        float4 cur[8], nxt[8];
-        auto load = [&](int u, int kc, float4(&v)[8]) {
-            const int col = kc * BK + q * 4;
+        int st = 0, op = 0;
+        uint32_t st_phase = 0, op_phase = 0;
+        for (int u = 0; u < units; u++) {
             const int64_t r0 = (int64_t)UNIT_TILE(u) * BM + rsub;
+            for (int kc = 0; kc < kc_total; kc++) {
+                const bool col_ok = kc * BK + q * 4 < D;
+                mbar_wait(&sfull[st], st_phase);
+                const uint8_t *raw = staging + st * RAW_BYTES;
+                float4 v[8];
 #pragma unroll
-            for (int i = 0; i < 8; i++) {
-                const int64_t r = r0 + i * 16;
-                v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (r < n && col < D) {
-                    const int64_t src = rows ? (int64_t)__ldg(rows + r) : r;
-                    v[i] = __ldg(reinterpret_cast<const float4 *>(X + src * ld + col));
+                for (int i = 0; i < 8; i++) {
+                    const int row = i * 16 + rsub;
+                    v[i] = (col_ok && r0 + i * 16 < n) ? *reinterpret_cast<const float4 *>(raw + row * 256 + q * 16)
+                                                     : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&sempty[st]);         // values are in registers: refill may start
+                if (++st == n_stage) { st = 0; st_phase ^= 1; }
+                mbar_wait(&empty[op], op_phase ^ 1);
+                uint8_t *dst = smem + op * op_bytes;
+#pragma unroll
+                for (int i = 0; i < 8; i++) {
+                    const int row = i * 16 + rsub;
+                    const int off = row * 128 + (((q >> 1) ^ (row & 7)) << 4) + (q & 1) * 8;
+                    uint2 hi, lo;
+                    split4(v[i], hi, lo);
+                    *reinterpret_cast<uint2 *>(dst + off) = hi;
+                    *reinterpret_cast<uint2 *>(dst + X_BYTES + off) = lo;
+                }
+                fence_proxy_async();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&full[op]);
+                if (++op == OP_STAGES) { op = 0; op_phase ^= 1; }
+            }
+        }
+    } else if (warp == W_COPY) {
+        // ===== producer of the raw X rows: one 256-byte bulk copy per row and K chunk (gather through rows[]) =====
+        int st = 0;
+        uint32_t st_phase = 0;
+        if (!rows) {
+            // contiguous rows: one 2-D TMA box per K chunk (out-of-range rows / columns arrive as zeros)
+            for (int u = 0; u < units; u++) {
+                const int row0 = UNIT_TILE(u) * BM;
+                for (int kc = 0; kc < kc_total; kc++) {
+                    mbar_wait(&sempty[st], st_phase ^ 1);
+                    if (lane == 0) {
+                        mbar_expect_tx(&sfull[st], RAW_BYTES);
+                        tma_load_2d(staging + st * RAW_BYTES, &maps.x, &sfull[st], kc * BK, row0);
+                    } else {
+                        mbar_arrive(&sfull[st]);
+                    }
+                    if (++st == n_stage) { st = 0; st_phase ^= 1; }
                 }
             }
-        };
-        int stage = 0;
-        uint32_t phase = 0;
-        int u = 0, kc = 0;
-        if (u < units) load(u, 0, cur);
-        while (u < units) {
-            int nu = u, nk = kc + 1;
-            if (nk == kc_total) { nk = 0; nu = u + 1; }
-            if (nu < units) load(nu, nk, nxt);
-            mbar_wait(&empty[stage], phase ^ 1);
-            uint8_t *st = smem + stage * stage_bytes;
+        } else
+        for (int u = 0; u < units; u++) {
+            const int64_t r0 = (int64_t)UNIT_TILE(u) * BM + lane;
+            const float *src[4];
 #pragma unroll
-            for (int i = 0; i < 8; i++) {
-                const int row = i * 16 + rsub;
-                const int off = row * 128 + (((q >> 1) ^ (row & 7)) << 4) + (q & 1) * 8;
-                uint2 hi, lo;
-                split4(cur[i], hi, lo);
-                *reinterpret_cast<uint2 *>(st + off) = hi;
-                *reinterpret_cast<uint2 *>(st + X_BYTES + off) = lo;
+            for (int i = 0; i < 4; i++) {
+                const int64_t r = r0 + i * 32;
+                src[i] = r < n ? X + (rows ? (int64_t)__ldg(rows + r) : r) * ld : nullptr;
             }
-            fence_proxy_async();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&full[stage]);
-            if (++stage == stages) { stage = 0; phase ^= 1; }
+            for (int kc = 0; kc < kc_total; kc++) {
+                const int col = kc * BK;
+                const uint32_t bytes = (uint32_t)min(BK, D - col) * 4u;
+                mbar_wait(&sempty[st], st_phase ^ 1);
+                uint8_t *raw = staging + st * RAW_BYTES;
+                uint32_t mine = 0;
 #pragma unroll
-            for (int i = 0; i < 8; i++) cur[i] = nxt[i];
-            u = nu;
-            kc = nk;
+                for (int i = 0; i < 4; i++) {
+                    if (src[i]) {
+                        bulk_g2s(raw + (lane + i * 32) * 256, src[i] + col, bytes, &sfull[st]);
+                        mine += bytes;
+                    }
+                }
+                mbar_expect_tx(&sfull[st], mine);
+                if (++st == n_stage) { st = 0; st_phase ^= 1; }
+            }
         }
-    } else if (warp == LOAD_WARPS) {
+    } else if (warp == W_TMA) {
         // ===== TMA producer of the W planes =====
         if (lane == 0) {
-            int stage = 0;
+            int op = 0;
             uint32_t phase = 0;
             for (int u = 0; u < units; u++) {
                 const int wrow = (u % passes) * npb;
                 for (int kc = 0; kc < kc_total; kc++) {
-                    mbar_wait(&empty[stage], phase ^ 1);
-                    uint8_t *st = smem + stage * stage_bytes + 2 * X_BYTES;
-                    mbar_expect_tx(&full[stage], 2 * w_bytes);
-                    tma_load_2d(st, &maps.hi, &full[stage], kc * BK, wrow);
-                    tma_load_2d(st + w_bytes, &maps.lo, &full[stage], kc * BK, wrow);
-                    if (++stage == stages) { stage = 0; phase ^= 1; }
+                    mbar_wait(&empty[op], phase ^ 1);
+                    uint8_t *dst = smem + op * op_bytes + 2 * X_BYTES;
+                    mbar_expect_tx(&full[op], 2 * w_bytes);
+                    tma_load_2d(dst, &maps.hi, &full[op], kc * BK, wrow);
+                    tma_load_2d(dst + w_bytes, &maps.lo, &full[op], kc * BK, wrow);
+                    if (++op == OP_STAGES) { op = 0; phase ^= 1; }
                 }
             }
         }
-    } else if (warp == LOAD_WARPS + 1) {
+    } else if (warp == W_MMA) {
         // ===== MMA issuer =====
         if (lane == 0) {
             const uint32_t idesc = umma_idesc_f16(BM, npb);
-            int stage = 0;
+            int op = 0;
             uint32_t phase = 0, it = 0;
             for (int u = 0; u < units; u++, it++) {
-                const uint32_t d_tmem = tmem_base + (it & 1) * 256;
+                const uint32_t d_tmem = tmem_base + (it & 1) * ACC_COLS;
                 mbar_wait(&tempty[it & 1], ((it >> 1) & 1) ^ 1);
                 tc_fence_after();
                 for (int kc = 0; kc < kc_total; kc++) {
-                    mbar_wait(&full[stage], phase);
+                    mbar_wait(&full[op], phase);
                     tc_fence_after();
-                    const uint32_t sa = smem_u32(smem + stage * stage_bytes);
+                    const uint32_t sa = smem_u32(smem + op * op_bytes);
                     const uint64_t d_xhi = umma_desc_sw128(sa);
                     const uint64_t d_xlo = umma_desc_sw128(sa + X_BYTES);
                     const uint64_t d_whi = umma_desc_sw128(sa + 2 * X_BYTES);
@@ -235,8 +304,8 @@ k_sqnorm_tc(const __grid_constant__ WMaps maps, const float *__restrict__ X, int
                         umma_f16(d_tmem, d_xhi + ko, d_wlo + ko, idesc, 1);
                         umma_f16(d_tmem, d_xhi + ko, d_whi + ko, idesc, 1);
                     }
-                    umma_commit(&empty[stage]);
-                    if (++stage == stages) { stage = 0; phase ^= 1; }
+                    umma_commit(&empty[op]);
+                    if (++op == OP_STAGES) { op = 0; phase ^= 1; }
                 }
                 umma_commit(&tfull[it & 1]);
             }
@@ -249,15 +318,15 @@ k_sqnorm_tc(const __grid_constant__ WMaps maps, const float *__restrict__ X, int
             const int tile = UNIT_TILE(u), pass = u % passes;
             mbar_wait(&tfull[it & 1], (it >> 1) & 1);
             tc_fence_after();
-            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (it & 1) * 256;
-            const float *inv = s_inv + pass * npb;
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (it & 1) * ACC_COLS;
+            const float *inv = w_inv + pass * npb;
             float ssq = 0.f;
             for (int j = 0; j < npb; j += 16) {
                 float v[16];
                 tmem_ld16(taddr + j, v);
 #pragma unroll
                 for (int e = 0; e < 16; e++) {
-                    const float t = v[e] * inv[j + e];
+                    const float t = v[e] * __ldg(inv + j + e);
                     ssq = fmaf(t, t, ssq);
                 }
             }
@@ -274,12 +343,11 @@ k_sqnorm_tc(const __grid_constant__ WMaps maps, const float *__restrict__ X, int
 
     tc_fence_before();
     __syncthreads();
-    if (warp == LOAD_WARPS + 1) {
+    if (warp == W_MMA) {
         tc_fence_after();
         tmem_dealloc<TMEM_COLS>(tmem_base);
     }
 }
-
 #undef UNIT_TILE
 
 }  // namespace
@@ -289,9 +357,9 @@ int dlco_sqnorm_tc(dlco_ctx *ctx, const float *d_X, int64_t ld, const int32_t *d
                    const float *d_W, int64_t ldw, int rank, int D, float *d_out)
 {
     if (n <= 0) return DLCO_OK;
-    DLCO_REQUIRE(rank > 0 && rank <= MAX_RPAD - 64 && D > 0 && (D & 3) == 0 && (ld & 3) == 0 &&
+    DLCO_REQUIRE(rank > 0 && rank <= MAX_RPAD - 128 && D > 0 && (D & 3) == 0 && (ld & 3) == 0 &&
                  ((uintptr_t)d_X & 15) == 0, "sqnorm_tc: unsupported shape / alignment");
-    const int passes = (rank + 255) / 256;
+    const int passes = (rank + NPB_MAX - 1) / NPB_MAX;
     const int npb = ((rank + passes - 1) / passes + 15) / 16 * 16;
     const int r_pad = passes * npb, d_pad = (D + BK - 1) / BK * BK;
     const size_t plane = (size_t)r_pad * d_pad * sizeof(__half);
@@ -304,12 +372,16 @@ int dlco_sqnorm_tc(dlco_ctx *ctx, const float *d_X, int64_t ld, const int32_t *d
     WMaps maps;
     int r = dlco_make_tmap_2d_ex(&maps.hi, hi, 2, (uint64_t)r_pad, (uint64_t)d_pad, (uint32_t)npb, BK);
     if (r == DLCO_OK) r = dlco_make_tmap_2d_ex(&maps.lo, lo, 2, (uint64_t)r_pad, (uint64_t)d_pad, (uint32_t)npb, BK);
+    if (r == DLCO_OK && !d_rows) r = dlco_make_tmap_2d_raw(&maps.x, d_X, (uint64_t)n, (uint64_t)D, (uint64_t)ld, BM, BK);
+    if (r == DLCO_OK && d_rows) maps.x = maps.hi;
     if (r != DLCO_OK) return r;
-    const int stage_bytes = 2 * X_BYTES + 2 * npb * 128;
-    const int tail = 1024 + 256 + MAX_RPAD * (int)sizeof(float);
-    int stages = (227 * 1024 - tail) / stage_bytes;
-    stages = stages > 4 ? 4 : stages;
-    const int smem_bytes = stages * stage_bytes + tail;
+    // shared memory: 2 operand stages + as many raw staging buffers as fit (the staging ring is the
+    // memory-level parallelism of the X stream: 32 KB in flight per buffer and SM)
+    const int op_bytes = 2 * X_BYTES + 2 * npb * 128;
+    const int tail = 1024 + 256;
+    int stages = (227 * 1024 - tail - OP_STAGES * op_bytes) / RAW_BYTES;
+    stages = stages > MAX_STAGING ? MAX_STAGING : stages;
+    const int smem_bytes = OP_STAGES * op_bytes + stages * RAW_BYTES + tail;
     static int attr_bytes = 0;
     if (smem_bytes > attr_bytes) {
         DLCO_CUDA(cudaFuncSetAttribute(k_sqnorm_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
