@@ -27,6 +27,7 @@ sys.path.insert(0, ROOT)
 
 RINGS, NFILT, K = 5120, 40960, 4096
 FLOP_PER_PAIR = 2.0 * 2 * NFILT * K * 8          # dense-equivalent fp32 flops
+NCU_POOL_TRAFFIC_BYTES = 1.20e9 + 39e6           # ncu --set full, k_pool_fulldist, per launch (round 1)
 GTX970_PAIRS_PER_S = 35.5                        # reference's own GPU path, derived from mtimes
 
 
@@ -261,6 +262,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-rows", action="store_true", help="skip the rows b/c/d block (bench_paths quick run)")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -389,7 +391,9 @@ def main():
     roofline = {
         "bound": "tensor", "kernel": "k_pool_fulldist (tcgen05 kind::f16, 3 fp16 passes = fp32-equivalent)",
         "achieved": issued_tflops, "peak": bf16, "unit": "TFLOP/s",
-        "frac": (issued_tflops / bf16) if issued_tflops else None, "traffic": None,
+        "frac": (issued_tflops / bf16) if issued_tflops else None,
+        # dram__bytes_read.sum + dram__bytes_write.sum of one 256-pair launch, profiles/r01_pool_fulldist_ncu_full.csv
+        "traffic": NCU_POOL_TRAFFIC_BYTES if batch == 256 else None,
         "peak_source": peak_src, "launches": pool_n, "avg_launch_ms": avg_ms,
         "achieved_is": "fp16 tensor flops the kernel issues (non-empty tile x K-chunk blocks x 3 passes)",
         "issued_gflop_per_pair": issued_flop_per_pair_slot / 1e9,
@@ -401,6 +405,35 @@ def main():
         "reduce_kernel_ms_total": red_ms, "reduce_launches": red_n,
         "out_stream_gbs": n_pairs * args.steps * (RINGS * 4 + 8192) / (ms * 1e-3) / 1e9,
     }
+    # ---- the other rows of the path (SURVEY 8 b/c/d): pj-learn RDA iters/s, pr-learn steps/s, GEMV / FPR95
+    # evaluation bandwidth -- BASELINE.json's metric names them next to full-dist pairs/s
+    rows = None
+    if world == 1 and not args.no_rows:
+        try:
+            import bench_paths
+            del patches, idx
+            if e2e is not None:
+                del h_out, h_patches, h_idx
+            bank.close()
+            torch.cuda.empty_cache()
+            r = bench_paths.run(ctx, quick=True)
+            rows = {
+                "pj_learn_rda_iters_per_s_1cfg": r["pj_step"]["iters_per_s"],
+                "pj_learn_sweep_cfg_iters_per_s_45cfg": r["pj_sweep_step"]["cfg_iters_per_s"],
+                "pj_syrk_grouped_frac_of_3xtf32_peak": r["pj_grad_grid"]["syrk_frac_of_3xtf32_peak"],
+                "pr_learn_rda_steps_per_s_1cfg": r["pr_rda_1cfg"]["steps_per_s_per_cfg"],
+                "pr_learn_rda_cfg_steps_per_s_256cfg": r["pr_rda_256cfg"]["cfg_steps_per_s"],
+                "pr_stats_gemv_gbs": r["pr_patchdist_gemv"]["achieved_gbs"],
+                "pr_stats_gemv_frac_hbm": r["pr_patchdist_gemv"]["frac_hbm"],
+                "pr_validate_frac_hbm": r["pr_validate"]["frac_hbm"],
+                "pj_stats_dist_rank80_gbs": r["pj_patchdist_rank80"]["achieved_gbs"],
+                "pj_stats_dist_rank80_frac_hbm": r["pj_patchdist_rank80"]["frac_hbm"],
+                "hinge_pairsum_gterms_per_s": r["hinge_pairsum_50k_x_50k"]["gterms_per_s"],
+                "roc_stats_100k_ms": r["roc_stats"]["ms"],
+                "source": "bench_paths.run(quick=True): 500k x 5120 full distances, 500k x 544 unprojected distances, synthetic",
+            }
+        except Exception as ex:   # the headline line must still be printed
+            rows = {"failed": repr(ex)}
     cpu = None
     if world == 1 and not args.no_cpu:
         try:
@@ -419,7 +452,7 @@ def main():
                    "l2": "inputs larger than L2 (1.04 GB of filter planes streamed per 256-pair batch, 10 GB of output per step)",
                    "reference_gtx970_pairs_per_s": GTX970_PAIRS_PER_S},
         "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
-        "cpu_baseline": cpu, "checksum": checksum,
+        "cpu_baseline": cpu, "rows": rows, "checksum": checksum,
     }
     print(json.dumps(line), flush=True)
     if world > 1:

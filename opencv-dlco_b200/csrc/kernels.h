@@ -49,6 +49,12 @@ int dlco_sqnorm_tc(dlco_ctx *ctx, const float *d_X, int64_t ld, const int32_t *d
                    const float *d_W, int64_t ldw, int rank, int D, float *d_out);
 
 // gemm_tc.cu: batched C = A * B^T on tcgen05 (3xTF32) from K-major tf32 hi/lo planes
+// rows a plane needs so that n rows cover whole 128-row A tiles and whole 192-row B tiles
+static inline int dlco_gemm3x_rows_pad(int n)
+{
+    const int a = (n + 127) / 128 * 128, b = (n + 191) / 192 * 192;
+    return a > b ? a : b;
+}
 int dlco_launch_gemm3x_nt(dlco_ctx *ctx, const float *a_hi, const float *a_lo, int a_rows_pad,
                           const float *b_hi, const float *b_lo, int b_rows_pad, int b_batched,
                           int k_pad, int batch, int M, int N, float *d_C, int64_t ldc,

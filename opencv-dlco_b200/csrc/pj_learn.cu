@@ -199,7 +199,7 @@ static int pj_grad_core(dlco_ctx *ctx, const float *d_dists, int64_t ld, int D, 
                         const int *h_rank, const int32_t *d_rank, float *d_dLoss)
 {
     const int nk = 2 * szBatch;
-    const int d_pad = (D + 127) / 128 * 128, k_pad = (nk + 31) / 32 * 32;
+    const int d_pad = dlco_gemm3x_rows_pad(D), k_pad = (nk + 31) / 32 * 32;
     const size_t plane = (size_t)d_pad * k_pad;
     int32_t *rows = (int32_t *)dlco_scratch(ctx, 16, (size_t)nk * sizeof(int32_t));
     float *m = (float *)dlco_scratch(ctx, 17, (size_t)nCfg * nk * 2 * sizeof(float));
@@ -275,7 +275,7 @@ extern "C" int dlco_pj_wsyrk(dlco_ctx *ctx, const float *d_dists, int64_t ld, in
         return DLCO_OK;
     }
     DLCO_REQUIRE(d_rows && d_c, "dlco_pj_wsyrk: NULL rows / weights");
-    const int d_pad = (D + 127) / 128 * 128, k_pad = (nk + 31) / 32 * 32;
+    const int d_pad = dlco_gemm3x_rows_pad(D), k_pad = (nk + 31) / 32 * 32;
     const size_t plane = (size_t)d_pad * k_pad;
     float *planes = (float *)dlco_scratch(ctx, 18, plane * 4 * sizeof(float));
     if (!planes) return DLCO_ENOMEM;

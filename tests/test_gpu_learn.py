@@ -484,3 +484,52 @@ def test_sqnorm_tc_saturates_out_of_contract_inputs(gpu_ctx):
     W = np.eye(64, dtype=np.float32)
     out = gpu_ctx.pj_patchdist(dev_t(gpu_ctx, x), dev_t(gpu_ctx, W), 64)
     assert torch.isfinite(out).all().item()
+
+
+def test_pr_rda_200k_steps_full_width_matches_c_oracle(gpu_ctx, oracle_lib):
+    """pr-learn parity after a fixed 200 000 steps at the real width (5120 rings),
+    (mu, gamma) = (0.035, 0.25), against the C restatement of src/pr-learn.cpp:303-329 (fp32
+    reference order); north_star: learnt w within 1e-4 relative."""
+    import ctypes
+    import dlco_b200
+    n, F, steps = 12000, 5120, 200000
+    rng = np.random.default_rng(77)
+    lab = (np.arange(n) % 2 == 0).astype(np.uint8)
+    dists = rng.random((n, F), dtype=np.float32)
+    dists *= (1.0 + 0.3 * (1 - lab[:, None])).astype(np.float32)
+    L = dlco_b200.learn.PrLearner(gpu_ctx, dev_t(gpu_ctx, dists), lab, 0.035, 0.25)
+    L.run_steps(steps)
+    gpu_ctx.sync()
+    ip, ineg = L.idx_pos.cpu().numpy().astype(np.int32), L.idx_neg.cpu().numpy().astype(np.int32)
+    w, df, st = np.zeros(F, np.float32), np.zeros(F, np.float32), ctypes.c_ulonglong(2215)
+    vp = ctypes.c_void_p
+    oracle_lib.dlco_oracle_pr_rda.restype = None
+    oracle_lib.dlco_oracle_pr_rda.argtypes = [vp, ctypes.c_long, ctypes.c_int, vp, ctypes.c_int, vp, ctypes.c_int,
+                                              ctypes.c_float, ctypes.c_float, ctypes.c_ulonglong,
+                                              ctypes.c_ulonglong, ctypes.POINTER(ctypes.c_ulonglong), vp, vp]
+    oracle_lib.dlco_oracle_pr_rda(dists.ctypes.data, F, F, ip.ctypes.data, L.n_pos_trn, ineg.ctypes.data,
+                                  L.n_neg_trn, 0.035, 0.25, 0, steps, ctypes.byref(st), w.ctypes.data, df.ctypes.data)
+    assert L.rng_state == st.value
+    w_g, df_g = L.w[0].cpu().numpy(), L.dfavg[0].cpu().numpy()
+    assert np.abs(df_g - df).max() <= 1e-4 * np.abs(df).max()
+    assert np.abs(w_g - w).max() <= 1e-4 * max(np.abs(w).max(), 1e-12)
+    assert (w > 0).sum() > 0
+
+
+def test_pj_sweep_batch200_150_steps_matches_oracle(gpu_ctx):
+    """the reference's batch size (200 + 200) over 150 iterations at D = 160: learnt A within 1e-4
+    relative of the fp64 oracle (north_star), same rank, same RNG stream."""
+    import dlco_b200
+    x, lab = synth_uprj(6000, 160, 31)
+    mus, gammas, steps = [0.001, 0.002], [0.1, 0.2], 150
+    S = dlco_b200.learn.PjSweep(gpu_ctx, dev_t(gpu_ctx, x), lab, mus, gammas)
+    for _ in range(steps):
+        S.step()
+    ranks = S.ranks()
+    ip, ineg, npt, nnt = O.split_train_val(lab)
+    for c in range(2):
+        st = O.pj_rda_steps(x, ip, ineg, npt, nnt, mus[c], gammas[c], steps, dt=np.float64)
+        A_g = S.A[c].cpu().numpy()
+        assert np.abs(A_g - st["A"]).max() <= 1e-4 * np.abs(st["A"]).max()
+        assert abs(int(ranks[c]) - st["W"].shape[0]) <= 1        # an eigenvalue within rounding of 0 may flip
+    assert int(S.rng_state.cpu().numpy().view(np.uint64)[0]) == st["rng"].state
