@@ -216,7 +216,44 @@ def run(ctx, n_train=500000, n_test=100000, quick=False, D=544, n_pj_cfg=45, n_p
                                            "tflops": 2.0 * n_train * D * r / (mean_ms * 1e-3) / 1e12}
     mean_ms, best_ms = timeit(torch, lambda: L.validate(), rep=5)
     res["pj_validate"] = {"ms": mean_ms, "n_pos": L.pos_val.numel(), "n_neg": L.neg_val.numel()}
+    del ud, L
+    torch.cuda.empty_cache()
+
+    # ---- (b1) comp-uprjdists builder: get_desc x2 + pooling with the nSel selected filters -------
+    res["uprjdist_build"] = run_uprj_builder(ctx, n_train if not quick else min(n_train, 200000), D // 8, hbm)
     return res
+
+
+def run_uprj_builder(ctx, n_pairs, n_sel, hbm):
+    """src/comp-uprjdists.cpp:298-335 over n_pairs synthetic pairs with n_sel filters picked from the
+    gen-poolregion-shaped bank.  Algorithmic bytes per pair: 8192 in + 32 * n_sel out."""
+    import torch
+    import bench as B
+    dev = ctx.device
+    full = B.synth_bank(torch, dev)
+    rows = (torch.arange(n_sel, device=dev) * 601 + 8 * 2000) % full.shape[0]
+    sel = full[rows].contiguous()
+    del full
+    torch.cuda.empty_cache()
+    bank = ctx.bank(sel)
+    per_point = 3
+    n_points = max(64, int(n_pairs * 0.9) // per_point)
+    patches = B.synth_patches(torch, dev, n_points, per_point)
+    idx = B.synth_pairs(torch, dev, n_points, per_point, n_pairs)
+    torch.cuda.synchronize()
+    ctx.profile(True)
+    mean_ms, best_ms = timeit(torch, lambda: ctx.uprjdist_build(bank, patches, idx), warm=1, rep=3)
+    desc_ms, desc_n = ctx.profile_read(0)
+    ctx.profile(False)
+    by = n_pairs * (8192 + 32 * n_sel)
+    out = {"pairs": n_pairs, "n_sel": n_sel, "ms": mean_ms, "best_ms": best_ms,
+           "pairs_per_s": n_pairs / (mean_ms * 1e-3), "desc_per_s": 2 * n_pairs / (mean_ms * 1e-3),
+           "algorithmic_bytes_per_pair": 8192 + 32 * n_sel,
+           "achieved_gbs": by / (mean_ms * 1e-3) / 1e9, "frac_hbm": by / (mean_ms * 1e-3) / 1e9 / hbm,
+           "desc_kernel_ms_per_pass": desc_ms / 4.0 if desc_n else None,
+           "pool_gflops": 2.0 * 2 * n_sel * 4096 * 8 * n_pairs / (mean_ms * 1e-3) / 1e9}
+    bank.close()
+    return out
 
 
 def cpu_leg(D=544, quick=False):
@@ -310,6 +347,7 @@ def main():
     ap.add_argument("--quick", action="store_true")
     ap.add_argument("--cpu", action="store_true", help="also time the oracle's CPU port of each row")
     ap.add_argument("--cpu-only", action="store_true")
+    ap.add_argument("--only-uprj", action="store_true", help="only the comp-uprjdists builder leg (row b1)")
     args = ap.parse_args()
     if args.cpu_only:
         print(json.dumps({"cpu_baseline": cpu_leg(args.dim, args.quick)}))
@@ -317,6 +355,9 @@ def main():
     import torch
     import dlco_b200
     ctx = dlco_b200.Context(0)
+    if args.only_uprj:
+        print(json.dumps({"uprjdist_build": run_uprj_builder(ctx, args.n_train, args.dim // 8, _peaks()[0])}))
+        return
     res = run(ctx, args.n_train, args.n_test, args.quick, D=args.dim)
     if args.cpu:
         res["cpu_baseline"] = cpu_leg(args.dim, args.quick)

@@ -31,76 +31,102 @@ struct DescParams {
 
 __device__ __forceinline__ int clampi(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
 
-// exact k-th smallest (0-based rank) of the 4096 non-negative floats in vals[] (as uint bits)
-__device__ uint32_t radix_select(const uint32_t *vals, int rank, uint32_t *hist, uint32_t *bcast)
+// ---- block-wide reductions over DESC_THREADS = 256 threads (8 warps): hardware redux inside a warp,
+// one 8-word shared buffer across warps.  Callers alternate between two buffers so that one
+// __syncthreads per reduction is enough (a writer of buffer A at step n+2 has passed the barrier of
+// step n+1, which every reader of A at step n reached before).
+__device__ __forceinline__ uint32_t block_sum(uint32_t c, uint32_t *buf)
 {
-    uint32_t prefix = 0, mask = 0;
-    int r = rank;
-    for (int shift = 24; shift >= 0; shift -= 8) {
-        for (int i = threadIdx.x; i < 256; i += DESC_THREADS) hist[i] = 0;
-        __syncthreads();
-        for (int i = threadIdx.x; i < NPIX; i += DESC_THREADS) {
-            uint32_t v = vals[i];
-            if ((v & mask) == prefix) atomicAdd(&hist[(v >> shift) & 255u], 1u);
-        }
-        __syncthreads();
-        if (threadIdx.x < 32) {
-            int lane = threadIdx.x;
-            uint32_t c[8], s = 0;
+    c = __reduce_add_sync(0xffffffffu, c);
+    if ((threadIdx.x & 31) == 0) buf[threadIdx.x >> 5] = c;
+    __syncthreads();
+    const uint4 a = reinterpret_cast<const uint4 *>(buf)[0], b = reinterpret_cast<const uint4 *>(buf)[1];
+    return a.x + a.y + a.z + a.w + b.x + b.y + b.z + b.w;
+}
+__device__ __forceinline__ uint32_t block_min(uint32_t c, uint32_t *buf)
+{
+    c = __reduce_min_sync(0xffffffffu, c);
+    if ((threadIdx.x & 31) == 0) buf[threadIdx.x >> 5] = c;
+    __syncthreads();
+    const uint4 a = reinterpret_cast<const uint4 *>(buf)[0], b = reinterpret_cast<const uint4 *>(buf)[1];
+    return min(min(min(a.x, a.y), min(a.z, a.w)), min(min(b.x, b.y), min(b.z, b.w)));
+}
+__device__ __forceinline__ uint32_t block_max(uint32_t c, uint32_t *buf)
+{
+    c = __reduce_max_sync(0xffffffffu, c);
+    if ((threadIdx.x & 31) == 0) buf[threadIdx.x >> 5] = c;
+    __syncthreads();
+    const uint4 a = reinterpret_cast<const uint4 *>(buf)[0], b = reinterpret_cast<const uint4 *>(buf)[1];
+    return max(max(max(a.x, a.y), max(a.z, a.w)), max(max(b.x, b.y), max(b.z, b.w)));
+}
+
+// exact k-th smallest (0-based rank) of the 4096 non-negative floats held 16 per thread (as uint
+// bits; non-negative floats order like their bit patterns): the largest t with #{v < t} <= rank,
+// built bit by bit from the top -- 31 block-wide counts, no shared-memory histogram (the top byte
+// of a patch's gradient magnitudes is almost constant: a 256-bin histogram pass serialises on one
+// or two bins).
+__device__ uint32_t block_select(const uint32_t (&v)[NPIX / DESC_THREADS], uint32_t rank, uint32_t (*red)[8])
+{
+    uint32_t ans = 0;
+    for (int bit = 30; bit >= 0; bit--) {
+        const uint32_t t = ans | (1u << bit);
+        uint32_t c = 0;
 #pragma unroll
-            for (int j = 0; j < 8; j++) { c[j] = hist[lane * 8 + j]; s += c[j]; }
-            uint32_t incl = s;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
-                if (lane >= o) incl += t;
-            }
-            uint32_t excl = incl - s;
-            if ((uint32_t)r >= excl && (uint32_t)r < incl) {
-                uint32_t acc = excl;
-#pragma unroll
-                for (int j = 0; j < 8; j++) {
-                    if ((uint32_t)r < acc + c[j]) {
-                        bcast[0] = (uint32_t)(lane * 8 + j);
-                        bcast[1] = (uint32_t)r - acc;
-                        break;
-                    }
-                    acc += c[j];
-                }
-            }
-        }
-        __syncthreads();
-        prefix |= bcast[0] << shift;
-        mask |= 255u << shift;
-        r = (int)bcast[1];
-        __syncthreads();
+        for (int i = 0; i < NPIX / DESC_THREADS; i++)      // compare + predicated add: 2 instructions per value
+            asm("{ .reg .pred p; setp.lt.u32 p, %1, %2; @p add.u32 %0, %0, 1; }" : "+r"(c) : "r"(v[i]), "r"(t));
+        if (block_sum(c, red[bit & 1]) <= rank) ans = t;
     }
-    return prefix;
+    return ans;
+}
+
+// separable blur, one line of 64 per thread quarter: 16 consecutive outputs from a sliding window
+// of 16 + KS - 1 inputs held in registers; per output the taps are accumulated in the order
+// j = 0..KS-1 (as the generic loop and the oracle do).  ALONG_ROWS: line = image row, else column.
+template <int KS, bool ALONG_ROWS>
+__device__ __forceinline__ void blur_lines(const float *__restrict__ src, float *__restrict__ dst, const float *taps)
+{
+    constexpr int H = KS / 2, RUN = 16;
+    const int line = threadIdx.x & 63, o0 = (threadIdx.x >> 6) * RUN;
+    float x[RUN + KS - 1];
+#pragma unroll
+    for (int j = 0; j < RUN + KS - 1; j++) {
+        const int o = clampi(o0 + j - H, 0, PS - 1);
+        x[j] = ALONG_ROWS ? src[line * SROW + o] : src[o * SROW + line];
+    }
+#pragma unroll
+    for (int e = 0; e < RUN; e++) {
+        float acc = 0.f;
+#pragma unroll
+        for (int j = 0; j < KS; j++) acc += taps[j] * x[e + j];
+        if (ALONG_ROWS) dst[line * SROW + o0 + e] = acc;
+        else dst[(o0 + e) * SROW + line] = acc;
+    }
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(DESC_THREADS)
+__global__ void __launch_bounds__(DESC_THREADS, 4)
 k_desc(const uint8_t *__restrict__ patches, const int32_t *__restrict__ ids, int id_stride,
        int n_slots, DescParams prm, float *__restrict__ out0, float *__restrict__ out1,
        float *__restrict__ inv_scale)
 {
-    __shared__ float s_a[PS * SROW];
-    __shared__ float s_b[PS * SROW];
-    uint32_t *s_mag = reinterpret_cast<uint32_t *>(s_b);   // s_b is dead after the column pass
-    __shared__ uint32_t s_hist[256];
-    __shared__ uint32_t s_bc[4];
+    __shared__ __align__(16) float s_a[PS * SROW];
+    __shared__ __align__(16) float s_b[PS * SROW];
+    __shared__ __align__(16) uint32_t s_red[2][8];
+    __shared__ __align__(16) uint8_t s_bin[NPIX];
 
     const int slot = blockIdx.x;
     const int tid = threadIdx.x;
     // slots beyond n_slots are padding rows of the GEMM operand: write zeros
     const bool valid = slot < n_slots;
     if (!valid) {
+        const uint4 z = make_uint4(0u, 0u, 0u, 0u);
         if (MODE == DESC_OUT_ROWS) {
-            for (int i = tid; i < NPIX * 8; i += DESC_THREADS) out0[(size_t)slot * 8 * NPIX + i] = 0.f;
+            uint4 *o = reinterpret_cast<uint4 *>(out0 + (size_t)slot * 8 * NPIX);
+            for (int i = tid; i < NPIX * 2; i += DESC_THREADS) o[i] = z;
         } else if (MODE == DESC_OUT_SPLIT) {
-            uint32_t *h = reinterpret_cast<uint32_t *>(reinterpret_cast<__half *>(out0) + (size_t)slot * 8 * NPIX);
-            uint32_t *l = reinterpret_cast<uint32_t *>(reinterpret_cast<__half *>(out1) + (size_t)slot * 8 * NPIX);
-            for (int i = tid; i < NPIX * 4; i += DESC_THREADS) { h[i] = 0u; l[i] = 0u; }
+            uint4 *h = reinterpret_cast<uint4 *>(reinterpret_cast<__half *>(out0) + (size_t)slot * 8 * NPIX);
+            uint4 *l = reinterpret_cast<uint4 *>(reinterpret_cast<__half *>(out1) + (size_t)slot * 8 * NPIX);
+            for (int i = tid; i < NPIX; i += DESC_THREADS) { h[i] = z; l[i] = z; }
             if (tid == 0) inv_scale[slot] = 1.0f;
         }
         return;
@@ -121,27 +147,34 @@ k_desc(const uint8_t *__restrict__ patches, const int32_t *__restrict__ ids, int
         for (int j = 0; j < 16; j++) s_a[r * SROW + c + j] = (float)((w[j >> 2] >> (8 * (j & 3))) & 255u);
     }
     __syncthreads();
-    const int half = prm.ksize >> 1;
-    // row pass: s_b[r][c] = sum_j k[j] * s_a[r][clamp(c + j - half)]
-    for (int i = tid; i < NPIX; i += DESC_THREADS) {
-        int r = i >> 6, c = i & 63;
-        float acc = 0.f;
-        for (int j = 0; j < prm.ksize; j++) acc += prm.taps[j] * s_a[r * SROW + clampi(c + j - half, 0, PS - 1)];
-        s_b[r * SROW + c] = acc;
-    }
-    __syncthreads();
-    // column pass -> s_a
-    for (int i = tid; i < NPIX; i += DESC_THREADS) {
-        int r = i >> 6, c = i & 63;
-        float acc = 0.f;
-        for (int j = 0; j < prm.ksize; j++) acc += prm.taps[j] * s_b[clampi(r + j - half, 0, PS - 1) * SROW + c];
-        s_a[r * SROW + c] = acc;
+    if (prm.ksize == 13) {          // sigma = 1.4, the reference's only setting (src/vgg-desc.cpp:46)
+        blur_lines<13, true>(s_a, s_b, prm.taps);
+        __syncthreads();
+        blur_lines<13, false>(s_b, s_a, prm.taps);
+    } else {
+        const int half = prm.ksize >> 1;
+        // row pass: s_b[r][c] = sum_j k[j] * s_a[r][clamp(c + j - half)]
+        for (int i = tid; i < NPIX; i += DESC_THREADS) {
+            int r = i >> 6, c = i & 63;
+            float acc = 0.f;
+            for (int j = 0; j < prm.ksize; j++) acc += prm.taps[j] * s_a[r * SROW + clampi(c + j - half, 0, PS - 1)];
+            s_b[r * SROW + c] = acc;
+        }
+        __syncthreads();
+        // column pass -> s_a
+        for (int i = tid; i < NPIX; i += DESC_THREADS) {
+            int r = i >> 6, c = i & 63;
+            float acc = 0.f;
+            for (int j = 0; j < prm.ksize; j++) acc += prm.taps[j] * s_b[clampi(r + j - half, 0, PS - 1) * SROW + c];
+            s_a[r * SROW + c] = acc;
+        }
     }
     __syncthreads();
 
     // per-pixel gradient; thread handles p = tid + 256*i, p = c*64 + r (r fastest)
     float mag[NPIX / DESC_THREADS], off1[NPIX / DESC_THREADS];
-    int bin1[NPIX / DESC_THREADS];
+    uint32_t magu[NPIX / DESC_THREADS];
+    uint32_t binp[2] = {0u, 0u};           // bin1 of the 16 pixels, 4 bits each (keeps 14 registers free)
     const int nb = prm.nbins;
 #pragma unroll
     for (int i = 0; i < NPIX / DESC_THREADS; i++) {
@@ -157,11 +190,10 @@ k_desc(const uint8_t *__restrict__ patches, const int32_t *__restrict__ ids, int
         int b1 = (int)ceilf(ratio - 1.0f);
         if (b1 < 0) b1 = nb - 1;
         if (b1 > nb - 1) b1 = nb - 1;
-        bin1[i] = b1;
+        binp[i >> 3] |= (uint32_t)b1 << (4 * (i & 7));
         mag[i] = m;
-        s_mag[p] = __float_as_uint(m);
+        magu[i] = __float_as_uint(m);
     }
-    __syncthreads();
 
     float scale = 1.0f;
     if (prm.bnorm) {
@@ -173,73 +205,120 @@ k_desc(const uint8_t *__restrict__ patches, const int32_t *__restrict__ ids, int
         if (k <= 1) k = 1;
         float gamma = aleph - (float)k;
         gamma = fminf(fmaxf(gamma, 0.f), 1.f);
-        uint32_t v1 = radix_select(s_mag, k - 1, s_hist, s_bc);
+        const uint32_t v1 = block_select(magu, (uint32_t)(k - 1), s_red);      // S[k-1]
         // S[k]: v1 again if duplicated past rank k, else the smallest value above v1
-        if (tid == 0) { s_bc[2] = 0u; s_bc[3] = 0x7f800000u; }
-        __syncthreads();
         uint32_t cnt = 0, mn = 0x7f800000u;
-        for (int i = tid; i < NPIX; i += DESC_THREADS) {
-            uint32_t v = s_mag[i];
-            cnt += (v <= v1);
-            if (v > v1) mn = min(mn, v);
+#pragma unroll
+        for (int i = 0; i < NPIX / DESC_THREADS; i++) {
+            cnt += (magu[i] <= v1);
+            if (magu[i] > v1) mn = min(mn, magu[i]);
         }
-        atomicAdd(&s_bc[2], cnt);
-        atomicMin(&s_bc[3], mn);
-        __syncthreads();
-        uint32_t v2 = (s_bc[2] >= (uint32_t)(k + 1)) ? v1 : s_bc[3];
+        cnt = block_sum(cnt, s_red[1]);        // block_select ended on s_red[0]
+        mn = block_min(mn, s_red[0]);
+        const uint32_t v2 = (cnt >= (uint32_t)(k + 1)) ? v1 : mn;
         float T = (1.0f - gamma) * __uint_as_float(v1) + gamma * __uint_as_float(v2);
         if (T != 0.0f) scale = (float)(1.0 / (double)(T / (float)nb));   // Mat /= s
     }
 
-    float pscale = 1.0f;       // fp16 planes: power-of-two scale of this patch
-    if (MODE == DESC_OUT_SPLIT) {
-        __syncthreads();
-        if (tid == 0) s_bc[0] = 0u;
-        __syncthreads();
-        float mx = 0.f;
+    if (MODE == DESC_OUT_PT) {
 #pragma unroll
-        for (int i = 0; i < NPIX / DESC_THREADS; i++) mx = fmaxf(mx, prm.bnorm ? mag[i] * scale : mag[i]);
+        for (int i = 0; i < NPIX / DESC_THREADS; i++) {
+            int p = tid + DESC_THREADS * i;
+            float g = prm.bnorm ? mag[i] * scale : mag[i];
+            int b1 = (int)((binp[i >> 3] >> (4 * (i & 7))) & 15u);
+            int b2 = (b1 + 1 > nb - 1) ? 0 : b1 + 1;
+            float v1 = (1.0f - off1[i]) * g;
+            float v2 = off1[i] * g;
+            float v[8];
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-        if ((tid & 31) == 0) atomicMax(&s_bc[0], __float_as_uint(mx));     // non-negative floats order as uints
-        __syncthreads();
-        mx = __uint_as_float(s_bc[0]);
-        if (mx > 0.f && isfinite(mx)) pscale = exp2f((float)(14 - ilogbf(mx)));
-        if (tid == 0) inv_scale[slot] = 1.0f / pscale;
-    }
-
+            for (int b = 0; b < 8; b++) v[b] = 0.f;
 #pragma unroll
-    for (int i = 0; i < NPIX / DESC_THREADS; i++) {
-        int p = tid + DESC_THREADS * i;
-        float g = prm.bnorm ? mag[i] * scale : mag[i];
-        int b1 = bin1[i];
-        int b2 = (b1 + 1 > nb - 1) ? 0 : b1 + 1;
-        float v1 = (1.0f - off1[i]) * g;
-        float v2 = off1[i] * g;
-        float v[8];
-#pragma unroll
-        for (int b = 0; b < 8; b++) v[b] = 0.f;
-#pragma unroll
-        for (int b = 0; b < 8; b++) {
-            if (b == b1) v[b] = v1;
-            if (b == b2) v[b] = v2;
-        }
-        if (MODE == DESC_OUT_PT) {
+            for (int b = 0; b < 8; b++) {
+                if (b == b1) v[b] = v1;
+                if (b == b2) v[b] = v2;
+            }
             float4 *dst = reinterpret_cast<float4 *>(out0 + ((size_t)slot * NPIX + p) * 8);
             dst[0] = make_float4(v[0], v[1], v[2], v[3]);
             dst[1] = make_float4(v[4], v[5], v[6], v[7]);
-        } else {
+        }
+        return;
+    }
+
+    // K-major row layouts: stage (v1, v2, bin1) per pixel in shared memory (s_a / s_b are free once
+    // every thread has its gradients), then each thread assembles 8 consecutive pixels of a bin row
+    // and writes 16 bytes per plane.
+    float pscale = 1.0f;       // fp16 planes: power-of-two scale of this patch
+    float mx = 0.f;
+    __syncthreads();           // all gradient reads of s_a are done (needed when bnorm = 0)
+#pragma unroll
+    for (int i = 0; i < NPIX / DESC_THREADS; i++) {
+        const int p = tid + DESC_THREADS * i;
+        const float g = prm.bnorm ? mag[i] * scale : mag[i];
+        mx = fmaxf(mx, g);
+        s_a[p] = (1.0f - off1[i]) * g;
+        s_b[p] = off1[i] * g;
+        s_bin[p] = (uint8_t)((binp[i >> 3] >> (4 * (i & 7))) & 15u);
+    }
+    if (MODE == DESC_OUT_SPLIT) {
+        mx = __uint_as_float(block_max(__float_as_uint(mx), s_red[1]));     // non-negative floats order as uints
+        if (mx > 0.f && isfinite(mx)) pscale = exp2f((float)(14 - ilogbf(mx)));
+        if (tid == 0) inv_scale[slot] = 1.0f / pscale;
+    } else {
+        __syncthreads();
+    }
+#pragma unroll
+    for (int k = 0; k < NPIX / 8 / DESC_THREADS; k++) {
+        const int p0 = 8 * (tid + DESC_THREADS * k);
+        float a1[8], a2[8];
+        *reinterpret_cast<float4 *>(a1) = *reinterpret_cast<const float4 *>(s_a + p0);
+        *reinterpret_cast<float4 *>(a1 + 4) = *reinterpret_cast<const float4 *>(s_a + p0 + 4);
+        *reinterpret_cast<float4 *>(a2) = *reinterpret_cast<const float4 *>(s_b + p0);
+        *reinterpret_cast<float4 *>(a2 + 4) = *reinterpret_cast<const float4 *>(s_b + p0 + 4);
+        const uint2 bb = *reinterpret_cast<const uint2 *>(s_bin + p0);
+        int b1[8], b2[8];
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            b1[j] = (int)(((j < 4 ? bb.x : bb.y) >> (8 * (j & 3))) & 255u);
+            b2[j] = (b1[j] + 1 > nb - 1) ? 0 : b1[j] + 1;
+        }
+        if (MODE == DESC_OUT_ROWS) {
 #pragma unroll
             for (int b = 0; b < 8; b++) {
-                size_t o = ((size_t)slot * 8 + b) * NPIX + p;
-                if (MODE == DESC_OUT_ROWS) {
-                    out0[o] = v[b];
-                } else {
-                    const float sv = v[b] * pscale;
-                    const __half hi = __float2half_rn(sv);
-                    reinterpret_cast<__half *>(out0)[o] = hi;
-                    reinterpret_cast<__half *>(out1)[o] = __float2half_rn(sv - __half2float(hi));
+                float v[8];
+#pragma unroll
+                for (int j = 0; j < 8; j++) {
+                    v[j] = (b == b1[j]) ? a1[j] : 0.f;
+                    if (b == b2[j]) v[j] = a2[j];
                 }
+                float4 *dst = reinterpret_cast<float4 *>(out0 + ((size_t)slot * 8 + b) * NPIX + p0);
+                dst[0] = make_float4(v[0], v[1], v[2], v[3]);
+                dst[1] = make_float4(v[4], v[5], v[6], v[7]);
+            }
+        } else {
+            uint32_t h1[8], l1[8], h2[8], l2[8];       // fp16 bit patterns
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                const float s1 = a1[j] * pscale, s2 = a2[j] * pscale;
+                const __half x1 = __float2half_rn(s1), x2 = __float2half_rn(s2);
+                h1[j] = __half_as_ushort(x1);
+                h2[j] = __half_as_ushort(x2);
+                l1[j] = __half_as_ushort(__float2half_rn(s1 - __half2float(x1)));
+                l2[j] = __half_as_ushort(__float2half_rn(s2 - __half2float(x2)));
+            }
+#pragma unroll
+            for (int b = 0; b < 8; b++) {
+                uint32_t hv[8], lv[8];
+#pragma unroll
+                for (int j = 0; j < 8; j++) {
+                    hv[j] = (b == b1[j]) ? h1[j] : 0u;
+                    lv[j] = (b == b1[j]) ? l1[j] : 0u;
+                    if (b == b2[j]) { hv[j] = h2[j]; lv[j] = l2[j]; }
+                }
+                const size_t o = ((size_t)slot * 8 + b) * NPIX + p0;
+                *reinterpret_cast<uint4 *>(reinterpret_cast<__half *>(out0) + o) =
+                    make_uint4(hv[0] | (hv[1] << 16), hv[2] | (hv[3] << 16), hv[4] | (hv[5] << 16), hv[6] | (hv[7] << 16));
+                *reinterpret_cast<uint4 *>(reinterpret_cast<__half *>(out1) + o) =
+                    make_uint4(lv[0] | (lv[1] << 16), lv[2] | (lv[3] << 16), lv[4] | (lv[5] << 16), lv[6] | (lv[7] << 16));
             }
         }
     }
