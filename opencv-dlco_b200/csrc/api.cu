@@ -55,6 +55,15 @@ void *dlco_pinned(dlco_ctx *ctx, int slot, size_t bytes)
     return p;
 }
 
+int dlco_side_stream(dlco_ctx *ctx)
+{
+    if (ctx->side_ready) return DLCO_OK;
+    DLCO_CUDA(cudaStreamCreateWithFlags(&ctx->side_stream, cudaStreamNonBlocking));
+    for (int i = 0; i < 6; i++) DLCO_CUDA(cudaEventCreateWithFlags(&ctx->side_ev[i], cudaEventDisableTiming));
+    ctx->side_ready = 1;
+    return DLCO_OK;
+}
+
 extern "C" int dlco_init(int device, dlco_ctx **out)
 {
     DLCO_REQUIRE(out != nullptr, "dlco_init: ctx is NULL");
@@ -92,6 +101,11 @@ extern "C" int dlco_shutdown(dlco_ctx *ctx)
     if (!ctx) return DLCO_OK;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
+    if (ctx->side_ready) {
+        cudaStreamSynchronize(ctx->side_stream);
+        for (int i = 0; i < 6; i++) cudaEventDestroy(ctx->side_ev[i]);
+        cudaStreamDestroy(ctx->side_stream);
+    }
     for (int i = 0; i < 32; i++)
         if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
     for (int i = 0; i < 8; i++)

@@ -32,6 +32,10 @@ struct dlco_ctx {
     int prof_n, prof_cap;
     double prof_ms[16];
     int64_t prof_cnt[16];
+    // side stream + events for two-stage pipelines inside one entry point (lazy, dlco_side_stream)
+    cudaStream_t side_stream;
+    cudaEvent_t side_ev[6];
+    int side_ready;
     void *cusolver;       // cusolverDnHandle_t (lazy)
     void *cusolver_lib;   // dlopen handle
 };
@@ -53,6 +57,7 @@ struct dlco_bank {
 void dlco_set_error(const char *fmt, ...);
 void *dlco_scratch(dlco_ctx *ctx, int slot, size_t bytes);
 void *dlco_pinned(dlco_ctx *ctx, int slot, size_t bytes);
+int dlco_side_stream(dlco_ctx *ctx);
 void dlco_prof_begin(dlco_ctx *ctx, int which);
 void dlco_prof_end(dlco_ctx *ctx);
 

@@ -168,13 +168,56 @@ extern "C" int dlco_uprjdist_build(dlco_ctx *ctx, const dlco_bank *bank, const u
     const int nb = batch_pairs();
     for (int64_t p = lo; p < hi; p += nb) {
         int n = (int)((hi - p) < nb ? (hi - p) : nb);
-        float *rows = (float *)dlco_scratch(ctx, 0, (size_t)n * 16 * 4096 * sizeof(float));
-        if (!rows) return DLCO_ENOMEM;
-        r = dlco_launch_desc(ctx, DESC_OUT_ROWS, d_patches, d_indices + p * 4, 4, 2 * n, 2 * n, nAngleBins,
-                             sigma, bNorm, rows, nullptr, nullptr);
+        if (use_simt() || bank->nRowsPad > 1536) {          // cross-check path (and very large banks): fp32 rows + SIMT pooling
+            float *rows = (float *)dlco_scratch(ctx, 0, (size_t)n * 16 * 4096 * sizeof(float));
+            if (!rows) return DLCO_ENOMEM;
+            r = dlco_launch_desc(ctx, DESC_OUT_ROWS, d_patches, d_indices + p * 4, 4, 2 * n, 2 * n, nAngleBins,
+                                 sigma, bNorm, rows, nullptr, nullptr);
+            if (r != DLCO_OK) return r;
+            r = dlco_launch_pool_simt(ctx, 1, bank->d_f32, bank->nF, rows, n, d_out + (p - lo) * ld_out, ld_out);
+            if (r != DLCO_OK) return r;
+            continue;
+        }
+        // tensor path: the same fp16 hi/lo planes and GEMM as comp-fulldists; the selected bank is one
+        // or two 128-row tiles, so the K range is split across CTAs to fill the GPU from a batch whose
+        // planes stay in L2.  Two-stage pipeline: get_desc of batch i+1 (ALU-bound, side stream) runs
+        // under the pooling GEMM + finish of batch i (main stream); planes are double-buffered.
+        const int64_t bi = (p - lo) / nb;
+        const int s2 = (int)(bi & 1);
+        const bool piped = !ctx->profile_on;            // per-kernel event timing wants one stream
+        if (piped && (r = dlco_side_stream(ctx)) != DLCO_OK) return r;
+        const int npad = (n + 15) / 16 * 16;
+        const int ksplit = dlco_pool_tc_ksplit(ctx, bank, nb);    // of the full batch: a ragged tail sums in the same order
+        const size_t plane = (size_t)((nb + 15) / 16 * 16) * 16 * 4096 * 2;
+        uint8_t *bhi = (uint8_t *)dlco_scratch(ctx, s2 ? 25 : 0, plane);
+        uint8_t *blo = (uint8_t *)dlco_scratch(ctx, s2 ? 26 : 1, plane);
+        float *binv = (float *)dlco_scratch(ctx, s2 ? 27 : 2, (size_t)(nb + 16) * 2 * sizeof(float));
+        float *P = (float *)dlco_scratch(ctx, 3, dlco_pool_tc_partial_bytes(bank, (nb + 15) / 16 * 16, ksplit));
+        if (!bhi || !blo || !binv || !P) return DLCO_ENOMEM;
+        cudaStream_t main_stream = ctx->stream;
+        if (piped) {
+            // side stream: after everything queued on the main stream at entry (first batch) and after the
+            // pool of batch i-2 released this plane buffer
+            if (bi == 0) {
+                DLCO_CUDA(cudaEventRecord(ctx->side_ev[4], main_stream));
+                DLCO_CUDA(cudaStreamWaitEvent(ctx->side_stream, ctx->side_ev[4], 0));
+            }
+            if (bi >= 2) DLCO_CUDA(cudaStreamWaitEvent(ctx->side_stream, ctx->side_ev[2 + s2], 0));
+            ctx->stream = ctx->side_stream;
+        }
+        dlco_prof_begin(ctx, 0);
+        r = dlco_launch_desc(ctx, DESC_OUT_SPLIT, d_patches, d_indices + p * 4, 4, 2 * n, 2 * npad, nAngleBins,
+                             sigma, bNorm, (float *)bhi, (float *)blo, binv);
+        dlco_prof_end(ctx);
+        ctx->stream = main_stream;
         if (r != DLCO_OK) return r;
-        r = dlco_launch_pool_simt(ctx, 1, bank->d_f32, bank->nF, rows, n, d_out + (p - lo) * ld_out, ld_out);
+        if (piped) {
+            DLCO_CUDA(cudaEventRecord(ctx->side_ev[s2], ctx->side_stream));
+            DLCO_CUDA(cudaStreamWaitEvent(main_stream, ctx->side_ev[s2], 0));
+        }
+        r = dlco_launch_pool_tc_uprj(ctx, bank, bhi, blo, binv, n, npad, ksplit, P, d_out + (p - lo) * ld_out, ld_out);
         if (r != DLCO_OK) return r;
+        if (piped) DLCO_CUDA(cudaEventRecord(ctx->side_ev[2 + s2], main_stream));
     }
     return DLCO_OK;
 }

@@ -32,6 +32,14 @@ int dlco_launch_pool_tc(dlco_ctx *ctx, const dlco_bank *bank, const void *d_bhi,
                         const float *d_binv, int n_pairs, int n_pairs_padded, float *d_S,
                         float *d_out, int64_t ld_out);
 
+// the same GEMM for comp-uprjdists (small banks): K split over `ksplit` CTAs per tile, raw partials
+// in d_P (dlco_pool_tc_partial_bytes), then out[pair][8 f + b] = min(Desc1.,1) - min(Desc2.,1)
+int dlco_pool_tc_ksplit(const dlco_ctx *ctx, const dlco_bank *bank, int n_pairs_padded);
+size_t dlco_pool_tc_partial_bytes(const dlco_bank *bank, int n_pairs_padded, int ksplit);
+int dlco_launch_pool_tc_uprj(dlco_ctx *ctx, const dlco_bank *bank, const void *d_bhi, const void *d_blo,
+                             const float *d_binv, int n_pairs, int n_pairs_padded, int ksplit, float *d_P,
+                             float *d_out, int64_t ld_out);
+
 // hinge.cu
 int dlco_hinge_pairsum_dev(dlco_ctx *ctx, const float *d_pos, int64_t n1, const float *d_neg,
                            int64_t n2, float margin, double *d_sum);

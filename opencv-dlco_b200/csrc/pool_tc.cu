@@ -53,10 +53,31 @@ struct __align__(64) TMaps {
     CUtensorMap a_hi, a_lo, b_hi, b_lo;
 };
 
+// the K chunks of M tile m that K-split `ks` of `ksplit` owns: every ksplit-th set bit of kmask[m]
+// (ksplit = 1: the whole mask).  All three roles derive their loop from this, so they agree.
+__device__ __forceinline__ uint64_t split_mask(uint64_t mask, int ks, int ksplit)
+{
+    if (ksplit == 1) return mask;
+    uint64_t out = 0;
+    int i = 0;
+    while (mask) {
+        const uint64_t low = mask & (~mask + 1);
+        if (i % ksplit == ks) out |= low;
+        mask ^= low;
+        i++;
+    }
+    return out;
+}
+
+// MODE 0 (comp-fulldists): S[pair][row] = sum over bins of the squared clamped difference.
+// MODE 1 (comp-uprjdists, small banks): the K range is split over `ksplit` CTAs per tile so that a
+// 256-pair batch (whose B planes stay in L2) still fills the GPU; each writes its raw fp32 partial
+// P[(tile * ksplit + ks)][col 256][row 128] and k_uprj_finish sums, scales, clamps and subtracts.
+template <int MODE>
 __global__ void __launch_bounds__(NTHREADS, 1)
 k_pool_fulldist(const __grid_constant__ TMaps maps, const uint64_t *__restrict__ kmask,
                 const float *__restrict__ a_inv, const float *__restrict__ b_inv, int m_tiles,
-                int n_tiles, int n_pairs, int n_rows, float *__restrict__ S, int64_t ld_s)
+                int n_tiles, int ksplit, int n_pairs, int n_rows, float *__restrict__ S, int64_t ld_s)
 {
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -68,7 +89,8 @@ k_pool_fulldist(const __grid_constant__ TMaps maps, const uint64_t *__restrict__
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * STAGES + 4);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int total = m_tiles * n_tiles;
+    const int total = m_tiles * n_tiles * ksplit;
+    const int per_m = n_tiles * ksplit;
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&maps.a_hi);
@@ -97,8 +119,8 @@ k_pool_fulldist(const __grid_constant__ TMaps maps, const uint64_t *__restrict__
             int stage = 0;
             uint32_t phase = 0;
             for (int t = blockIdx.x; t < total; t += gridDim.x) {
-                const int m = t / n_tiles, n = t % n_tiles;
-                uint64_t mask = kmask[m];
+                const int m = t / per_m, n = (t % per_m) / ksplit;
+                uint64_t mask = split_mask(kmask[m], t % ksplit, ksplit);
                 while (mask) {
                     const int kc = __ffsll((long long)mask) - 1;
                     mask &= mask - 1;
@@ -121,7 +143,7 @@ k_pool_fulldist(const __grid_constant__ TMaps maps, const uint64_t *__restrict__
             uint32_t phase = 0;
             uint32_t it = 0;                       // drains so far (accumulator = it & 1)
             for (int t = blockIdx.x; t < total; t += gridDim.x) {
-                uint64_t mask = kmask[t / n_tiles];
+                uint64_t mask = split_mask(kmask[t / per_m], t % ksplit, ksplit);
                 int in_flush = 0;
                 while (mask) {
                     mask &= mask - 1;
@@ -159,8 +181,8 @@ k_pool_fulldist(const __grid_constant__ TMaps maps, const uint64_t *__restrict__
         const int q = warp & 3, half = (warp - 2) >> 2;
         uint32_t it = 0;
         for (int t = blockIdx.x; t < total; t += gridDim.x) {
-            const int m = t / n_tiles, n = t % n_tiles;
-            const int n_flush = (__popcll(kmask[m]) + FLUSH - 1) / FLUSH;
+            const int m = t / per_m, n = (t % per_m) / ksplit;
+            const int n_flush = (__popcll(split_mask(kmask[m], t % ksplit, ksplit)) + FLUSH - 1) / FLUSH;
             float acc[BN / 2];
 #pragma unroll
             for (int i = 0; i < BN / 2; i++) acc[i] = 0.f;
@@ -183,6 +205,13 @@ k_pool_fulldist(const __grid_constant__ TMaps maps, const uint64_t *__restrict__
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&tempty[it & 1]);
+            }
+            if (MODE == 1) {
+                // raw partial sums, [col][row] so that a warp stores 128 contiguous bytes per column
+                float *P = S + (size_t)t * (BM * BN) + (size_t)(half * (BN / 2)) * BM + q * 32 + lane;
+#pragma unroll
+                for (int j = 0; j < BN / 2; j++) P[(size_t)j * BM] = acc[j];
+                continue;
             }
             // clamp, difference, square, sum over the 8 bins -> S[pair][row]
             const int row = m * BM + q * 32 + lane;
@@ -227,7 +256,88 @@ k_ring_reduce(const float *__restrict__ S, int64_t ld_s, const int32_t *__restri
     }
 }
 
+// comp-uprjdists epilogue over the K-split partials (src/comp-uprjdists.cpp:322-327):
+// out[pair][8 f + b] = min(Desc1 pooled, 1) - min(Desc2 pooled, 1), partials summed in the order ks = 0..
+// One CTA per pair: coalesced reads down the rows of each partial column, values staged in shared
+// memory as [row][bin], then written through `map` (filter -> row of the sorted distinct bank).
+__global__ void __launch_bounds__(256)
+k_uprj_finish(const float *__restrict__ P, int m_tiles, int n_tiles, int ksplit, const int32_t *__restrict__ map,
+              const float *__restrict__ a_inv, const float *__restrict__ b_inv, int nF,
+              float *__restrict__ out, int64_t ld_out)
+{
+    extern __shared__ float s_val[];           // m_tiles * 128 rows x 8 bins
+    const int pair = blockIdx.x;
+    const int n = pair >> 4, pl = pair & 15;
+    const float s1b = b_inv[2 * pair], s2b = b_inv[2 * pair + 1];
+    for (int i = threadIdx.x; i < m_tiles * BM * 8; i += 256) {
+        const int r = i & (BM - 1), b = (i >> 7) & 7, m = i >> 10;
+        const float *p = P + ((size_t)(m * n_tiles + n) * ksplit) * (BM * BN) + (size_t)(pl * 16 + b) * BM + r;
+        float a1 = 0.f, a2 = 0.f;
+        for (int ks = 0; ks < ksplit; ks++) {
+            a1 += p[(size_t)ks * (BM * BN)];
+            a2 += p[(size_t)ks * (BM * BN) + 8 * BM];
+        }
+        const float ra = a_inv[m * BM + r];
+        s_val[(m * BM + r) * 8 + b] = fminf(a1 * (ra * s1b), 1.f) - fminf(a2 * (ra * s2b), 1.f);
+    }
+    __syncthreads();
+    for (int o = threadIdx.x; o < nF * 8; o += 256)
+        out[(size_t)pair * ld_out + o] = s_val[map[o >> 3] * 8 + (o & 7)];
+}
+
 }  // namespace
+
+// K-split factor for a small bank: enough CTAs for the GPU, a divisor-free choice among 1, 2, 4, 8, 16
+int dlco_pool_tc_ksplit(const dlco_ctx *ctx, const dlco_bank *bank, int n_pairs_padded)
+{
+    const int tiles = (bank->nRowsPad / BM) * (n_pairs_padded / 16);
+    int ks = 1;
+    while (ks < 16 && tiles * ks * 2 <= ctx->sm_count + ctx->sm_count / 8) ks *= 2;
+    return ks;
+}
+
+size_t dlco_pool_tc_partial_bytes(const dlco_bank *bank, int n_pairs_padded, int ksplit)
+{
+    return (size_t)(bank->nRowsPad / BM) * (n_pairs_padded / 16) * ksplit * BM * BN * sizeof(float);
+}
+
+int dlco_launch_pool_tc_uprj(dlco_ctx *ctx, const dlco_bank *bank, const void *d_bhi, const void *d_blo,
+                             const float *d_binv, int n_pairs, int n_pairs_padded, int ksplit, float *d_P,
+                             float *d_out, int64_t ld_out)
+{
+    if (n_pairs <= 0) return DLCO_OK;
+    DLCO_REQUIRE(n_pairs_padded % 16 == 0 && n_pairs_padded >= n_pairs, "pool_tc_uprj: bad padding");
+    DLCO_REQUIRE(n_pairs <= 65535, "pool_tc_uprj: at most 65535 pairs per launch");
+    TMaps maps;
+    maps.a_hi = bank->map_hi;
+    maps.a_lo = bank->map_lo;
+    int r = dlco_make_tmap_2d_ex(&maps.b_hi, d_bhi, 2, (uint64_t)n_pairs_padded * 16, KTOT, BN, BK);
+    if (r != DLCO_OK) return r;
+    r = dlco_make_tmap_2d_ex(&maps.b_lo, d_blo, 2, (uint64_t)n_pairs_padded * 16, KTOT, BN, BK);
+    if (r != DLCO_OK) return r;
+    static bool attr_set = false;
+    if (!attr_set) {
+        DLCO_CUDA(cudaFuncSetAttribute(k_pool_fulldist<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+        attr_set = true;
+    }
+    const int m_tiles = bank->nRowsPad / BM, n_tiles = n_pairs_padded / 16;
+    const int total = m_tiles * n_tiles * ksplit;
+    const int grid = total < ctx->sm_count ? total : ctx->sm_count;
+    dlco_prof_begin(ctx, 1);
+    k_pool_fulldist<1><<<grid, NTHREADS, SMEM_BYTES, ctx->stream>>>(maps, bank->d_kmask, bank->d_inv_scale, d_binv,
+                                                                   m_tiles, n_tiles, ksplit, n_pairs, bank->nRows,
+                                                                   d_P, 0);
+    dlco_prof_end(ctx);
+    DLCO_CHECK_LAUNCH(ctx);
+    const size_t fin_smem = (size_t)bank->nRowsPad * 8 * sizeof(float);
+    DLCO_REQUIRE(fin_smem <= 48 * 1024, "pool_tc_uprj: bank of %d distinct filters is too large for this path", bank->nRows);
+    dlco_prof_begin(ctx, 6);
+    k_uprj_finish<<<n_pairs, 256, fin_smem, ctx->stream>>>(d_P, m_tiles, n_tiles, ksplit, bank->d_map,
+                                                           bank->d_inv_scale, d_binv, bank->nF, d_out, ld_out);
+    dlco_prof_end(ctx);
+    DLCO_CHECK_LAUNCH(ctx);
+    return DLCO_OK;
+}
 
 int dlco_launch_pool_tc(dlco_ctx *ctx, const dlco_bank *bank, const void *d_bhi, const void *d_blo,
                         const float *d_binv, int n_pairs, int n_pairs_padded, float *d_S,
@@ -245,16 +355,16 @@ int dlco_launch_pool_tc(dlco_ctx *ctx, const dlco_bank *bank, const void *d_bhi,
     if (r != DLCO_OK) return r;
     static bool attr_set = false;
     if (!attr_set) {
-        DLCO_CUDA(cudaFuncSetAttribute(k_pool_fulldist, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+        DLCO_CUDA(cudaFuncSetAttribute(k_pool_fulldist<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
         attr_set = true;
     }
     const int m_tiles = bank->nRowsPad / BM, n_tiles = n_pairs_padded / 16;
     const int total = m_tiles * n_tiles;
     const int grid = total < ctx->sm_count ? total : ctx->sm_count;
     dlco_prof_begin(ctx, 1);
-    k_pool_fulldist<<<grid, NTHREADS, SMEM_BYTES, ctx->stream>>>(maps, bank->d_kmask, bank->d_inv_scale, d_binv,
-                                                                m_tiles, n_tiles, n_pairs, bank->nRows, d_S,
-                                                                bank->nRowsPad);
+    k_pool_fulldist<0><<<grid, NTHREADS, SMEM_BYTES, ctx->stream>>>(maps, bank->d_kmask, bank->d_inv_scale, d_binv,
+                                                                   m_tiles, n_tiles, 1, n_pairs, bank->nRows, d_S,
+                                                                   bank->nRowsPad);
     dlco_prof_end(ctx);
     DLCO_CHECK_LAUNCH(ctx);
     const int n_rings = bank->nF / 8;

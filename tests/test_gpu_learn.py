@@ -42,6 +42,40 @@ def test_uprjdist_matches_oracle(gpu_ctx, synth, oracle_lib):
     assert np.abs(got - want).max() <= 2e-6, np.abs(got - want).max()
 
 
+@pytest.mark.parametrize("n_sel,n_pairs", [(68, 700), (60, 17), (130, 300), (5, 256)])
+def test_uprjdist_tensor_path_matches_simt_path(gpu_ctx, oracle_lib, n_sel, n_pairs, monkeypatch):
+    """K-split tcgen05 pooling (k_pool_fulldist<1> + k_uprj_finish) against the fp32 SIMT cross-check
+    kernel over ragged multi-batch ranges, banks of one and two 128-row tiles and duplicate filters;
+    plus the domain's own invariants: swapping the pair negates the row, a patch against itself is 0."""
+    rings = O.ring_params()
+    pick = (np.arange((n_sel + 7) // 8) * 577 + 900) % len(rings)
+    filt, _ = make_bank(oracle_lib, rings[pick])
+    sel = filt[:n_sel].copy()
+    if n_sel > 8:
+        sel[7] = sel[2]                                       # a duplicate row: both outputs must agree
+    patches, pid = O.synth_patches(40, per_point=3, seed=3)
+    idx = O.synth_pairs(pid, n_pairs, seed=4)
+    idx[0, 2] = idx[0, 0]                                     # a patch against itself
+    d_p, d_i = dev_t(gpu_ctx, patches), dev_t(gpu_ctx, idx)
+    swapped = idx[:, [2, 3, 0, 1]].copy()
+    bank = gpu_ctx.bank(sel)
+    got = gpu_ctx.uprjdist_build(bank, d_p, d_i).cpu().numpy()
+    got_sw = gpu_ctx.uprjdist_build(bank, d_p, dev_t(gpu_ctx, swapped)).cpu().numpy()
+    part = gpu_ctx.uprjdist_build(bank, d_p, d_i, lo=3, hi=min(n_pairs, 270)).cpu().numpy()
+    monkeypatch.setenv("DLCO_POOL_IMPL", "simt")
+    ref = gpu_ctx.uprjdist_build(bank, d_p, d_i).cpu().numpy()
+    monkeypatch.delenv("DLCO_POOL_IMPL")
+    bank.close()
+    assert got.shape == (n_pairs, 8 * n_sel)
+    assert np.abs(got - ref).max() <= 2e-6, np.abs(got - ref).max()
+    assert np.abs(got).max() > 0.05
+    assert np.array_equal(got_sw, -got)
+    assert not got[0].any()
+    assert np.array_equal(part, got[3:min(n_pairs, 270)])
+    if n_sel > 8:
+        assert np.array_equal(got[:, 56:64], got[:, 16:24])
+
+
 # ------------------------------------------------------------------------------------------
 # SubtractVectorsByRows + sum: src/kernelop-opencv.cu:49-80
 # ------------------------------------------------------------------------------------------
