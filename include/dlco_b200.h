@@ -197,6 +197,26 @@ int dlco_pj_eig_batched(dlco_ctx *ctx, int D, int nCfg, const float *d_A, float 
 int dlco_pj_prox_apply_grid(dlco_ctx *ctx, int D, int nCfg, const float *d_eval,
                             const float *d_evec, float *d_A, float *d_W, int64_t w_stride,
                             int32_t *d_rank);
+/* dlco_pj_rda_step_grid with the prox's projection done by dlco_pj_psd_project instead of an
+ * eigen-decomposition: margins are x^T A x (no W), A is projected in place, d_rank updated, W is not
+ * produced.  d_work >= nCfg * D * D floats.  No host synchronisation. */
+int dlco_pj_rda_step_grid_sign(dlco_ctx *ctx, const float *d_dists, int64_t ld, int D,
+                               const int32_t *d_idx_pos, int32_t nPosTrn, const int32_t *d_idx_neg,
+                               int32_t nNegTrn, int szBatch, uint64_t *d_rng_state, int nCfg,
+                               const float *d_mu, const float *d_gamma, uint64_t t, float *d_A,
+                               float *d_dfavg, int32_t *d_rank, float *d_work);
+/* W of src/pj-learn.cpp:472-490 from already projected matrices: rows sqrt(l_k) v_k^T of the d_rank[g]
+ * largest eigenpairs of A_g, ascending (library eigensolver).  For the points where a sign-prox run
+ * needs W: validation, statistics, saving the model.  d_work >= nCfg * (D * D + D) floats.
+ * Synchronises and checks the solver's info words. */
+int dlco_pj_factor_grid(dlco_ctx *ctx, int D, int nCfg, const float *d_A, const int32_t *d_rank,
+                        float *d_W, int64_t w_stride, float *d_work);
+/* The prox's projection alone, without an eigen-decomposition (src/pj-learn.cpp:434-470 computes
+ * V max(L,0) V^T through LAPACKE_ssyevr): nCfg symmetric D x D matrices at d_A are replaced by their
+ * PSD parts (A + A sign(A)) / 2, sign(A) by a minimax-polynomial iteration of tcgen05 GEMMs
+ * (fp32-equivalent 3xTF32).  d_rank[g] = rank of the result; d_S (optional, nCfg x D x D) receives
+ * sign(A).  Asynchronous on the context's stream. */
+int dlco_pj_psd_project(dlco_ctx *ctx, int D, int nCfg, float *d_A, int32_t *d_rank, float *d_S);
 /* iteration t of all configurations: sample, gradient, dual average, batched eig, prox
  * (src/pj-learn.cpp:305-490).  d_work: nCfg * (2 D D + D) floats.  Asynchronous. */
 int dlco_pj_rda_step_grid(dlco_ctx *ctx, const float *d_dists, int64_t ld, int D,

@@ -79,6 +79,11 @@ SIGNATURES = {
                                       ctypes.c_int32, c_int, c_void_p, c_int, c_void_p, c_void_p, c_uint64,
                                       c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "dlco_pj_grid_check": (c_int, [c_void_p, c_int]),
+    "dlco_pj_rda_step_grid_sign": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_void_p, ctypes.c_int32, c_void_p,
+                                           ctypes.c_int32, c_int, c_void_p, c_int, c_void_p, c_void_p, c_uint64,
+                                           c_void_p, c_void_p, c_void_p, c_void_p]),
+    "dlco_pj_factor_grid": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_int64, c_void_p]),
+    "dlco_pj_psd_project": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "dlco_pj_validate": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_void_p, c_int64, c_void_p, c_int64,
                                  c_void_p, c_int, c_void_p, c_float, P(c_float), P(c_float)]),
     "dlco_pr_patchdist": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int, c_void_p, c_void_p]),
@@ -385,6 +390,26 @@ class Context:
                                               _ptr(idx_pos), n_pos_trn, _ptr(idx_neg), n_neg_trn, sz_batch,
                                               _ptr(rng_state), W.shape[0], _ptr(d_mu), _ptr(d_gamma), t, _ptr(W),
                                               _ptr(A), _ptr(dfavg), _ptr(d_rank), _ptr(work)))
+
+    def pj_rda_step_grid_sign(self, dists, idx_pos, n_pos_trn, idx_neg, n_neg_trn, sz_batch, rng_state, d_mu,
+                              d_gamma, t, A, dfavg, d_rank, work):
+        _check(self.lib.dlco_pj_rda_step_grid_sign(self.handle, _ptr(dists), dists.stride(0), dists.shape[1],
+                                                   _ptr(idx_pos), n_pos_trn, _ptr(idx_neg), n_neg_trn, sz_batch,
+                                                   _ptr(rng_state), A.shape[0], _ptr(d_mu), _ptr(d_gamma), t,
+                                                   _ptr(A), _ptr(dfavg), _ptr(d_rank), _ptr(work)))
+
+    def pj_factor_grid(self, A, d_rank, W, work):
+        _check(self.lib.dlco_pj_factor_grid(self.handle, A.shape[-1], A.shape[0], _ptr(A), _ptr(d_rank), _ptr(W),
+                                            W.stride(0), _ptr(work)))
+
+    def pj_psd_project(self, A, want_sign=False):
+        """In place: every symmetric matrix of A (n_cfg, D, D) becomes its PSD part; returns (ranks, sign)."""
+        torch = self.torch
+        n_cfg, D = A.shape[0], A.shape[-1]
+        rank = torch.zeros((n_cfg,), dtype=torch.int32, device=self.device)
+        S = torch.empty_like(A) if want_sign else None
+        _check(self.lib.dlco_pj_psd_project(self.handle, D, n_cfg, _ptr(A), _ptr(rank), _ptr(S) if want_sign else None))
+        return rank, S
 
     def pj_grid_check(self, n_cfg):
         _check(self.lib.dlco_pj_grid_check(self.handle, n_cfg))

@@ -106,7 +106,7 @@ extern "C" int dlco_shutdown(dlco_ctx *ctx)
         for (int i = 0; i < 6; i++) cudaEventDestroy(ctx->side_ev[i]);
         cudaStreamDestroy(ctx->side_stream);
     }
-    for (int i = 0; i < 32; i++)
+    for (int i = 0; i < 48; i++)
         if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
     for (int i = 0; i < 8; i++)
         if (ctx->pinned[i]) cudaFreeHost(ctx->pinned[i]);

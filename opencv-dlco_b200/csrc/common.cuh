@@ -20,8 +20,8 @@ struct dlco_ctx {
     cudaStream_t stream;
     int64_t launches;
     // scratch buffers, grown on demand
-    void *scratch[32];
-    size_t scratch_bytes[32];
+    void *scratch[48];
+    size_t scratch_bytes[48];
     // pinned staging
     void *pinned[8];
     size_t pinned_bytes[8];

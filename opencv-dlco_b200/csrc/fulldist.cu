@@ -189,9 +189,9 @@ extern "C" int dlco_uprjdist_build(dlco_ctx *ctx, const dlco_bank *bank, const u
         const int npad = (n + 15) / 16 * 16;
         const int ksplit = dlco_pool_tc_ksplit(ctx, bank, nb);    // of the full batch: a ragged tail sums in the same order
         const size_t plane = (size_t)((nb + 15) / 16 * 16) * 16 * 4096 * 2;
-        uint8_t *bhi = (uint8_t *)dlco_scratch(ctx, s2 ? 25 : 0, plane);
-        uint8_t *blo = (uint8_t *)dlco_scratch(ctx, s2 ? 26 : 1, plane);
-        float *binv = (float *)dlco_scratch(ctx, s2 ? 27 : 2, (size_t)(nb + 16) * 2 * sizeof(float));
+        uint8_t *bhi = (uint8_t *)dlco_scratch(ctx, s2 ? 32 : 0, plane);
+        uint8_t *blo = (uint8_t *)dlco_scratch(ctx, s2 ? 33 : 1, plane);
+        float *binv = (float *)dlco_scratch(ctx, s2 ? 34 : 2, (size_t)(nb + 16) * 2 * sizeof(float));
         float *P = (float *)dlco_scratch(ctx, 3, dlco_pool_tc_partial_bytes(bank, (nb + 15) / 16 * 16, ksplit));
         if (!bhi || !blo || !binv || !P) return DLCO_ENOMEM;
         cudaStream_t main_stream = ctx->stream;

@@ -6,9 +6,10 @@
 // is 5 x 3 tiles per (mu, gamma) configuration and the configurations of a sweep are the batch
 // dimension.  (128 x 64 tiles moved 1.26 GB from L2 into shared memory per 45-configuration launch
 // and sat at 25 % of the 3xTF32 rate; the wide tile halves the bytes per flop.)
-// Roles: warp 0 = TMA producer, warp 1 = MMA issuer + TMEM owner, warps 2..5 = epilogue.
+// Roles: warp 0 = TMA producer, warp 1 = MMA issuer + TMEM owner, warps 2..9 = epilogue (drains).
 #include "common.cuh"
 #include "kernels.h"
+#include <stdlib.h>
 
 namespace {
 
@@ -20,15 +21,21 @@ constexpr int A_BYTES = BM * BK * 4;
 constexpr int B_BYTES = BN * BK * 4;
 constexpr int STAGE_BYTES = 2 * A_BYTES + 2 * B_BYTES;
 constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256;
-constexpr int NTHREADS = 192;
-constexpr int TMEM_COLS = 256;
+constexpr int EPI_WARPS = 8;
+constexpr int NTHREADS = 64 + EPI_WARPS * 32;
+constexpr int TMEM_COLS = 512;               // two 192-column accumulators
+constexpr int EN = BN / 2;                   // columns per epilogue warp
 
 struct __align__(64) GemmMaps {
     CUtensorMap a_hi, a_lo, b_hi, b_lo;
 };
 
+// The tensor core adds into its fp32 TMEM accumulator with truncation (bias ~ -3e-8 relative per
+// accumulated MMA, see pool_tc.cu): the accumulation is cut every FLUSH chunks, the epilogue warps
+// drain the partial sums and add them in round-to-nearest registers while the MMAs continue into the
+// other accumulator.  Matters for the chained GEMMs of the matrix-sign iteration (pj_sign.cu).
 __global__ void __launch_bounds__(NTHREADS, 1)
-k_gemm3x_nt(const __grid_constant__ GemmMaps maps, int k_chunks, int a_batch_rows, int b_batch_rows,
+k_gemm3x_nt(const __grid_constant__ GemmMaps maps, int k_chunks, int FLUSH, int a_batch_rows, int b_batch_rows,
             int M, int N, float *__restrict__ C, int64_t ldc, int64_t c_batch_stride)
 {
     extern __shared__ uint8_t smem_raw[];
@@ -36,8 +43,9 @@ k_gemm3x_nt(const __grid_constant__ GemmMaps maps, int k_chunks, int a_batch_row
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + STAGES * STAGE_BYTES);
     uint64_t *full = bars;
     uint64_t *empty = bars + STAGES;
-    uint64_t *tfull = bars + 2 * STAGES;
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * STAGES + 1);
+    uint64_t *tfull = bars + 2 * STAGES;          // [2]
+    uint64_t *tempty = bars + 2 * STAGES + 2;     // [2]
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * STAGES + 4);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int nt = blockIdx.x, mt = blockIdx.y, g = blockIdx.z;
@@ -51,7 +59,10 @@ k_gemm3x_nt(const __grid_constant__ GemmMaps maps, int k_chunks, int a_batch_row
             mbar_init(&full[s], 1);
             mbar_init(&empty[s], 1);
         }
-        mbar_init(tfull, 1);
+        for (int a = 0; a < 2; a++) {
+            mbar_init(&tfull[a], 1);
+            mbar_init(&tempty[a], EPI_WARPS);
+        }
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc<TMEM_COLS>(tmem_slot);
@@ -81,7 +92,14 @@ k_gemm3x_nt(const __grid_constant__ GemmMaps maps, int k_chunks, int a_batch_row
             constexpr uint32_t idesc = umma_idesc_tf32(BM, BN);
             int stage = 0;
             uint32_t phase = 0;
+            uint32_t it = 0;                       // drains so far (accumulator = it & 1)
+            int in_flush = 0;
             for (int kc = 0; kc < k_chunks; kc++) {
+                const uint32_t d_tmem = tmem_base + (it & 1) * BN;
+                if (in_flush == 0) {
+                    mbar_wait(&tempty[it & 1], ((it >> 1) & 1) ^ 1);
+                    tc_fence_after();
+                }
                 mbar_wait(&full[stage], phase);
                 tc_fence_after();
                 const uint32_t sa = smem_u32(smem + stage * STAGE_BYTES);
@@ -92,35 +110,62 @@ k_gemm3x_nt(const __grid_constant__ GemmMaps maps, int k_chunks, int a_batch_row
 #pragma unroll
                 for (int k = 0; k < BK / 8; k++) {
                     const uint64_t ko = (uint64_t)(k * 2);
-                    umma_tf32(tmem_base, d_alo + ko, d_bhi + ko, idesc, (kc | k) != 0);
-                    umma_tf32(tmem_base, d_ahi + ko, d_blo + ko, idesc, 1);
-                    umma_tf32(tmem_base, d_ahi + ko, d_bhi + ko, idesc, 1);
+                    umma_tf32(d_tmem, d_alo + ko, d_bhi + ko, idesc, (in_flush | k) != 0);
+                    umma_tf32(d_tmem, d_ahi + ko, d_blo + ko, idesc, 1);
+                    umma_tf32(d_tmem, d_ahi + ko, d_bhi + ko, idesc, 1);
                 }
                 umma_commit(&empty[stage]);
                 if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                if (++in_flush == FLUSH || kc == k_chunks - 1) {
+                    umma_commit(&tfull[it & 1]);
+                    it++;
+                    in_flush = 0;
+                }
             }
-            umma_commit(tfull);
         }
     } else {
-        const int q = warp & 3;
-        mbar_wait(tfull, 0);
-        tc_fence_after();
-        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
+        // epilogue warps 2..9: TMEM lane quarter = warp % 4, column half = (warp - 2) / 4
+        const int q = warp & 3, half = (warp - 2) >> 2;
+        const int n_flush = (k_chunks + FLUSH - 1) / FLUSH;
+        float acc[EN];
+#pragma unroll
+        for (int i = 0; i < EN; i++) acc[i] = 0.f;
+        for (uint32_t it = 0; it < (uint32_t)n_flush; it++) {
+            mbar_wait(&tfull[it & 1], (it >> 1) & 1);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (it & 1) * BN + half * EN;
+#pragma unroll
+            for (int j = 0; j < EN / 16; j += 2) {
+                uint32_t r0[16], r1[16];
+                tmem_ld16_nowait(taddr + j * 16, r0);
+                tmem_ld16_nowait(taddr + (j + 1) * 16, r1);
+                tmem_ld_wait();
+#pragma unroll
+                for (int e = 0; e < 16; e++) {
+                    acc[j * 16 + e] += __uint_as_float(r0[e]);
+                    acc[(j + 1) * 16 + e] += __uint_as_float(r1[e]);
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tempty[it & 1]);
+        }
         const int row = mt * BM + q * 32 + lane;
-        float *crow = C + (size_t)g * c_batch_stride + (size_t)row * ldc;
+        const int col0 = nt * BN + half * EN;
+        if (row < M) {
+            float *crow = C + (size_t)g * c_batch_stride + (size_t)row * ldc + col0;
+            if (col0 + EN <= N && ((reinterpret_cast<uintptr_t>(crow) & 15) == 0)) {
 #pragma unroll
-        for (int j = 0; j < BN / 16; j++) {
-            float v[16];
-            tmem_ld16(taddr + j * 16, v);
-            const int col0 = nt * BN + j * 16;
-            if (row < M) {
+                for (int e = 0; e < EN; e += 4)
+                    *reinterpret_cast<float4 *>(crow + e) = make_float4(acc[e], acc[e + 1], acc[e + 2], acc[e + 3]);
+            } else {
 #pragma unroll
-                for (int e = 0; e < 16; e++)
-                    if (col0 + e < N) crow[col0 + e] = v[e];
+                for (int e = 0; e < EN; e++)
+                    if (col0 + e < N) crow[e] = acc[e];
             }
         }
-        tc_fence_before();
     }
+    tc_fence_before();
     __syncthreads();
     if (warp == 1) {
         tc_fence_after();
@@ -153,7 +198,12 @@ int dlco_launch_gemm3x_nt(dlco_ctx *ctx, const float *a_hi, const float *a_lo, i
     }
     dim3 grid((N + BN - 1) / BN, (M + BM - 1) / BM, batch);
     dlco_prof_begin(ctx, 2);
-    k_gemm3x_nt<<<grid, NTHREADS, SMEM_BYTES, ctx->stream>>>(maps, k_pad / BK, a_rows_pad,
+    static int flush = 0;                     // K chunks (of 32) accumulated in TMEM between drains
+    if (!flush) {
+        const char *e = getenv("DLCO_GEMM_FLUSH");
+        flush = e && atoi(e) > 0 ? atoi(e) : 2;
+    }
+    k_gemm3x_nt<<<grid, NTHREADS, SMEM_BYTES, ctx->stream>>>(maps, k_pad / BK, flush, a_rows_pad,
                                                            b_batched ? b_rows_pad : 0, M, N, d_C, ldc,
                                                            c_batch_stride);
     dlco_prof_end(ctx);

@@ -67,3 +67,10 @@ int dlco_launch_gemm3x_nt(dlco_ctx *ctx, const float *a_hi, const float *a_lo, i
                           const float *b_hi, const float *b_lo, int b_rows_pad, int b_batched,
                           int k_pad, int batch, int M, int N, float *d_C, int64_t ldc,
                           int64_t c_batch_stride);
+
+// pj_sign.cu: PSD projection of nCfg symmetric D x D matrices in place by the tensor-core matrix-sign
+// iteration (no eigen-decomposition); d_rank[g] = rank of the result; d_S optional (sign matrices)
+int dlco_pj_psd_sign(dlco_ctx *ctx, int D, int nCfg, float *d_A, int32_t *d_rank, float *d_S);
+// margins m[g][i] = x_i^T A_g x_i of the nk gathered rows for nCfg configurations (no W needed)
+int dlco_pj_margins_quad_grid(dlco_ctx *ctx, const float *d_dists, int64_t ld, int D, const int32_t *d_rows,
+                              int nk, int nCfg, const float *d_A, float *d_m);

@@ -196,7 +196,7 @@ k_pj_planes(const float *__restrict__ dists, int64_t ld, int D, const int32_t *_
 // d_dLoss: config g at d_dLoss + g * D * D.
 static int pj_grad_core(dlco_ctx *ctx, const float *d_dists, int64_t ld, int D, const int32_t *d_rows_pos,
                         const int32_t *d_rows_neg, int szBatch, int nCfg, const float *d_W, int64_t w_stride,
-                        const int *h_rank, const int32_t *d_rank, float *d_dLoss)
+                        const int *h_rank, const int32_t *d_rank, float *d_dLoss, const float *d_A_quad = nullptr)
 {
     const int nk = 2 * szBatch;
     const int d_pad = dlco_gemm3x_rows_pad(D), k_pad = (nk + 31) / 32 * 32;
@@ -210,7 +210,10 @@ static int pj_grad_core(dlco_ctx *ctx, const float *d_dists, int64_t ld, int D, 
     float *yt_hi = planes + 2 * plane, *yt_lo = yt_hi + plane * nCfg;
     DLCO_CUDA(cudaMemcpyAsync(rows, d_rows_pos, szBatch * sizeof(int32_t), cudaMemcpyDeviceToDevice, ctx->stream));
     DLCO_CUDA(cudaMemcpyAsync(rows + szBatch, d_rows_neg, szBatch * sizeof(int32_t), cudaMemcpyDeviceToDevice, ctx->stream));
-    if (d_rank) {
+    if (d_A_quad) {            // margins x^T A x from A itself (sign-iteration prox: no W is kept)
+        int r = dlco_pj_margins_quad_grid(ctx, d_dists, ld, D, rows, nk, nCfg, d_A_quad, m);
+        if (r != DLCO_OK) return r;
+    } else if (d_rank) {
         int r = dlco_sqnorm_proj_grid(ctx, d_dists, ld, rows, nk, d_W, w_stride, d_rank, nCfg, D, m);
         if (r != DLCO_OK) return r;
     } else {
@@ -827,6 +830,43 @@ extern "C" int dlco_pj_rda_step_grid(dlco_ctx *ctx, const float *d_dists, int64_
     if (r == DLCO_OK) r = pj_eig_batched_async(ctx, D, nCfg, d_A, eval, evec);
     if (r == DLCO_OK) r = dlco_pj_prox_apply_grid(ctx, D, nCfg, eval, evec, d_A, d_W, (int64_t)dd, d_rank);
     return r;
+}
+
+// The same iteration with the prox's projection done by the tensor-core matrix-sign iteration
+// (pj_sign.cu) instead of an eigen-decomposition: margins are x^T A x, A is projected in place and
+// d_rank updated; d_W is NOT touched (dlco_pj_factor_grid rebuilds it when a caller needs W: the
+// validation / statistics / save points).  d_work >= nCfg * D * D floats.
+extern "C" int dlco_pj_rda_step_grid_sign(dlco_ctx *ctx, const float *d_dists, int64_t ld, int D,
+                                          const int32_t *d_idx_pos, int32_t nPosTrn, const int32_t *d_idx_neg,
+                                          int32_t nNegTrn, int szBatch, uint64_t *d_rng_state, int nCfg,
+                                          const float *d_mu, const float *d_gamma, uint64_t t, float *d_A,
+                                          float *d_dfavg, int32_t *d_rank, float *d_work)
+{
+    DLCO_REQUIRE(ctx && d_dists && d_idx_pos && d_idx_neg && d_rng_state && d_mu && d_gamma && d_A && d_dfavg &&
+                 d_rank && d_work, "dlco_pj_rda_step_grid_sign: NULL argument");
+    DLCO_REQUIRE(D > 0 && szBatch > 0 && szBatch <= 4096 && nCfg > 0 && ld >= D, "dlco_pj_rda_step_grid_sign: bad shapes");
+    float *dLoss = d_work;
+    int32_t *rows = (int32_t *)dlco_scratch(ctx, 25, (size_t)2 * szBatch * sizeof(int32_t));
+    if (!rows) return DLCO_ENOMEM;
+    int r = dlco_pj_sample_batch(ctx, d_idx_pos, nPosTrn, d_idx_neg, nNegTrn, szBatch, d_rng_state, rows, rows + szBatch);
+    if (r == DLCO_OK) r = pj_grad_core(ctx, d_dists, ld, D, rows, rows + szBatch, szBatch, nCfg, nullptr, 0, nullptr, d_rank, dLoss, d_A);
+    if (r == DLCO_OK) r = dlco_pj_rda_update_grid(ctx, D, t, szBatch, nCfg, d_mu, d_gamma, dLoss, d_dfavg, d_A);
+    if (r == DLCO_OK) r = dlco_pj_psd_sign(ctx, D, nCfg, d_A, d_rank, nullptr);
+    return r;
+}
+
+// W_g = rows sqrt(l_k) v_k^T of the d_rank[g] largest eigenpairs of the (already projected) A_g, in the
+// reference's ascending order (src/pj-learn.cpp:472-490); cusolverDnXsyevBatched.  d_work >= nCfg * (D D + D).
+extern "C" int dlco_pj_factor_grid(dlco_ctx *ctx, int D, int nCfg, const float *d_A, const int32_t *d_rank,
+                                   float *d_W, int64_t w_stride, float *d_work)
+{
+    DLCO_REQUIRE(ctx && d_A && d_rank && d_W && d_work && D > 0 && nCfg > 0, "dlco_pj_factor_grid: bad arguments");
+    float *evec = d_work, *eval = d_work + (size_t)nCfg * D * D;
+    int r = pj_eig_batched_async(ctx, D, nCfg, d_A, eval, evec);
+    if (r != DLCO_OK) return r;
+    k_pj_prox_w_grid<<<dim3(D, nCfg), 256, 0, ctx->stream>>>(D, d_rank, eval, evec, d_W, w_stride);
+    DLCO_CHECK_LAUNCH(ctx);
+    return pj_eig_batched_check(ctx, nCfg);
 }
 
 // info words of the batched eigen-decompositions issued so far (synchronises)

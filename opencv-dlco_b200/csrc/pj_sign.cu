@@ -1,0 +1,277 @@
+// pj-learn prox on the tensor cores: the projection onto the PSD cone
+//
+//     A+ = V max(L, 0) V^T = (A + A sign(A)) / 2            (reference: src/pj-learn.cpp:434-470,
+//                                                            LAPACKE_ssyevr + clip + V L V^T)
+//
+// without an eigen-decomposition.  sign(A) is computed by an odd-quintic iteration
+// X <- X (a_k I + b_k X^2 + c_k X^4), X_0 = A / ||A||_F, whose coefficients are the minimax
+// polynomials for the interval the spectrum occupies at step k (tools/sign_poly.py: LP per step,
+// start interval [1e-4, 1]); 8 minimax steps + 1 Newton-Schulz polish = 27 GEMMs, + 1 for A sign(A).
+// All GEMMs are k_gemm3x_nt (tcgen05, 3xTF32 = fp32-equivalent), batched over the (mu, gamma)
+// configurations of a sweep.  Eigenvalues with |l| < 1e-4 ||A||_F are not driven all the way to
+// +-1; their contribution to A+ is wrong by at most |l| (1 - |s|) / 2 |v v^T| -- below fp32
+// rounding of the eigen-decomposition route.  rank(A+) = (D + trace sign(A)) / 2.
+//
+// What this buys: cusolverDnXsyevBatched spends 38 ms on 45 matrices of 544 x 544 (97 % of a sweep
+// iteration); the 28 GEMMs are ~0.45 TFLOP of tensor work.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace {
+
+constexpr int SIGN_STEPS = 9;
+// tools/sign_poly.py 1e-4  (a, b, c) per step
+__constant__ float c_sign_coef[SIGN_STEPS][3] = {
+    {8.509885880f, -25.264305658f, 18.753568789f},
+    {4.228659615f, -3.108344126f, 0.571498694f},
+    {4.205812483f, -3.092890486f, 0.569812591f},
+    {4.114157757f, -3.030669974f, 0.563027579f},
+    {3.782556611f, -2.802261125f, 0.538186614f},
+    {2.943282063f, -2.192549912f, 0.472857879f},
+    {2.077505958f, -1.466020591f, 0.400932419f},
+    {1.891149032f, -1.279511400f, 0.388326974f},
+    {1.875000000f, -1.250000000f, 0.375000000f},
+};
+
+constexpr int NORM_BLOCKS = 32;
+
+// partial[g][b] = sum of squares of a slice of A_g (double), fixed order inside the block
+__global__ void __launch_bounds__(256)
+k_sign_norm(const float *__restrict__ A, size_t dd, double *__restrict__ partial)
+{
+    __shared__ double s[8];
+    const int g = blockIdx.y;
+    const float *a = A + (size_t)g * dd;
+    double acc = 0.0;
+    for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < dd; i += (size_t)NORM_BLOCKS * 256) {
+        const double v = (double)a[i];
+        acc += v * v;
+    }
+    acc = warp_sum_d(acc);
+    if ((threadIdx.x & 31) == 0) s[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int w = 0; w < 8; w++) t += s[w];
+        partial[(size_t)g * NORM_BLOCKS + blockIdx.x] = t;
+    }
+}
+
+__device__ __forceinline__ float sign_inv_alpha(const double *__restrict__ partial, int g)
+{
+    double t = 0.0;
+    for (int b = 0; b < NORM_BLOCKS; b++) t += partial[(size_t)g * NORM_BLOCKS + b];
+    return t > 0.0 ? (float)(1.0 / sqrt(t)) : 0.f;
+}
+
+enum { PREP_INIT = 0, PREP_COPY = 1, PREP_POLY = 2, PREP_SYM = 3, PREP_FINAL = 4 };
+
+// One 32 x 32 tile of configuration blockIdx.z: form the next operand elementwise, optionally store it
+// in fp32 (out) and always as K-major tf32 hi / lo planes (rows_pad x k_pad per configuration, zero
+// padding written too, so no plane ever needs a memset).
+//   PREP_INIT : v = in0 / ||in0||_F                        (X_0; out = X)
+//   PREP_COPY : v = in0                                    (planes of Y = X^2, or of A)
+//   PREP_POLY : v = a [i == j] + b in0 + c in1             (Z = a I + b Y + c Y^2)
+//   PREP_SYM  : v = (in0[i][j] + in0[j][i]) / 2            (X <- sym(X Z); out = X)
+//   PREP_FINAL: out = (out + sym(in0)) / 2, no planes      (A+ = (A + sym(A S)) / 2, in place)
+template <int MODE>
+__global__ void __launch_bounds__(256)
+k_sign_prep(int D, int rows_pad, int k_pad, const float *__restrict__ in0, const float *__restrict__ in1,
+            const double *__restrict__ partial, int step, float *__restrict__ out, float *__restrict__ hi,
+            float *__restrict__ lo)
+{
+    __shared__ float tile[32][33];
+    const int g = blockIdx.z;
+    const int j0 = blockIdx.x * 32, i0 = blockIdx.y * 32;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const size_t dd = (size_t)D * D;
+    const float *p0 = in0 + (size_t)g * dd;
+    if (MODE == PREP_SYM || MODE == PREP_FINAL) {         // transposed tile through shared memory
+        for (int r = ty; r < 32; r += 8) {
+            const int i = j0 + r, j = i0 + tx;            // element (j0 + r, i0 + tx) of in0
+            tile[r][tx] = (i < D && j < D) ? p0[(size_t)i * D + j] : 0.f;
+        }
+        __syncthreads();
+    }
+    float inv_alpha = 0.f, ca = 0.f, cb = 0.f, cc = 0.f;
+    if (MODE == PREP_INIT) inv_alpha = sign_inv_alpha(partial, g);
+    if (MODE == PREP_POLY) { ca = c_sign_coef[step][0]; cb = c_sign_coef[step][1]; cc = c_sign_coef[step][2]; }
+    for (int r = ty; r < 32; r += 8) {
+        const int i = i0 + r, j = j0 + tx;
+        float v = 0.f;
+        if (i < D && j < D) {
+            const size_t o = (size_t)i * D + j;
+            if (MODE == PREP_INIT) v = p0[o] * inv_alpha;
+            else if (MODE == PREP_COPY) v = p0[o];
+            else if (MODE == PREP_POLY) v = fmaf(cc, in1[(size_t)g * dd + o], fmaf(cb, p0[o], i == j ? ca : 0.f));
+            else if (MODE == PREP_SYM) v = 0.5f * (p0[o] + tile[tx][r]);
+            else v = 0.5f * (out[(size_t)g * dd + o] + 0.5f * (p0[o] + tile[tx][r]));
+            if (MODE == PREP_INIT || MODE == PREP_SYM || MODE == PREP_FINAL) out[(size_t)g * dd + o] = v;
+        }
+        if (MODE != PREP_FINAL && i < rows_pad && j < k_pad) {
+            float h, l;
+            tf32_split(v, h, l);
+            const size_t po = ((size_t)g * rows_pad + i) * k_pad + j;
+            hi[po] = h;
+            lo[po] = l;
+        }
+    }
+}
+
+// rank[g] = round((D + trace S_g) / 2); a zero matrix (||A||_F = 0) has rank 0
+__global__ void __launch_bounds__(256)
+k_sign_rank(int D, const float *__restrict__ S, const double *__restrict__ partial, int32_t *__restrict__ rank)
+{
+    __shared__ double s[8];
+    const int g = blockIdx.x;
+    double acc = 0.0;
+    for (int i = threadIdx.x; i < D; i += 256) acc += (double)S[(size_t)g * D * D + (size_t)i * D + i];
+    acc = warp_sum_d(acc);
+    if ((threadIdx.x & 31) == 0) s[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int w = 0; w < 8; w++) t += s[w];
+        rank[g] = sign_inv_alpha(partial, g) > 0.f ? (int32_t)llrint(0.5 * ((double)D + t)) : 0;
+    }
+}
+
+}  // namespace
+
+template <int MODE>
+static int sign_prep(dlco_ctx *ctx, int D, int nCfg, int rows_pad, int k_pad, const float *in0, const float *in1,
+                     const double *partial, int step, float *out, float *hi, float *lo)
+{
+    dim3 grid(MODE == PREP_FINAL ? (D + 31) / 32 : k_pad / 32, MODE == PREP_FINAL ? (D + 31) / 32 : rows_pad / 32, nCfg);
+    k_sign_prep<MODE><<<grid, 256, 0, ctx->stream>>>(D, rows_pad, k_pad, in0, in1, partial, step, out, hi, lo);
+    DLCO_CHECK_LAUNCH(ctx);
+    return DLCO_OK;
+}
+
+// d_A: nCfg symmetric D x D matrices, replaced by their PSD parts; d_rank[g] = rank(A+_g);
+// d_S (optional, nCfg x D x D): sign(A_g) as computed.
+int dlco_pj_psd_sign(dlco_ctx *ctx, int D, int nCfg, float *d_A, int32_t *d_rank, float *d_S)
+{
+    const size_t dd = (size_t)D * D;
+    const int rows_pad = dlco_gemm3x_rows_pad(D), k_pad = (D + 31) / 32 * 32;
+    const size_t plane = (size_t)nCfg * rows_pad * k_pad;
+    float *X = d_S ? d_S : (float *)dlco_scratch(ctx, 36, nCfg * dd * sizeof(float));
+    float *Y = (float *)dlco_scratch(ctx, 37, nCfg * dd * sizeof(float));
+    float *T = (float *)dlco_scratch(ctx, 38, nCfg * dd * sizeof(float));
+    float *P1 = (float *)dlco_scratch(ctx, 39, 2 * plane * sizeof(float));
+    float *P2 = (float *)dlco_scratch(ctx, 40, 2 * plane * sizeof(float));
+    double *partial = (double *)dlco_scratch(ctx, 41, (size_t)nCfg * NORM_BLOCKS * sizeof(double));
+    if (!X || !Y || !T || !P1 || !P2 || !partial) return DLCO_ENOMEM;
+    float *p1h = P1, *p1l = P1 + plane, *p2h = P2, *p2l = P2 + plane;
+    const int64_t cs = (int64_t)dd;
+    int r;
+    k_sign_norm<<<dim3(NORM_BLOCKS, nCfg), 256, 0, ctx->stream>>>(d_A, dd, partial);
+    DLCO_CHECK_LAUNCH(ctx);
+    r = sign_prep<PREP_INIT>(ctx, D, nCfg, rows_pad, k_pad, d_A, nullptr, partial, 0, X, p1h, p1l);
+    for (int k = 0; k < SIGN_STEPS && r == DLCO_OK; k++) {
+        // Y = X X^T (= X^2: X is kept symmetric)
+        r = dlco_launch_gemm3x_nt(ctx, p1h, p1l, rows_pad, p1h, p1l, rows_pad, 1, k_pad, nCfg, D, D, Y, D, cs);
+        if (r == DLCO_OK) r = sign_prep<PREP_COPY>(ctx, D, nCfg, rows_pad, k_pad, Y, nullptr, partial, k, nullptr, p2h, p2l);
+        // T = Y Y^T = X^4
+        if (r == DLCO_OK) r = dlco_launch_gemm3x_nt(ctx, p2h, p2l, rows_pad, p2h, p2l, rows_pad, 1, k_pad, nCfg, D, D, T, D, cs);
+        // Z = a I + b Y + c T
+        if (r == DLCO_OK) r = sign_prep<PREP_POLY>(ctx, D, nCfg, rows_pad, k_pad, Y, T, partial, k, nullptr, p2h, p2l);
+        // T = X Z^T, X <- sym(T)
+        if (r == DLCO_OK) r = dlco_launch_gemm3x_nt(ctx, p1h, p1l, rows_pad, p2h, p2l, rows_pad, 1, k_pad, nCfg, D, D, T, D, cs);
+        if (r == DLCO_OK) r = sign_prep<PREP_SYM>(ctx, D, nCfg, rows_pad, k_pad, T, nullptr, partial, k, X, p1h, p1l);
+    }
+    // A+ = (A + sym(A S)) / 2
+    if (r == DLCO_OK) r = sign_prep<PREP_COPY>(ctx, D, nCfg, rows_pad, k_pad, d_A, nullptr, partial, 0, nullptr, p2h, p2l);
+    if (r == DLCO_OK) r = dlco_launch_gemm3x_nt(ctx, p2h, p2l, rows_pad, p1h, p1l, rows_pad, 1, k_pad, nCfg, D, D, T, D, cs);
+    if (r == DLCO_OK) r = sign_prep<PREP_FINAL>(ctx, D, nCfg, rows_pad, k_pad, T, nullptr, partial, 0, d_A, nullptr, nullptr);
+    if (r != DLCO_OK) return r;
+    k_sign_rank<<<nCfg, 256, 0, ctx->stream>>>(D, X, partial, d_rank);
+    DLCO_CHECK_LAUNCH(ctx);
+    return DLCO_OK;
+}
+
+// C ABI: the projection alone (tests, and callers that keep their own iteration)
+extern "C" int dlco_pj_psd_project(dlco_ctx *ctx, int D, int nCfg, float *d_A, int32_t *d_rank, float *d_S)
+{
+    DLCO_REQUIRE(ctx && d_A && d_rank && D > 0 && nCfg > 0, "dlco_pj_psd_project: bad arguments");
+    return dlco_pj_psd_sign(ctx, D, nCfg, d_A, d_rank, d_S);
+}
+
+// ---------------------------------------------------------------------------------------------
+// margins without W: m[g][i] = x_i^T A_g x_i  (= ||W_g x_i||^2 of src/pj-learn.cpp:332-365 when
+// A_g = W_g^T W_g).  One batched GEMM Ct_g = A_g Xb^T (D x nk) + a column dot with Xb.
+// ---------------------------------------------------------------------------------------------
+namespace {
+
+// gathered batch rows as K-major planes: row i = sample rows[i], K = feature
+__global__ void __launch_bounds__(256)
+k_rows_planes(const float *__restrict__ dists, int64_t ld, int D, const int32_t *__restrict__ rows, int nk,
+              int rows_pad, int k_pad, float *__restrict__ hi, float *__restrict__ lo)
+{
+    const int j = blockIdx.x * 32 + (threadIdx.x & 31);
+    for (int i = blockIdx.y * 32 + (threadIdx.x >> 5); i < blockIdx.y * 32 + 32; i += 8) {
+        if (i >= rows_pad || j >= k_pad) continue;
+        const float v = (i < nk && j < D) ? dists[(int64_t)rows[i] * ld + j] : 0.f;
+        float h, l;
+        tf32_split(v, h, l);
+        hi[(size_t)i * k_pad + j] = h;
+        lo[(size_t)i * k_pad + j] = l;
+    }
+}
+
+// m[g][i] = sum_j Ct[g][j][i] * x_i[j]; block = 32 samples x 8 j-lanes, fixed summation order
+__global__ void __launch_bounds__(256)
+k_quad_coldot(const float *__restrict__ Ct, const float *__restrict__ dists, int64_t ld, int D,
+              const int32_t *__restrict__ rows, int nk, float *__restrict__ m)
+{
+    __shared__ float tile[32][33];
+    __shared__ float part[8][32];
+    const int g = blockIdx.y, i0 = blockIdx.x * 32;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const float *ct = Ct + (size_t)g * D * nk;
+    float acc = 0.f;
+    for (int j0 = 0; j0 < D; j0 += 32) {
+        for (int r = ty; r < 32; r += 8) {
+            const int i = i0 + r, j = j0 + tx;
+            tile[r][tx] = (i < nk && j < D) ? dists[(int64_t)rows[i] * ld + j] : 0.f;
+        }
+        __syncthreads();
+        for (int jj = ty; jj < 32; jj += 8) {
+            const int i = i0 + tx, j = j0 + jj;
+            if (i < nk && j < D) acc = fmaf(ct[(size_t)j * nk + i], tile[tx][jj], acc);
+        }
+        __syncthreads();
+    }
+    part[ty][tx] = acc;
+    __syncthreads();
+    if (ty == 0 && i0 + tx < nk) {
+        float t = 0.f;
+        for (int w = 0; w < 8; w++) t += part[w][tx];
+        m[(size_t)g * nk + i0 + tx] = t;
+    }
+}
+
+}  // namespace
+
+int dlco_pj_margins_quad_grid(dlco_ctx *ctx, const float *d_dists, int64_t ld, int D, const int32_t *d_rows,
+                              int nk, int nCfg, const float *d_A, float *d_m)
+{
+    const int rows_pad = dlco_gemm3x_rows_pad(D), k_pad = (D + 31) / 32 * 32;
+    const int xrows_pad = dlco_gemm3x_rows_pad(nk);
+    const size_t plane = (size_t)nCfg * rows_pad * k_pad, xplane = (size_t)xrows_pad * k_pad;
+    float *PA = (float *)dlco_scratch(ctx, 40, 2 * plane * sizeof(float));
+    float *PX = (float *)dlco_scratch(ctx, 42, 2 * xplane * sizeof(float));
+    float *Ct = (float *)dlco_scratch(ctx, 38, (size_t)nCfg * D * (nk > D ? nk : D) * sizeof(float));
+    if (!PA || !PX || !Ct) return DLCO_ENOMEM;
+    int r = sign_prep<PREP_COPY>(ctx, D, nCfg, rows_pad, k_pad, d_A, nullptr, nullptr, 0, nullptr, PA, PA + plane);
+    if (r != DLCO_OK) return r;
+    k_rows_planes<<<dim3(k_pad / 32, xrows_pad / 32), 256, 0, ctx->stream>>>(d_dists, ld, D, d_rows, nk, xrows_pad, k_pad,
+                                                                          PX, PX + xplane);
+    DLCO_CHECK_LAUNCH(ctx);
+    r = dlco_launch_gemm3x_nt(ctx, PA, PA + plane, rows_pad, PX, PX + xplane, xrows_pad, 0, k_pad, nCfg, D, nk, Ct, nk,
+                              (int64_t)D * nk);
+    if (r != DLCO_OK) return r;
+    k_quad_coldot<<<dim3((nk + 31) / 32, nCfg), 256, 0, ctx->stream>>>(Ct, d_dists, ld, D, d_rows, nk, d_m);
+    DLCO_CHECK_LAUNCH(ctx);
+    return DLCO_OK;
+}

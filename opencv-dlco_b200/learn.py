@@ -267,8 +267,15 @@ class PjSweep:
     an iteration never synchronises with the host.  Logs are the reference's lines, prefixed
     with "[mu/gamma] " as PrLearner does for its grid."""
 
-    def __init__(self, ctx, dists, labels, mus, gammas, sz_batch=200, log_step=100, emit=None, split=None):
+    def __init__(self, ctx, dists, labels, mus, gammas, sz_batch=200, log_step=100, emit=None, split=None,
+                 prox="eig"):
+        """prox="eig": the reference's route (eigen-decomposition, clip, V L V^T; batched cuSOLVER).
+        prox="sign": the projection by the tensor-core matrix-sign iteration (dlco_pj_psd_project); W is
+        rebuilt from the projected A only where it is needed (ranks are exact, validation / statistics /
+        saved models go through one eigen-decomposition per log step instead of one per iteration)."""
         import torch
+        assert prox in ("eig", "sign")
+        self.prox, self._w_stale = prox, False
         self.ctx, self.dists, self.torch = ctx, dists, torch
         self.labels = np.asarray(labels).reshape(-1).astype(np.uint8)
         self.mu = np.atleast_1d(np.asarray(mus, np.float32))
@@ -300,20 +307,35 @@ class PjSweep:
         self.W_save, self.A_save = [None] * n, [None] * n
 
     def step(self):
-        self.ctx.pj_rda_step_grid(self.dists, self.idx_pos, self.n_pos_trn, self.idx_neg, self.n_neg_trn,
-                                  self.sz_batch, self.rng_state, self.d_mu, self.d_gamma, self.t, self.W, self.A,
-                                  self.dfavg, self.d_rank, self.work)
+        if self.prox == "sign":
+            self.ctx.pj_rda_step_grid_sign(self.dists, self.idx_pos, self.n_pos_trn, self.idx_neg, self.n_neg_trn,
+                                           self.sz_batch, self.rng_state, self.d_mu, self.d_gamma, self.t, self.A,
+                                           self.dfavg, self.d_rank, self.work)
+            self._w_stale = True
+        else:
+            self.ctx.pj_rda_step_grid(self.dists, self.idx_pos, self.n_pos_trn, self.idx_neg, self.n_neg_trn,
+                                      self.sz_batch, self.rng_state, self.d_mu, self.d_gamma, self.t, self.W, self.A,
+                                      self.dfavg, self.d_rank, self.work)
         self.t += 1
 
     def ranks(self):
-        self.ctx.pj_grid_check(self.n_cfg)                       # synchronises; raises on a failed eig
+        if self.prox == "eig":
+            self.ctx.pj_grid_check(self.n_cfg)                   # synchronises; raises on a failed eig
         return self.d_rank.cpu().numpy().astype(int)
 
+    def refresh_w(self):
+        """prox="sign": W from the current (projected) A -- one batched eigen-decomposition."""
+        if self._w_stale:
+            self.ctx.pj_factor_grid(self.A, self.d_rank, self.W, self.work)
+            self._w_stale = False
+
     def validate(self, c, rank):
+        self.refresh_w()
         return self.ctx.pj_validate(self.dists, self.pos_val, self.neg_val, self.W[c], int(rank), self.A[c],
                                     float(self.mu[c]))
 
     def stats(self, c, rank):
+        self.refresh_w()
         pd = self.ctx.pj_patchdist(self.dists, self.W[c], int(rank))
         return self.ctx.roc_stats(pd, self.d_labels)
 
