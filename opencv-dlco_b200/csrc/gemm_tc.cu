@@ -35,9 +35,10 @@ struct __align__(64) GemmMaps {
 // drain the partial sums and add them in round-to-nearest registers while the MMAs continue into the
 // other accumulator.  Matters for the chained GEMMs of the matrix-sign iteration (pj_sign.cu).
 __global__ void __launch_bounds__(NTHREADS, 1)
-k_gemm3x_nt(const __grid_constant__ GemmMaps maps, int k_chunks, int FLUSH, int a_batch_rows, int b_batch_rows,
+k_gemm3x_nt(const __grid_constant__ GemmMaps maps, int k_chunks, int FLUSH, int sym, int a_batch_rows, int b_batch_rows,
             int M, int N, float *__restrict__ C, int64_t ldc, int64_t c_batch_stride)
 {
+    if (sym && dlco_gemm3x_tile_skipped(blockIdx.y * BM, blockIdx.x * BN)) return;   // mirrored by the consumer
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + STAGES * STAGE_BYTES);
@@ -176,10 +177,10 @@ k_gemm3x_nt(const __grid_constant__ GemmMaps maps, int k_chunks, int FLUSH, int 
 }  // namespace
 
 // A planes: (batch * a_rows_pad) x k_pad, B planes: (b_batch ? batch : 1) * b_rows_pad x k_pad.
-int dlco_launch_gemm3x_nt(dlco_ctx *ctx, const float *a_hi, const float *a_lo, int a_rows_pad,
-                          const float *b_hi, const float *b_lo, int b_rows_pad, int b_batched,
-                          int k_pad, int batch, int M, int N, float *d_C, int64_t ldc,
-                          int64_t c_batch_stride)
+static int gemm3x_launch(dlco_ctx *ctx, int sym, const float *a_hi, const float *a_lo, int a_rows_pad,
+                         const float *b_hi, const float *b_lo, int b_rows_pad, int b_batched,
+                         int k_pad, int batch, int M, int N, float *d_C, int64_t ldc,
+                         int64_t c_batch_stride)
 {
     DLCO_REQUIRE(k_pad % BK == 0 && k_pad > 0 && M > 0 && N > 0 && batch > 0, "gemm3x_nt: bad shapes");
     DLCO_REQUIRE((M + BM - 1) / BM * BM <= a_rows_pad && (N + BN - 1) / BN * BN <= b_rows_pad,
@@ -203,12 +204,30 @@ int dlco_launch_gemm3x_nt(dlco_ctx *ctx, const float *a_hi, const float *a_lo, i
         const char *e = getenv("DLCO_GEMM_FLUSH");
         flush = e && atoi(e) > 0 ? atoi(e) : 2;
     }
-    k_gemm3x_nt<<<grid, NTHREADS, SMEM_BYTES, ctx->stream>>>(maps, k_pad / BK, flush, a_rows_pad,
+    k_gemm3x_nt<<<grid, NTHREADS, SMEM_BYTES, ctx->stream>>>(maps, k_pad / BK, flush, sym, a_rows_pad,
                                                            b_batched ? b_rows_pad : 0, M, N, d_C, ldc,
                                                            c_batch_stride);
     dlco_prof_end(ctx);
     DLCO_CHECK_LAUNCH(ctx);
     return DLCO_OK;
+}
+
+int dlco_launch_gemm3x_nt(dlco_ctx *ctx, const float *a_hi, const float *a_lo, int a_rows_pad,
+                          const float *b_hi, const float *b_lo, int b_rows_pad, int b_batched,
+                          int k_pad, int batch, int M, int N, float *d_C, int64_t ldc,
+                          int64_t c_batch_stride)
+{
+    return gemm3x_launch(ctx, 0, a_hi, a_lo, a_rows_pad, b_hi, b_lo, b_rows_pad, b_batched, k_pad, batch, M, N, d_C,
+                         ldc, c_batch_stride);
+}
+
+int dlco_launch_gemm3x_nt_sym(dlco_ctx *ctx, const float *a_hi, const float *a_lo, int a_rows_pad,
+                              const float *b_hi, const float *b_lo, int b_rows_pad, int b_batched,
+                              int k_pad, int batch, int M, int N, float *d_C, int64_t ldc,
+                              int64_t c_batch_stride)
+{
+    return gemm3x_launch(ctx, 1, a_hi, a_lo, a_rows_pad, b_hi, b_lo, b_rows_pad, b_batched, k_pad, batch, M, N, d_C,
+                         ldc, c_batch_stride);
 }
 
 // ---- fp32 front end: split row-major A (M x K) and B (N x K) into padded tf32 planes ----------

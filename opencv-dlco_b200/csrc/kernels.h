@@ -63,6 +63,15 @@ static inline int dlco_gemm3x_rows_pad(int n)
     const int a = (n + 127) / 128 * 128, b = (n + 191) / 192 * 192;
     return a > b ? a : b;
 }
+// symmetric products: output tiles wholly below the diagonal are not computed (nor written)
+__host__ __device__ static inline bool dlco_gemm3x_tile_skipped(int row, int col)
+{
+    return (row / 128) * 128 >= (col / 192 + 1) * 192;
+}
+int dlco_launch_gemm3x_nt_sym(dlco_ctx *ctx, const float *a_hi, const float *a_lo, int a_rows_pad,
+                              const float *b_hi, const float *b_lo, int b_rows_pad, int b_batched,
+                              int k_pad, int batch, int M, int N, float *d_C, int64_t ldc,
+                              int64_t c_batch_stride);
 int dlco_launch_gemm3x_nt(dlco_ctx *ctx, const float *a_hi, const float *a_lo, int a_rows_pad,
                           const float *b_hi, const float *b_lo, int b_rows_pad, int b_batched,
                           int k_pad, int batch, int M, int N, float *d_C, int64_t ldc,

@@ -66,9 +66,27 @@ __device__ __forceinline__ float sign_inv_alpha(const double *__restrict__ parti
 
 enum { PREP_INIT = 0, PREP_COPY = 1, PREP_POLY = 2, PREP_SYM = 3, PREP_FINAL = 4 };
 
+// Every product of the iteration is symmetric, so the GEMMs skip the 128 x 192 output tiles that lie
+// wholly below the diagonal (dlco_gemm3x_tile_skipped: 5 of 15 at D = 544); a skipped element (a, b) is
+// read from its mirror (b, a).  32 divides both tile sizes, so a 32 x 32 block is either all computed
+// or all skipped.  load_logical stages block (a0.., b0..) of p in `tile` with coalesced reads either way
+// and returns whether the tile holds it transposed.
+__device__ __forceinline__ bool load_logical(float (*tile)[33], const float *__restrict__ p, int D, int a0, int b0,
+                                             bool sym, int tx, int ty)
+{
+    const bool tr = sym && dlco_gemm3x_tile_skipped(a0, b0);
+    const int r0 = tr ? b0 : a0, c0 = tr ? a0 : b0;
+    for (int r = ty; r < 32; r += 8) {
+        const int i = r0 + r, j = c0 + tx;
+        tile[r][tx] = (i < D && j < D) ? p[(size_t)i * D + j] : 0.f;
+    }
+    return tr;
+}
+
 // One 32 x 32 tile of configuration blockIdx.z: form the next operand elementwise, optionally store it
 // in fp32 (out) and always as K-major tf32 hi / lo planes (rows_pad x k_pad per configuration, zero
-// padding written too, so no plane ever needs a memset).
+// padding written too, so no plane ever needs a memset).  sym: in0 / in1 are GEMM outputs with skipped
+// lower tiles.
 //   PREP_INIT : v = in0 / ||in0||_F                        (X_0; out = X)
 //   PREP_COPY : v = in0                                    (planes of Y = X^2, or of A)
 //   PREP_POLY : v = a [i == j] + b in0 + c in1             (Z = a I + b Y + c Y^2)
@@ -77,22 +95,21 @@ enum { PREP_INIT = 0, PREP_COPY = 1, PREP_POLY = 2, PREP_SYM = 3, PREP_FINAL = 4
 template <int MODE>
 __global__ void __launch_bounds__(256)
 k_sign_prep(int D, int rows_pad, int k_pad, const float *__restrict__ in0, const float *__restrict__ in1,
-            const double *__restrict__ partial, int step, float *__restrict__ out, float *__restrict__ hi,
-            float *__restrict__ lo)
+            const double *__restrict__ partial, int step, int sym, float *__restrict__ out,
+            float *__restrict__ hi, float *__restrict__ lo)
 {
-    __shared__ float tile[32][33];
+    __shared__ float t0[32][33];
+    __shared__ float t1[32][33];
     const int g = blockIdx.z;
     const int j0 = blockIdx.x * 32, i0 = blockIdx.y * 32;
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     const size_t dd = (size_t)D * D;
     const float *p0 = in0 + (size_t)g * dd;
-    if (MODE == PREP_SYM || MODE == PREP_FINAL) {         // transposed tile through shared memory
-        for (int r = ty; r < 32; r += 8) {
-            const int i = j0 + r, j = i0 + tx;            // element (j0 + r, i0 + tx) of in0
-            tile[r][tx] = (i < D && j < D) ? p0[(size_t)i * D + j] : 0.f;
-        }
-        __syncthreads();
-    }
+    const bool tr0 = load_logical(t0, p0, D, i0, j0, sym != 0, tx, ty);
+    bool tr1 = false;
+    if (MODE == PREP_POLY) tr1 = load_logical(t1, in1 + (size_t)g * dd, D, i0, j0, sym != 0, tx, ty);
+    if (MODE == PREP_SYM || MODE == PREP_FINAL) tr1 = !load_logical(t1, p0, D, j0, i0, sym != 0, tx, ty);
+    __syncthreads();
     float inv_alpha = 0.f, ca = 0.f, cb = 0.f, cc = 0.f;
     if (MODE == PREP_INIT) inv_alpha = sign_inv_alpha(partial, g);
     if (MODE == PREP_POLY) { ca = c_sign_coef[step][0]; cb = c_sign_coef[step][1]; cc = c_sign_coef[step][2]; }
@@ -101,11 +118,13 @@ k_sign_prep(int D, int rows_pad, int k_pad, const float *__restrict__ in0, const
         float v = 0.f;
         if (i < D && j < D) {
             const size_t o = (size_t)i * D + j;
-            if (MODE == PREP_INIT) v = p0[o] * inv_alpha;
-            else if (MODE == PREP_COPY) v = p0[o];
-            else if (MODE == PREP_POLY) v = fmaf(cc, in1[(size_t)g * dd + o], fmaf(cb, p0[o], i == j ? ca : 0.f));
-            else if (MODE == PREP_SYM) v = 0.5f * (p0[o] + tile[tx][r]);
-            else v = 0.5f * (out[(size_t)g * dd + o] + 0.5f * (p0[o] + tile[tx][r]));
+            const float a = tr0 ? t0[tx][r] : t0[r][tx];           // in0 at (i, j)
+            const float b = tr1 ? t1[tx][r] : t1[r][tx];           // POLY: in1 at (i, j); SYM / FINAL: in0 at (j, i)
+            if (MODE == PREP_INIT) v = a * inv_alpha;
+            else if (MODE == PREP_COPY) v = a;
+            else if (MODE == PREP_POLY) v = fmaf(cc, b, fmaf(cb, a, i == j ? ca : 0.f));
+            else if (MODE == PREP_SYM) v = 0.5f * (a + b);
+            else v = 0.5f * (out[(size_t)g * dd + o] + 0.5f * (a + b));
             if (MODE == PREP_INIT || MODE == PREP_SYM || MODE == PREP_FINAL) out[(size_t)g * dd + o] = v;
         }
         if (MODE != PREP_FINAL && i < rows_pad && j < k_pad) {
@@ -140,10 +159,10 @@ k_sign_rank(int D, const float *__restrict__ S, const double *__restrict__ parti
 
 template <int MODE>
 static int sign_prep(dlco_ctx *ctx, int D, int nCfg, int rows_pad, int k_pad, const float *in0, const float *in1,
-                     const double *partial, int step, float *out, float *hi, float *lo)
+                     const double *partial, int step, int sym, float *out, float *hi, float *lo)
 {
     dim3 grid(MODE == PREP_FINAL ? (D + 31) / 32 : k_pad / 32, MODE == PREP_FINAL ? (D + 31) / 32 : rows_pad / 32, nCfg);
-    k_sign_prep<MODE><<<grid, 256, 0, ctx->stream>>>(D, rows_pad, k_pad, in0, in1, partial, step, out, hi, lo);
+    k_sign_prep<MODE><<<grid, 256, 0, ctx->stream>>>(D, rows_pad, k_pad, in0, in1, partial, step, sym, out, hi, lo);
     DLCO_CHECK_LAUNCH(ctx);
     return DLCO_OK;
 }
@@ -167,23 +186,23 @@ int dlco_pj_psd_sign(dlco_ctx *ctx, int D, int nCfg, float *d_A, int32_t *d_rank
     int r;
     k_sign_norm<<<dim3(NORM_BLOCKS, nCfg), 256, 0, ctx->stream>>>(d_A, dd, partial);
     DLCO_CHECK_LAUNCH(ctx);
-    r = sign_prep<PREP_INIT>(ctx, D, nCfg, rows_pad, k_pad, d_A, nullptr, partial, 0, X, p1h, p1l);
+    r = sign_prep<PREP_INIT>(ctx, D, nCfg, rows_pad, k_pad, d_A, nullptr, partial, 0, 0, X, p1h, p1l);
     for (int k = 0; k < SIGN_STEPS && r == DLCO_OK; k++) {
         // Y = X X^T (= X^2: X is kept symmetric)
-        r = dlco_launch_gemm3x_nt(ctx, p1h, p1l, rows_pad, p1h, p1l, rows_pad, 1, k_pad, nCfg, D, D, Y, D, cs);
-        if (r == DLCO_OK) r = sign_prep<PREP_COPY>(ctx, D, nCfg, rows_pad, k_pad, Y, nullptr, partial, k, nullptr, p2h, p2l);
+        r = dlco_launch_gemm3x_nt_sym(ctx, p1h, p1l, rows_pad, p1h, p1l, rows_pad, 1, k_pad, nCfg, D, D, Y, D, cs);
+        if (r == DLCO_OK) r = sign_prep<PREP_COPY>(ctx, D, nCfg, rows_pad, k_pad, Y, nullptr, partial, k, 1, nullptr, p2h, p2l);
         // T = Y Y^T = X^4
-        if (r == DLCO_OK) r = dlco_launch_gemm3x_nt(ctx, p2h, p2l, rows_pad, p2h, p2l, rows_pad, 1, k_pad, nCfg, D, D, T, D, cs);
+        if (r == DLCO_OK) r = dlco_launch_gemm3x_nt_sym(ctx, p2h, p2l, rows_pad, p2h, p2l, rows_pad, 1, k_pad, nCfg, D, D, T, D, cs);
         // Z = a I + b Y + c T
-        if (r == DLCO_OK) r = sign_prep<PREP_POLY>(ctx, D, nCfg, rows_pad, k_pad, Y, T, partial, k, nullptr, p2h, p2l);
+        if (r == DLCO_OK) r = sign_prep<PREP_POLY>(ctx, D, nCfg, rows_pad, k_pad, Y, T, partial, k, 1, nullptr, p2h, p2l);
         // T = X Z^T, X <- sym(T)
-        if (r == DLCO_OK) r = dlco_launch_gemm3x_nt(ctx, p1h, p1l, rows_pad, p2h, p2l, rows_pad, 1, k_pad, nCfg, D, D, T, D, cs);
-        if (r == DLCO_OK) r = sign_prep<PREP_SYM>(ctx, D, nCfg, rows_pad, k_pad, T, nullptr, partial, k, X, p1h, p1l);
+        if (r == DLCO_OK) r = dlco_launch_gemm3x_nt_sym(ctx, p1h, p1l, rows_pad, p2h, p2l, rows_pad, 1, k_pad, nCfg, D, D, T, D, cs);
+        if (r == DLCO_OK) r = sign_prep<PREP_SYM>(ctx, D, nCfg, rows_pad, k_pad, T, nullptr, partial, k, 1, X, p1h, p1l);
     }
     // A+ = (A + sym(A S)) / 2
-    if (r == DLCO_OK) r = sign_prep<PREP_COPY>(ctx, D, nCfg, rows_pad, k_pad, d_A, nullptr, partial, 0, nullptr, p2h, p2l);
-    if (r == DLCO_OK) r = dlco_launch_gemm3x_nt(ctx, p2h, p2l, rows_pad, p1h, p1l, rows_pad, 1, k_pad, nCfg, D, D, T, D, cs);
-    if (r == DLCO_OK) r = sign_prep<PREP_FINAL>(ctx, D, nCfg, rows_pad, k_pad, T, nullptr, partial, 0, d_A, nullptr, nullptr);
+    if (r == DLCO_OK) r = sign_prep<PREP_COPY>(ctx, D, nCfg, rows_pad, k_pad, d_A, nullptr, partial, 0, 0, nullptr, p2h, p2l);
+    if (r == DLCO_OK) r = dlco_launch_gemm3x_nt_sym(ctx, p2h, p2l, rows_pad, p1h, p1l, rows_pad, 1, k_pad, nCfg, D, D, T, D, cs);
+    if (r == DLCO_OK) r = sign_prep<PREP_FINAL>(ctx, D, nCfg, rows_pad, k_pad, T, nullptr, partial, 0, 1, d_A, nullptr, nullptr);
     if (r != DLCO_OK) return r;
     k_sign_rank<<<nCfg, 256, 0, ctx->stream>>>(D, X, partial, d_rank);
     DLCO_CHECK_LAUNCH(ctx);
@@ -263,7 +282,7 @@ int dlco_pj_margins_quad_grid(dlco_ctx *ctx, const float *d_dists, int64_t ld, i
     float *PX = (float *)dlco_scratch(ctx, 42, 2 * xplane * sizeof(float));
     float *Ct = (float *)dlco_scratch(ctx, 38, (size_t)nCfg * D * (nk > D ? nk : D) * sizeof(float));
     if (!PA || !PX || !Ct) return DLCO_ENOMEM;
-    int r = sign_prep<PREP_COPY>(ctx, D, nCfg, rows_pad, k_pad, d_A, nullptr, nullptr, 0, nullptr, PA, PA + plane);
+    int r = sign_prep<PREP_COPY>(ctx, D, nCfg, rows_pad, k_pad, d_A, nullptr, nullptr, 0, 0, nullptr, PA, PA + plane);
     if (r != DLCO_OK) return r;
     k_rows_planes<<<dim3(k_pad / 32, xrows_pad / 32), 256, 0, ctx->stream>>>(d_dists, ld, D, d_rows, nk, xrows_pad, k_pad,
                                                                           PX, PX + xplane);
