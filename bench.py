@@ -420,6 +420,10 @@ def main():
             rows = {
                 "pj_learn_rda_iters_per_s_1cfg": r["pj_step"]["iters_per_s"],
                 "pj_learn_sweep_cfg_iters_per_s_45cfg": r["pj_sweep_step"]["cfg_iters_per_s"],
+                "pj_learn_rda_iters_per_s_1cfg_sign_prox": r["pj_step_sign_1cfg"]["cfg_iters_per_s"],
+                "pj_learn_sweep_cfg_iters_per_s_45cfg_sign_prox": r["pj_sweep_step_sign"]["cfg_iters_per_s"],
+                "pj_sign_prox_gemm_frac_of_3xtf32_peak": r["pj_sweep_step_sign"]["gemm_frac_of_3xtf32_peak"],
+                "uprjdist_build_pairs_per_s": r["uprjdist_build"]["pairs_per_s"],
                 "pj_syrk_grouped_frac_of_3xtf32_peak": r["pj_grad_grid"]["syrk_frac_of_3xtf32_peak"],
                 "pr_learn_rda_steps_per_s_1cfg": r["pr_rda_1cfg"]["steps_per_s_per_cfg"],
                 "pr_learn_rda_cfg_steps_per_s_256cfg": r["pr_rda_256cfg"]["cfg_steps_per_s"],

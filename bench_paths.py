@@ -199,7 +199,7 @@ def run(ctx, n_train=500000, n_test=100000, quick=False, D=544, n_pj_cfg=45, n_p
     del S
     torch.cuda.empty_cache()
     # the same sweep with the prox's projection by the tensor-core matrix-sign iteration (no eig per iteration)
-    for tag, mm, gg in (("pj_sweep_step_sign", mus, gammas), ("pj_step_sign_1cfg", mus[:1], gammas[:1])):
+    for tag, mm, gg in (("pj_sweep_step_sign", mus, gms), ("pj_step_sign_1cfg", mus[2:3], gms[2:3])):
         S = learn.PjSweep(ctx, ud, ulabels, mm, gg, split=split, prox="sign")
         for _ in range(5):
             S.step()

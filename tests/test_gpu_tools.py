@@ -219,6 +219,16 @@ def test_pipeline(workspace, gpu_ctx):
     assert np.abs(W_s.T.astype(np.float64) @ W_s - A_s).max() <= 1e-5 * max(np.abs(A_s).max(), 1e-30)
     f2 = H5File(os.path.join(sw, "train-0.0020-0.1-pj.h5"))
     assert f2.read("A").shape == (D, D)
+    # -prox sign: the projection by the tensor-core sign iteration; same files, model within the bar
+    rc, so4, se = run("pj-sweep", os.path.join(tmp, "train-unproj.h5"), os.path.join(tmp, "sweep_sign"), "-mu", "0.001,0.0020",
+                      "-gamma", "0.1", "-iters", 300, "-prox", "sign")
+    assert rc == 0, se
+    fg = H5File(os.path.join(tmp, "sweep_sign", "train-0.001-0.1-pj.h5"))
+    A_g, W_g = fg.read("A"), fg.read("W")
+    assert W_g.shape == W_s.shape and np.abs(A_g - A_s).max() <= 1e-4 * np.abs(A_s).max()
+    assert np.abs(W_g.T.astype(np.float64) @ W_g - A_g).max() <= 3e-5 * max(np.abs(A_g).max(), 1e-30)
+    c = toks(open(os.path.join(tmp, "sweep_sign", "logging", "train-0.001-0.1-pj.log")).read())
+    assert len(c) == len(b) and [ln[0] for ln in c] == [ln[0] for ln in b]
     # -shard r/n partitions the grid
     rc, so3, se = run("pj-sweep", os.path.join(tmp, "train-unproj.h5"), os.path.join(tmp, "sweep1"), "-mu", "0.001,0.0020",
                       "-gamma", "0.1", "-iters", 20, "-shard", "1/2")

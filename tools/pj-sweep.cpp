@@ -10,8 +10,11 @@
 // with pj-learn's stdout lines -- so 09-pjstats.sh / 10-pj-top.sh read them unchanged.
 //
 //   pj-sweep src_h5_dist_file out_dir -mu m1,m2,.. -gamma g1,g2,.. [-iters n] [-ds name]
-//            [-gpu i] [-shard r/n]
+//            [-gpu i] [-shard r/n] [-prox eig|sign]
 // -shard r/n: this process owns grid points c with c % n == r (one process per GPU of the box).
+// -prox eig (default): the reference's prox, an eigen-decomposition per iteration (src/pj-learn.cpp:434-490).
+// -prox sign: the projection by the tensor-core matrix-sign iteration (dlco_pj_rda_step_grid_sign); W is
+//             rebuilt from the projected A (dlco_pj_factor_grid) at the validation points only.
 #include "common.hpp"
 
 #include <cfloat>
@@ -48,6 +51,7 @@ int main(int argc, char **argv)
     unsigned int n_iter = 50000;
     const unsigned int log_step = 100, sz_batch = 200;
     int gpu = 0, shard_r = 0, shard_n = 1;
+    bool prox_sign = false;
     bool help = false;
     const char *dists = nullptr, *outdir = nullptr, *mus = nullptr, *gammas = nullptr, *ds_name = nullptr;
     for (int i = 1; i < argc; i++) {
@@ -58,6 +62,13 @@ int main(int argc, char **argv)
             if (i + 1 < argc && !strcmp(argv[i], "-iters")) { n_iter = (unsigned int)atoi(argv[++i]); continue; }
             if (i + 1 < argc && !strcmp(argv[i], "-ds")) { ds_name = argv[++i]; continue; }
             if (i + 1 < argc && !strcmp(argv[i], "-gpu")) { gpu = atoi(argv[++i]); continue; }
+            if (i + 1 < argc && !strcmp(argv[i], "-prox")) {
+                const char *v = argv[++i];
+                if (!strcmp(v, "sign")) prox_sign = true;
+                else if (!strcmp(v, "eig")) prox_sign = false;
+                else { printf("ERROR: Invalid -prox value (eig | sign).\n"); return 1; }
+                continue;
+            }
             if (i + 1 < argc && !strcmp(argv[i], "-shard")) {
                 if (sscanf(argv[++i], "%d/%d", &shard_r, &shard_n) != 2 || shard_n < 1 || shard_r < 0 || shard_r >= shard_n) {
                     printf("ERROR: -shard wants r/n with 0 <= r < n.\n");
@@ -161,12 +172,21 @@ int main(int argc, char **argv)
         double t_train = now_sec();
         const double t_all = now_sec();
         for (unsigned int t = 0; t <= n_iter; t++) {
-            check(dlco_pj_rda_step_grid(ctx.h, d_dists.p, D, D, d_pos.p, (int32_t)sp.n_pos_trn, d_neg.p, (int32_t)sp.n_neg_trn,
-                                        (int)sz_batch, d_rng.p, n_cfg, d_mu.p, d_gamma.p, t, d_W.p, d_A.p, d_dfavg.p, d_rank.p,
-                                        d_work.p),
-                  "dlco_pj_rda_step_grid");
+            if (prox_sign)
+                check(dlco_pj_rda_step_grid_sign(ctx.h, d_dists.p, D, D, d_pos.p, (int32_t)sp.n_pos_trn, d_neg.p,
+                                                 (int32_t)sp.n_neg_trn, (int)sz_batch, d_rng.p, n_cfg, d_mu.p, d_gamma.p, t,
+                                                 d_A.p, d_dfavg.p, d_rank.p, d_work.p),
+                      "dlco_pj_rda_step_grid_sign");
+            else
+                check(dlco_pj_rda_step_grid(ctx.h, d_dists.p, D, D, d_pos.p, (int32_t)sp.n_pos_trn, d_neg.p, (int32_t)sp.n_neg_trn,
+                                            (int)sz_batch, d_rng.p, n_cfg, d_mu.p, d_gamma.p, t, d_W.p, d_A.p, d_dfavg.p, d_rank.p,
+                                            d_work.p),
+                      "dlco_pj_rda_step_grid");
             if (step == log_step) {
-                check(dlco_pj_grid_check(ctx.h, n_cfg), "dlco_pj_grid_check");      // synchronises
+                if (prox_sign)      // W of the projected A for validation, statistics and the saved model (synchronises)
+                    check(dlco_pj_factor_grid(ctx.h, D, n_cfg, d_A.p, d_rank.p, d_W.p, (int64_t)DD, d_work.p), "dlco_pj_factor_grid");
+                else
+                    check(dlco_pj_grid_check(ctx.h, n_cfg), "dlco_pj_grid_check");      // synchronises
                 d_rank.download(ranks.data(), n_cfg);
                 const double ttime = now_sec() - t_train;
                 for (int c = 0; c < n_cfg; c++) {
