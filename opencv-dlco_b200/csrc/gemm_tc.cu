@@ -34,9 +34,14 @@ struct __align__(64) GemmMaps {
 // accumulated MMA, see pool_tc.cu): the accumulation is cut every FLUSH chunks, the epilogue warps
 // drain the partial sums and add them in round-to-nearest registers while the MMAs continue into the
 // other accumulator.  Matters for the chained GEMMs of the matrix-sign iteration (pj_sign.cu).
+// F16 = false: tf32 hi / lo planes (3xTF32, 32 floats per 128-byte K chunk).
+// F16 = true : fp16 hi / lo planes of power-of-two-scaled operands (64 halfs per chunk, kind::f16: the
+//              same 22 mantissa bits at twice the tensor rate and half the operand bytes, as in
+//              pool_tc.cu); the accumulator is multiplied by out_scale = 1 / (scale_a * scale_b).
+template <bool F16>
 __global__ void __launch_bounds__(NTHREADS, 1)
 k_gemm3x_nt(const __grid_constant__ GemmMaps maps, int k_chunks, int FLUSH, int sym, int a_batch_rows, int b_batch_rows,
-            int M, int N, float *__restrict__ C, int64_t ldc, int64_t c_batch_stride)
+            int M, int N, float *__restrict__ C, int64_t ldc, int64_t c_batch_stride, float out_scale)
 {
     if (sym && dlco_gemm3x_tile_skipped(blockIdx.y * BM, blockIdx.x * BN)) return;   // mirrored by the consumer
     extern __shared__ uint8_t smem_raw[];
@@ -81,16 +86,17 @@ k_gemm3x_nt(const __grid_constant__ GemmMaps maps, int k_chunks, int FLUSH, int 
                 mbar_wait(&empty[stage], phase ^ 1);
                 uint8_t *st = smem + stage * STAGE_BYTES;
                 mbar_expect_tx(&full[stage], STAGE_BYTES);
-                tma_load_2d(st, &maps.a_hi, &full[stage], kc * BK, arow);
-                tma_load_2d(st + A_BYTES, &maps.a_lo, &full[stage], kc * BK, arow);
-                tma_load_2d(st + 2 * A_BYTES, &maps.b_hi, &full[stage], kc * BK, brow);
-                tma_load_2d(st + 2 * A_BYTES + B_BYTES, &maps.b_lo, &full[stage], kc * BK, brow);
+                const int kcol = kc * (F16 ? 2 * BK : BK);          // elements per 128-byte chunk
+                tma_load_2d(st, &maps.a_hi, &full[stage], kcol, arow);
+                tma_load_2d(st + A_BYTES, &maps.a_lo, &full[stage], kcol, arow);
+                tma_load_2d(st + 2 * A_BYTES, &maps.b_hi, &full[stage], kcol, brow);
+                tma_load_2d(st + 2 * A_BYTES + B_BYTES, &maps.b_lo, &full[stage], kcol, brow);
                 if (++stage == STAGES) { stage = 0; phase ^= 1; }
             }
         }
     } else if (warp == 1) {
         if (lane == 0) {
-            constexpr uint32_t idesc = umma_idesc_tf32(BM, BN);
+            constexpr uint32_t idesc = F16 ? umma_idesc_f16(BM, BN) : umma_idesc_tf32(BM, BN);
             int stage = 0;
             uint32_t phase = 0;
             uint32_t it = 0;                       // drains so far (accumulator = it & 1)
@@ -111,9 +117,15 @@ k_gemm3x_nt(const __grid_constant__ GemmMaps maps, int k_chunks, int FLUSH, int 
 #pragma unroll
                 for (int k = 0; k < BK / 8; k++) {
                     const uint64_t ko = (uint64_t)(k * 2);
-                    umma_tf32(d_tmem, d_alo + ko, d_bhi + ko, idesc, (in_flush | k) != 0);
-                    umma_tf32(d_tmem, d_ahi + ko, d_blo + ko, idesc, 1);
-                    umma_tf32(d_tmem, d_ahi + ko, d_bhi + ko, idesc, 1);
+                    if (F16) {
+                        umma_f16(d_tmem, d_alo + ko, d_bhi + ko, idesc, (in_flush | k) != 0);
+                        umma_f16(d_tmem, d_ahi + ko, d_blo + ko, idesc, 1);
+                        umma_f16(d_tmem, d_ahi + ko, d_bhi + ko, idesc, 1);
+                    } else {
+                        umma_tf32(d_tmem, d_alo + ko, d_bhi + ko, idesc, (in_flush | k) != 0);
+                        umma_tf32(d_tmem, d_ahi + ko, d_blo + ko, idesc, 1);
+                        umma_tf32(d_tmem, d_ahi + ko, d_bhi + ko, idesc, 1);
+                    }
                 }
                 umma_commit(&empty[stage]);
                 if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -150,6 +162,10 @@ k_gemm3x_nt(const __grid_constant__ GemmMaps maps, int k_chunks, int FLUSH, int 
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&tempty[it & 1]);
+        }
+        if (F16) {
+#pragma unroll
+            for (int e = 0; e < EN; e++) acc[e] *= out_scale;
         }
         const int row = mt * BM + q * 32 + lane;
         const int col0 = nt * BN + half * EN;
@@ -194,7 +210,8 @@ static int gemm3x_launch(dlco_ctx *ctx, int sym, const float *a_hi, const float 
     if (r != DLCO_OK) return r;
     static bool attr = false;
     if (!attr) {
-        DLCO_CUDA(cudaFuncSetAttribute(k_gemm3x_nt, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+        DLCO_CUDA(cudaFuncSetAttribute(k_gemm3x_nt<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+        DLCO_CUDA(cudaFuncSetAttribute(k_gemm3x_nt<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
         attr = true;
     }
     dim3 grid((N + BN - 1) / BN, (M + BM - 1) / BM, batch);
@@ -204,9 +221,9 @@ static int gemm3x_launch(dlco_ctx *ctx, int sym, const float *a_hi, const float 
         const char *e = getenv("DLCO_GEMM_FLUSH");
         flush = e && atoi(e) > 0 ? atoi(e) : 2;
     }
-    k_gemm3x_nt<<<grid, NTHREADS, SMEM_BYTES, ctx->stream>>>(maps, k_pad / BK, flush, sym, a_rows_pad,
-                                                           b_batched ? b_rows_pad : 0, M, N, d_C, ldc,
-                                                           c_batch_stride);
+    k_gemm3x_nt<false><<<grid, NTHREADS, SMEM_BYTES, ctx->stream>>>(maps, k_pad / BK, flush, sym, a_rows_pad,
+                                                                  b_batched ? b_rows_pad : 0, M, N, d_C, ldc,
+                                                                  c_batch_stride, 1.0f);
     dlco_prof_end(ctx);
     DLCO_CHECK_LAUNCH(ctx);
     return DLCO_OK;
@@ -228,6 +245,37 @@ int dlco_launch_gemm3x_nt_sym(dlco_ctx *ctx, const float *a_hi, const float *a_l
 {
     return gemm3x_launch(ctx, 1, a_hi, a_lo, a_rows_pad, b_hi, b_lo, b_rows_pad, b_batched, k_pad, batch, M, N, d_C,
                          ldc, c_batch_stride);
+}
+
+// fp16 hi / lo planes (K-major, k_pad halfs a multiple of 64, rows padded as for the tf32 planes), symmetric
+// product (tiles below the diagonal skipped), C = out_scale * A B^T
+int dlco_launch_gemm3h_nt_sym(dlco_ctx *ctx, const void *a_hi, const void *a_lo, int a_rows_pad, const void *b_hi,
+                              const void *b_lo, int b_rows_pad, int k_pad, int batch, int M, int N, float out_scale,
+                              float *d_C, int64_t ldc, int64_t c_batch_stride)
+{
+    DLCO_REQUIRE(k_pad % (2 * BK) == 0 && k_pad > 0 && M > 0 && N > 0 && batch > 0, "gemm3h_nt: bad shapes");
+    DLCO_REQUIRE((M + BM - 1) / BM * BM <= a_rows_pad && (N + BN - 1) / BN * BN <= b_rows_pad,
+                 "gemm3h_nt: operand rows must be padded to whole %d / %d-row tiles", BM, BN);
+    GemmMaps maps;
+    int r = dlco_make_tmap_2d_ex(&maps.a_hi, a_hi, 2, (uint64_t)batch * a_rows_pad, k_pad, BM, 2 * BK);
+    if (r == DLCO_OK) r = dlco_make_tmap_2d_ex(&maps.a_lo, a_lo, 2, (uint64_t)batch * a_rows_pad, k_pad, BM, 2 * BK);
+    if (r == DLCO_OK) r = dlco_make_tmap_2d_ex(&maps.b_hi, b_hi, 2, (uint64_t)batch * b_rows_pad, k_pad, BN, 2 * BK);
+    if (r == DLCO_OK) r = dlco_make_tmap_2d_ex(&maps.b_lo, b_lo, 2, (uint64_t)batch * b_rows_pad, k_pad, BN, 2 * BK);
+    if (r != DLCO_OK) return r;
+    static bool attr = false;
+    if (!attr) {
+        DLCO_CUDA(cudaFuncSetAttribute(k_gemm3x_nt<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+        attr = true;
+    }
+    const char *e = getenv("DLCO_GEMM_FLUSH");
+    const int flush = e && atoi(e) > 0 ? atoi(e) : 1;      // K = 64 per chunk here: drain every chunk
+    dim3 grid((N + BN - 1) / BN, (M + BM - 1) / BM, batch);
+    dlco_prof_begin(ctx, 2);
+    k_gemm3x_nt<true><<<grid, NTHREADS, SMEM_BYTES, ctx->stream>>>(maps, k_pad / (2 * BK), flush, 1, a_rows_pad, b_rows_pad, M,
+                                                                 N, d_C, ldc, c_batch_stride, out_scale);
+    dlco_prof_end(ctx);
+    DLCO_CHECK_LAUNCH(ctx);
+    return DLCO_OK;
 }
 
 // ---- fp32 front end: split row-major A (M x K) and B (N x K) into padded tf32 planes ----------

@@ -16,6 +16,8 @@
 // iteration); the 28 GEMMs are ~0.45 TFLOP of tensor work.
 #include "common.cuh"
 #include "kernels.h"
+#include <cuda_fp16.h>
+#include <stdlib.h>
 
 namespace {
 
@@ -64,6 +66,13 @@ __device__ __forceinline__ float sign_inv_alpha(const double *__restrict__ parti
     return t > 0.0 ? (float)(1.0 / sqrt(t)) : 0.f;
 }
 
+__device__ __forceinline__ float sign_alpha(const double *__restrict__ partial, int g)
+{
+    double t = 0.0;
+    for (int b = 0; b < NORM_BLOCKS; b++) t += partial[(size_t)g * NORM_BLOCKS + b];
+    return (float)sqrt(t);
+}
+
 enum { PREP_INIT = 0, PREP_COPY = 1, PREP_POLY = 2, PREP_SYM = 3, PREP_FINAL = 4 };
 
 // Every product of the iteration is symmetric, so the GEMMs skip the 128 x 192 output tiles that lie
@@ -92,11 +101,13 @@ __device__ __forceinline__ bool load_logical(float (*tile)[33], const float *__r
 //   PREP_POLY : v = a [i == j] + b in0 + c in1             (Z = a I + b Y + c Y^2)
 //   PREP_SYM  : v = (in0[i][j] + in0[j][i]) / 2            (X <- sym(X Z); out = X)
 //   PREP_FINAL: out = (out + sym(in0)) / 2, no planes      (A+ = (A + sym(A S)) / 2, in place)
-template <int MODE>
+// F16: planes are fp16 hi / lo of v * pscale (a power of two that keeps the operand inside fp16's normal
+// range: |X|, |Y| <= 1.01 -> 2^13, |Z| <= 53 -> 2^9), else tf32 hi / lo of v.
+template <int MODE, bool F16>
 __global__ void __launch_bounds__(256)
 k_sign_prep(int D, int rows_pad, int k_pad, const float *__restrict__ in0, const float *__restrict__ in1,
-            const double *__restrict__ partial, int step, int sym, float *__restrict__ out,
-            float *__restrict__ hi, float *__restrict__ lo)
+            const double *__restrict__ partial, int step, int sym, float pscale, float *__restrict__ out,
+            void *__restrict__ hi, void *__restrict__ lo)
 {
     __shared__ float t0[32][33];
     __shared__ float t1[32][33];
@@ -110,8 +121,9 @@ k_sign_prep(int D, int rows_pad, int k_pad, const float *__restrict__ in0, const
     if (MODE == PREP_POLY) tr1 = load_logical(t1, in1 + (size_t)g * dd, D, i0, j0, sym != 0, tx, ty);
     if (MODE == PREP_SYM || MODE == PREP_FINAL) tr1 = !load_logical(t1, p0, D, j0, i0, sym != 0, tx, ty);
     __syncthreads();
-    float inv_alpha = 0.f, ca = 0.f, cb = 0.f, cc = 0.f;
+    float inv_alpha = 0.f, alpha = 0.f, ca = 0.f, cb = 0.f, cc = 0.f;
     if (MODE == PREP_INIT) inv_alpha = sign_inv_alpha(partial, g);
+    if (MODE == PREP_FINAL) alpha = sign_alpha(partial, g);
     if (MODE == PREP_POLY) { ca = c_sign_coef[step][0]; cb = c_sign_coef[step][1]; cc = c_sign_coef[step][2]; }
     for (int r = ty; r < 32; r += 8) {
         const int i = i0 + r, j = j0 + tx;
@@ -124,15 +136,22 @@ k_sign_prep(int D, int rows_pad, int k_pad, const float *__restrict__ in0, const
             else if (MODE == PREP_COPY) v = a;
             else if (MODE == PREP_POLY) v = fmaf(cc, b, fmaf(cb, a, i == j ? ca : 0.f));
             else if (MODE == PREP_SYM) v = 0.5f * (a + b);
-            else v = 0.5f * (out[(size_t)g * dd + o] + 0.5f * (a + b));
-            if (MODE == PREP_INIT || MODE == PREP_SYM || MODE == PREP_FINAL) out[(size_t)g * dd + o] = v;
+            else v = 0.5f * (out[(size_t)g * dd + o] + alpha * (0.5f * (a + b)));   // in0 = (A / alpha) S
+            if ((MODE == PREP_INIT || MODE == PREP_SYM || MODE == PREP_FINAL) && out) out[(size_t)g * dd + o] = v;
         }
         if (MODE != PREP_FINAL && i < rows_pad && j < k_pad) {
-            float h, l;
-            tf32_split(v, h, l);
             const size_t po = ((size_t)g * rows_pad + i) * k_pad + j;
-            hi[po] = h;
-            lo[po] = l;
+            if (F16) {
+                const float sv = v * pscale;
+                const __half h = __float2half_rn(sv);
+                reinterpret_cast<__half *>(hi)[po] = h;
+                reinterpret_cast<__half *>(lo)[po] = __float2half_rn(sv - __half2float(h));
+            } else {
+                float h, l;
+                tf32_split(v, h, l);
+                reinterpret_cast<float *>(hi)[po] = h;
+                reinterpret_cast<float *>(lo)[po] = l;
+            }
         }
     }
 }
@@ -158,51 +177,67 @@ k_sign_rank(int D, const float *__restrict__ S, const double *__restrict__ parti
 }  // namespace
 
 template <int MODE>
-static int sign_prep(dlco_ctx *ctx, int D, int nCfg, int rows_pad, int k_pad, const float *in0, const float *in1,
-                     const double *partial, int step, int sym, float *out, float *hi, float *lo)
+static int sign_prep(dlco_ctx *ctx, bool f16, int D, int nCfg, int rows_pad, int k_pad, const float *in0, const float *in1,
+                     const double *partial, int step, int sym, float pscale, float *out, void *hi, void *lo)
 {
     dim3 grid(MODE == PREP_FINAL ? (D + 31) / 32 : k_pad / 32, MODE == PREP_FINAL ? (D + 31) / 32 : rows_pad / 32, nCfg);
-    k_sign_prep<MODE><<<grid, 256, 0, ctx->stream>>>(D, rows_pad, k_pad, in0, in1, partial, step, sym, out, hi, lo);
+    if (f16)
+        k_sign_prep<MODE, true><<<grid, 256, 0, ctx->stream>>>(D, rows_pad, k_pad, in0, in1, partial, step, sym, pscale, out, hi, lo);
+    else
+        k_sign_prep<MODE, false><<<grid, 256, 0, ctx->stream>>>(D, rows_pad, k_pad, in0, in1, partial, step, sym, pscale, out, hi, lo);
     DLCO_CHECK_LAUNCH(ctx);
     return DLCO_OK;
+}
+
+// DLCO_SIGN_PLANES=tf32 keeps the iteration on 3xTF32 planes (cross-check); default fp16 hi / lo
+static bool sign_f16()
+{
+    const char *e = getenv("DLCO_SIGN_PLANES");
+    return !(e && strcmp(e, "tf32") == 0);
 }
 
 // d_A: nCfg symmetric D x D matrices, replaced by their PSD parts; d_rank[g] = rank(A+_g);
 // d_S (optional, nCfg x D x D): sign(A_g) as computed.
 int dlco_pj_psd_sign(dlco_ctx *ctx, int D, int nCfg, float *d_A, int32_t *d_rank, float *d_S)
 {
+    const bool f16 = sign_f16();
     const size_t dd = (size_t)D * D;
-    const int rows_pad = dlco_gemm3x_rows_pad(D), k_pad = (D + 31) / 32 * 32;
-    const size_t plane = (size_t)nCfg * rows_pad * k_pad;
+    const int rows_pad = dlco_gemm3x_rows_pad(D), k_pad = f16 ? (D + 63) / 64 * 64 : (D + 31) / 32 * 32;
+    const size_t plane = (size_t)nCfg * rows_pad * k_pad;              // elements per plane
+    const size_t esz = f16 ? 2 : 4;
     float *X = d_S ? d_S : (float *)dlco_scratch(ctx, 36, nCfg * dd * sizeof(float));
     float *Y = (float *)dlco_scratch(ctx, 37, nCfg * dd * sizeof(float));
     float *T = (float *)dlco_scratch(ctx, 38, nCfg * dd * sizeof(float));
-    float *P1 = (float *)dlco_scratch(ctx, 39, 2 * plane * sizeof(float));
-    float *P2 = (float *)dlco_scratch(ctx, 40, 2 * plane * sizeof(float));
+    uint8_t *P1 = (uint8_t *)dlco_scratch(ctx, 39, 2 * plane * esz);
+    uint8_t *P2 = (uint8_t *)dlco_scratch(ctx, 40, 2 * plane * esz);
     double *partial = (double *)dlco_scratch(ctx, 41, (size_t)nCfg * NORM_BLOCKS * sizeof(double));
     if (!X || !Y || !T || !P1 || !P2 || !partial) return DLCO_ENOMEM;
-    float *p1h = P1, *p1l = P1 + plane, *p2h = P2, *p2l = P2 + plane;
+    void *p1h = P1, *p1l = P1 + plane * esz, *p2h = P2, *p2l = P2 + plane * esz;
     const int64_t cs = (int64_t)dd;
+    const float sx = 8192.f, sz = 512.f;                               // plane scales (fp16 route)
+    // one product C = A B^T from planes; symmetric, tiles below the diagonal skipped
+    auto gemm = [&](const void *ah, const void *al, const void *bh, const void *bl, float sa, float sb, float *C) -> int {
+        if (f16)
+            return dlco_launch_gemm3h_nt_sym(ctx, ah, al, rows_pad, bh, bl, rows_pad, k_pad, nCfg, D, D, 1.0f / (sa * sb), C, D, cs);
+        return dlco_launch_gemm3x_nt_sym(ctx, (const float *)ah, (const float *)al, rows_pad, (const float *)bh,
+                                         (const float *)bl, rows_pad, 1, k_pad, nCfg, D, D, C, D, cs);
+    };
     int r;
     k_sign_norm<<<dim3(NORM_BLOCKS, nCfg), 256, 0, ctx->stream>>>(d_A, dd, partial);
     DLCO_CHECK_LAUNCH(ctx);
-    r = sign_prep<PREP_INIT>(ctx, D, nCfg, rows_pad, k_pad, d_A, nullptr, partial, 0, 0, X, p1h, p1l);
+    r = sign_prep<PREP_INIT>(ctx, f16, D, nCfg, rows_pad, k_pad, d_A, nullptr, partial, 0, 0, sx, X, p1h, p1l);
     for (int k = 0; k < SIGN_STEPS && r == DLCO_OK; k++) {
-        // Y = X X^T (= X^2: X is kept symmetric)
-        r = dlco_launch_gemm3x_nt_sym(ctx, p1h, p1l, rows_pad, p1h, p1l, rows_pad, 1, k_pad, nCfg, D, D, Y, D, cs);
-        if (r == DLCO_OK) r = sign_prep<PREP_COPY>(ctx, D, nCfg, rows_pad, k_pad, Y, nullptr, partial, k, 1, nullptr, p2h, p2l);
-        // T = Y Y^T = X^4
-        if (r == DLCO_OK) r = dlco_launch_gemm3x_nt_sym(ctx, p2h, p2l, rows_pad, p2h, p2l, rows_pad, 1, k_pad, nCfg, D, D, T, D, cs);
-        // Z = a I + b Y + c T
-        if (r == DLCO_OK) r = sign_prep<PREP_POLY>(ctx, D, nCfg, rows_pad, k_pad, Y, T, partial, k, 1, nullptr, p2h, p2l);
-        // T = X Z^T, X <- sym(T)
-        if (r == DLCO_OK) r = dlco_launch_gemm3x_nt_sym(ctx, p1h, p1l, rows_pad, p2h, p2l, rows_pad, 1, k_pad, nCfg, D, D, T, D, cs);
-        if (r == DLCO_OK) r = sign_prep<PREP_SYM>(ctx, D, nCfg, rows_pad, k_pad, T, nullptr, partial, k, 1, X, p1h, p1l);
+        r = gemm(p1h, p1l, p1h, p1l, sx, sx, Y);                       // Y = X X^T (= X^2: X is kept symmetric)
+        if (r == DLCO_OK) r = sign_prep<PREP_COPY>(ctx, f16, D, nCfg, rows_pad, k_pad, Y, nullptr, partial, k, 1, sx, nullptr, p2h, p2l);
+        if (r == DLCO_OK) r = gemm(p2h, p2l, p2h, p2l, sx, sx, T);     // T = Y Y^T = X^4
+        if (r == DLCO_OK) r = sign_prep<PREP_POLY>(ctx, f16, D, nCfg, rows_pad, k_pad, Y, T, partial, k, 1, sz, nullptr, p2h, p2l);
+        if (r == DLCO_OK) r = gemm(p1h, p1l, p2h, p2l, sx, sz, T);     // T = X Z^T, Z = a I + b Y + c Y^2
+        if (r == DLCO_OK) r = sign_prep<PREP_SYM>(ctx, f16, D, nCfg, rows_pad, k_pad, T, nullptr, partial, k, 1, sx, X, p1h, p1l);
     }
-    // A+ = (A + sym(A S)) / 2
-    if (r == DLCO_OK) r = sign_prep<PREP_COPY>(ctx, D, nCfg, rows_pad, k_pad, d_A, nullptr, partial, 0, 0, nullptr, p2h, p2l);
-    if (r == DLCO_OK) r = dlco_launch_gemm3x_nt_sym(ctx, p2h, p2l, rows_pad, p1h, p1l, rows_pad, 1, k_pad, nCfg, D, D, T, D, cs);
-    if (r == DLCO_OK) r = sign_prep<PREP_FINAL>(ctx, D, nCfg, rows_pad, k_pad, T, nullptr, partial, 0, 1, d_A, nullptr, nullptr);
+    // A+ = (A + alpha sym((A / alpha) S)) / 2
+    if (r == DLCO_OK) r = sign_prep<PREP_INIT>(ctx, f16, D, nCfg, rows_pad, k_pad, d_A, nullptr, partial, 0, 0, sx, nullptr, p2h, p2l);
+    if (r == DLCO_OK) r = gemm(p2h, p2l, p1h, p1l, sx, sx, T);
+    if (r == DLCO_OK) r = sign_prep<PREP_FINAL>(ctx, f16, D, nCfg, rows_pad, k_pad, T, nullptr, partial, 0, 1, 1.f, d_A, nullptr, nullptr);
     if (r != DLCO_OK) return r;
     k_sign_rank<<<nCfg, 256, 0, ctx->stream>>>(D, X, partial, d_rank);
     DLCO_CHECK_LAUNCH(ctx);
@@ -282,7 +317,7 @@ int dlco_pj_margins_quad_grid(dlco_ctx *ctx, const float *d_dists, int64_t ld, i
     float *PX = (float *)dlco_scratch(ctx, 42, 2 * xplane * sizeof(float));
     float *Ct = (float *)dlco_scratch(ctx, 38, (size_t)nCfg * D * (nk > D ? nk : D) * sizeof(float));
     if (!PA || !PX || !Ct) return DLCO_ENOMEM;
-    int r = sign_prep<PREP_COPY>(ctx, D, nCfg, rows_pad, k_pad, d_A, nullptr, nullptr, 0, 0, nullptr, PA, PA + plane);
+    int r = sign_prep<PREP_COPY>(ctx, false, D, nCfg, rows_pad, k_pad, d_A, nullptr, nullptr, 0, 0, 1.f, nullptr, PA, PA + plane);
     if (r != DLCO_OK) return r;
     k_rows_planes<<<dim3(k_pad / 32, xrows_pad / 32), 256, 0, ctx->stream>>>(d_dists, ld, D, d_rows, nk, xrows_pad, k_pad,
                                                                           PX, PX + xplane);
