@@ -9,6 +9,7 @@
 // Roles: warp 0 = TMA producer, warp 1 = MMA issuer + TMEM owner, warps 2..9 = epilogue (drains).
 #include "common.cuh"
 #include "kernels.h"
+#include <cuda_fp16.h>
 #include <stdlib.h>
 
 namespace {
@@ -30,6 +31,18 @@ struct __align__(64) GemmMaps {
     CUtensorMap a_hi, a_lo, b_hi, b_lo;
 };
 
+// optional fused epilogue (fp16 route): the output, or a polynomial of it, leaves the kernel as the fp16
+// hi / lo planes the next GEMM reads, so no separate pass re-reads C.
+//   mode 1: planes(C), C also stored        mode 2: planes(ca [i == j] + cb aux + cc C), C not stored
+struct GemmEpi {
+    int mode;
+    void *phi, *plo;
+    int rows_pad, k_pad;
+    float pscale;
+    const float *aux;          // same layout as C
+    float ca, cb, cc;
+};
+
 // The tensor core adds into its fp32 TMEM accumulator with truncation (bias ~ -3e-8 relative per
 // accumulated MMA, see pool_tc.cu): the accumulation is cut every FLUSH chunks, the epilogue warps
 // drain the partial sums and add them in round-to-nearest registers while the MMAs continue into the
@@ -41,7 +54,7 @@ struct __align__(64) GemmMaps {
 template <bool F16>
 __global__ void __launch_bounds__(NTHREADS, 1)
 k_gemm3x_nt(const __grid_constant__ GemmMaps maps, int k_chunks, int FLUSH, int sym, int a_batch_rows, int b_batch_rows,
-            int M, int N, float *__restrict__ C, int64_t ldc, int64_t c_batch_stride, float out_scale)
+            int M, int N, float *__restrict__ C, int64_t ldc, int64_t c_batch_stride, float out_scale, GemmEpi epi)
 {
     if (sym && dlco_gemm3x_tile_skipped(blockIdx.y * BM, blockIdx.x * BN)) return;   // mirrored by the consumer
     extern __shared__ uint8_t smem_raw[];
@@ -169,7 +182,36 @@ k_gemm3x_nt(const __grid_constant__ GemmMaps maps, int k_chunks, int FLUSH, int 
         }
         const int row = mt * BM + q * 32 + lane;
         const int col0 = nt * BN + half * EN;
-        if (row < M) {
+        if (F16 && epi.mode && row < M) {
+            const float *aux = epi.mode == 2 ? epi.aux + (size_t)g * c_batch_stride + (size_t)row * ldc : nullptr;
+            __half *ph = reinterpret_cast<__half *>(epi.phi) + ((size_t)g * epi.rows_pad + row) * epi.k_pad;
+            __half *pl = reinterpret_cast<__half *>(epi.plo) + ((size_t)g * epi.rows_pad + row) * epi.k_pad;
+#pragma unroll
+            for (int e = 0; e < EN; e += 8) {
+                if (col0 + e + 8 > epi.k_pad) break;
+                uint32_t hw[4], lw[4];
+#pragma unroll
+                for (int t = 0; t < 8; t++) {
+                    const int col = col0 + e + t;
+                    float x = acc[e + t];
+                    if (epi.mode == 2) x = fmaf(epi.cc, x, fmaf(epi.cb, col < N ? __ldg(aux + col) : 0.f, col == row ? epi.ca : 0.f));
+                    if (col >= N) x = 0.f;
+                    const float sv = x * epi.pscale;
+                    const __half h = __float2half_rn(sv);
+                    const __half l = __float2half_rn(sv - __half2float(h));
+                    if (t & 1) {
+                        hw[t >> 1] |= (uint32_t)__half_as_ushort(h) << 16;
+                        lw[t >> 1] |= (uint32_t)__half_as_ushort(l) << 16;
+                    } else {
+                        hw[t >> 1] = __half_as_ushort(h);
+                        lw[t >> 1] = __half_as_ushort(l);
+                    }
+                }
+                *reinterpret_cast<uint4 *>(ph + col0 + e) = make_uint4(hw[0], hw[1], hw[2], hw[3]);
+                *reinterpret_cast<uint4 *>(pl + col0 + e) = make_uint4(lw[0], lw[1], lw[2], lw[3]);
+            }
+        }
+        if (row < M && !(F16 && epi.mode == 2)) {
             float *crow = C + (size_t)g * c_batch_stride + (size_t)row * ldc + col0;
             if (col0 + EN <= N && ((reinterpret_cast<uintptr_t>(crow) & 15) == 0)) {
 #pragma unroll
@@ -223,7 +265,7 @@ static int gemm3x_launch(dlco_ctx *ctx, int sym, const float *a_hi, const float 
     }
     k_gemm3x_nt<false><<<grid, NTHREADS, SMEM_BYTES, ctx->stream>>>(maps, k_pad / BK, flush, sym, a_rows_pad,
                                                                   b_batched ? b_rows_pad : 0, M, N, d_C, ldc,
-                                                                  c_batch_stride, 1.0f);
+                                                                  c_batch_stride, 1.0f, GemmEpi{});
     dlco_prof_end(ctx);
     DLCO_CHECK_LAUNCH(ctx);
     return DLCO_OK;
@@ -249,9 +291,9 @@ int dlco_launch_gemm3x_nt_sym(dlco_ctx *ctx, const float *a_hi, const float *a_l
 
 // fp16 hi / lo planes (K-major, k_pad halfs a multiple of 64, rows padded as for the tf32 planes), symmetric
 // product (tiles below the diagonal skipped), C = out_scale * A B^T
-int dlco_launch_gemm3h_nt_sym(dlco_ctx *ctx, const void *a_hi, const void *a_lo, int a_rows_pad, const void *b_hi,
-                              const void *b_lo, int b_rows_pad, int k_pad, int batch, int M, int N, float out_scale,
-                              float *d_C, int64_t ldc, int64_t c_batch_stride)
+static int gemm3h_launch(dlco_ctx *ctx, int sym, const GemmEpi &epi, const void *a_hi, const void *a_lo, int a_rows_pad,
+                         const void *b_hi, const void *b_lo, int b_rows_pad, int k_pad, int batch, int M, int N,
+                         float out_scale, float *d_C, int64_t ldc, int64_t c_batch_stride)
 {
     DLCO_REQUIRE(k_pad % (2 * BK) == 0 && k_pad > 0 && M > 0 && N > 0 && batch > 0, "gemm3h_nt: bad shapes");
     DLCO_REQUIRE((M + BM - 1) / BM * BM <= a_rows_pad && (N + BN - 1) / BN * BN <= b_rows_pad,
@@ -271,11 +313,33 @@ int dlco_launch_gemm3h_nt_sym(dlco_ctx *ctx, const void *a_hi, const void *a_lo,
     const int flush = e && atoi(e) > 0 ? atoi(e) : 1;      // K = 64 per chunk here: drain every chunk
     dim3 grid((N + BN - 1) / BN, (M + BM - 1) / BM, batch);
     dlco_prof_begin(ctx, 2);
-    k_gemm3x_nt<true><<<grid, NTHREADS, SMEM_BYTES, ctx->stream>>>(maps, k_pad / (2 * BK), flush, 1, a_rows_pad, b_rows_pad, M,
-                                                                 N, d_C, ldc, c_batch_stride, out_scale);
+    k_gemm3x_nt<true><<<grid, NTHREADS, SMEM_BYTES, ctx->stream>>>(maps, k_pad / (2 * BK), flush, sym, a_rows_pad, b_rows_pad, M,
+                                                                 N, d_C, ldc, c_batch_stride, out_scale, epi);
     dlco_prof_end(ctx);
     DLCO_CHECK_LAUNCH(ctx);
     return DLCO_OK;
+}
+
+int dlco_launch_gemm3h_nt_sym(dlco_ctx *ctx, const void *a_hi, const void *a_lo, int a_rows_pad, const void *b_hi,
+                              const void *b_lo, int b_rows_pad, int k_pad, int batch, int M, int N, float out_scale,
+                              float *d_C, int64_t ldc, int64_t c_batch_stride)
+{
+    return gemm3h_launch(ctx, 1, GemmEpi{}, a_hi, a_lo, a_rows_pad, b_hi, b_lo, b_rows_pad, k_pad, batch, M, N, out_scale,
+                         d_C, ldc, c_batch_stride);
+}
+
+// all tiles computed; the result (mode 1, also stored in d_C) or ca I + cb aux + cc result (mode 2, d_C untouched)
+// is written as fp16 hi / lo planes (p_rows_pad x p_k_pad per batch entry, scaled by pscale) for the next GEMM
+int dlco_launch_gemm3h_nt_planes(dlco_ctx *ctx, const void *a_hi, const void *a_lo, int a_rows_pad, const void *b_hi,
+                                 const void *b_lo, int b_rows_pad, int k_pad, int batch, int M, int N, float out_scale,
+                                 float *d_C, int64_t ldc, int64_t c_batch_stride, int mode, void *p_hi, void *p_lo,
+                                 int p_rows_pad, int p_k_pad, float pscale, const float *aux, float ca, float cb, float cc)
+{
+    DLCO_REQUIRE((mode == 1 || mode == 2) && p_hi && p_lo && (mode == 1 || aux), "gemm3h_nt_planes: bad epilogue");
+    DLCO_REQUIRE(p_k_pad % 8 == 0, "gemm3h_nt_planes: plane pitch must be a multiple of 8 halfs");
+    GemmEpi epi{mode, p_hi, p_lo, p_rows_pad, p_k_pad, pscale, aux, ca, cb, cc};
+    return gemm3h_launch(ctx, 0, epi, a_hi, a_lo, a_rows_pad, b_hi, b_lo, b_rows_pad, k_pad, batch, M, N, out_scale,
+                         d_C, ldc, c_batch_stride);
 }
 
 // ---- fp32 front end: split row-major A (M x K) and B (N x K) into padded tf32 planes ----------

@@ -125,33 +125,56 @@ k_sign_prep(int D, int rows_pad, int k_pad, const float *__restrict__ in0, const
     if (MODE == PREP_INIT) inv_alpha = sign_inv_alpha(partial, g);
     if (MODE == PREP_FINAL) alpha = sign_alpha(partial, g);
     if (MODE == PREP_POLY) { ca = c_sign_coef[step][0]; cb = c_sign_coef[step][1]; cc = c_sign_coef[step][2]; }
-    for (int r = ty; r < 32; r += 8) {
-        const int i = i0 + r, j = j0 + tx;
-        float v = 0.f;
+    // output: thread = (row r, group of 4 consecutive columns): 16-byte fp32 stores, 8-byte plane stores
+    const int r = threadIdx.x >> 3, c4 = (threadIdx.x & 7) * 4;
+    const int i = i0 + r;
+    float v[4];
+#pragma unroll
+    for (int t = 0; t < 4; t++) {
+        const int j = j0 + c4 + t;
+        v[t] = 0.f;
         if (i < D && j < D) {
-            const size_t o = (size_t)i * D + j;
-            const float a = tr0 ? t0[tx][r] : t0[r][tx];           // in0 at (i, j)
-            const float b = tr1 ? t1[tx][r] : t1[r][tx];           // POLY: in1 at (i, j); SYM / FINAL: in0 at (j, i)
-            if (MODE == PREP_INIT) v = a * inv_alpha;
-            else if (MODE == PREP_COPY) v = a;
-            else if (MODE == PREP_POLY) v = fmaf(cc, b, fmaf(cb, a, i == j ? ca : 0.f));
-            else if (MODE == PREP_SYM) v = 0.5f * (a + b);
-            else v = 0.5f * (out[(size_t)g * dd + o] + alpha * (0.5f * (a + b)));   // in0 = (A / alpha) S
-            if ((MODE == PREP_INIT || MODE == PREP_SYM || MODE == PREP_FINAL) && out) out[(size_t)g * dd + o] = v;
+            const float a = tr0 ? t0[c4 + t][r] : t0[r][c4 + t];           // in0 at (i, j)
+            const float b = tr1 ? t1[c4 + t][r] : t1[r][c4 + t];           // POLY: in1 at (i, j); SYM / FINAL: in0 at (j, i)
+            if (MODE == PREP_INIT) v[t] = a * inv_alpha;
+            else if (MODE == PREP_COPY) v[t] = a;
+            else if (MODE == PREP_POLY) v[t] = fmaf(cc, b, fmaf(cb, a, i == j ? ca : 0.f));
+            else if (MODE == PREP_SYM) v[t] = 0.5f * (a + b);
+            else v[t] = 0.5f * (out[(size_t)g * dd + (size_t)i * D + j] + alpha * (0.5f * (a + b)));   // in0 = (A / alpha) S
         }
-        if (MODE != PREP_FINAL && i < rows_pad && j < k_pad) {
-            const size_t po = ((size_t)g * rows_pad + i) * k_pad + j;
-            if (F16) {
-                const float sv = v * pscale;
+    }
+    if ((MODE == PREP_INIT || MODE == PREP_SYM || MODE == PREP_FINAL) && out && i < D) {
+        float *o = out + (size_t)g * dd + (size_t)i * D + j0 + c4;
+        if (j0 + c4 + 4 <= D && (D & 3) == 0) *reinterpret_cast<float4 *>(o) = make_float4(v[0], v[1], v[2], v[3]);
+        else
+            for (int t = 0; t < 4; t++)
+                if (j0 + c4 + t < D) o[t] = v[t];
+    }
+    if (MODE != PREP_FINAL && i < rows_pad && j0 + c4 < k_pad) {          // k_pad is a multiple of 32: whole group inside
+        const size_t po = ((size_t)g * rows_pad + i) * k_pad + j0 + c4;
+        if (F16) {
+            uint32_t hw[2], lw[2];
+#pragma unroll
+            for (int t = 0; t < 4; t++) {
+                const float sv = v[t] * pscale;
                 const __half h = __float2half_rn(sv);
-                reinterpret_cast<__half *>(hi)[po] = h;
-                reinterpret_cast<__half *>(lo)[po] = __float2half_rn(sv - __half2float(h));
-            } else {
-                float h, l;
-                tf32_split(v, h, l);
-                reinterpret_cast<float *>(hi)[po] = h;
-                reinterpret_cast<float *>(lo)[po] = l;
+                const __half l = __float2half_rn(sv - __half2float(h));
+                if (t & 1) {
+                    hw[t >> 1] |= (uint32_t)__half_as_ushort(h) << 16;
+                    lw[t >> 1] |= (uint32_t)__half_as_ushort(l) << 16;
+                } else {
+                    hw[t >> 1] = __half_as_ushort(h);
+                    lw[t >> 1] = __half_as_ushort(l);
+                }
             }
+            *reinterpret_cast<uint2 *>(reinterpret_cast<__half *>(hi) + po) = make_uint2(hw[0], hw[1]);
+            *reinterpret_cast<uint2 *>(reinterpret_cast<__half *>(lo) + po) = make_uint2(lw[0], lw[1]);
+        } else {
+            float h[4], l[4];
+#pragma unroll
+            for (int t = 0; t < 4; t++) tf32_split(v[t], h[t], l[t]);
+            *reinterpret_cast<float4 *>(reinterpret_cast<float *>(hi) + po) = make_float4(h[0], h[1], h[2], h[3]);
+            *reinterpret_cast<float4 *>(reinterpret_cast<float *>(lo) + po) = make_float4(l[0], l[1], l[2], l[3]);
         }
     }
 }
@@ -213,6 +236,14 @@ int dlco_pj_psd_sign(dlco_ctx *ctx, int D, int nCfg, float *d_A, int32_t *d_rank
     double *partial = (double *)dlco_scratch(ctx, 41, (size_t)nCfg * NORM_BLOCKS * sizeof(double));
     if (!X || !Y || !T || !P1 || !P2 || !partial) return DLCO_ENOMEM;
     void *p1h = P1, *p1l = P1 + plane * esz, *p2h = P2, *p2l = P2 + plane * esz;
+    uint8_t *P3 = nullptr;
+    void *p3h = nullptr, *p3l = nullptr;
+    if (f16) {
+        P3 = (uint8_t *)dlco_scratch(ctx, 43, 2 * plane * esz);
+        if (!P3) return DLCO_ENOMEM;
+        p3h = P3;
+        p3l = P3 + plane * esz;
+    }
     const int64_t cs = (int64_t)dd;
     const float sx = 8192.f, sz = 512.f;                               // plane scales (fp16 route)
     // one product C = A B^T from planes; symmetric, tiles below the diagonal skipped
@@ -226,7 +257,33 @@ int dlco_pj_psd_sign(dlco_ctx *ctx, int D, int nCfg, float *d_A, int32_t *d_rank
     k_sign_norm<<<dim3(NORM_BLOCKS, nCfg), 256, 0, ctx->stream>>>(d_A, dd, partial);
     DLCO_CHECK_LAUNCH(ctx);
     r = sign_prep<PREP_INIT>(ctx, f16, D, nCfg, rows_pad, k_pad, d_A, nullptr, partial, 0, 0, sx, X, p1h, p1l);
-    for (int k = 0; k < SIGN_STEPS && r == DLCO_OK; k++) {
+    static const float h_coef[SIGN_STEPS][3] = {
+        {8.509885880f, -25.264305658f, 18.753568789f}, {4.228659615f, -3.108344126f, 0.571498694f},
+        {4.205812483f, -3.092890486f, 0.569812591f},   {4.114157757f, -3.030669974f, 0.563027579f},
+        {3.782556611f, -2.802261125f, 0.538186614f},   {2.943282063f, -2.192549912f, 0.472857879f},
+        {2.077505958f, -1.466020591f, 0.400932419f},   {1.891149032f, -1.279511400f, 0.388326974f},
+        {1.875000000f, -1.250000000f, 0.375000000f}};      // = c_sign_coef
+    const char *fe = getenv("DLCO_SIGN_FUSED");
+    const bool fused = f16 && fe && fe[0] == '1';      // measured slower than the unfused flow: opt-in
+    if (fused && r == DLCO_OK) {
+        // the planes written by GEMM epilogues cover the D x D block only: zero the padding once
+        DLCO_CUDA(cudaMemsetAsync(P2, 0, 2 * plane * esz, ctx->stream));
+        DLCO_CUDA(cudaMemsetAsync(P3, 0, 2 * plane * esz, ctx->stream));
+    }
+    for (int k = 0; k < SIGN_STEPS && r == DLCO_OK && fused; k++) {
+        const float inv = 1.0f / (sx * sx);
+        // Y = X X^T, stored and written as planes by the epilogue (all tiles: the planes need every row)
+        r = dlco_launch_gemm3h_nt_planes(ctx, p1h, p1l, rows_pad, p1h, p1l, rows_pad, k_pad, nCfg, D, D, inv, Y, D, cs, 1,
+                                         p2h, p2l, rows_pad, k_pad, sx, nullptr, 0.f, 0.f, 0.f);
+        // Z = a I + b Y + c Y Y^T straight into planes (in place over Y's planes is not possible: other CTAs
+        // still read them), so Z goes to X's spare plane set P3
+        if (r == DLCO_OK)
+            r = dlco_launch_gemm3h_nt_planes(ctx, p2h, p2l, rows_pad, p2h, p2l, rows_pad, k_pad, nCfg, D, D, inv, nullptr, D, cs, 2,
+                                             p3h, p3l, rows_pad, k_pad, sz, Y, h_coef[k][0], h_coef[k][1], h_coef[k][2]);
+        if (r == DLCO_OK) r = gemm(p1h, p1l, p3h, p3l, sx, sz, T);     // T = X Z^T (tiles below the diagonal skipped)
+        if (r == DLCO_OK) r = sign_prep<PREP_SYM>(ctx, f16, D, nCfg, rows_pad, k_pad, T, nullptr, partial, k, 1, sx, X, p1h, p1l);
+    }
+    for (int k = 0; k < SIGN_STEPS && r == DLCO_OK && !fused; k++) {
         r = gemm(p1h, p1l, p1h, p1l, sx, sx, Y);                       // Y = X X^T (= X^2: X is kept symmetric)
         if (r == DLCO_OK) r = sign_prep<PREP_COPY>(ctx, f16, D, nCfg, rows_pad, k_pad, Y, nullptr, partial, k, 1, sx, nullptr, p2h, p2l);
         if (r == DLCO_OK) r = gemm(p2h, p2l, p2h, p2l, sx, sx, T);     // T = Y Y^T = X^4
