@@ -361,6 +361,38 @@ def main():
                "h2d_bytes_per_step": n_pairs * (2 * 4096 + 16), "d2h_bytes_per_step": n_pairs * RINGS * 4,
                "steps": e2e_steps, "host_checksum": float(h_out[:: max(1, n_pairs // 1000)].double().sum().item())}
 
+    # ---- N > 1: the 5 x 9 (mu, gamma) pj-learn sweep of one data set sharded over the ranks by configuration
+    # (c % world == rank, as `pj-sweep -shard r/n`), unprojected distances replicated, no collective
+    sweep_sharded = None
+    if world > 1 and not args.no_rows:
+        try:
+            import bench_paths
+            from dlco_b200 import learn
+            D, n_u = 544, 100000
+            ud, ulabels = bench_paths.synth_uprj(torch, dev, n_u, D, 12)
+            mus = np.repeat(np.array([0.0001, 0.0005, 0.001, 0.002, 0.003], np.float32), 9)
+            gms = np.tile(np.array([0.025, 0.05, 0.1, 0.15, 0.2, 0.25, 0.5, 0.75, 1.0], np.float32), 5)
+            mine = [c for c in range(45) if c % world == rank]
+            S = learn.PjSweep(ctx, ud, ulabels, mus[mine], gms[mine], prox="sign")
+            for _ in range(5):
+                S.step()
+            n_it = 20
+            barrier()
+            s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s0.record()
+            for _ in range(n_it):
+                S.step()
+            s1.record()
+            barrier()
+            tm = torch.tensor([s0.elapsed_time(s1)], dtype=torch.float64, device=dev)
+            dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+            sweep_sharded = {"n_cfg_total": 45, "cfg_per_rank_max": -(-45 // world), "D": D, "prox": "sign",
+                             "ms_per_iter": float(tm.item()) / n_it,
+                             "cfg_iters_per_s": 45 * n_it / (float(tm.item()) * 1e-3)}
+            del S, ud
+        except Exception as ex:
+            sweep_sharded = {"failed": repr(ex)}
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -456,7 +488,7 @@ def main():
                    "l2": "inputs larger than L2 (1.04 GB of filter planes streamed per 256-pair batch, 10 GB of output per step)",
                    "reference_gtx970_pairs_per_s": GTX970_PAIRS_PER_S},
         "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
-        "cpu_baseline": cpu, "rows": rows, "checksum": checksum,
+        "cpu_baseline": cpu, "rows": rows, "pj_sweep_sharded": sweep_sharded, "checksum": checksum,
     }
     print(json.dumps(line), flush=True)
     if world > 1:
