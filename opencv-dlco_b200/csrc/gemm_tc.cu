@@ -15,16 +15,16 @@
 namespace {
 
 constexpr int BM = 128;
-constexpr int BN = 192;
+constexpr int BN = DLCO_GEMM_BN;
 constexpr int BK = 32;
-constexpr int STAGES = 2;
+constexpr int STAGES = BN <= 128 ? 3 : 2;     // 64 KB / 80 KB stages: as many as fit 227 KB
 constexpr int A_BYTES = BM * BK * 4;
 constexpr int B_BYTES = BN * BK * 4;
 constexpr int STAGE_BYTES = 2 * A_BYTES + 2 * B_BYTES;
 constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256;
 constexpr int EPI_WARPS = 8;
 constexpr int NTHREADS = 64 + EPI_WARPS * 32;
-constexpr int TMEM_COLS = 512;               // two 192-column accumulators
+constexpr int TMEM_COLS = 2 * BN <= 256 ? 256 : 512;   // two BN-column accumulators
 constexpr int EN = BN / 2;                   // columns per epilogue warp
 
 struct __align__(64) GemmMaps {
@@ -51,12 +51,21 @@ struct GemmEpi {
 // F16 = true : fp16 hi / lo planes of power-of-two-scaled operands (64 halfs per chunk, kind::f16: the
 //              same 22 mantissa bits at twice the tensor rate and half the operand bytes, as in
 //              pool_tc.cu); the accumulator is multiplied by out_scale = 1 / (scale_a * scale_b).
+// the output tiles of one batch entry that are computed (all, or those not below the diagonal)
+struct GemmTiles {
+    int n;
+    uint8_t mt[96], nt[96];
+};
+
+// Persistent: each CTA walks tiles t = blockIdx.x, blockIdx.x + gridDim.x, ... of batch x tiles.n; the
+// operand ring and the two TMEM accumulators carry on across tiles, so the TMA producer prefetches the
+// next tile while the epilogue warps store the previous one.
 template <bool F16>
 __global__ void __launch_bounds__(NTHREADS, 1)
-k_gemm3x_nt(const __grid_constant__ GemmMaps maps, int k_chunks, int FLUSH, int sym, int a_batch_rows, int b_batch_rows,
-            int M, int N, float *__restrict__ C, int64_t ldc, int64_t c_batch_stride, float out_scale, GemmEpi epi)
+k_gemm3x_nt(const __grid_constant__ GemmMaps maps, const __grid_constant__ GemmTiles tiles, int total, int k_chunks,
+            int FLUSH, int a_batch_rows, int b_batch_rows, int M, int N, float *__restrict__ C, int64_t ldc,
+            int64_t c_batch_stride, float out_scale, GemmEpi epi)
 {
-    if (sym && dlco_gemm3x_tile_skipped(blockIdx.y * BM, blockIdx.x * BN)) return;   // mirrored by the consumer
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + STAGES * STAGE_BYTES);
@@ -67,7 +76,6 @@ k_gemm3x_nt(const __grid_constant__ GemmMaps maps, int k_chunks, int FLUSH, int 
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * STAGES + 4);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int nt = blockIdx.x, mt = blockIdx.y, g = blockIdx.z;
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&maps.a_hi);
@@ -92,19 +100,22 @@ k_gemm3x_nt(const __grid_constant__ GemmMaps maps, int k_chunks, int FLUSH, int 
 
     if (warp == 0) {
         if (lane == 0) {
-            const int arow = g * a_batch_rows + mt * BM, brow = g * b_batch_rows + nt * BN;
             int stage = 0;
             uint32_t phase = 0;
-            for (int kc = 0; kc < k_chunks; kc++) {
-                mbar_wait(&empty[stage], phase ^ 1);
-                uint8_t *st = smem + stage * STAGE_BYTES;
-                mbar_expect_tx(&full[stage], STAGE_BYTES);
-                const int kcol = kc * (F16 ? 2 * BK : BK);          // elements per 128-byte chunk
-                tma_load_2d(st, &maps.a_hi, &full[stage], kcol, arow);
-                tma_load_2d(st + A_BYTES, &maps.a_lo, &full[stage], kcol, arow);
-                tma_load_2d(st + 2 * A_BYTES, &maps.b_hi, &full[stage], kcol, brow);
-                tma_load_2d(st + 2 * A_BYTES + B_BYTES, &maps.b_lo, &full[stage], kcol, brow);
-                if (++stage == STAGES) { stage = 0; phase ^= 1; }
+            for (int t = blockIdx.x; t < total; t += gridDim.x) {
+                const int g = t / tiles.n, k = t % tiles.n;
+                const int arow = g * a_batch_rows + tiles.mt[k] * BM, brow = g * b_batch_rows + tiles.nt[k] * BN;
+                for (int kc = 0; kc < k_chunks; kc++) {
+                    mbar_wait(&empty[stage], phase ^ 1);
+                    uint8_t *st = smem + stage * STAGE_BYTES;
+                    mbar_expect_tx(&full[stage], STAGE_BYTES);
+                    const int kcol = kc * (F16 ? 2 * BK : BK);          // elements per 128-byte chunk
+                    tma_load_2d(st, &maps.a_hi, &full[stage], kcol, arow);
+                    tma_load_2d(st + A_BYTES, &maps.a_lo, &full[stage], kcol, arow);
+                    tma_load_2d(st + 2 * A_BYTES, &maps.b_hi, &full[stage], kcol, brow);
+                    tma_load_2d(st + 2 * A_BYTES + B_BYTES, &maps.b_lo, &full[stage], kcol, brow);
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
             }
         }
     } else if (warp == 1) {
@@ -113,39 +124,41 @@ k_gemm3x_nt(const __grid_constant__ GemmMaps maps, int k_chunks, int FLUSH, int 
             int stage = 0;
             uint32_t phase = 0;
             uint32_t it = 0;                       // drains so far (accumulator = it & 1)
-            int in_flush = 0;
-            for (int kc = 0; kc < k_chunks; kc++) {
-                const uint32_t d_tmem = tmem_base + (it & 1) * BN;
-                if (in_flush == 0) {
-                    mbar_wait(&tempty[it & 1], ((it >> 1) & 1) ^ 1);
-                    tc_fence_after();
-                }
-                mbar_wait(&full[stage], phase);
-                tc_fence_after();
-                const uint32_t sa = smem_u32(smem + stage * STAGE_BYTES);
-                const uint64_t d_ahi = umma_desc_sw128(sa);
-                const uint64_t d_alo = umma_desc_sw128(sa + A_BYTES);
-                const uint64_t d_bhi = umma_desc_sw128(sa + 2 * A_BYTES);
-                const uint64_t d_blo = umma_desc_sw128(sa + 2 * A_BYTES + B_BYTES);
-#pragma unroll
-                for (int k = 0; k < BK / 8; k++) {
-                    const uint64_t ko = (uint64_t)(k * 2);
-                    if (F16) {
-                        umma_f16(d_tmem, d_alo + ko, d_bhi + ko, idesc, (in_flush | k) != 0);
-                        umma_f16(d_tmem, d_ahi + ko, d_blo + ko, idesc, 1);
-                        umma_f16(d_tmem, d_ahi + ko, d_bhi + ko, idesc, 1);
-                    } else {
-                        umma_tf32(d_tmem, d_alo + ko, d_bhi + ko, idesc, (in_flush | k) != 0);
-                        umma_tf32(d_tmem, d_ahi + ko, d_blo + ko, idesc, 1);
-                        umma_tf32(d_tmem, d_ahi + ko, d_bhi + ko, idesc, 1);
+            for (int t = blockIdx.x; t < total; t += gridDim.x) {
+                int in_flush = 0;
+                for (int kc = 0; kc < k_chunks; kc++) {
+                    const uint32_t d_tmem = tmem_base + (it & 1) * BN;
+                    if (in_flush == 0) {
+                        mbar_wait(&tempty[it & 1], ((it >> 1) & 1) ^ 1);
+                        tc_fence_after();
                     }
-                }
-                umma_commit(&empty[stage]);
-                if (++stage == STAGES) { stage = 0; phase ^= 1; }
-                if (++in_flush == FLUSH || kc == k_chunks - 1) {
-                    umma_commit(&tfull[it & 1]);
-                    it++;
-                    in_flush = 0;
+                    mbar_wait(&full[stage], phase);
+                    tc_fence_after();
+                    const uint32_t sa = smem_u32(smem + stage * STAGE_BYTES);
+                    const uint64_t d_ahi = umma_desc_sw128(sa);
+                    const uint64_t d_alo = umma_desc_sw128(sa + A_BYTES);
+                    const uint64_t d_bhi = umma_desc_sw128(sa + 2 * A_BYTES);
+                    const uint64_t d_blo = umma_desc_sw128(sa + 2 * A_BYTES + B_BYTES);
+#pragma unroll
+                    for (int k = 0; k < BK / 8; k++) {
+                        const uint64_t ko = (uint64_t)(k * 2);
+                        if (F16) {
+                            umma_f16(d_tmem, d_alo + ko, d_bhi + ko, idesc, (in_flush | k) != 0);
+                            umma_f16(d_tmem, d_ahi + ko, d_blo + ko, idesc, 1);
+                            umma_f16(d_tmem, d_ahi + ko, d_bhi + ko, idesc, 1);
+                        } else {
+                            umma_tf32(d_tmem, d_alo + ko, d_bhi + ko, idesc, (in_flush | k) != 0);
+                            umma_tf32(d_tmem, d_ahi + ko, d_blo + ko, idesc, 1);
+                            umma_tf32(d_tmem, d_ahi + ko, d_bhi + ko, idesc, 1);
+                        }
+                    }
+                    umma_commit(&empty[stage]);
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                    if (++in_flush == FLUSH || kc == k_chunks - 1) {
+                        umma_commit(&tfull[it & 1]);
+                        it++;
+                        in_flush = 0;
+                    }
                 }
             }
         }
@@ -153,74 +166,78 @@ k_gemm3x_nt(const __grid_constant__ GemmMaps maps, int k_chunks, int FLUSH, int 
         // epilogue warps 2..9: TMEM lane quarter = warp % 4, column half = (warp - 2) / 4
         const int q = warp & 3, half = (warp - 2) >> 2;
         const int n_flush = (k_chunks + FLUSH - 1) / FLUSH;
-        float acc[EN];
+        uint32_t it = 0;
+        for (int t = blockIdx.x; t < total; t += gridDim.x) {
+            const int g = t / tiles.n, mt = tiles.mt[t % tiles.n], nt = tiles.nt[t % tiles.n];
+            float acc[EN];
 #pragma unroll
-        for (int i = 0; i < EN; i++) acc[i] = 0.f;
-        for (uint32_t it = 0; it < (uint32_t)n_flush; it++) {
-            mbar_wait(&tfull[it & 1], (it >> 1) & 1);
-            tc_fence_after();
-            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (it & 1) * BN + half * EN;
+            for (int i = 0; i < EN; i++) acc[i] = 0.f;
+            for (int f = 0; f < n_flush; f++, it++) {
+                mbar_wait(&tfull[it & 1], (it >> 1) & 1);
+                tc_fence_after();
+                const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (it & 1) * BN + half * EN;
 #pragma unroll
-            for (int j = 0; j < EN / 16; j += 2) {
-                uint32_t r0[16], r1[16];
-                tmem_ld16_nowait(taddr + j * 16, r0);
-                tmem_ld16_nowait(taddr + (j + 1) * 16, r1);
-                tmem_ld_wait();
+                for (int j = 0; j < EN / 16; j += 2) {
+                    uint32_t r0[16], r1[16];
+                    tmem_ld16_nowait(taddr + j * 16, r0);
+                    tmem_ld16_nowait(taddr + (j + 1) * 16, r1);
+                    tmem_ld_wait();
 #pragma unroll
-                for (int e = 0; e < 16; e++) {
-                    acc[j * 16 + e] += __uint_as_float(r0[e]);
-                    acc[(j + 1) * 16 + e] += __uint_as_float(r1[e]);
-                }
-            }
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&tempty[it & 1]);
-        }
-        if (F16) {
-#pragma unroll
-            for (int e = 0; e < EN; e++) acc[e] *= out_scale;
-        }
-        const int row = mt * BM + q * 32 + lane;
-        const int col0 = nt * BN + half * EN;
-        if (F16 && epi.mode && row < M) {
-            const float *aux = epi.mode == 2 ? epi.aux + (size_t)g * c_batch_stride + (size_t)row * ldc : nullptr;
-            __half *ph = reinterpret_cast<__half *>(epi.phi) + ((size_t)g * epi.rows_pad + row) * epi.k_pad;
-            __half *pl = reinterpret_cast<__half *>(epi.plo) + ((size_t)g * epi.rows_pad + row) * epi.k_pad;
-#pragma unroll
-            for (int e = 0; e < EN; e += 8) {
-                if (col0 + e + 8 > epi.k_pad) break;
-                uint32_t hw[4], lw[4];
-#pragma unroll
-                for (int t = 0; t < 8; t++) {
-                    const int col = col0 + e + t;
-                    float x = acc[e + t];
-                    if (epi.mode == 2) x = fmaf(epi.cc, x, fmaf(epi.cb, col < N ? __ldg(aux + col) : 0.f, col == row ? epi.ca : 0.f));
-                    if (col >= N) x = 0.f;
-                    const float sv = x * epi.pscale;
-                    const __half h = __float2half_rn(sv);
-                    const __half l = __float2half_rn(sv - __half2float(h));
-                    if (t & 1) {
-                        hw[t >> 1] |= (uint32_t)__half_as_ushort(h) << 16;
-                        lw[t >> 1] |= (uint32_t)__half_as_ushort(l) << 16;
-                    } else {
-                        hw[t >> 1] = __half_as_ushort(h);
-                        lw[t >> 1] = __half_as_ushort(l);
+                    for (int e = 0; e < 16; e++) {
+                        acc[j * 16 + e] += __uint_as_float(r0[e]);
+                        acc[(j + 1) * 16 + e] += __uint_as_float(r1[e]);
                     }
                 }
-                *reinterpret_cast<uint4 *>(ph + col0 + e) = make_uint4(hw[0], hw[1], hw[2], hw[3]);
-                *reinterpret_cast<uint4 *>(pl + col0 + e) = make_uint4(lw[0], lw[1], lw[2], lw[3]);
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&tempty[it & 1]);
             }
-        }
-        if (row < M && !(F16 && epi.mode == 2)) {
-            float *crow = C + (size_t)g * c_batch_stride + (size_t)row * ldc + col0;
-            if (col0 + EN <= N && ((reinterpret_cast<uintptr_t>(crow) & 15) == 0)) {
+            if (F16) {
 #pragma unroll
-                for (int e = 0; e < EN; e += 4)
-                    *reinterpret_cast<float4 *>(crow + e) = make_float4(acc[e], acc[e + 1], acc[e + 2], acc[e + 3]);
-            } else {
+                for (int e = 0; e < EN; e++) acc[e] *= out_scale;
+            }
+            const int row = mt * BM + q * 32 + lane;
+            const int col0 = nt * BN + half * EN;
+            if (F16 && epi.mode && row < M) {
+                const float *aux = epi.mode == 2 ? epi.aux + (size_t)g * c_batch_stride + (size_t)row * ldc : nullptr;
+                __half *ph = reinterpret_cast<__half *>(epi.phi) + ((size_t)g * epi.rows_pad + row) * epi.k_pad;
+                __half *pl = reinterpret_cast<__half *>(epi.plo) + ((size_t)g * epi.rows_pad + row) * epi.k_pad;
 #pragma unroll
-                for (int e = 0; e < EN; e++)
-                    if (col0 + e < N) crow[e] = acc[e];
+                for (int e = 0; e < EN; e += 8) {
+                    if (col0 + e + 8 > epi.k_pad) break;
+                    uint32_t hw[4], lw[4];
+#pragma unroll
+                    for (int u = 0; u < 8; u++) {
+                        const int col = col0 + e + u;
+                        float x = acc[e + u];
+                        if (epi.mode == 2) x = fmaf(epi.cc, x, fmaf(epi.cb, col < N ? __ldg(aux + col) : 0.f, col == row ? epi.ca : 0.f));
+                        if (col >= N) x = 0.f;
+                        const float sv = x * epi.pscale;
+                        const __half h = __float2half_rn(sv);
+                        const __half l = __float2half_rn(sv - __half2float(h));
+                        if (u & 1) {
+                            hw[u >> 1] |= (uint32_t)__half_as_ushort(h) << 16;
+                            lw[u >> 1] |= (uint32_t)__half_as_ushort(l) << 16;
+                        } else {
+                            hw[u >> 1] = __half_as_ushort(h);
+                            lw[u >> 1] = __half_as_ushort(l);
+                        }
+                    }
+                    *reinterpret_cast<uint4 *>(ph + col0 + e) = make_uint4(hw[0], hw[1], hw[2], hw[3]);
+                    *reinterpret_cast<uint4 *>(pl + col0 + e) = make_uint4(lw[0], lw[1], lw[2], lw[3]);
+                }
+            }
+            if (row < M && !(F16 && epi.mode == 2)) {
+                float *crow = C + (size_t)g * c_batch_stride + (size_t)row * ldc + col0;
+                if (col0 + EN <= N && ((reinterpret_cast<uintptr_t>(crow) & 15) == 0)) {
+#pragma unroll
+                    for (int e = 0; e < EN; e += 4)
+                        *reinterpret_cast<float4 *>(crow + e) = make_float4(acc[e], acc[e + 1], acc[e + 2], acc[e + 3]);
+                } else {
+#pragma unroll
+                    for (int e = 0; e < EN; e++)
+                        if (col0 + e < N) crow[e] = acc[e];
+                }
             }
         }
     }
@@ -230,6 +247,21 @@ k_gemm3x_nt(const __grid_constant__ GemmMaps maps, int k_chunks, int FLUSH, int 
         tc_fence_after();
         tmem_dealloc<TMEM_COLS>(tmem_base);
     }
+}
+
+static int gemm_tiles(GemmTiles *tl, int M, int N, int sym)
+{
+    const int mts = (M + BM - 1) / BM, nts = (N + BN - 1) / BN;
+    tl->n = 0;
+    for (int m = 0; m < mts; m++)
+        for (int n = 0; n < nts; n++) {
+            if (sym && dlco_gemm3x_tile_skipped(m * BM, n * BN)) continue;
+            if (tl->n >= 96) return -1;
+            tl->mt[tl->n] = (uint8_t)m;
+            tl->nt[tl->n] = (uint8_t)n;
+            tl->n++;
+        }
+    return 0;
 }
 
 }  // namespace
@@ -256,14 +288,17 @@ static int gemm3x_launch(dlco_ctx *ctx, int sym, const float *a_hi, const float 
         DLCO_CUDA(cudaFuncSetAttribute(k_gemm3x_nt<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
         attr = true;
     }
-    dim3 grid((N + BN - 1) / BN, (M + BM - 1) / BM, batch);
+    GemmTiles tl;
+    DLCO_REQUIRE(gemm_tiles(&tl, M, N, sym) == 0, "gemm3x_nt: more than 96 output tiles per batch entry");
+    const int total = batch * tl.n;
+    const int grid = total < ctx->sm_count ? total : ctx->sm_count;
     dlco_prof_begin(ctx, 2);
     static int flush = 0;                     // K chunks (of 32) accumulated in TMEM between drains
     if (!flush) {
         const char *e = getenv("DLCO_GEMM_FLUSH");
         flush = e && atoi(e) > 0 ? atoi(e) : 2;
     }
-    k_gemm3x_nt<false><<<grid, NTHREADS, SMEM_BYTES, ctx->stream>>>(maps, k_pad / BK, flush, sym, a_rows_pad,
+    k_gemm3x_nt<false><<<grid, NTHREADS, SMEM_BYTES, ctx->stream>>>(maps, tl, total, k_pad / BK, flush, a_rows_pad,
                                                                   b_batched ? b_rows_pad : 0, M, N, d_C, ldc,
                                                                   c_batch_stride, 1.0f, GemmEpi{});
     dlco_prof_end(ctx);
@@ -311,10 +346,13 @@ static int gemm3h_launch(dlco_ctx *ctx, int sym, const GemmEpi &epi, const void 
     }
     const char *e = getenv("DLCO_GEMM_FLUSH");
     const int flush = e && atoi(e) > 0 ? atoi(e) : 1;      // K = 64 per chunk here: drain every chunk
-    dim3 grid((N + BN - 1) / BN, (M + BM - 1) / BM, batch);
+    GemmTiles tl;
+    DLCO_REQUIRE(gemm_tiles(&tl, M, N, sym) == 0, "gemm3h_nt: more than 96 output tiles per batch entry");
+    const int total = batch * tl.n;
+    const int grid = total < ctx->sm_count ? total : ctx->sm_count;
     dlco_prof_begin(ctx, 2);
-    k_gemm3x_nt<true><<<grid, NTHREADS, SMEM_BYTES, ctx->stream>>>(maps, k_pad / (2 * BK), flush, sym, a_rows_pad, b_rows_pad, M,
-                                                                 N, d_C, ldc, c_batch_stride, out_scale, epi);
+    k_gemm3x_nt<true><<<grid, NTHREADS, SMEM_BYTES, ctx->stream>>>(maps, tl, total, k_pad / (2 * BK), flush, a_rows_pad,
+                                                                 b_rows_pad, M, N, d_C, ldc, c_batch_stride, out_scale, epi);
     dlco_prof_end(ctx);
     DLCO_CHECK_LAUNCH(ctx);
     return DLCO_OK;

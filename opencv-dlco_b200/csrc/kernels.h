@@ -57,16 +57,20 @@ int dlco_sqnorm_tc(dlco_ctx *ctx, const float *d_X, int64_t ld, const int32_t *d
                    const float *d_W, int64_t ldw, int rank, int D, float *d_out);
 
 // gemm_tc.cu: batched C = A * B^T on tcgen05 (3xTF32) from K-major tf32 hi/lo planes
-// rows a plane needs so that n rows cover whole 128-row A tiles and whole 192-row B tiles
+// output tile of k_gemm3x_nt: 128 rows x DLCO_GEMM_BN columns
+#ifndef DLCO_GEMM_BN
+#define DLCO_GEMM_BN 128
+#endif
+// rows a plane needs so that n rows cover whole 128-row A tiles and whole DLCO_GEMM_BN-row B tiles
 static inline int dlco_gemm3x_rows_pad(int n)
 {
-    const int a = (n + 127) / 128 * 128, b = (n + 191) / 192 * 192;
+    const int a = (n + 127) / 128 * 128, b = (n + DLCO_GEMM_BN - 1) / DLCO_GEMM_BN * DLCO_GEMM_BN;
     return a > b ? a : b;
 }
 // symmetric products: output tiles wholly below the diagonal are not computed (nor written)
 __host__ __device__ static inline bool dlco_gemm3x_tile_skipped(int row, int col)
 {
-    return (row / 128) * 128 >= (col / 192 + 1) * 192;
+    return (row / 128) * 128 >= (col / DLCO_GEMM_BN + 1) * DLCO_GEMM_BN;
 }
 int dlco_launch_gemm3x_nt_sym(dlco_ctx *ctx, const float *a_hi, const float *a_lo, int a_rows_pad,
                               const float *b_hi, const float *b_lo, int b_rows_pad, int b_batched,
