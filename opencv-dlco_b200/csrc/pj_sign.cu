@@ -6,7 +6,7 @@
 // without an eigen-decomposition.  sign(A) is computed by an odd-quintic iteration
 // X <- X (a_k I + b_k X^2 + c_k X^4), X_0 = A / ||A||_F, whose coefficients are the minimax
 // polynomials for the interval the spectrum occupies at step k (tools/sign_poly.py: LP per step,
-// start interval [1e-4, 1]); 8 minimax steps + 1 Newton-Schulz polish = 27 GEMMs, + 1 for A sign(A).
+// start interval [1e-4, 1]); 8 minimax quintic steps + 1 Newton-Schulz cubic polish = 26 GEMMs, + 1 for A sign(A).
 // All GEMMs are k_gemm3x_nt (tcgen05, 3xTF32 = fp32-equivalent), batched over the (mu, gamma)
 // configurations of a sweep.  Eigenvalues with |l| < 1e-4 ||A||_F are not driven all the way to
 // +-1; their contribution to A+ is wrong by at most |l| (1 - |s|) / 2 |v v^T| -- below fp32
@@ -23,7 +23,7 @@ namespace {
 
 constexpr int SIGN_STEPS = 9;
 // tools/sign_poly.py 1e-4  (a, b, c) per step
-__constant__ float c_sign_coef[SIGN_STEPS][3] = {
+__constant__ float c_sign_coef[SIGN_STEPS + 1][3] = {
     {8.509885880f, -25.264305658f, 18.753568789f},
     {4.228659615f, -3.108344126f, 0.571498694f},
     {4.205812483f, -3.092890486f, 0.569812591f},
@@ -33,6 +33,7 @@ __constant__ float c_sign_coef[SIGN_STEPS][3] = {
     {2.077505958f, -1.466020591f, 0.400932419f},
     {1.891149032f, -1.279511400f, 0.388326974f},
     {1.875000000f, -1.250000000f, 0.375000000f},
+    {1.5f, -0.5f, 0.f},       // Newton-Schulz cubic: the last step uses this one (2 GEMMs; 9e-4 -> 1e-6)
 };
 
 constexpr int NORM_BLOCKS = 32;
@@ -284,10 +285,11 @@ int dlco_pj_psd_sign(dlco_ctx *ctx, int D, int nCfg, float *d_A, int32_t *d_rank
         if (r == DLCO_OK) r = sign_prep<PREP_SYM>(ctx, f16, D, nCfg, rows_pad, k_pad, T, nullptr, partial, k, 1, sx, X, p1h, p1l);
     }
     for (int k = 0; k < SIGN_STEPS && r == DLCO_OK && !fused; k++) {
+        const bool last = k == SIGN_STEPS - 1;                         // cubic polish: Z = 1.5 I - 0.5 Y, no X^4
         r = gemm(p1h, p1l, p1h, p1l, sx, sx, Y);                       // Y = X X^T (= X^2: X is kept symmetric)
-        if (r == DLCO_OK) r = sign_prep<PREP_COPY>(ctx, f16, D, nCfg, rows_pad, k_pad, Y, nullptr, partial, k, 1, sx, nullptr, p2h, p2l);
-        if (r == DLCO_OK) r = gemm(p2h, p2l, p2h, p2l, sx, sx, T);     // T = Y Y^T = X^4
-        if (r == DLCO_OK) r = sign_prep<PREP_POLY>(ctx, f16, D, nCfg, rows_pad, k_pad, Y, T, partial, k, 1, sz, nullptr, p2h, p2l);
+        if (r == DLCO_OK && !last) r = sign_prep<PREP_COPY>(ctx, f16, D, nCfg, rows_pad, k_pad, Y, nullptr, partial, k, 1, sx, nullptr, p2h, p2l);
+        if (r == DLCO_OK && !last) r = gemm(p2h, p2l, p2h, p2l, sx, sx, T);     // T = Y Y^T = X^4
+        if (r == DLCO_OK) r = sign_prep<PREP_POLY>(ctx, f16, D, nCfg, rows_pad, k_pad, Y, last ? Y : T, partial, last ? SIGN_STEPS : k, 1, sz, nullptr, p2h, p2l);
         if (r == DLCO_OK) r = gemm(p1h, p1l, p2h, p2l, sx, sz, T);     // T = X Z^T, Z = a I + b Y + c Y^2
         if (r == DLCO_OK) r = sign_prep<PREP_SYM>(ctx, f16, D, nCfg, rows_pad, k_pad, T, nullptr, partial, k, 1, sx, X, p1h, p1l);
     }
