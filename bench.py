@@ -389,6 +389,24 @@ def main():
             sweep_sharded = {"n_cfg_total": 45, "cfg_per_rank_max": -(-45 // world), "D": D, "prox": "sign",
                              "ms_per_iter": float(tm.item()) / n_it,
                              "cfg_iters_per_s": 45 * n_it / (float(tm.item()) * 1e-3)}
+            del S
+            # the 9 x 45 sweep of workspace/08-pjlearn.sh shards better by data set: every rank advances all 45
+            # configurations of its own unprojected-distance matrix (9 data sets over `world` ranks)
+            S = learn.PjSweep(ctx, ud, ulabels, mus, gms, prox="sign")
+            for _ in range(3):
+                S.step()
+            n_it = 10
+            barrier()
+            s0.record()
+            for _ in range(n_it):
+                S.step()
+            s1.record()
+            barrier()
+            tm = torch.tensor([s0.elapsed_time(s1)], dtype=torch.float64, device=dev)
+            dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+            sweep_sharded["by_data_set"] = {"data_sets_in_flight": world, "cfg_per_rank": 45,
+                                            "ms_per_iter": float(tm.item()) / n_it,
+                                            "cfg_iters_per_s": world * 45 * n_it / (float(tm.item()) * 1e-3)}
             del S, ud
         except Exception as ex:
             sweep_sharded = {"failed": repr(ex)}
