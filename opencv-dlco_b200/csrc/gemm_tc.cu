@@ -41,6 +41,7 @@ struct GemmEpi {
     float pscale;
     const float *aux;          // same layout as C
     float ca, cb, cc;
+    int mirror;                // symmetric product with skipped lower tiles: also write planes[col][row]
 };
 
 // The tensor core adds into its fp32 TMEM accumulator with truncation (bias ~ -3e-8 relative per
@@ -225,6 +226,17 @@ k_gemm3x_nt(const __grid_constant__ GemmMaps maps, const __grid_constant__ GemmT
                     }
                     *reinterpret_cast<uint4 *>(ph + col0 + e) = make_uint4(hw[0], hw[1], hw[2], hw[3]);
                     *reinterpret_cast<uint4 *>(pl + col0 + e) = make_uint4(lw[0], lw[1], lw[2], lw[3]);
+                    if (epi.mirror && mt != nt) {            // the tile below the diagonal is never computed: write it too
+#pragma unroll
+                        for (int u = 0; u < 8; u++) {
+                            const int col = col0 + e + u;
+                            if (col < N) {
+                                const size_t mo = ((size_t)g * epi.rows_pad + col) * epi.k_pad + row;
+                                reinterpret_cast<uint16_t *>(epi.phi)[mo] = (uint16_t)(hw[u >> 1] >> (16 * (u & 1)));
+                                reinterpret_cast<uint16_t *>(epi.plo)[mo] = (uint16_t)(lw[u >> 1] >> (16 * (u & 1)));
+                            }
+                        }
+                    }
                 }
             }
             if (row < M && !(F16 && epi.mode == 2)) {
@@ -366,7 +378,7 @@ int dlco_launch_gemm3h_nt_sym(dlco_ctx *ctx, const void *a_hi, const void *a_lo,
                          d_C, ldc, c_batch_stride);
 }
 
-// all tiles computed; the result (mode 1, also stored in d_C) or ca I + cb aux + cc result (mode 2, d_C untouched)
+// symmetric product, tiles below the diagonal skipped; the result (mode 1, also stored in d_C) or ca I + cb aux + cc result (mode 2, d_C untouched)
 // is written as fp16 hi / lo planes (p_rows_pad x p_k_pad per batch entry, scaled by pscale) for the next GEMM
 int dlco_launch_gemm3h_nt_planes(dlco_ctx *ctx, const void *a_hi, const void *a_lo, int a_rows_pad, const void *b_hi,
                                  const void *b_lo, int b_rows_pad, int k_pad, int batch, int M, int N, float out_scale,
@@ -375,8 +387,8 @@ int dlco_launch_gemm3h_nt_planes(dlco_ctx *ctx, const void *a_hi, const void *a_
 {
     DLCO_REQUIRE((mode == 1 || mode == 2) && p_hi && p_lo && (mode == 1 || aux), "gemm3h_nt_planes: bad epilogue");
     DLCO_REQUIRE(p_k_pad % 8 == 0, "gemm3h_nt_planes: plane pitch must be a multiple of 8 halfs");
-    GemmEpi epi{mode, p_hi, p_lo, p_rows_pad, p_k_pad, pscale, aux, ca, cb, cc};
-    return gemm3h_launch(ctx, 0, epi, a_hi, a_lo, a_rows_pad, b_hi, b_lo, b_rows_pad, k_pad, batch, M, N, out_scale,
+    GemmEpi epi{mode, p_hi, p_lo, p_rows_pad, p_k_pad, pscale, aux, ca, cb, cc, 1};
+    return gemm3h_launch(ctx, 1, epi, a_hi, a_lo, a_rows_pad, b_hi, b_lo, b_rows_pad, k_pad, batch, M, N, out_scale,
                          d_C, ldc, c_batch_stride);
 }
 

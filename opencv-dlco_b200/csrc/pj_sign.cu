@@ -265,7 +265,9 @@ int dlco_pj_psd_sign(dlco_ctx *ctx, int D, int nCfg, float *d_A, int32_t *d_rank
         {2.077505958f, -1.466020591f, 0.400932419f},   {1.891149032f, -1.279511400f, 0.388326974f},
         {1.875000000f, -1.250000000f, 0.375000000f}};      // = c_sign_coef
     const char *fe = getenv("DLCO_SIGN_FUSED");
-    const bool fused = f16 && fe && fe[0] == '1';      // measured slower than the unfused flow: opt-in
+    // DLCO_SIGN_FUSED=1: Y and Z planes written by the GEMM epilogues (direct + mirrored) instead of prep passes.
+    // Bitwise the same result; measured equal at 45 configurations and slower at one: opt-in.
+    const bool fused = f16 && fe && fe[0] == '1';
     if (fused && r == DLCO_OK) {
         // the planes written by GEMM epilogues cover the D x D block only: zero the padding once
         DLCO_CUDA(cudaMemsetAsync(P2, 0, 2 * plane * esz, ctx->stream));
@@ -273,7 +275,14 @@ int dlco_pj_psd_sign(dlco_ctx *ctx, int D, int nCfg, float *d_A, int32_t *d_rank
     }
     for (int k = 0; k < SIGN_STEPS && r == DLCO_OK && fused; k++) {
         const float inv = 1.0f / (sx * sx);
-        // Y = X X^T, stored and written as planes by the epilogue (all tiles: the planes need every row)
+        if (k == SIGN_STEPS - 1) {                      // cubic polish: Z = 1.5 I - 0.5 Y needs no second product
+            r = gemm(p1h, p1l, p1h, p1l, sx, sx, Y);
+            if (r == DLCO_OK) r = sign_prep<PREP_POLY>(ctx, f16, D, nCfg, rows_pad, k_pad, Y, Y, partial, SIGN_STEPS, 1, sz, nullptr, p3h, p3l);
+            if (r == DLCO_OK) r = gemm(p1h, p1l, p3h, p3l, sx, sz, T);
+            if (r == DLCO_OK) r = sign_prep<PREP_SYM>(ctx, f16, D, nCfg, rows_pad, k_pad, T, nullptr, partial, k, 1, sx, X, p1h, p1l);
+            break;
+        }
+        // Y = X X^T, stored and written as planes by the epilogue (direct and mirrored below the diagonal)
         r = dlco_launch_gemm3h_nt_planes(ctx, p1h, p1l, rows_pad, p1h, p1l, rows_pad, k_pad, nCfg, D, D, inv, Y, D, cs, 1,
                                          p2h, p2l, rows_pad, k_pad, sx, nullptr, 0.f, 0.f, 0.f);
         // Z = a I + b Y + c Y Y^T straight into planes (in place over Y's planes is not possible: other CTAs
