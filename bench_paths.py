@@ -209,15 +209,15 @@ def run(ctx, n_train=500000, n_test=100000, quick=False, D=544, n_pj_cfg=45, n_p
         ctx.profile(False)
         mean_ms, best_ms = timeit(torch, lambda: [S.step() for _ in range(n_it)], warm=1, rep=3)
         rk = S.ranks()
-        # 30 GEMMs per iteration: 27 (sign) + 1 (A sign(A)) at K = D, margins at K = D, SYRK at K = 2 * batch
-        flop = len(mm) * (2.0 * D * D * D * 28 + 2.0 * 400 * D * D * 2)
+        # 29 GEMMs per iteration: 26 (sign) + 1 (A sign(A)) at K = D, margins at K = D, SYRK at K = 2 * batch
+        flop = len(mm) * (2.0 * D * D * D * 27 + 2.0 * 400 * D * D * 2)
         res[tag] = {"n_cfg": int(len(mm)), "D": D, "ms_per_iter": mean_ms / n_it,
                     "cfg_iters_per_s": len(mm) * n_it / (mean_ms * 1e-3),
                     "rank_min": int(rk.min()), "rank_max": int(rk.max()),
                     "gemm_launches_per_iter": gemm_n / (4.0 * n_it), "gemm_ms_per_iter_profiled": gemm_ms / (4.0 * n_it),
                     "gemm_tflops_fp32_equiv": flop / (mean_ms / n_it * 1e-3) / 1e12,
                     "gemm_frac_of_3xtf32_peak": flop / (mean_ms / n_it * 1e-3) / 1e12 / tf32x3,
-                    "note": "sample + x^T A x margins + hinge + grouped SYRK + update + 28-GEMM matrix-sign projection, no host sync"}
+                    "note": "sample + x^T A x margins + hinge + grouped SYRK + update + 27-GEMM matrix-sign projection, no host sync"}
         del S
         torch.cuda.empty_cache()
 

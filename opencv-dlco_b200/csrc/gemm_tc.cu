@@ -1,11 +1,11 @@
 // K_gemm3x_nt: C[g][m, n] = sum_k A[g][m, k] * B[g][n, k] in fp32-equivalent accuracy on the
-// tensor cores (tcgen05.mma kind::tf32, 3xTF32: hi*hi + hi*lo + lo*hi into one fp32 TMEM
-// accumulator).  Both operands are K-major tf32 hi / lo planes (rows padded to the tile, K
-// padded to 32, padding zero), fetched by TMA with the 128-byte swizzle.  One 128 x 192 output
-// tile per CTA, grid = (n tiles, m tiles, batch): the pj-learn weighted SYRK (D = 544 = 2.83 x 192)
-// is 5 x 3 tiles per (mu, gamma) configuration and the configurations of a sweep are the batch
-// dimension.  (128 x 64 tiles moved 1.26 GB from L2 into shared memory per 45-configuration launch
-// and sat at 25 % of the 3xTF32 rate; the wide tile halves the bytes per flop.)
+// tensor cores: tcgen05.mma with hi*hi + hi*lo + lo*hi into one fp32 TMEM accumulator, operands as
+// K-major hi / lo planes -- tf32 (kind::tf32, 3xTF32) or fp16 of power-of-two-scaled values
+// (kind::f16) -- rows padded to the tile, K padded to the 128-byte chunk, padding zero, fetched by
+// TMA with the 128-byte swizzle.  Persistent: one CTA per SM walks a list of 128 x 128 output tiles
+// over all batch entries (the (mu, gamma) configurations of a pj-learn sweep); 3 stages of 64 KB.
+// The kernel is bound by the operand bytes in flight from L2, not by the tensor pipe: 128 x 192
+// tiles with two 80 KB stages were slower although they read fewer bytes per flop.
 // Roles: warp 0 = TMA producer, warp 1 = MMA issuer + TMEM owner, warps 2..9 = epilogue (drains).
 #include "common.cuh"
 #include "kernels.h"
