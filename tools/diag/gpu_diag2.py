@@ -1,7 +1,7 @@
 """tcgen05 3xTF32 accuracy probe (not a pytest file)."""
 import os, sys
 import numpy as np, torch
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 import dlco_b200
 ctx = dlco_b200.Context(0)
