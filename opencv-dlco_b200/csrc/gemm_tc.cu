@@ -55,8 +55,15 @@ struct GemmEpi {
 // the output tiles of one batch entry that are computed (all, or those not below the diagonal)
 struct GemmTiles {
     int n;
+    int nts;                   // table == 0: tile k = (k / nts, k % nts), every tile computed
+    int table;
     uint8_t mt[96], nt[96];
 };
+__device__ __forceinline__ void gemm_tile(const GemmTiles &tl, int k, int &mt, int &nt)
+{
+    if (tl.table) { mt = tl.mt[k]; nt = tl.nt[k]; }
+    else { mt = k / tl.nts; nt = k % tl.nts; }
+}
 
 // Persistent: each CTA walks tiles t = blockIdx.x, blockIdx.x + gridDim.x, ... of batch x tiles.n; the
 // operand ring and the two TMEM accumulators carry on across tiles, so the TMA producer prefetches the
@@ -104,8 +111,10 @@ k_gemm3x_nt(const __grid_constant__ GemmMaps maps, const __grid_constant__ GemmT
             int stage = 0;
             uint32_t phase = 0;
             for (int t = blockIdx.x; t < total; t += gridDim.x) {
-                const int g = t / tiles.n, k = t % tiles.n;
-                const int arow = g * a_batch_rows + tiles.mt[k] * BM, brow = g * b_batch_rows + tiles.nt[k] * BN;
+                const int g = t / tiles.n;
+                int mt, nt;
+                gemm_tile(tiles, t % tiles.n, mt, nt);
+                const int arow = g * a_batch_rows + mt * BM, brow = g * b_batch_rows + nt * BN;
                 for (int kc = 0; kc < k_chunks; kc++) {
                     mbar_wait(&empty[stage], phase ^ 1);
                     uint8_t *st = smem + stage * STAGE_BYTES;
@@ -169,7 +178,9 @@ k_gemm3x_nt(const __grid_constant__ GemmMaps maps, const __grid_constant__ GemmT
         const int n_flush = (k_chunks + FLUSH - 1) / FLUSH;
         uint32_t it = 0;
         for (int t = blockIdx.x; t < total; t += gridDim.x) {
-            const int g = t / tiles.n, mt = tiles.mt[t % tiles.n], nt = tiles.nt[t % tiles.n];
+            const int g = t / tiles.n;
+            int mt, nt;
+            gemm_tile(tiles, t % tiles.n, mt, nt);
             float acc[EN];
 #pragma unroll
             for (int i = 0; i < EN; i++) acc[i] = 0.f;
@@ -261,14 +272,22 @@ k_gemm3x_nt(const __grid_constant__ GemmMaps maps, const __grid_constant__ GemmT
     }
 }
 
+// sym: tiles below the diagonal are left out -- unless the list would not fit the table, in which case every
+// tile is computed (consumers of a symmetric product only ever read the upper ones, so that is still correct)
 static int gemm_tiles(GemmTiles *tl, int M, int N, int sym)
 {
     const int mts = (M + BM - 1) / BM, nts = (N + BN - 1) / BN;
     tl->n = 0;
+    tl->nts = nts;
+    tl->table = 1;
     for (int m = 0; m < mts; m++)
         for (int n = 0; n < nts; n++) {
             if (sym && dlco_gemm3x_tile_skipped(m * BM, n * BN)) continue;
-            if (tl->n >= 96) return -1;
+            if (tl->n >= 96) {
+                tl->n = mts * nts;
+                tl->table = 0;
+                return 0;
+            }
             tl->mt[tl->n] = (uint8_t)m;
             tl->nt[tl->n] = (uint8_t)n;
             tl->n++;

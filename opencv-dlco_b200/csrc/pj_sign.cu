@@ -257,7 +257,7 @@ int dlco_pj_psd_sign(dlco_ctx *ctx, int D, int nCfg, float *d_A, int32_t *d_rank
     int r;
     k_sign_norm<<<dim3(NORM_BLOCKS, nCfg), 256, 0, ctx->stream>>>(d_A, dd, partial);
     DLCO_CHECK_LAUNCH(ctx);
-    r = sign_prep<PREP_INIT>(ctx, f16, D, nCfg, rows_pad, k_pad, d_A, nullptr, partial, 0, 0, sx, X, p1h, p1l);
+    r = sign_prep<PREP_INIT>(ctx, f16, D, nCfg, rows_pad, k_pad, d_A, nullptr, partial, 0, 0, sx, nullptr, p1h, p1l);   // X lives in its planes
     static const float h_coef[SIGN_STEPS][3] = {
         {8.509885880f, -25.264305658f, 18.753568789f}, {4.228659615f, -3.108344126f, 0.571498694f},
         {4.205812483f, -3.092890486f, 0.569812591f},   {4.114157757f, -3.030669974f, 0.563027579f},
@@ -291,7 +291,7 @@ int dlco_pj_psd_sign(dlco_ctx *ctx, int D, int nCfg, float *d_A, int32_t *d_rank
             r = dlco_launch_gemm3h_nt_planes(ctx, p2h, p2l, rows_pad, p2h, p2l, rows_pad, k_pad, nCfg, D, D, inv, nullptr, D, cs, 2,
                                              p3h, p3l, rows_pad, k_pad, sz, Y, h_coef[k][0], h_coef[k][1], h_coef[k][2]);
         if (r == DLCO_OK) r = gemm(p1h, p1l, p3h, p3l, sx, sz, T);     // T = X Z^T (tiles below the diagonal skipped)
-        if (r == DLCO_OK) r = sign_prep<PREP_SYM>(ctx, f16, D, nCfg, rows_pad, k_pad, T, nullptr, partial, k, 1, sx, X, p1h, p1l);
+        if (r == DLCO_OK) r = sign_prep<PREP_SYM>(ctx, f16, D, nCfg, rows_pad, k_pad, T, nullptr, partial, k, 1, sx, nullptr, p1h, p1l);
     }
     for (int k = 0; k < SIGN_STEPS && r == DLCO_OK && !fused; k++) {
         const bool last = k == SIGN_STEPS - 1;                         // cubic polish: Z = 1.5 I - 0.5 Y, no X^4
@@ -300,7 +300,8 @@ int dlco_pj_psd_sign(dlco_ctx *ctx, int D, int nCfg, float *d_A, int32_t *d_rank
         if (r == DLCO_OK && !last) r = gemm(p2h, p2l, p2h, p2l, sx, sx, T);     // T = Y Y^T = X^4
         if (r == DLCO_OK) r = sign_prep<PREP_POLY>(ctx, f16, D, nCfg, rows_pad, k_pad, Y, last ? Y : T, partial, last ? SIGN_STEPS : k, 1, sz, nullptr, p2h, p2l);
         if (r == DLCO_OK) r = gemm(p1h, p1l, p2h, p2l, sx, sz, T);     // T = X Z^T, Z = a I + b Y + c Y^2
-        if (r == DLCO_OK) r = sign_prep<PREP_SYM>(ctx, f16, D, nCfg, rows_pad, k_pad, T, nullptr, partial, k, 1, sx, X, p1h, p1l);
+        // fp32 X is only read after the last step (trace, optional d_S)
+        if (r == DLCO_OK) r = sign_prep<PREP_SYM>(ctx, f16, D, nCfg, rows_pad, k_pad, T, nullptr, partial, k, 1, sx, last ? X : nullptr, p1h, p1l);
     }
     // A+ = (A + alpha sym((A / alpha) S)) / 2
     if (r == DLCO_OK) r = sign_prep<PREP_INIT>(ctx, f16, D, nCfg, rows_pad, k_pad, d_A, nullptr, partial, 0, 0, sx, nullptr, p2h, p2l);

@@ -215,7 +215,7 @@ def test_pr_patchdist_and_stats(gpu_ctx):
 # ------------------------------------------------------------------------------------------
 # tcgen05 3xTF32 GEMM used by the pj-learn SYRK
 # ------------------------------------------------------------------------------------------
-@pytest.mark.parametrize("m,n,k", [(128, 64, 32), (544, 544, 400), (100, 70, 50), (640, 65, 1000)])
+@pytest.mark.parametrize("m,n,k", [(128, 64, 32), (544, 544, 400), (100, 70, 50), (640, 65, 1000), (1500, 1300, 96)])
 def test_gemm3x_nt_fp32_accuracy(gpu_ctx, m, n, k):
     rng = np.random.default_rng(m + n + k)
     a = rng.normal(0, 1, (m, k)).astype(np.float32)
@@ -632,7 +632,7 @@ def test_pj_sweep_batch200_150_steps_matches_oracle(gpu_ctx, prox):
     assert int(S.rng_state.cpu().numpy().view(np.uint64)[0]) == st64["rng"].state
 
 
-@pytest.mark.parametrize("D,n_cfg", [(32, 3), (160, 2), (544, 5), (100, 1)])
+@pytest.mark.parametrize("D,n_cfg", [(32, 3), (160, 2), (544, 5), (100, 1), (1400, 1)])
 def test_pj_psd_project_matches_eigh(gpu_ctx, D, n_cfg):
     """the prox's projection (src/pj-learn.cpp:434-470: ssyevr, clip, V L V^T) by the tensor-core sign
     iteration: A+ within 1e-5 relative of the fp64 eigen-decomposition route (the fp32 LAPACK route of
