@@ -229,6 +229,22 @@ def test_pipeline(workspace, gpu_ctx):
     assert np.abs(W_g.T.astype(np.float64) @ W_g - A_g).max() <= 3e-5 * max(np.abs(A_g).max(), 1e-30)
     c = toks(open(os.path.join(tmp, "sweep_sign", "logging", "train-0.001-0.1-pj.log")).read())
     assert len(c) == len(b) and [ln[0] for ln in c] == [ln[0] for ln in b]
+    # pj-learn itself with the sign prox: through the flag and through the environment (unchanged scripts)
+    pjs = os.path.join(tmp, "train-pj-sign.h5")
+    rc, so5, se = run("pj-learn", "-iters", 300, "-mu", 0.001, "-gamma", 0.1, "-prox", "sign",
+                      os.path.join(tmp, "train-unproj.h5"), pjs)
+    assert rc == 0, se
+    fl = H5File(pjs)
+    A_l, W_l = fl.read("A"), fl.read("W")
+    assert W_l.shape == W_g.shape and np.array_equal(A_l, A_g)                       # same kernels as pj-sweep
+    assert np.abs(W_l.T.astype(np.float64) @ W_l - A_l).max() <= 3e-5 * np.abs(A_l).max()   # W: batch-1 library eig
+    assert [ln[0] for ln in toks(so5)] == [ln[0] for ln in b]
+    env = dict(os.environ, DLCO_PJ_PROX="sign")
+    pje = os.path.join(tmp, "train-pj-env.h5")
+    r = subprocess.run([os.path.join(BIN, "pj-learn"), "-iters", "300", "-mu", "0.001", "-gamma", "0.1",
+                        os.path.join(tmp, "train-unproj.h5"), pje], capture_output=True, text=True, env=env)
+    assert r.returncode == 0, r.stderr
+    assert np.array_equal(H5File(pje).read("A"), A_l)
     # -shard r/n partitions the grid
     rc, so3, se = run("pj-sweep", os.path.join(tmp, "train-unproj.h5"), os.path.join(tmp, "sweep1"), "-mu", "0.001,0.0020",
                       "-gamma", "0.1", "-iters", 20, "-shard", "1/2")
