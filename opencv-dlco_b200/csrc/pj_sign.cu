@@ -76,9 +76,9 @@ __device__ __forceinline__ float sign_alpha(const double *__restrict__ partial, 
 
 enum { PREP_INIT = 0, PREP_COPY = 1, PREP_POLY = 2, PREP_SYM = 3, PREP_FINAL = 4 };
 
-// Every product of the iteration is symmetric, so the GEMMs skip the 128 x 192 output tiles that lie
-// wholly below the diagonal (dlco_gemm3x_tile_skipped: 5 of 15 at D = 544); a skipped element (a, b) is
-// read from its mirror (b, a).  32 divides both tile sizes, so a 32 x 32 block is either all computed
+// Every product of the iteration is symmetric, so the GEMMs skip the 128 x 128 output tiles that lie
+// below the diagonal (dlco_gemm3x_tile_skipped: 10 of 25 at D = 544); a skipped element (a, b) is
+// read from its mirror (b, a).  32 divides the tile size, so a 32 x 32 block is either all computed
 // or all skipped.  load_logical stages block (a0.., b0..) of p in `tile` with coalesced reads either way
 // and returns whether the tile holds it transposed.
 __device__ __forceinline__ bool load_logical(float (*tile)[33], const float *__restrict__ p, int D, int a0, int b0,
