@@ -359,7 +359,7 @@ int dlco_launch_gemm3x_nt_sym(dlco_ctx *ctx, const float *a_hi, const float *a_l
 // product (tiles below the diagonal skipped), C = out_scale * A B^T
 static int gemm3h_launch(dlco_ctx *ctx, int sym, const GemmEpi &epi, const void *a_hi, const void *a_lo, int a_rows_pad,
                          const void *b_hi, const void *b_lo, int b_rows_pad, int k_pad, int batch, int M, int N,
-                         float out_scale, float *d_C, int64_t ldc, int64_t c_batch_stride)
+                         float out_scale, float *d_C, int64_t ldc, int64_t c_batch_stride, int b_batched = 1)
 {
     DLCO_REQUIRE(k_pad % (2 * BK) == 0 && k_pad > 0 && M > 0 && N > 0 && batch > 0, "gemm3h_nt: bad shapes");
     DLCO_REQUIRE((M + BM - 1) / BM * BM <= a_rows_pad && (N + BN - 1) / BN * BN <= b_rows_pad,
@@ -367,8 +367,9 @@ static int gemm3h_launch(dlco_ctx *ctx, int sym, const GemmEpi &epi, const void 
     GemmMaps maps;
     int r = dlco_make_tmap_2d_ex(&maps.a_hi, a_hi, 2, (uint64_t)batch * a_rows_pad, k_pad, BM, 2 * BK);
     if (r == DLCO_OK) r = dlco_make_tmap_2d_ex(&maps.a_lo, a_lo, 2, (uint64_t)batch * a_rows_pad, k_pad, BM, 2 * BK);
-    if (r == DLCO_OK) r = dlco_make_tmap_2d_ex(&maps.b_hi, b_hi, 2, (uint64_t)batch * b_rows_pad, k_pad, BN, 2 * BK);
-    if (r == DLCO_OK) r = dlco_make_tmap_2d_ex(&maps.b_lo, b_lo, 2, (uint64_t)batch * b_rows_pad, k_pad, BN, 2 * BK);
+    const uint64_t brows = (uint64_t)(b_batched ? batch : 1) * b_rows_pad;
+    if (r == DLCO_OK) r = dlco_make_tmap_2d_ex(&maps.b_hi, b_hi, 2, brows, k_pad, BN, 2 * BK);
+    if (r == DLCO_OK) r = dlco_make_tmap_2d_ex(&maps.b_lo, b_lo, 2, brows, k_pad, BN, 2 * BK);
     if (r != DLCO_OK) return r;
     static bool attr = false;
     if (!attr) {
@@ -383,7 +384,8 @@ static int gemm3h_launch(dlco_ctx *ctx, int sym, const GemmEpi &epi, const void 
     const int grid = total < ctx->sm_count ? total : ctx->sm_count;
     dlco_prof_begin(ctx, 2);
     k_gemm3x_nt<true><<<grid, NTHREADS, SMEM_BYTES, ctx->stream>>>(maps, tl, total, k_pad / (2 * BK), flush, a_rows_pad,
-                                                                 b_rows_pad, M, N, d_C, ldc, c_batch_stride, out_scale, epi);
+                                                                 b_batched ? b_rows_pad : 0, M, N, d_C, ldc,
+                                                                 c_batch_stride, out_scale, epi);
     dlco_prof_end(ctx);
     DLCO_CHECK_LAUNCH(ctx);
     return DLCO_OK;
@@ -395,6 +397,15 @@ int dlco_launch_gemm3h_nt_sym(dlco_ctx *ctx, const void *a_hi, const void *a_lo,
 {
     return gemm3h_launch(ctx, 1, GemmEpi{}, a_hi, a_lo, a_rows_pad, b_hi, b_lo, b_rows_pad, k_pad, batch, M, N, out_scale,
                          d_C, ldc, c_batch_stride);
+}
+
+// general product from fp16 planes (every tile computed); B shared by all batch entries when !b_batched
+int dlco_launch_gemm3h_nt(dlco_ctx *ctx, const void *a_hi, const void *a_lo, int a_rows_pad, const void *b_hi,
+                          const void *b_lo, int b_rows_pad, int b_batched, int k_pad, int batch, int M, int N,
+                          float out_scale, float *d_C, int64_t ldc, int64_t c_batch_stride)
+{
+    return gemm3h_launch(ctx, 0, GemmEpi{}, a_hi, a_lo, a_rows_pad, b_hi, b_lo, b_rows_pad, k_pad, batch, M, N, out_scale,
+                         d_C, ldc, c_batch_stride, b_batched);
 }
 
 // symmetric product, tiles below the diagonal skipped; the result (mode 1, also stored in d_C) or ca I + cb aux + cc result (mode 2, d_C untouched)

@@ -79,6 +79,9 @@ int dlco_launch_gemm3x_nt_sym(dlco_ctx *ctx, const float *a_hi, const float *a_l
 int dlco_launch_gemm3h_nt_sym(dlco_ctx *ctx, const void *a_hi, const void *a_lo, int a_rows_pad, const void *b_hi,
                               const void *b_lo, int b_rows_pad, int k_pad, int batch, int M, int N, float out_scale,
                               float *d_C, int64_t ldc, int64_t c_batch_stride);
+int dlco_launch_gemm3h_nt(dlco_ctx *ctx, const void *a_hi, const void *a_lo, int a_rows_pad, const void *b_hi,
+                          const void *b_lo, int b_rows_pad, int b_batched, int k_pad, int batch, int M, int N,
+                          float out_scale, float *d_C, int64_t ldc, int64_t c_batch_stride);
 int dlco_launch_gemm3h_nt_planes(dlco_ctx *ctx, const void *a_hi, const void *a_lo, int a_rows_pad, const void *b_hi,
                                  const void *b_lo, int b_rows_pad, int k_pad, int batch, int M, int N, float out_scale,
                                  float *d_C, int64_t ldc, int64_t c_batch_stride, int mode, void *p_hi, void *p_lo,

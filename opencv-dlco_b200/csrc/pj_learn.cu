@@ -9,6 +9,7 @@
 //   prox      A = V diag(e+) V^T,  W = rows sqrt(e+) v  K_pj_prox_*               (:448-490)
 #include "common.cuh"
 #include "kernels.h"
+#include <cuda_fp16.h>
 #include <dlfcn.h>
 #include <math.h>
 #include <stdlib.h>
@@ -162,10 +163,12 @@ k_pj_hinge(const float *__restrict__ m, int b, float *__restrict__ c)
 // K-major operand planes of the SYRK: Xt[d][k] = x_k[d] (shared by all configs) and, per config g,
 // Yt[g][d][k] = c_g[k] * x_k[d]; tf32 hi / lo split, zero padding up to (d_pad, k_pad).
 // grid (k_pad/32, d_pad/32, 1 + nCfg): z == 0 writes Xt, z = g + 1 writes Yt[g].
+// F16: fp16 hi / lo planes of sx * x and sy * c x (powers of two; kind::f16 at twice the tf32 rate).
+template <bool F16>
 __global__ void __launch_bounds__(256)
 k_pj_planes(const float *__restrict__ dists, int64_t ld, int D, const int32_t *__restrict__ rows, int nk,
-            const float *__restrict__ c, int d_pad, int k_pad, float *__restrict__ xt_hi,
-            float *__restrict__ xt_lo, float *__restrict__ yt_hi, float *__restrict__ yt_lo)
+            const float *__restrict__ c, int d_pad, int k_pad, float sx, float sy, void *__restrict__ xt_hi,
+            void *__restrict__ xt_lo, void *__restrict__ yt_hi, void *__restrict__ yt_lo)
 {
     __shared__ float tile[32][33];
     const int k0 = blockIdx.x * 32, d0 = blockIdx.y * 32, z = blockIdx.z;
@@ -180,15 +183,29 @@ k_pj_planes(const float *__restrict__ dists, int64_t ld, int D, const int32_t *_
         tile[r][tx] = v;
     }
     __syncthreads();
-    float *hi = z == 0 ? xt_hi : yt_hi + (size_t)(z - 1) * d_pad * k_pad;
-    float *lo = z == 0 ? xt_lo : yt_lo + (size_t)(z - 1) * d_pad * k_pad;
+    const size_t base = z == 0 ? 0 : (size_t)(z - 1) * d_pad * k_pad;
     for (int r = ty; r < 32; r += 8) {                    // r: feature within tile, tx: sample
-        float h, l;
-        tf32_split(tile[tx][r], h, l);
-        const size_t o = (size_t)(d0 + r) * k_pad + k0 + tx;
-        hi[o] = h;
-        lo[o] = l;
+        const size_t o = base + (size_t)(d0 + r) * k_pad + k0 + tx;
+        if (F16) {
+            // fp16 hi / lo of the scaled value; out-of-contract magnitudes saturate instead of becoming inf
+            const float sv = fminf(fmaxf(tile[tx][r] * (z == 0 ? sx : sy), -65000.f), 65000.f);
+            const __half h = __float2half_rn(sv);
+            reinterpret_cast<__half *>(z == 0 ? xt_hi : yt_hi)[o] = h;
+            reinterpret_cast<__half *>(z == 0 ? xt_lo : yt_lo)[o] = __float2half_rn(sv - __half2float(h));
+        } else {
+            float h, l;
+            tf32_split(tile[tx][r], h, l);
+            reinterpret_cast<float *>(z == 0 ? xt_hi : yt_hi)[o] = h;
+            reinterpret_cast<float *>(z == 0 ? xt_lo : yt_lo)[o] = l;
+        }
     }
+}
+
+// DLCO_SYRK_PLANES=tf32 keeps the weighted SYRK on 3xTF32 planes (cross-check); default fp16 hi / lo
+static bool pj_syrk_f16()
+{
+    const char *e = getenv("DLCO_SYRK_PLANES");
+    return !(e && strcmp(e, "tf32") == 0);
 }
 
 // dLoss for nCfg configurations that share one sampled batch (rows) but have their own W.
@@ -199,15 +216,16 @@ static int pj_grad_core(dlco_ctx *ctx, const float *d_dists, int64_t ld, int D, 
                         const int *h_rank, const int32_t *d_rank, float *d_dLoss, const float *d_A_quad = nullptr)
 {
     const int nk = 2 * szBatch;
-    const int d_pad = dlco_gemm3x_rows_pad(D), k_pad = (nk + 31) / 32 * 32;
-    const size_t plane = (size_t)d_pad * k_pad;
+    const bool f16 = pj_syrk_f16();
+    const int d_pad = dlco_gemm3x_rows_pad(D), k_pad = f16 ? (nk + 63) / 64 * 64 : (nk + 31) / 32 * 32;
+    const size_t plane = (size_t)d_pad * k_pad, esz = f16 ? 2 : 4;
     int32_t *rows = (int32_t *)dlco_scratch(ctx, 16, (size_t)nk * sizeof(int32_t));
     float *m = (float *)dlco_scratch(ctx, 17, (size_t)nCfg * nk * 2 * sizeof(float));
-    float *planes = (float *)dlco_scratch(ctx, 18, plane * 2 * (1 + (size_t)nCfg) * sizeof(float));
+    uint8_t *planes = (uint8_t *)dlco_scratch(ctx, 18, plane * 2 * (1 + (size_t)nCfg) * esz);
     if (!rows || !m || !planes) return DLCO_ENOMEM;
     float *c = m + (size_t)nCfg * nk;
-    float *xt_hi = planes, *xt_lo = planes + plane;
-    float *yt_hi = planes + 2 * plane, *yt_lo = yt_hi + plane * nCfg;
+    void *xt_hi = planes, *xt_lo = planes + plane * esz;
+    void *yt_hi = planes + 2 * plane * esz, *yt_lo = planes + (2 + (size_t)nCfg) * plane * esz;
     DLCO_CUDA(cudaMemcpyAsync(rows, d_rows_pos, szBatch * sizeof(int32_t), cudaMemcpyDeviceToDevice, ctx->stream));
     DLCO_CUDA(cudaMemcpyAsync(rows + szBatch, d_rows_neg, szBatch * sizeof(int32_t), cudaMemcpyDeviceToDevice, ctx->stream));
     if (d_A_quad) {            // margins x^T A x from A itself (sign-iteration prox: no W is kept)
@@ -227,10 +245,22 @@ static int pj_grad_core(dlco_ctx *ctx, const float *d_dists, int64_t ld, int D, 
     k_pj_hinge<<<nCfg, 256, (size_t)nk * sizeof(float), ctx->stream>>>(m, szBatch, c);
     DLCO_CHECK_LAUNCH(ctx);
     dim3 pg(k_pad / 32, d_pad / 32, 1 + nCfg);
-    k_pj_planes<<<pg, 256, 0, ctx->stream>>>(d_dists, ld, D, rows, nk, c, d_pad, k_pad, xt_hi, xt_lo, yt_hi, yt_lo);
+    if (f16) {
+        // |x| <= 1 by construction (differences of values clamped to [0, 1], src/comp-uprjdists.cpp:322-327): 2^13
+        // keeps hi AND lo normal fp16 numbers down to |x| ~ 1e-5 and saturates only beyond |x| = 8; c x with
+        // |c| <= szBatch gets 2^13 / 2^ceil(log2 szBatch)
+        int lg = 0;
+        while ((1 << lg) < szBatch) lg++;
+        const float sx = 8192.f, sy = ldexpf(8192.f, -lg);
+        k_pj_planes<true><<<pg, 256, 0, ctx->stream>>>(d_dists, ld, D, rows, nk, c, d_pad, k_pad, sx, sy, xt_hi, xt_lo, yt_hi, yt_lo);
+        DLCO_CHECK_LAUNCH(ctx);
+        return dlco_launch_gemm3h_nt(ctx, yt_hi, yt_lo, d_pad, xt_hi, xt_lo, d_pad, 0, k_pad, nCfg, D, D, 1.0f / (sx * sy),
+                                     d_dLoss, D, (int64_t)D * D);
+    }
+    k_pj_planes<false><<<pg, 256, 0, ctx->stream>>>(d_dists, ld, D, rows, nk, c, d_pad, k_pad, 1.f, 1.f, xt_hi, xt_lo, yt_hi, yt_lo);
     DLCO_CHECK_LAUNCH(ctx);
-    return dlco_launch_gemm3x_nt(ctx, yt_hi, yt_lo, d_pad, xt_hi, xt_lo, d_pad, 0, k_pad, nCfg, D, D, d_dLoss, D,
-                                 (int64_t)D * D);
+    return dlco_launch_gemm3x_nt(ctx, (const float *)yt_hi, (const float *)yt_lo, d_pad, (const float *)xt_hi,
+                                 (const float *)xt_lo, d_pad, 0, k_pad, nCfg, D, D, d_dLoss, D, (int64_t)D * D);
 }
 
 extern "C" int dlco_pj_rda_grad_grid(dlco_ctx *ctx, const float *d_dists, int64_t ld, int D,
@@ -283,8 +313,8 @@ extern "C" int dlco_pj_wsyrk(dlco_ctx *ctx, const float *d_dists, int64_t ld, in
     float *planes = (float *)dlco_scratch(ctx, 18, plane * 4 * sizeof(float));
     if (!planes) return DLCO_ENOMEM;
     dim3 pg(k_pad / 32, d_pad / 32, 2);
-    k_pj_planes<<<pg, 256, 0, ctx->stream>>>(d_dists, ld, D, d_rows, nk, d_c, d_pad, k_pad, planes, planes + plane,
-                                             planes + 2 * plane, planes + 3 * plane);
+    k_pj_planes<false><<<pg, 256, 0, ctx->stream>>>(d_dists, ld, D, d_rows, nk, d_c, d_pad, k_pad, 1.f, 1.f, planes,
+                                                    planes + plane, planes + 2 * plane, planes + 3 * plane);
     DLCO_CHECK_LAUNCH(ctx);
     return dlco_launch_gemm3x_nt(ctx, planes + 2 * plane, planes + 3 * plane, d_pad, planes, planes + plane, d_pad, 0,
                                  k_pad, 1, D, D, d_dLoss, D, (int64_t)D * D);

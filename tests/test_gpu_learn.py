@@ -338,7 +338,9 @@ def test_pj_staged_grad_equals_fused(gpu_ctx):
     m = gpu_ctx.pj_margins(d_x, rows, d_W, 30)
     c = gpu_ctx.pj_hinge_weights(m)
     staged = gpu_ctx.pj_wsyrk(d_x, rows, c).cpu().numpy()
-    assert np.array_equal(fused, staged)
+    # staged: general weights, 3xTF32 planes; fused: hinge counts, fp16 hi/lo planes (DLCO_SYRK_PLANES=tf32 makes
+    # them bitwise equal) -- the same 22-bit operands, different rounding of the sums
+    assert np.abs(fused - staged).max() <= 2e-6 * np.abs(fused).max()
     # split the batch rows in two "ranks": partial SYRKs add up to the whole
     half = rows.numel() // 3
     part = gpu_ctx.pj_wsyrk(d_x, rows[:half].contiguous(), c[:half].contiguous()) + \
@@ -364,7 +366,9 @@ def test_sharded_driver_world1_matches_direct(gpu_ctx):
     rp, rn = ip[:40], ineg[:40]
     g = sp.grad(rp, rn, d_W, 16).cpu().numpy()
     want = gpu_ctx.pj_rda_grad(d_x, dev_t(gpu_ctx, rp), dev_t(gpu_ctx, rn), d_W, 16).cpu().numpy()
-    assert np.array_equal(g, want)
+    # the staged SYRK keeps general weights on 3xTF32 planes, the fused one runs fp16 hi/lo planes: same
+    # 22-bit operands, different rounding of the sums
+    assert np.abs(g - want).max() <= 2e-6 * np.abs(want).max()
     loss, regul = sp.validate(ip[npt:], ineg[nnt:], d_W, 16, A, 0.001)
     l2, r2 = gpu_ctx.pj_validate(d_x, dev_t(gpu_ctx, ip[npt:]), dev_t(gpu_ctx, ineg[nnt:]), d_W, 16, A, 0.001)
     assert abs(loss - l2) <= 1e-6 * abs(l2) and abs(regul - r2) <= 1e-6 * abs(r2)

@@ -176,7 +176,17 @@ def test_pipeline(workspace, gpu_ctx):
     P = dlco_b200.learn.PjLearner(gpu_ctx, torch.from_numpy(x_tr).to(dev), lab_tr, 0.001, 0.1, emit=lines.append)
     P.train(300)
     strip = lambda s: re.sub(r" Ttime: .*$", "", s)                                   # noqa: E731
-    assert [strip(x) for x in so.splitlines() if x[:5] in ("Best:", "Step:", "Stat:")] == [strip(x) for x in lines]
+    la = [strip(x).split() for x in so.splitlines() if x[:5] in ("Best:", "Step:", "Stat:")]
+    lb = [strip(x).split() for x in lines]
+    assert len(la) == len(lb)
+    for ta, tb in zip(la, lb):                  # same lines; printed floats may differ in the last digit (library eig
+        assert len(ta) == len(tb)               # is not bitwise reproducible from run to run)
+        for xa, xb in zip(ta, tb):
+            fa, fb = xa.strip("()"), xb.strip("()")
+            if re.fullmatch(r"-?\d+\.\d+", fa):
+                assert abs(float(fa) - float(fb)) <= 2e-6 + 0.0101 * (len(fa.split(".")[1]) == 2), (ta, tb)
+            else:
+                assert xa == xb, (ta, tb)
     f = H5File(pjm)
     W, A = f.read("W"), f.read("A")
     assert A.shape == (D, D) and W.shape[1] == D and f.info("W")["layout"][0] == "contiguous"
