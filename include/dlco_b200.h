@@ -133,7 +133,10 @@ int dlco_pr_validate(dlco_ctx *ctx, const float *d_dists, int64_t ld, int F,
 
 /* ---- pj-learn inner step (src/pj-learn.cpp:311-432) ------------------------------------
  * dlco_pj_rda_grad: gather the 2 x szBatch sampled rows, margins ||W d||^2, hinge mask,
- * dLoss = X^T diag(c) X (tensor-core SYRK, 3xTF32).  d_W: rank x D (ldW = D).
+ * dLoss = X^T diag(c) X (tensor-core SYRK: fp16 hi/lo planes of 2^13 x and 2^13 c x / 2^ceil(log2 szBatch),
+ * three products per fp32 product, 22 mantissa bits as 3xTF32; DLCO_SYRK_PLANES=tf32 selects 3xTF32 planes).
+ * Input contract of the fp16 route: |x| <= 8 (comp-uprjdists' differences of values clamped to [0, 1]
+ * satisfy |x| <= 1); larger magnitudes saturate.  d_W: rank x D (ldW = D).
  * d_rows_pos/neg: szBatch row indices into d_dists. */
 int dlco_pj_rda_grad(dlco_ctx *ctx, const float *d_dists, int64_t ld, int D,
                      const int32_t *d_rows_pos, const int32_t *d_rows_neg, int szBatch,
