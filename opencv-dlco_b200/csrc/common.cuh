@@ -36,6 +36,7 @@ struct dlco_ctx {
     cudaStream_t side_stream;
     cudaEvent_t side_ev[6];
     int side_ready;
+    uint32_t attr_mask;   // which kernels had their dynamic-smem limit raised on THIS context's device
     void *cusolver;       // cusolverDnHandle_t (lazy)
     void *cusolver_lib;   // dlopen handle
 };
@@ -60,6 +61,15 @@ void *dlco_pinned(dlco_ctx *ctx, int slot, size_t bytes);
 int dlco_side_stream(dlco_ctx *ctx);
 void dlco_prof_begin(dlco_ctx *ctx, int which);
 void dlco_prof_end(dlco_ctx *ctx);
+
+// cudaFuncSetAttribute is per device: remember it per context (one context per GPU), not per process
+#define DLCO_SMEM_ONCE(ctx, bit, func, bytes)                                                        \
+    do {                                                                                             \
+        if (!((ctx)->attr_mask & (1u << (bit)))) {                                                   \
+            DLCO_CUDA(cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes)); \
+            (ctx)->attr_mask |= 1u << (bit);                                                         \
+        }                                                                                            \
+    } while (0)
 
 #define DLCO_CUDA(call)                                                                     \
     do {                                                                                    \

@@ -313,12 +313,7 @@ static int gemm3x_launch(dlco_ctx *ctx, int sym, const float *a_hi, const float 
     if (r == DLCO_OK) r = dlco_make_tmap_2d(&maps.b_hi, b_hi, brows, k_pad, BN, BK);
     if (r == DLCO_OK) r = dlco_make_tmap_2d(&maps.b_lo, b_lo, brows, k_pad, BN, BK);
     if (r != DLCO_OK) return r;
-    static bool attr = false;
-    if (!attr) {
-        DLCO_CUDA(cudaFuncSetAttribute(k_gemm3x_nt<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-        DLCO_CUDA(cudaFuncSetAttribute(k_gemm3x_nt<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-        attr = true;
-    }
+    DLCO_SMEM_ONCE(ctx, 0, k_gemm3x_nt<false>, SMEM_BYTES);
     GemmTiles tl;
     DLCO_REQUIRE(gemm_tiles(&tl, M, N, sym) == 0, "gemm3x_nt: more than 96 output tiles per batch entry");
     const int total = batch * tl.n;
@@ -371,11 +366,7 @@ static int gemm3h_launch(dlco_ctx *ctx, int sym, const GemmEpi &epi, const void 
     if (r == DLCO_OK) r = dlco_make_tmap_2d_ex(&maps.b_hi, b_hi, 2, brows, k_pad, BN, 2 * BK);
     if (r == DLCO_OK) r = dlco_make_tmap_2d_ex(&maps.b_lo, b_lo, 2, brows, k_pad, BN, 2 * BK);
     if (r != DLCO_OK) return r;
-    static bool attr = false;
-    if (!attr) {
-        DLCO_CUDA(cudaFuncSetAttribute(k_gemm3x_nt<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-        attr = true;
-    }
+    DLCO_SMEM_ONCE(ctx, 1, k_gemm3x_nt<true>, SMEM_BYTES);
     const char *e = getenv("DLCO_GEMM_FLUSH");
     const int flush = e && atoi(e) > 0 ? atoi(e) : 1;      // K = 64 per chunk here: drain every chunk
     GemmTiles tl;

@@ -315,11 +315,7 @@ int dlco_launch_pool_tc_uprj(dlco_ctx *ctx, const dlco_bank *bank, const void *d
     if (r != DLCO_OK) return r;
     r = dlco_make_tmap_2d_ex(&maps.b_lo, d_blo, 2, (uint64_t)n_pairs_padded * 16, KTOT, BN, BK);
     if (r != DLCO_OK) return r;
-    static bool attr_set = false;
-    if (!attr_set) {
-        DLCO_CUDA(cudaFuncSetAttribute(k_pool_fulldist<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-        attr_set = true;
-    }
+    DLCO_SMEM_ONCE(ctx, 2, k_pool_fulldist<1>, SMEM_BYTES);
     const int m_tiles = bank->nRowsPad / BM, n_tiles = n_pairs_padded / 16;
     const int total = m_tiles * n_tiles * ksplit;
     const int grid = total < ctx->sm_count ? total : ctx->sm_count;
@@ -353,11 +349,7 @@ int dlco_launch_pool_tc(dlco_ctx *ctx, const dlco_bank *bank, const void *d_bhi,
     if (r != DLCO_OK) return r;
     r = dlco_make_tmap_2d_ex(&maps.b_lo, d_blo, 2, (uint64_t)n_pairs_padded * 16, KTOT, BN, BK);
     if (r != DLCO_OK) return r;
-    static bool attr_set = false;
-    if (!attr_set) {
-        DLCO_CUDA(cudaFuncSetAttribute(k_pool_fulldist<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-        attr_set = true;
-    }
+    DLCO_SMEM_ONCE(ctx, 3, k_pool_fulldist<0>, SMEM_BYTES);
     const int m_tiles = bank->nRowsPad / BM, n_tiles = n_pairs_padded / 16;
     const int total = m_tiles * n_tiles;
     const int grid = total < ctx->sm_count ? total : ctx->sm_count;

@@ -164,12 +164,8 @@ static int pr_rda_launch(dlco_ctx *ctx, const float *d_dists, int64_t ld, int F,
     const size_t stage = (size_t)2 * F * sizeof(float);
     const int stages = stage * 4 <= 200 * 1024 ? 4 : 2;
     const size_t smem = stage * stages;
-    static bool attr = false;
-    if (!attr) {
-        DLCO_CUDA(cudaFuncSetAttribute(k_pr_rda<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
-        DLCO_CUDA(cudaFuncSetAttribute(k_pr_rda<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
-        attr = true;
-    }
+    DLCO_SMEM_ONCE(ctx, 4, k_pr_rda<4>, 220 * 1024);
+    DLCO_SMEM_ONCE(ctx, 5, k_pr_rda<2>, 220 * 1024);
     if (stages == 4)
         k_pr_rda<4><<<nCfg, threads, smem, ctx->stream>>>(d_dists, ld, F, d_rows, n, t0, d_mu, d_gamma, d_w, d_dfavg);
     else
@@ -362,11 +358,7 @@ int dlco_gemv_rows(dlco_ctx *ctx, const float *d_dists, int64_t ld, int F, const
     const int64_t want = (n + GEMV_THREADS / 32 - 1) / (GEMV_THREADS / 32);
     const int64_t cap = (int64_t)ctx->sm_count * 4;
     const int grid = (int)(want < cap ? want : cap);
-    static bool attr = false;
-    if (!attr) {
-        DLCO_CUDA(cudaFuncSetAttribute(k_gemv_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, 48 * 1024));
-        attr = true;
-    }
+    DLCO_SMEM_ONCE(ctx, 6, k_gemv_rows, 48 * 1024);
     dlco_prof_begin(ctx, 3);
     k_gemv_rows<<<grid, GEMV_THREADS, (size_t)F * sizeof(float), ctx->stream>>>(d_dists, ld, F, d_rows, n, d_w, d_out,
                                                                                gemv_sparse_enabled() ? 1 : 0);

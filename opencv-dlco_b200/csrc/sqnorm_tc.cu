@@ -382,11 +382,7 @@ int dlco_sqnorm_tc(dlco_ctx *ctx, const float *d_X, int64_t ld, const int32_t *d
     int stages = (227 * 1024 - tail - OP_STAGES * op_bytes) / RAW_BYTES;
     stages = stages > MAX_STAGING ? MAX_STAGING : stages;
     const int smem_bytes = OP_STAGES * op_bytes + stages * RAW_BYTES + tail;
-    static int attr_bytes = 0;
-    if (smem_bytes > attr_bytes) {
-        DLCO_CUDA(cudaFuncSetAttribute(k_sqnorm_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-        attr_bytes = 227 * 1024;
-    }
+    DLCO_SMEM_ONCE(ctx, 7, k_sqnorm_tc, 227 * 1024);
     const int64_t n_tiles = (n + BM - 1) / BM;
     const int grid = (int)(n_tiles < ctx->sm_count ? n_tiles : ctx->sm_count);
     dlco_prof_begin(ctx, 5);
