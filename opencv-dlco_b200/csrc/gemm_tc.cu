@@ -368,7 +368,7 @@ static int gemm3h_launch(dlco_ctx *ctx, int sym, const GemmEpi &epi, const void 
     if (r != DLCO_OK) return r;
     DLCO_SMEM_ONCE(ctx, 1, k_gemm3x_nt<true>, SMEM_BYTES);
     const char *e = getenv("DLCO_GEMM_FLUSH");
-    const int flush = e && atoi(e) > 0 ? atoi(e) : 1;      // K = 64 per chunk here: drain every chunk
+    const int flush = e && atoi(e) > 0 ? atoi(e) : 2;      // K = 64 per chunk here: drain every 128 (measured: 1 -> 2 is 3 % faster, error 4.3e-6 -> 4.6e-6)
     GemmTiles tl;
     DLCO_REQUIRE(gemm_tiles(&tl, M, N, sym) == 0, "gemm3h_nt: more than 96 output tiles per batch entry");
     const int total = batch * tl.n;
