@@ -321,11 +321,12 @@ int dlco_make_tmap_2d(CUtensorMap *map, const float *base, uint64_t rows, uint64
 // ---- bank construction -------------------------------------------------------------------
 // The GEMM A operand is not the bank as given: identical filters are computed once (the default
 // gen-poolregion bank has 31 776 distinct rows among 40 960: rings at phi = 0, pi/4 and r = 0
-// repeat members), rows are sorted by their K support so that a 128-row tile touches few
-// 64-wide K chunks (K index = x*64 + y, so chunk c is image row x = c; a Gaussian of width
-// sigma covers rows x0 +- 3 sigma only), and each row is scaled by a power of two so that its
-// largest entry lies in [2^14, 2^15): then hi = rn16(v) and lo = rn16(v - hi) are both normal
-// fp16 numbers and hi + lo carries 22 mantissa bits of v.
+// repeat members); the K axis is permuted into 8 x 8 pixel blocks (dlco_kperm: K chunk c is the
+// pixel block (c / 8, c % 8)) and the distinct rows are clustered by the set of blocks their
+// support touches, so that a 128-row tile skips the K chunks in which all its filters are zero
+// (a Gaussian of width sigma covers x0 +- 3 sigma, y0 +- 3 sigma only); and each row is scaled by
+// a power of two so that its largest entry lies in [2^14, 2^15): then hi = rn16(v) and
+// lo = rn16(v - hi) are both normal fp16 numbers and hi + lo carries 22 mantissa bits of v.
 __global__ void k_bank_planes(const float *__restrict__ src, const int32_t *__restrict__ row_src, int n_rows,
                               int n_rows_pad, __half *__restrict__ hi, __half *__restrict__ lo,
                               float *__restrict__ inv_scale)
@@ -360,8 +361,9 @@ __global__ void k_bank_planes(const float *__restrict__ src, const int32_t *__re
     for (int k = threadIdx.x; k < K; k += 256) {
         const float v = f[k] * sc;
         const __half a = __float2half_rn(v);
-        h[k] = a;
-        l[k] = __float2half_rn(v - __half2float(a));
+        const int kp = dlco_kperm(k);
+        h[kp] = a;
+        l[kp] = __float2half_rn(v - __half2float(a));
     }
 }
 
@@ -372,9 +374,45 @@ static inline uint64_t mix64(uint64_t h, uint64_t v)
 }
 
 struct BankKey {
-    uint64_t mask, hash;
-    int lo, hi, idx;
+    uint64_t mask, hash;     // mask: bit (x/8)*8 + y/8 set <=> the filter is non-zero somewhere in that pixel block
+    int idx;
 };
+
+// Order the distinct filters so that the 128-row tiles touch few K chunks: greedy over the groups of rows with
+// equal block masks (a few hundred for a gen-poolregion bank).  A tile is seeded with the smallest remaining mask and
+// takes, row group by row group, whatever enlarges the union of its masks least.  Deterministic.
+static void bank_cluster(const std::vector<BankKey> &keys, std::vector<int> &rows)
+{
+    struct Group { uint64_t mask; std::vector<int> rows; size_t next; };
+    std::vector<int> by_mask(rows);
+    std::stable_sort(by_mask.begin(), by_mask.end(), [&](int a, int c) { return keys[a].mask < keys[c].mask; });
+    std::vector<Group> groups;
+    for (int i : by_mask) {
+        if (groups.empty() || groups.back().mask != keys[i].mask) groups.push_back(Group{keys[i].mask, {}, 0});
+        groups.back().rows.push_back(i);
+    }
+    std::stable_sort(groups.begin(), groups.end(), [](const Group &a, const Group &c) {
+        const int pa = __builtin_popcountll(a.mask), pc = __builtin_popcountll(c.mask);
+        return pa != pc ? pa < pc : a.mask < c.mask;
+    });
+    size_t left = rows.size(), out = 0;
+    while (left > 0) {
+        uint64_t u = 0;
+        int fill = 0;
+        while (fill < 128 && left > 0) {
+            int best = -1, best_grow = 65, best_own = -1;
+            for (int g = 0; g < (int)groups.size(); g++) {
+                if (groups[g].next == groups[g].rows.size()) continue;
+                if (fill == 0) { best = g; break; }           // seed: smallest remaining mask
+                const int grow = __builtin_popcountll(u | groups[g].mask), own = __builtin_popcountll(groups[g].mask);
+                if (grow < best_grow || (grow == best_grow && own > best_own)) { best = g; best_grow = grow; best_own = own; }
+            }
+            Group &g = groups[best];
+            u |= g.mask;
+            while (fill < 128 && g.next < g.rows.size()) { rows[out++] = g.rows[g.next++]; fill++; left--; }
+        }
+    }
+}
 
 static int bank_finish(dlco_ctx *ctx, dlco_bank *b, const float *h_filters)
 {
@@ -384,31 +422,31 @@ static int bank_finish(dlco_ctx *ctx, dlco_bank *b, const float *h_filters)
         const uint32_t *p = (const uint32_t *)(h_filters + (size_t)i * K);
         uint64_t mask = 0, hash = 0x1234567ULL;
         for (int x = 0; x < 64; x++) {
-            uint32_t any = 0;
-            for (int y = 0; y < 64; y++) {
-                const uint32_t v = p[x * 64 + y];
-                any |= (v << 1);                          // -0.0f counts as zero
-                hash = mix64(hash, v);
+            for (int yb = 0; yb < 8; yb++) {
+                uint32_t any = 0;
+                for (int y = 8 * yb; y < 8 * yb + 8; y++) {
+                    const uint32_t v = p[x * 64 + y];
+                    any |= (v << 1);                      // -0.0f counts as zero
+                    hash = mix64(hash, v);
+                }
+                if (any) mask |= 1ULL << ((x >> 3) * 8 + yb);
             }
-            if (any) mask |= 1ULL << x;
         }
         keys[i].mask = mask;
         keys[i].hash = hash;
         keys[i].idx = i;
-        keys[i].lo = mask ? __builtin_ctzll(mask) : 64;
-        keys[i].hi = mask ? 63 - __builtin_clzll(mask) : 64;
     }
+    // identical filters: equal (hash, mask) neighbours compared byte by byte; the first in bank order is kept
     std::vector<int> order(nF);
     for (int i = 0; i < nF; i++) order[i] = i;
     std::sort(order.begin(), order.end(), [&](int a, int c) {
         const BankKey &x = keys[a], &y = keys[c];
-        if (x.lo != y.lo) return x.lo < y.lo;
-        if (x.hi != y.hi) return x.hi < y.hi;
         if (x.hash != y.hash) return x.hash < y.hash;
+        if (x.mask != y.mask) return x.mask < y.mask;
         return x.idx < y.idx;
     });
-    std::vector<int32_t> row_src, map(nF);
-    row_src.reserve(nF);
+    std::vector<int> rep(nF);                 // representative (first identical filter) of every filter
+    std::vector<int> distinct;
     for (int o = 0; o < nF; o++) {
         const int i = order[o];
         bool dup = false;
@@ -416,10 +454,15 @@ static int bank_finish(dlco_ctx *ctx, dlco_bank *b, const float *h_filters)
             const int j = order[o - 1];
             dup = keys[i].hash == keys[j].hash && keys[i].mask == keys[j].mask &&
                   memcmp(h_filters + (size_t)i * K, h_filters + (size_t)j * K, (size_t)K * 4) == 0;
+            if (dup) rep[i] = rep[j];
         }
-        if (!dup) row_src.push_back(i);
-        map[i] = (int32_t)row_src.size() - 1;
+        if (!dup) { rep[i] = i; distinct.push_back(i); }
     }
+    std::sort(distinct.begin(), distinct.end());
+    bank_cluster(keys, distinct);
+    std::vector<int32_t> row_src(distinct.begin(), distinct.end()), map(nF), row_of(nF, -1);
+    for (int r = 0; r < (int)row_src.size(); r++) row_of[row_src[r]] = r;
+    for (int i = 0; i < nF; i++) map[i] = row_of[rep[i]];
     b->nRows = (int)row_src.size();
     b->nRowsPad = (b->nRows + 127) / 128 * 128;
     const int tiles = b->nRowsPad / 128;

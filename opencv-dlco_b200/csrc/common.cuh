@@ -244,6 +244,16 @@ __device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t adesc, uint64
         : "memory");
 }
 
+// K index of pixel p = x*64 + y in the fp16 operand planes of the tensor-core pooling GEMM (the filter bank's and
+// the descriptors' alike): the patch is cut into 8 x 8 pixel blocks, one block per 64-wide K chunk, so that a
+// Gaussian whose +-3 sigma box is w pixels wide touches about (w/8 + 1)^2 of the 64 chunks rather than w of them.
+// Eight consecutive y of one x stay contiguous (16 bytes of fp16).
+__host__ __device__ static inline int dlco_kperm(int p)
+{
+    const int x = p >> 6, y = p & 63;
+    return ((((x >> 3) << 3) | (y >> 3)) << 6) | ((x & 7) << 3) | (y & 7);
+}
+
 // K-major, 128B-swizzled operand tile: rows of 128 bytes, 8-row groups 1024 B apart.
 __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr)
 {

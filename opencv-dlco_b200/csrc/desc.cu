@@ -314,7 +314,7 @@ k_desc(const uint8_t *__restrict__ patches, const int32_t *__restrict__ ids, int
                     lv[j] = (b == b1[j]) ? l1[j] : 0u;
                     if (b == b2[j]) { hv[j] = h2[j]; lv[j] = l2[j]; }
                 }
-                const size_t o = ((size_t)slot * 8 + b) * NPIX + p0;
+                const size_t o = ((size_t)slot * 8 + b) * NPIX + dlco_kperm(p0);      // 8 x 8 pixel blocks, see kernels.h
                 *reinterpret_cast<uint4 *>(reinterpret_cast<__half *>(out0) + o) =
                     make_uint4(hv[0] | (hv[1] << 16), hv[2] | (hv[3] << 16), hv[4] | (hv[5] << 16), hv[6] | (hv[7] << 16));
                 *reinterpret_cast<uint4 *>(reinterpret_cast<__half *>(out1) + o) =
