@@ -379,8 +379,10 @@ struct BankKey {
 };
 
 // Order the distinct filters so that the 128-row tiles touch few K chunks: greedy over the groups of rows with
-// equal block masks (a few hundred for a gen-poolregion bank).  A tile is seeded with the smallest remaining mask and
-// takes, row group by row group, whatever enlarges the union of its masks least.  Deterministic.
+// equal block masks (a few hundred for a gen-poolregion bank).  A tile is seeded with the largest remaining mask and
+// takes, row group by row group, whatever enlarges the union of its masks least (the largest such group first, so
+// that the small masks are left to tiles of their own).  Deterministic.  Default bank: 9 718 chunks; seeding with the
+// smallest mask instead: 9 912; lower bound (sum of own chunks / 128): 9 119.
 static void bank_cluster(const std::vector<BankKey> &keys, std::vector<int> &rows)
 {
     struct Group { uint64_t mask; std::vector<int> rows; size_t next; };
@@ -393,7 +395,7 @@ static void bank_cluster(const std::vector<BankKey> &keys, std::vector<int> &row
     }
     std::stable_sort(groups.begin(), groups.end(), [](const Group &a, const Group &c) {
         const int pa = __builtin_popcountll(a.mask), pc = __builtin_popcountll(c.mask);
-        return pa != pc ? pa < pc : a.mask < c.mask;
+        return pa != pc ? pa > pc : a.mask < c.mask;
     });
     size_t left = rows.size(), out = 0;
     while (left > 0) {
@@ -403,7 +405,7 @@ static void bank_cluster(const std::vector<BankKey> &keys, std::vector<int> &row
             int best = -1, best_grow = 65, best_own = -1;
             for (int g = 0; g < (int)groups.size(); g++) {
                 if (groups[g].next == groups[g].rows.size()) continue;
-                if (fill == 0) { best = g; break; }           // seed: smallest remaining mask
+                if (fill == 0) { best = g; break; }           // seed: largest remaining mask
                 const int grow = __builtin_popcountll(u | groups[g].mask), own = __builtin_popcountll(groups[g].mask);
                 if (grow < best_grow || (grow == best_grow && own > best_own)) { best = g; best_grow = grow; best_own = own; }
             }
