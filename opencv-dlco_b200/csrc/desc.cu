@@ -20,6 +20,7 @@
 #define PS DLCO_PATCH
 #define NPIX (PS * PS)
 #define SROW (PS + 1)   // padded row stride: column walks are bank-conflict free
+#define OROW (PS + 4)   // row stride of the output staging: 16-byte aligned rows, conflict-free float4 reads down a column
 
 struct DescParams {
     float taps[32];
@@ -109,8 +110,8 @@ k_desc(const uint8_t *__restrict__ patches, const int32_t *__restrict__ ids, int
        int n_slots, DescParams prm, float *__restrict__ out0, float *__restrict__ out1,
        float *__restrict__ inv_scale)
 {
-    __shared__ __align__(16) float s_a[PS * SROW];
-    __shared__ __align__(16) float s_b[PS * SROW];
+    __shared__ __align__(16) float s_a[PS * OROW];     // PS * SROW while blurring, PS * OROW as output staging
+    __shared__ __align__(16) float s_b[PS * OROW];
     __shared__ __align__(16) uint32_t s_red[2][8];
     __shared__ __align__(16) uint8_t s_bin[NPIX];
 
@@ -255,8 +256,8 @@ k_desc(const uint8_t *__restrict__ patches, const int32_t *__restrict__ ids, int
         const int p = tid + DESC_THREADS * i;
         const float g = prm.bnorm ? mag[i] * scale : mag[i];
         mx = fmaxf(mx, g);
-        s_a[p] = (1.0f - off1[i]) * g;
-        s_b[p] = off1[i] * g;
+        s_a[p + 4 * (p >> 6)] = (1.0f - off1[i]) * g;
+        s_b[p + 4 * (p >> 6)] = off1[i] * g;
         s_bin[p] = (uint8_t)((binp[i >> 3] >> (4 * (i & 7))) & 15u);
     }
     if (MODE == DESC_OUT_SPLIT) {
@@ -268,12 +269,17 @@ k_desc(const uint8_t *__restrict__ patches, const int32_t *__restrict__ ids, int
     }
 #pragma unroll
     for (int k = 0; k < NPIX / 8 / DESC_THREADS; k++) {
-        const int p0 = 8 * (tid + DESC_THREADS * k);
+        // group of 8 pixels (one x, 8 consecutive y).  Plain rows: consecutive threads take consecutive groups.
+        // fp16 planes in dlco_kperm order: 8 consecutive threads take the 8 x of one pixel block, so that they
+        // write its 128 bytes together and a warp writes 4 adjacent blocks.
+        const int g = tid + DESC_THREADS * k;
+        const int p0 = MODE == DESC_OUT_SPLIT ? ((((g >> 6) << 3) | (g & 7)) << 6) | (((g >> 3) & 7) << 3) : 8 * g;
+        const int q0 = p0 + 4 * (p0 >> 6);
         float a1[8], a2[8];
-        *reinterpret_cast<float4 *>(a1) = *reinterpret_cast<const float4 *>(s_a + p0);
-        *reinterpret_cast<float4 *>(a1 + 4) = *reinterpret_cast<const float4 *>(s_a + p0 + 4);
-        *reinterpret_cast<float4 *>(a2) = *reinterpret_cast<const float4 *>(s_b + p0);
-        *reinterpret_cast<float4 *>(a2 + 4) = *reinterpret_cast<const float4 *>(s_b + p0 + 4);
+        *reinterpret_cast<float4 *>(a1) = *reinterpret_cast<const float4 *>(s_a + q0);
+        *reinterpret_cast<float4 *>(a1 + 4) = *reinterpret_cast<const float4 *>(s_a + q0 + 4);
+        *reinterpret_cast<float4 *>(a2) = *reinterpret_cast<const float4 *>(s_b + q0);
+        *reinterpret_cast<float4 *>(a2 + 4) = *reinterpret_cast<const float4 *>(s_b + q0 + 4);
         const uint2 bb = *reinterpret_cast<const uint2 *>(s_bin + p0);
         int b1[8], b2[8];
 #pragma unroll
