@@ -43,7 +43,7 @@ struct dlco_ctx {
 
 struct dlco_bank {
     int nF;              // filters as given by the caller
-    int nRows;           // distinct filters, sorted by K support (rows of the GEMM A operand)
+    int nRows;           // distinct filters, clustered by the pixel blocks they touch (rows of the GEMM A operand)
     int nRowsPad;        // rows padded to a multiple of 128 (zero rows)
     void *d_hi;          // nRowsPad x 4096 fp16: hi = rn16(f * scale_row)
     void *d_lo;          // nRowsPad x 4096 fp16: lo = rn16(f * scale_row - hi)

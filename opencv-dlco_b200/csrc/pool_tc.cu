@@ -17,9 +17,11 @@
 // the partial sums from TMEM and add them in round-to-nearest fp32 registers, which bounds the
 // truncation bias by that of a K = 256 product (< 1e-6).
 //
-// Sparsity: rows of the A operand are the DISTINCT filters of the bank sorted by K support
-// (api.cu), and kmask[m] says which 64-wide K chunks contain a non-zero of M tile m; producer
-// and MMA issuer walk only those chunks (56 % of the dense work for the gen-poolregion bank).
+// Sparsity: rows of the A operand are the DISTINCT filters of the bank, the K axis of both operands runs over
+// 8 x 8 pixel blocks (dlco_kperm, common.cuh: K chunk c = pixel block (c / 8, c % 8)) and the rows are clustered by
+// the blocks their support touches (bank_cluster, api.cu); kmask[m] says which 64-wide K chunks contain a non-zero
+// of M tile m, and producer and MMA issuer walk only those chunks (61 % of the distinct rows' dense work, 47 % of
+// the whole bank's, for the gen-poolregion bank).
 //
 // CTA tile 128 rows (TMEM lanes) x 256 columns (16 pairs x 2 patches x 8 bins), K chunk 64 fp16 =
 // one 128-byte swizzle row.  Roles: warp 0 = TMA producer, warp 1 = MMA issuer (one lane) + TMEM
