@@ -112,16 +112,35 @@ extern "C" int dlco_fulldist_build_host(dlco_ctx *ctx, const dlco_bank *bank, co
         if (!h_stage[s]) return DLCO_ENOMEM;
     }
     uint8_t *d_stage = (uint8_t *)dlco_scratch(ctx, 23, 2 * (pbytes + ibytes));
-    float *d_o = (float *)dlco_scratch(ctx, 24, (size_t)nb * rings * sizeof(float));
+    const size_t obytes = (size_t)nb * rings * sizeof(float);
+    uint8_t *d_o = (uint8_t *)dlco_scratch(ctx, 24, 2 * obytes);
     if (!d_stage || !d_o) return DLCO_ENOMEM;
-    cudaEvent_t ev[2];
-    for (int s = 0; s < 2; s++) DLCO_CUDA(cudaEventCreateWithFlags(&ev[s], cudaEventDisableTiming));
+    // Three streams so that neither copy sits in front of the pooling GEMM: uploads run ahead on cs_in, the batch's
+    // kernels on the context stream, downloads behind on cs_out; device staging and the output block are double
+    // buffered.  Per slot s: ev_in = upload done, ev_k = kernels of the batch done, ev_out = download done.
+    cudaStream_t cs_in = nullptr, cs_out = nullptr;
+    cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_k[2] = {nullptr, nullptr}, ev_out[2] = {nullptr, nullptr};
+    cudaError_t e = cudaStreamCreateWithFlags(&cs_in, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&cs_out, cudaStreamNonBlocking);
+    for (int s = 0; s < 2 && e == cudaSuccess; s++) {
+        e = cudaEventCreateWithFlags(&ev_in[s], cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ev_k[s], cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ev_out[s], cudaEventDisableTiming);
+    }
     int rc = DLCO_OK;
+    if (e != cudaSuccess) { dlco_set_error("dlco_fulldist_build_host: %s", cudaGetErrorString(e)); rc = DLCO_ECUDA; }
+    // the copy streams start after whatever the caller queued on the context stream
+    if (rc == DLCO_OK) {
+        e = cudaEventRecord(ev_k[0], ctx->stream);
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(cs_in, ev_k[0], 0);
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(cs_out, ev_k[0], 0);
+        if (e != cudaSuccess) { dlco_set_error("dlco_fulldist_build_host: %s", cudaGetErrorString(e)); rc = DLCO_ECUDA; }
+    }
     int64_t bi = 0;
     for (int64_t p = lo; p < hi && rc == DLCO_OK; p += nb, bi++) {
         const int s = (int)(bi & 1);
         const int n = (int)((hi - p) < nb ? (hi - p) : nb);
-        if (bi >= 2) cudaEventSynchronize(ev[s]);     // slot's previous upload has been consumed
+        if (bi >= 2) cudaEventSynchronize(ev_in[s]);     // the slot's previous upload has left the host staging buffer
         uint8_t *hp = h_stage[s];
         int32_t *hi_ = (int32_t *)(h_stage[s] + pbytes);
         for (int k = 0; k < n; k++) {
@@ -141,19 +160,38 @@ extern "C" int dlco_fulldist_build_host(dlco_ctx *ctx, const dlco_bank *bank, co
         }
         if (rc != DLCO_OK) break;
         uint8_t *dp = d_stage + (size_t)s * (pbytes + ibytes);
-        cudaError_t e = cudaMemcpyAsync(dp, hp, pbytes + ibytes, cudaMemcpyHostToDevice, ctx->stream);
-        if (e == cudaSuccess) e = cudaEventRecord(ev[s], ctx->stream);
+        float *dout = (float *)(d_o + (size_t)s * obytes);
+        e = cudaSuccess;
+        if (bi >= 2) e = cudaStreamWaitEvent(cs_in, ev_k[s], 0);         // batch bi-2 has read this staging slot
+        if (e == cudaSuccess) e = cudaMemcpyAsync(dp, hp, pbytes + ibytes, cudaMemcpyHostToDevice, cs_in);
+        if (e == cudaSuccess) e = cudaEventRecord(ev_in[s], cs_in);
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(ctx->stream, ev_in[s], 0);
+        if (e == cudaSuccess && bi >= 2) e = cudaStreamWaitEvent(ctx->stream, ev_out[s], 0);   // its output block has been downloaded
         if (e != cudaSuccess) { dlco_set_error("upload failed: %s", cudaGetErrorString(e)); rc = DLCO_ECUDA; break; }
-        rc = fulldist_batch(ctx, bank, dp, (const int32_t *)(dp + pbytes), n, nAngleBins, sigma, bNorm, d_o, rings);
+        rc = fulldist_batch(ctx, bank, dp, (const int32_t *)(dp + pbytes), n, nAngleBins, sigma, bNorm, dout, rings);
         if (rc != DLCO_OK) break;
-        e = cudaMemcpy2DAsync(h_out + (p - lo) * ld_out, (size_t)ld_out * sizeof(float), d_o,
-                              (size_t)rings * sizeof(float), (size_t)rings * sizeof(float), n,
-                              cudaMemcpyDeviceToHost, ctx->stream);
+        e = cudaEventRecord(ev_k[s], ctx->stream);
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(cs_out, ev_k[s], 0);
+        if (e == cudaSuccess)
+            e = cudaMemcpy2DAsync(h_out + (p - lo) * ld_out, (size_t)ld_out * sizeof(float), dout,
+                                  (size_t)rings * sizeof(float), (size_t)rings * sizeof(float), n,
+                                  cudaMemcpyDeviceToHost, cs_out);
+        if (e == cudaSuccess) e = cudaEventRecord(ev_out[s], cs_out);
         if (e != cudaSuccess) { dlco_set_error("download failed: %s", cudaGetErrorString(e)); rc = DLCO_ECUDA; }
     }
-    cudaError_t e = cudaStreamSynchronize(ctx->stream);
+    // drain all three streams whatever happened: the staging buffers belong to the context
+    cudaError_t e1 = cs_in ? cudaStreamSynchronize(cs_in) : cudaSuccess;
+    cudaError_t e2 = cudaStreamSynchronize(ctx->stream);
+    cudaError_t e3 = cs_out ? cudaStreamSynchronize(cs_out) : cudaSuccess;
+    e = e1 != cudaSuccess ? e1 : (e2 != cudaSuccess ? e2 : e3);
     if (rc == DLCO_OK && e != cudaSuccess) { dlco_set_error("fulldist_build_host: %s", cudaGetErrorString(e)); rc = DLCO_ECUDA; }
-    for (int s = 0; s < 2; s++) cudaEventDestroy(ev[s]);
+    for (int s = 0; s < 2; s++) {
+        if (ev_in[s]) cudaEventDestroy(ev_in[s]);
+        if (ev_k[s]) cudaEventDestroy(ev_k[s]);
+        if (ev_out[s]) cudaEventDestroy(ev_out[s]);
+    }
+    if (cs_in) cudaStreamDestroy(cs_in);
+    if (cs_out) cudaStreamDestroy(cs_out);
     return rc;
 }
 
