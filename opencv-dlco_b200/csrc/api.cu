@@ -472,6 +472,10 @@ static int bank_finish(dlco_ctx *ctx, dlco_bank *b, const float *h_filters)
     b->chunks_total = 0;
     for (int r = 0; r < b->nRows; r++) kmask[r / 128] |= keys[row_src[r]].mask;
     for (int t = 0; t < tiles; t++) b->chunks_total += __builtin_popcountll(kmask[t]);
+    free(b->h_kmask);
+    b->h_kmask = (uint64_t *)malloc((size_t)tiles * 8);
+    if (!b->h_kmask) return DLCO_ENOMEM;
+    memcpy(b->h_kmask, kmask.data(), (size_t)tiles * 8);
 
     const size_t plane = (size_t)b->nRowsPad * K * sizeof(__half);
     int32_t *d_row_src = nullptr;
@@ -554,6 +558,8 @@ extern "C" int dlco_bank_destroy(dlco_ctx *ctx, dlco_bank *b)
     cudaFree(b->d_kmask);
     cudaFree(b->d_map);
     cudaFree(b->d_f32);
+    cudaFree(b->d_sched);
+    free(b->h_kmask);
     free(b);
     return DLCO_OK;
 }

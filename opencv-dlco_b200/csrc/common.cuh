@@ -52,6 +52,9 @@ struct dlco_bank {
     int32_t *d_map;      // nF: filter -> distinct row
     float *d_f32;        // nF x 4096 original (SIMT cross-check path, comp-uprjdists)
     int64_t chunks_total;   // sum over M tiles of popcount(kmask)  (vs 64 * tiles when dense)
+    uint64_t *h_kmask;   // host copy of d_kmask (work schedule of the pooling kernel)
+    int32_t *d_sched;    // (len + 1) x sched_grid work items (m_tile * n_tiles + n_tile, -1 = none), see dlco_launch_pool_tc
+    int sched_n_tiles, sched_grid;   // the launch shape d_sched was built for
     CUtensorMap map_hi, map_lo;   // box 64 (K) x 128 (rows), 128B swizzle
 };
 

@@ -34,6 +34,9 @@
 #include "common.cuh"
 #include "kernels.h"
 #include <cuda_fp16.h>
+#include <algorithm>
+#include <queue>
+#include <vector>
 
 namespace {
 
@@ -71,6 +74,14 @@ __device__ __forceinline__ uint64_t split_mask(uint64_t mask, int ks, int ksplit
     return out;
 }
 
+// Work items of a CTA: item blockIdx.x + i * gridDim.x for i = 0, 1, ... or, when the launcher supplies a schedule
+// (comp-fulldists: the tiles' K-chunk counts differ 8 : 1), sched[i * gridDim.x + blockIdx.x] until the first -1.
+// The three roles walk the same sequence.
+#define POOL_FOR_ITEMS(t)                                                                                          \
+    for (int i_ = 0, t; (t = sched ? __ldg(sched + (size_t)i_ * gridDim.x + blockIdx.x) : (int)(blockIdx.x + i_ * gridDim.x)), \
+                        (sched ? t >= 0 : t < total);                                                              \
+         i_++)
+
 // MODE 0 (comp-fulldists): S[pair][row] = sum over bins of the squared clamped difference.
 // MODE 1 (comp-uprjdists, small banks): the K range is split over `ksplit` CTAs per tile so that a
 // 256-pair batch (whose B planes stay in L2) still fills the GPU; each writes its raw fp32 partial
@@ -79,7 +90,8 @@ template <int MODE>
 __global__ void __launch_bounds__(NTHREADS, 1)
 k_pool_fulldist(const __grid_constant__ TMaps maps, const uint64_t *__restrict__ kmask,
                 const float *__restrict__ a_inv, const float *__restrict__ b_inv, int m_tiles,
-                int n_tiles, int ksplit, int n_pairs, int n_rows, float *__restrict__ S, int64_t ld_s)
+                int n_tiles, int ksplit, int n_pairs, int n_rows, float *__restrict__ S, int64_t ld_s,
+                const int32_t *__restrict__ sched)
 {
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -120,7 +132,7 @@ k_pool_fulldist(const __grid_constant__ TMaps maps, const uint64_t *__restrict__
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
-            for (int t = blockIdx.x; t < total; t += gridDim.x) {
+            POOL_FOR_ITEMS(t) {
                 const int m = t / per_m, n = (t % per_m) / ksplit;
                 uint64_t mask = split_mask(kmask[m], t % ksplit, ksplit);
                 while (mask) {
@@ -144,7 +156,7 @@ k_pool_fulldist(const __grid_constant__ TMaps maps, const uint64_t *__restrict__
             int stage = 0;
             uint32_t phase = 0;
             uint32_t it = 0;                       // drains so far (accumulator = it & 1)
-            for (int t = blockIdx.x; t < total; t += gridDim.x) {
+            POOL_FOR_ITEMS(t) {
                 uint64_t mask = split_mask(kmask[t / per_m], t % ksplit, ksplit);
                 int in_flush = 0;
                 while (mask) {
@@ -182,7 +194,7 @@ k_pool_fulldist(const __grid_constant__ TMaps maps, const uint64_t *__restrict__
         // ===== epilogue: warps 2..9; TMEM lane quarter = warp % 4, column half = (warp - 2) / 4 =====
         const int q = warp & 3, half = (warp - 2) >> 2;
         uint32_t it = 0;
-        for (int t = blockIdx.x; t < total; t += gridDim.x) {
+        POOL_FOR_ITEMS(t) {
             const int m = t / per_m, n = (t % per_m) / ksplit;
             const int n_flush = (__popcll(split_mask(kmask[m], t % ksplit, ksplit)) + FLUSH - 1) / FLUSH;
             float acc[BN / 2];
@@ -324,7 +336,7 @@ int dlco_launch_pool_tc_uprj(dlco_ctx *ctx, const dlco_bank *bank, const void *d
     dlco_prof_begin(ctx, 1);
     k_pool_fulldist<1><<<grid, NTHREADS, SMEM_BYTES, ctx->stream>>>(maps, bank->d_kmask, bank->d_inv_scale, d_binv,
                                                                    m_tiles, n_tiles, ksplit, n_pairs, bank->nRows,
-                                                                   d_P, 0);
+                                                                   d_P, 0, nullptr);
     dlco_prof_end(ctx);
     DLCO_CHECK_LAUNCH(ctx);
     const size_t fin_smem = (size_t)bank->nRowsPad * 8 * sizeof(float);
@@ -334,6 +346,50 @@ int dlco_launch_pool_tc_uprj(dlco_ctx *ctx, const dlco_bank *bank, const void *d
                                                            bank->d_inv_scale, d_binv, bank->nF, d_out, ld_out);
     dlco_prof_end(ctx);
     DLCO_CHECK_LAUNCH(ctx);
+    return DLCO_OK;
+}
+
+// Static work schedule of k_pool_fulldist<0>: items (m tile, n tile) cost popcount(kmask[m]) K chunks plus an
+// epilogue, between 8 and 64 chunks for the gen-poolregion bank, so dealing them out round-robin leaves the CTAs
+// 3 % apart.  Longest-processing-time-first instead: items in tile order (n fastest: the CTAs running at one time
+// share a few A tiles) sorted by cost, each to the least loaded CTA.  Cached in the bank per launch shape.
+static int pool_schedule(dlco_ctx *ctx, dlco_bank *bank, int m_tiles, int n_tiles, int grid, const int32_t **out)
+{
+    *out = nullptr;
+    if (!bank->h_kmask || m_tiles * n_tiles <= grid || n_tiles < 8) return DLCO_OK;   // small launches (a ragged last batch): round-robin
+    if (bank->d_sched && bank->sched_n_tiles == n_tiles && bank->sched_grid == grid) { *out = bank->d_sched; return DLCO_OK; }
+    const int total = m_tiles * n_tiles;
+    std::vector<int> order(total);
+    for (int t = 0; t < total; t++) order[t] = t;
+    auto cost = [&](int t) { return 2 * __builtin_popcountll(bank->h_kmask[t / n_tiles]) + 1; };   // epilogue ~ half a chunk
+    std::stable_sort(order.begin(), order.end(), [&](int a, int c) { return cost(a) > cost(c); });
+    std::vector<std::vector<int32_t>> items(grid);
+    typedef std::pair<int64_t, int> Load;                      // (load, cta): the least loaded CTA, lowest index first
+    std::priority_queue<Load, std::vector<Load>, std::greater<Load>> heap;
+    for (int c = 0; c < grid; c++) heap.push(Load(0, c));
+    size_t len = 0;
+    for (int t : order) {
+        Load l = heap.top();
+        heap.pop();
+        items[l.second].push_back(t);
+        len = std::max(len, items[l.second].size());
+        heap.push(Load(l.first + cost(t), l.second));
+    }
+    std::vector<int32_t> tab((len + 1) * grid, -1);
+    for (int c = 0; c < grid; c++)
+        for (size_t i = 0; i < items[c].size(); i++) tab[i * grid + c] = items[c][i];
+    // the previous table may still be read by a kernel in flight
+    DLCO_CUDA(cudaStreamSynchronize(ctx->stream));
+    cudaFree(bank->d_sched);
+    bank->d_sched = nullptr;
+    if (cudaMalloc(&bank->d_sched, tab.size() * 4) != cudaSuccess) {
+        dlco_set_error("pool_tc: out of device memory for the work schedule");
+        return DLCO_ENOMEM;
+    }
+    DLCO_CUDA(cudaMemcpy(bank->d_sched, tab.data(), tab.size() * 4, cudaMemcpyHostToDevice));
+    bank->sched_n_tiles = n_tiles;
+    bank->sched_grid = grid;
+    *out = bank->d_sched;
     return DLCO_OK;
 }
 
@@ -355,10 +411,13 @@ int dlco_launch_pool_tc(dlco_ctx *ctx, const dlco_bank *bank, const void *d_bhi,
     const int m_tiles = bank->nRowsPad / BM, n_tiles = n_pairs_padded / 16;
     const int total = m_tiles * n_tiles;
     const int grid = total < ctx->sm_count ? total : ctx->sm_count;
+    const int32_t *sched = nullptr;
+    r = pool_schedule(ctx, const_cast<dlco_bank *>(bank), m_tiles, n_tiles, grid, &sched);
+    if (r != DLCO_OK) return r;
     dlco_prof_begin(ctx, 1);
     k_pool_fulldist<0><<<grid, NTHREADS, SMEM_BYTES, ctx->stream>>>(maps, bank->d_kmask, bank->d_inv_scale, d_binv,
                                                                    m_tiles, n_tiles, 1, n_pairs, bank->nRows, d_S,
-                                                                   bank->nRowsPad);
+                                                                   bank->nRowsPad, sched);
     dlco_prof_end(ctx);
     DLCO_CHECK_LAUNCH(ctx);
     const int n_rings = bank->nF / 8;
