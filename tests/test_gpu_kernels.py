@@ -128,6 +128,41 @@ def test_fulldist_host_entry_point(gpu_ctx, synth, small_bank):
     assert np.array_equal(dev, host)
 
 
+def test_fulldist_full_bank_three_batches(gpu_ctx, synth, full_bank):
+    """The gen-poolregion bank at full size and more pairs than two batches: exercises the block-sparse bank order
+    (8 x 8 pixel-block K chunks, clustered rows), the cached work schedule of the pooling kernel and the
+    three-stream host path with both staging slots reused.  Checked against the fp64 oracle on a spread of rings,
+    bit for bit between the device and host entry points and between one call and ragged sub-ranges."""
+    patches, _, idx0 = synth
+    _, filt, _ = full_bank
+    rng = np.random.default_rng(11)
+    n = 600                                                    # 256 + 256 + 88
+    idx = np.zeros((n, 4), np.int32)
+    idx[:, 0] = rng.integers(0, patches.shape[0], n)
+    idx[:, 2] = rng.integers(0, patches.shape[0], n)
+    idx[:40] = idx0
+    d_p, d_i = dev_t(gpu_ctx, patches), dev_t(gpu_ctx, idx)
+    bank = gpu_ctx.bank(filt)
+    info = bank.info()
+    assert info["filters"] == 40960 and info["rows"] == 31776 and info["tiles"] == 249
+    assert info["k_chunks"] <= 9800, info                      # x*64+y order sorted by row range: 11 571
+    got = gpu_ctx.fulldist_build(bank, d_p, d_i).cpu().numpy()
+    host = gpu_ctx.fulldist_build_host(bank, torch.from_numpy(patches), torch.from_numpy(idx)).numpy()
+    part = gpu_ctx.fulldist_build(bank, d_p, d_i, 250, 530).cpu().numpy()
+    bank.close()
+    assert np.isfinite(got).all()
+    assert np.array_equal(got, host)
+    assert np.array_equal(part, got[250:530])
+    ids = torch.arange(patches.shape[0], dtype=torch.int32, device=gpu_ctx.device)
+    pt = gpu_ctx.get_desc(d_p, ids).cpu().numpy()
+    rings = np.r_[0:5120:97, 5119]                             # all sigmas, radii and angles show up
+    rows = (rings[:, None] * 8 + np.arange(8)[None, :]).reshape(-1)
+    for k in (0, 7, 255, 256, 511, 512, 599):
+        want = O.full_distance(filt[rows], pt[idx[k, 0]], pt[idx[k, 2]])
+        scale = max(got[k].max(), 1e-30)
+        assert np.abs(got[k, rings] - want).max() / scale <= DIST_RTOL, k
+
+
 def test_fulldist_identical_patches_give_zero(gpu_ctx, synth, small_bank):
     patches, pid, _ = synth
     filt, _ = small_bank
