@@ -398,6 +398,11 @@ static void bank_cluster(const std::vector<BankKey> &keys, std::vector<int> &row
         return pa != pc ? pa > pc : a.mask < c.mask;
     });
     size_t left = rows.size(), out = 0;
+    if (groups.size() > 4096) {           // arbitrary banks with thousands of distinct supports: the sorted order as it is
+        for (Group &g : groups)
+            for (int i : g.rows) rows[out++] = i;
+        return;
+    }
     while (left > 0) {
         uint64_t u = 0;
         int fill = 0;
