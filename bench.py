@@ -27,7 +27,7 @@ sys.path.insert(0, ROOT)
 
 RINGS, NFILT, K = 5120, 40960, 4096
 FLOP_PER_PAIR = 2.0 * 2 * NFILT * K * 8          # dense-equivalent fp32 flops
-NCU_POOL_TRAFFIC_BYTES = 1.470e9 + 39.7e6        # ncu --set full, k_pool_fulldist, per launch (round 1)
+NCU_POOL_TRAFFIC_BYTES = 1.492e9 + 42.0e6        # ncu --set full, k_pool_fulldist, per launch (round 1)
 GTX970_PAIRS_PER_S = 35.5                        # reference's own GPU path, derived from mtimes
 
 
