@@ -42,11 +42,13 @@ def test_uprjdist_matches_oracle(gpu_ctx, synth, oracle_lib):
     assert np.abs(got - want).max() <= 2e-6, np.abs(got - want).max()
 
 
-@pytest.mark.parametrize("n_sel,n_pairs", [(68, 700), (60, 17), (130, 300), (5, 256)])
-def test_uprjdist_tensor_path_matches_simt_path(gpu_ctx, oracle_lib, n_sel, n_pairs, monkeypatch):
+@pytest.mark.parametrize("n_sel,n_pairs,batch", [(68, 700, 256), (68, 1700, 0), (60, 17, 0), (130, 300, 128), (5, 256, 0)])
+def test_uprjdist_tensor_path_matches_simt_path(gpu_ctx, oracle_lib, n_sel, n_pairs, batch, monkeypatch):
     """K-split tcgen05 pooling (k_pool_fulldist<1> + k_uprj_finish) against the fp32 SIMT cross-check
     kernel over ragged multi-batch ranges, banks of one and two 128-row tiles and duplicate filters;
     plus the domain's own invariants: swapping the pair negates the row, a patch against itself is 0."""
+    if batch:
+        monkeypatch.setenv("DLCO_UPRJDIST_BATCH", str(batch))   # default 768: force several batches on few pairs
     rings = O.ring_params()
     pick = (np.arange((n_sel + 7) // 8) * 577 + 900) % len(rings)
     filt, _ = make_bank(oracle_lib, rings[pick])
