@@ -48,7 +48,15 @@ static int check_common(dlco_ctx *ctx, const dlco_bank *bank, const void *patche
     return DLCO_OK;
 }
 
-// one batch, everything on device: pairs [0,n) of d_idx (N x 4 rows) -> d_out rows
+// get_desc can run over a group of pooling batches at once (DLCO_FULLDIST_DESC_GROUP=g, default 1 = per batch): one
+// 256-pair batch is 512 CTAs, less than one wave of k_desc (148 SMs x 4 CTAs), and costs 91 ns/patch where launches of
+// 1536 patches cost 56 ns/patch in comp-uprjdists.  The planes of a group no longer stay in L2 between k_desc and the
+// pooling kernel; each batch's 64 MB come back from HBM once.  Measured with g = 3: k_desc 89 -> 71 ms per 500k pairs,
+// the pooling launch 1.309 -> 1.320 ms, the build 183.7k -> 184.0k pairs/s (same bits): a wash, so it stays opt-in.
+static int desc_group() { int g = env_int("DLCO_FULLDIST_DESC_GROUP", 1); return g < 1 ? 1 : (g > 16 ? 16 : g); }
+static int group_pairs() { return batch_pairs() * desc_group(); }
+
+// one group of batches, everything on device: pairs [0,n) of d_idx (N x 4 rows) -> d_out rows
 static int fulldist_batch(dlco_ctx *ctx, const dlco_bank *bank, const uint8_t *d_patches,
                           const int32_t *d_idx, int n, int nbins, float sigma, int bnorm,
                           float *d_out, int64_t ld_out)
@@ -67,14 +75,21 @@ static int fulldist_batch(dlco_ctx *ctx, const dlco_bank *bank, const uint8_t *d
     uint8_t *bhi = (uint8_t *)dlco_scratch(ctx, 0, plane);
     uint8_t *blo = (uint8_t *)dlco_scratch(ctx, 1, plane);
     float *binv = (float *)dlco_scratch(ctx, 2, (size_t)npad * 2 * sizeof(float));
-    float *S = (float *)dlco_scratch(ctx, 3, (size_t)n * bank->nRowsPad * sizeof(float));
+    float *S = (float *)dlco_scratch(ctx, 3, (size_t)(n < batch_pairs() ? n : batch_pairs()) * bank->nRowsPad * sizeof(float));
     if (!bhi || !blo || !binv || !S) return DLCO_ENOMEM;
     dlco_prof_begin(ctx, 0);
     r = dlco_launch_desc(ctx, DESC_OUT_SPLIT, d_patches, d_idx, 4, 2 * n, 2 * npad, nbins, sigma, bnorm,
                          (float *)bhi, (float *)blo, binv);
     dlco_prof_end(ctx);
     if (r != DLCO_OK) return r;
-    return dlco_launch_pool_tc(ctx, bank, bhi, blo, binv, n, npad, S, d_out, ld_out);
+    const int nb = batch_pairs();                       // a multiple of 16: every batch starts on a 16-pair tile
+    for (int p = 0; p < n; p += nb) {
+        const int m = n - p < nb ? n - p : nb;
+        r = dlco_launch_pool_tc(ctx, bank, bhi + (size_t)p * 16 * 4096 * 2, blo + (size_t)p * 16 * 4096 * 2, binv + 2 * p,
+                                m, (m + 15) / 16 * 16, S, d_out + (size_t)p * ld_out, ld_out);
+        if (r != DLCO_OK) return r;
+    }
+    return DLCO_OK;
 }
 
 extern "C" int dlco_fulldist_build(dlco_ctx *ctx, const dlco_bank *bank, const uint8_t *d_patches,
@@ -85,7 +100,7 @@ extern "C" int dlco_fulldist_build(dlco_ctx *ctx, const dlco_bank *bank, const u
     if (r != DLCO_OK) return r;
     DLCO_REQUIRE(bank->nF % 8 == 0, "dlco_fulldist_build: bank has %d filters, need 8 per ring", bank->nF);
     DLCO_REQUIRE(ld_out >= bank->nF / 8, "dlco_fulldist_build: ld_out=%lld < %d rings", (long long)ld_out, bank->nF / 8);
-    const int nb = batch_pairs();
+    const int nb = group_pairs();
     for (int64_t p = lo; p < hi; p += nb) {
         int n = (int)((hi - p) < nb ? (hi - p) : nb);
         r = fulldist_batch(ctx, bank, d_patches, d_indices + p * 4, n, nAngleBins, sigma, bNorm,
@@ -106,7 +121,7 @@ extern "C" int dlco_fulldist_build_host(dlco_ctx *ctx, const dlco_bank *bank, co
     DLCO_REQUIRE(bank->nF % 8 == 0, "dlco_fulldist_build_host: bank has %d filters, need 8 per ring", bank->nF);
     DLCO_REQUIRE(ld_out >= rings, "dlco_fulldist_build_host: ld_out too small");
     DLCO_CUDA(cudaSetDevice(ctx->device));
-    const int nb = batch_pairs();
+    const int nb = group_pairs();
     // staging: per slot, 2*nb patches (pair order) + nb index rows rewritten to local ids
     const size_t pbytes = (size_t)nb * 2 * 4096, ibytes = (size_t)nb * 4 * sizeof(int32_t);
     uint8_t *h_stage[2];
