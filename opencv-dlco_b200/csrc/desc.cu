@@ -81,8 +81,10 @@ __device__ uint32_t block_select(const uint32_t (&v)[NPIX / DESC_THREADS], uint3
 }
 
 // separable blur, one line of 64 per thread quarter: 16 consecutive outputs from a sliding window
-// of 16 + KS - 1 inputs held in registers; per output the taps are accumulated in the order
-// j = 0..KS-1 (as the generic loop and the oracle do).  ALONG_ROWS: line = image row, else column.
+// of 16 + KS - 1 inputs held in registers.  The evaluation order is OpenCV's (cv::sepFilter2D on
+// CV_32F, established bit for bit against cv2 4.13, tests/golden/make_desc_golden.py):
+//   ALONG_ROWS (row filter, RowVec_32f):  acc = 0; acc = fma(k[j], x[j], acc), j = 0..KS-1
+//   columns (SymmColumnVec_32f):          acc = k[H]*x[H]; acc = fma(x[H+j] + x[H-j], k[H+j], acc), j = 1..H
 template <int KS, bool ALONG_ROWS>
 __device__ __forceinline__ void blur_lines(const float *__restrict__ src, float *__restrict__ dst, const float *taps)
 {
@@ -96,11 +98,18 @@ __device__ __forceinline__ void blur_lines(const float *__restrict__ src, float 
     }
 #pragma unroll
     for (int e = 0; e < RUN; e++) {
-        float acc = 0.f;
+        float acc;
+        if (ALONG_ROWS) {
+            acc = 0.f;
 #pragma unroll
-        for (int j = 0; j < KS; j++) acc += taps[j] * x[e + j];
-        if (ALONG_ROWS) dst[line * SROW + o0 + e] = acc;
-        else dst[(o0 + e) * SROW + line] = acc;
+            for (int j = 0; j < KS; j++) acc = fmaf(taps[j], x[e + j], acc);
+            dst[line * SROW + o0 + e] = acc;
+        } else {
+            acc = __fmul_rn(taps[H], x[e + H]);
+#pragma unroll
+            for (int j = 1; j <= H; j++) acc = fmaf(__fadd_rn(x[e + H + j], x[e + H - j]), taps[H + j], acc);
+            dst[(o0 + e) * SROW + line] = acc;
+        }
     }
 }
 
@@ -154,19 +163,21 @@ k_desc(const uint8_t *__restrict__ patches, const int32_t *__restrict__ ids, int
         blur_lines<13, false>(s_b, s_a, prm.taps);
     } else {
         const int half = prm.ksize >> 1;
-        // row pass: s_b[r][c] = sum_j k[j] * s_a[r][clamp(c + j - half)]
+        // row pass: s_b[r][c] = sum_j k[j] * s_a[r][clamp(c + j - half)] (left to right, fused)
         for (int i = tid; i < NPIX; i += DESC_THREADS) {
             int r = i >> 6, c = i & 63;
             float acc = 0.f;
-            for (int j = 0; j < prm.ksize; j++) acc += prm.taps[j] * s_a[r * SROW + clampi(c + j - half, 0, PS - 1)];
+            for (int j = 0; j < prm.ksize; j++) acc = fmaf(prm.taps[j], s_a[r * SROW + clampi(c + j - half, 0, PS - 1)], acc);
             s_b[r * SROW + c] = acc;
         }
         __syncthreads();
-        // column pass -> s_a
+        // column pass -> s_a (symmetric form)
         for (int i = tid; i < NPIX; i += DESC_THREADS) {
             int r = i >> 6, c = i & 63;
-            float acc = 0.f;
-            for (int j = 0; j < prm.ksize; j++) acc += prm.taps[j] * s_b[clampi(r + j - half, 0, PS - 1) * SROW + c];
+            float acc = __fmul_rn(prm.taps[half], s_b[r * SROW + c]);
+            for (int j = 1; j <= half; j++)
+                acc = fmaf(__fadd_rn(s_b[clampi(r + j, 0, PS - 1) * SROW + c], s_b[clampi(r - j, 0, PS - 1) * SROW + c]),
+                           prm.taps[half + j], acc);
             s_a[r * SROW + c] = acc;
         }
     }
@@ -183,9 +194,12 @@ k_desc(const uint8_t *__restrict__ patches, const int32_t *__restrict__ ids, int
         int c = p >> 6, r = p & 63;
         float ix = s_a[r * SROW + min(c + 1, PS - 1)] - s_a[r * SROW + max(c - 1, 0)];
         float iy = s_a[min(r + 1, PS - 1) * SROW + c] - s_a[max(r - 1, 0) * SROW + c];
-        float m = sqrtf(ix * ix + iy * iy);
-        float ang = (float)((double)atan2f(iy, ix) + 3.1415926535897932384626433832795);
-        float ratio = ang * prm.inv_step - 0.5f;
+        // cv::magnitude (non-IPP kernel) = sqrt(fma(x, x, y*y)); the angle is ::atan2 of the promoted
+        // floats + CV_PI in double, stored as float (src/vgg-desc.cpp:66); GAngle / AngleStep - 0.5f is a
+        // scaled convertTo = one fused multiply-add (src/vgg-desc.cpp:70)
+        float m = sqrtf(fmaf(ix, ix, __fmul_rn(iy, iy)));
+        float ang = (float)(atan2((double)iy, (double)ix) + 3.1415926535897932384626433832795);
+        float ratio = fmaf(ang, prm.inv_step, -0.5f);
         float fl = floorf(ratio);
         off1[i] = ratio - fl;
         int b1 = (int)ceilf(ratio - 1.0f);
@@ -217,7 +231,8 @@ k_desc(const uint8_t *__restrict__ patches, const int32_t *__restrict__ ids, int
         cnt = block_sum(cnt, s_red[1]);        // block_select ended on s_red[0]
         mn = block_min(mn, s_red[0]);
         const uint32_t v2 = (cnt >= (uint32_t)(k + 1)) ? v1 : mn;
-        float T = (1.0f - gamma) * __uint_as_float(v1) + gamma * __uint_as_float(v2);
+        // two rounded products and a rounded sum (the reference builds without -march: no contraction)
+        float T = __fadd_rn(__fmul_rn(1.0f - gamma, __uint_as_float(v1)), __fmul_rn(gamma, __uint_as_float(v2)));
         if (T != 0.0f) scale = (float)(1.0 / (double)(T / (float)nb));   // Mat /= s
     }
 

@@ -201,25 +201,48 @@ def gaussian_kernel_1d(sigma, dt=f32):
     return k.astype(dt)
 
 
+def _fma32(a, b, c):
+    """float32 fused multiply-add, elementwise: the product of two f32 is exact in f64, so
+    f32(f64(a)*f64(b) + f64(c)) is the fused result (up to a double rounding that needs a 29-bit
+    coincidence)."""
+    return (np.asarray(a, np.float64) * np.asarray(b, np.float64) + np.asarray(c, np.float64)).astype(f32)
+
+
 def _sep_blur_replicate(img, k):
-    """Separable correlation, BORDER_REPLICATE, rows then columns (cv::sepFilter2D)."""
+    """cv::GaussianBlur -> cv::sepFilter2D, BORDER_REPLICATE, rows then columns.
+    fp32: OpenCV's own evaluation order, established against cv2 4.13 (AVX2 dispatch) bit for bit
+    (tests/test_oracle_golden.py): the row filter accumulates the taps left to right with fused
+    multiply-adds (RowVec_32f), the column filter is the symmetric form
+    k[c]*x0 + sum_j k[c+j]*(x[+j] + x[-j]) with fused multiply-adds (SymmColumnVec_32f).
+    fp64: plain sums (truth mode)."""
     r = len(k) // 2
     dt = img.dtype
+    w = img.shape[1]
+    h = img.shape[0]
     p = np.pad(img, ((0, 0), (r, r)), mode="edge")
+    if dt == f32:
+        tmp = np.zeros_like(img)
+        for j in range(len(k)):
+            tmp = _fma32(p[:, j:j + w], k[j], tmp)
+        p = np.pad(tmp, ((r, r), (0, 0)), mode="edge")
+        out = (k[r] * p[r:r + h, :]).astype(f32)
+        for j in range(1, r + 1):
+            out = _fma32((p[r + j:r + j + h, :] + p[r - j:r - j + h, :]).astype(f32), k[r + j], out)
+        return out
     tmp = np.zeros_like(img)
     for j in range(len(k)):
-        tmp = tmp + k[j] * p[:, j:j + img.shape[1]]
-    tmp = tmp.astype(dt)
+        tmp = tmp + k[j] * p[:, j:j + w]
     p = np.pad(tmp, ((r, r), (0, 0)), mode="edge")
     out = np.zeros_like(img)
     for j in range(len(k)):
-        out = out + k[j] * p[j:j + img.shape[0], :]
+        out = out + k[j] * p[j:j + h, :]
     return out.astype(dt)
 
 
 def quantile_threshold(gmag, q=0.8):
     """src/vgg-desc.cpp:104-129: scipy-mquantiles rule (alphap=betap=0.5) on the
-    ascending sort of all magnitudes; the index arithmetic is float32 as written."""
+    ascending sort of all magnitudes; the index arithmetic is float32 as written; T is two
+    products and a sum, each rounded (the reference is built without -march, no contraction)."""
     s = np.sort(gmag.reshape(-1))
     n = s.size
     aleph = f32(f32(n) * f32(q)) + f32(0.5)
@@ -231,13 +254,17 @@ def quantile_threshold(gmag, q=0.8):
     gamma = f32(aleph - f32(k))
     gamma = min(max(gamma, f32(0.0)), f32(1.0))
     dt = gmag.dtype.type
-    return (dt(1.0) - dt(gamma)) * s[k - 1] + dt(gamma) * s[k]
+    return dt(dt(dt(1.0) - dt(gamma)) * s[k - 1]) + dt(dt(gamma) * s[k])
 
 
-def get_desc(patch, n_bins=8, init_sigma=1.4, b_norm=True, dt=f32):
-    """64x64 u8 patch -> PatchTrans (4096 x n_bins), row p = column-major pixel index
-    (c*64 + r) because every operand is transposed before the flatten
-    (src/vgg-desc.cpp:76-77,134-148)."""
+def get_desc_parts(patch, n_bins=8, init_sigma=1.4, b_norm=True, dt=f32, atan2_float=False):
+    """src/vgg-desc.cpp:41-132 -> (w1*GMag, w2*GMag, Bin1, Bin2, T) as 64x64 images (row = y).
+    dt=f32 follows OpenCV's arithmetic to the bit (pinned by tests/golden/desc_kat.npz, generated
+    by driving cv2 through the reference's call sequence, tests/golden/make_desc_golden.py):
+      * blur: see _sep_blur_replicate;  gradients: exact differences;
+      * cv::magnitude = sqrt(fma(x, x, y*y)) (the non-IPP kernel; IPP's is +-2 ulp around it);
+      * GAngle = float(atan2(double Iy, double Ix) + CV_PI) (atan2_float: float(double(atan2f) + CV_PI));
+      * GAngle / AngleStep - 0.5f and GMag /= s are scaled convertTo's: x * float(1/s) + b, fused."""
     dt = np.dtype(dt).type
     img = np.asarray(patch).astype(dt)
     img = _sep_blur_replicate(img, gaussian_kernel_1d(init_sigma, dt))       # :46
@@ -245,33 +272,46 @@ def get_desc(patch, n_bins=8, init_sigma=1.4, b_norm=True, dt=f32):
     py = np.pad(img, ((1, 1), (0, 0)), mode="edge")
     ix = px[:, 2:] - px[:, :-2]                                              # :50-53
     iy = py[2:, :] - py[:-2, :]
-    gmag = np.sqrt(ix * ix + iy * iy).astype(dt)                             # :59
-    # GAngle = atan2(Iy, Ix) + CV_PI : float atan2 promoted to double for the add,
-    # stored as float (:64-66)
-    if dt is np.float64:
-        gang = np.arctan2(iy, ix) + CV_PI
+    if dt is f32:
+        gmag = np.sqrt(_fma32(ix, ix, (iy * iy).astype(f32))).astype(f32)    # :59
+        if atan2_float:
+            gang = (np.arctan2(iy, ix).astype(np.float64) + CV_PI).astype(f32)
+        else:
+            gang = (np.arctan2(iy.astype(np.float64), ix.astype(np.float64)) + CV_PI).astype(f32)   # :64-66
+        step = f32(2.0 * CV_PI / float(f32(n_bins)))                         # :69
+        ratio = _fma32(gang, f32(1.0 / float(step)), f32(-0.5))              # :70
     else:
-        gang = (np.arctan2(iy, ix).astype(np.float64) + CV_PI).astype(f32)
-    step = dt(f32(2.0) * f32(CV_PI) / f32(n_bins)) if dt is f32 else dt(2.0 * CV_PI / n_bins)
-    ratio = (gang / step - dt(0.5)).astype(dt)                               # :69-70
+        gmag = np.sqrt(ix * ix + iy * iy)
+        gang = np.arctan2(iy, ix) + CV_PI
+        ratio = gang / dt(2.0 * CV_PI / n_bins) - dt(0.5)
     off1 = (ratio - np.floor(ratio)).astype(dt)                              # :72-74
     b1 = np.ceil(ratio - dt(1.0))                                            # :84-91
     b1 = np.where(b1 == -1.0, n_bins - 1, b1).astype(np.int64)
     b2 = np.where(b1 + 1 > n_bins - 1, 0, b1 + 1)                            # :95-101
+    t = dt(0)
     if b_norm:                                                               # :104-132
         t = quantile_threshold(gmag)
         if t != 0:
-            gmag = (gmag / dt(t / dt(n_bins))).astype(dt)
-    w1 = (dt(1.0) - off1)
-    w2 = off1
-    n = img.size
-    pt = np.zeros((n, n_bins), dt)
+            if dt is f32:
+                gmag = (gmag * f32(1.0 / float(f32(t / f32(n_bins))))).astype(f32)   # Mat /= s
+            else:
+                gmag = gmag / (t / n_bins)
+    v1 = ((dt(1.0) - off1) * gmag).astype(dt)                                # :76, :144
+    v2 = (off1 * gmag).astype(dt)                                            # :77, :146
+    return v1, v2, b1, b2, t
+
+
+def get_desc(patch, n_bins=8, init_sigma=1.4, b_norm=True, dt=f32, atan2_float=False):
+    """64x64 u8 patch -> PatchTrans (4096 x n_bins), row p = column-major pixel index
+    (c*64 + r) because every operand is transposed before the flatten
+    (src/vgg-desc.cpp:76-77,134-148)."""
+    v1, v2, b1, b2, _ = get_desc_parts(patch, n_bins, init_sigma, b_norm, dt, atan2_float)
+    n = v1.size
+    pt = np.zeros((n, n_bins), v1.dtype)
     # transposed flatten: p = c*rows + r
-    b1t, b2t = b1.T.reshape(-1), b2.T.reshape(-1)
-    g = gmag.T.reshape(-1)
     p = np.arange(n)
-    pt[p, b1t] = w1.T.reshape(-1) * g
-    pt[p, b2t] = w2.T.reshape(-1) * g      # Bin2 assignment comes second (:143-146)
+    pt[p, b1.T.reshape(-1)] = v1.T.reshape(-1)
+    pt[p, b2.T.reshape(-1)] = v2.T.reshape(-1)      # Bin2 assignment comes second (:143-146)
     return pt
 
 

@@ -62,6 +62,30 @@ def test_get_desc_constant_patch_is_zero(gpu_ctx):
     assert np.isfinite(pt).all() and np.abs(pt).max() == 0.0
 
 
+def test_get_desc_matches_cv2_driven_fixture(gpu_ctx):
+    """k_desc against OpenCV's own get_desc (tests/golden/desc_kat.npz: cv2 4.13 driven through the
+    reference's call sequence).  k_desc follows OpenCV's evaluation order (fused row taps, symmetric fused
+    column taps, sqrt(fma) magnitude, double atan2 + CV_PI, fused scaled converts), so the only freedom left
+    is CUDA's double atan2 against glibc's in the last bit of a double: bins identical, values bit-exact
+    except where that bit decides a float rounding."""
+    from test_oracle_golden import kat_patchtrans, load_desc_kat
+    patches, v1, v2, b1, _ = load_desc_kat("pt")
+    want = kat_patchtrans(v1, v2, b1)
+    ids = torch.arange(patches.shape[0], dtype=torch.int32, device=gpu_ctx.device)
+    got = gpu_ctx.get_desc(dev_t(gpu_ctx, patches), ids).cpu().numpy()
+    assert got.shape == want.shape
+    assert np.array_equal(got != 0, want != 0)                            # same bins, same zeros
+    np.testing.assert_allclose(got, want, rtol=3e-7, atol=0)              # never more than 2 ulp
+    exact = (got.view(np.uint32) == want.view(np.uint32)).mean()
+    assert exact >= 0.9999, exact
+    # the two other variants of the fixture (atan2f overload; IPP's approximate magnitude) bracket what
+    # another build of the reference would produce: a few ulp, no structural change
+    for variant in ("pt_atan2f", "pt_ipp"):
+        _, a1, a2, ab1, _ = load_desc_kat(variant)
+        alt = kat_patchtrans(a1, a2, ab1)
+        assert np.abs(got - alt).max() <= 1e-6 * max(1.0, np.abs(alt).max())
+
+
 # ------------------------------------------------------------------------------------------
 # comp-fulldists: src/comp-fulldists.cpp:294-356
 # ------------------------------------------------------------------------------------------
@@ -98,10 +122,10 @@ def test_fulldist_matches_oracle(gpu_ctx, synth, small_bank, impl):
     assert np.isfinite(got).all()
     rel = np.abs(got - want).max(axis=1) / want.max(axis=1)
     assert rel.max() <= DIST_RTOL, rel.max()
-    # end to end against the oracle's own fp32 descriptors (looser: descriptor conditioning)
+    # end to end against the oracle's own (cv2-pinned) fp32 descriptors: the same bar
     want_e2e = O.full_distances(filt, patches, idx)
     rel = np.abs(got - want_e2e).max(axis=1) / want_e2e.max(axis=1)
-    assert rel.max() <= 2e-4, rel.max()
+    assert rel.max() <= DIST_RTOL, rel.max()
 
 
 @pytest.mark.parametrize("n", [0, 1, 15, 16, 17, 33])
@@ -188,3 +212,92 @@ def test_pair_labels(gpu_ctx, synth):
     _, _, idx = synth
     got = gpu_ctx.pair_labels(dev_t(gpu_ctx, idx)).cpu().numpy()
     assert np.array_equal(got, O.pair_labels(idx))
+
+
+# ------------------------------------------------------------------------------------------
+# BASELINE configs[0]: 10 000 pairs x the full gen-poolregion bank, end to end at north_star's 1e-5
+# ------------------------------------------------------------------------------------------
+def _pool_fp64_torch(filt64, pt1, pt2, uprj=False):
+    """The oracle's pooling formula (oracle/dlco_oracle.py full_distance / uprj_distance, i.e.
+    src/comp-fulldists.cpp:328-342, src/comp-uprjdists.cpp:320-329) as fp64 torch matmuls: the checker for
+    sizes numpy cannot finish in seconds; cross-checked against the numpy oracle inside the tests."""
+    n = pt1.shape[0]
+    a = torch.clamp_max(torch.matmul(filt64, pt1.permute(1, 0, 2).reshape(4096, n * 8)), 1.0)
+    b = torch.clamp_max(torch.matmul(filt64, pt2.permute(1, 0, 2).reshape(4096, n * 8)), 1.0)
+    if uprj:
+        return (a - b).reshape(-1, n, 8).permute(1, 0, 2).reshape(n, -1)   # Desc1 - Desc2, [filter][bin]
+    d = ((b - a) ** 2).reshape(-1, n, 8).sum(dim=2)                        # per filter
+    return d.reshape(-1, 8, n).sum(dim=1).t().contiguous()                 # 8 members per ring
+
+
+@pytest.fixture(scope="module")
+def configs0(gpu_ctx):
+    """10 000 synthetic pairs over 10 002 patches; descriptors from the cv2-pinned fp32 oracle."""
+    patches, pid = O.synth_patches(3334, per_point=3, seed=20240601)
+    idx = O.synth_pairs(pid, 10000, seed=20240602)
+    used = np.unique(np.concatenate([idx[:, 0], idx[:, 2]]))
+    pt = np.zeros((patches.shape[0], 4096, 8), np.float32)
+    for i in used:
+        pt[i] = O.get_desc(patches[i])
+    return patches, idx, pt
+
+
+def test_fulldist_configs0_end_to_end(gpu_ctx, configs0, full_bank):
+    patches, idx, pt = configs0
+    _, filt, _ = full_bank
+    dev = gpu_ctx.device
+    bank = gpu_ctx.bank(filt)
+    got = gpu_ctx.fulldist_build(bank, dev_t(gpu_ctx, patches), dev_t(gpu_ctx, idx))
+    torch.cuda.synchronize()
+    bank.close()
+    assert got.shape == (10000, 5120) and bool(torch.isfinite(got).all())
+    f64 = torch.from_numpy(filt).to(dev).double()
+    d_pt = torch.from_numpy(pt).to(dev)
+    worst, worst_abs = 0.0, 0.0
+    for lo in range(0, len(idx), 500):
+        sl = idx[lo:lo + 500]
+        want = _pool_fp64_torch(f64, d_pt[torch.from_numpy(sl[:, 0]).long().to(dev)].double(),
+                                d_pt[torch.from_numpy(sl[:, 2]).long().to(dev)].double())
+        if lo == 0:                                                        # the torch checker == the numpy oracle
+            w0 = O.full_distance(filt[np.r_[0:8, 8 * 2600:8 * 2600 + 8]], pt[sl[3, 0]], pt[sl[3, 2]])
+            np.testing.assert_allclose(want[3, [0, 2600]].cpu().numpy(), w0, rtol=1e-12)
+        g = got[lo:lo + 500].double()
+        rel = (g - want).abs().amax(dim=1) / want.amax(dim=1)
+        worst = max(worst, float(rel.max()))
+        worst_abs = max(worst_abs, float((g - want).abs().max()))
+    print("configs[0] full distances: worst row-relative error %.3g (abs %.3g)" % (worst, worst_abs))
+    assert worst <= DIST_RTOL, worst
+
+
+def test_uprjdist_configs0_end_to_end(gpu_ctx, configs0, full_bank):
+    """comp-uprjdists on the same 10 000 pairs with the 68 filters of the shipped liberty model
+    (tests/golden/pr_select_kat.json), against fp64 pooling of the oracle's descriptors."""
+    import json
+    patches, idx, pt = configs0
+    _, filt, _ = full_bank
+    kat = [k for k in json.load(open(os.path.join(os.path.dirname(__file__), "golden", "pr_select_kat.json")))
+           if k["rows"] == 68][0]
+    w = np.zeros(5120, np.float32)
+    w[kat["rings"]] = kat["w"]
+    sel = O.select_pr_filters(filt, w)
+    assert sel.shape == (68, 4096)
+    dev = gpu_ctx.device
+    bank = gpu_ctx.bank(sel)
+    got = gpu_ctx.uprjdist_build(bank, dev_t(gpu_ctx, patches), dev_t(gpu_ctx, idx))
+    torch.cuda.synchronize()
+    bank.close()
+    assert got.shape == (10000, 544)
+    f64 = torch.from_numpy(sel).to(dev).double()
+    d_pt = torch.from_numpy(pt).to(dev)
+    i1, i2 = torch.from_numpy(idx[:, 0]).long().to(dev), torch.from_numpy(idx[:, 2]).long().to(dev)
+    worst = 0.0
+    for lo in range(0, len(idx), 2000):
+        want = _pool_fp64_torch(f64, d_pt[i1[lo:lo + 2000]].double(), d_pt[i2[lo:lo + 2000]].double(), uprj=True)
+        if lo == 0:
+            np.testing.assert_allclose(want[5].cpu().numpy(), O.uprj_distance(sel, pt[idx[5, 0]], pt[idx[5, 2]]),
+                                       rtol=1e-12, atol=1e-15)
+        g = got[lo:lo + 2000].double()
+        rel = (g - want).abs().amax(dim=1) / want.abs().amax(dim=1)
+        worst = max(worst, float(rel.max()))
+    print("configs[0] unprojected distances: worst row-relative error %.3g" % worst)
+    assert worst <= DIST_RTOL, worst

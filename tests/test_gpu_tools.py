@@ -90,10 +90,9 @@ def test_pipeline(workspace, gpu_ctx):
         assert lab.shape == (len(idx), 1) and lab.dtype == np.uint8 and d.shape == (len(idx), 24) and d.dtype == np.float32
         assert np.array_equal(lab.ravel(), O.pair_labels(idx))
         want = O.full_distances(ws["filt"], patches[:], idx[:64])
-        # end to end against the oracle's own fp32 get_desc: the descriptor's conditioning (atan2, soft
-        # bins) bounds this, as in tests/test_gpu_kernels.py; the pooling itself is checked there at 1e-5
+        # end to end against the oracle's own (cv2-pinned) fp32 get_desc at north_star's 1e-5
         rel = np.abs(d[:64] - want).max(axis=1) / want.max(axis=1)
-        assert rel.max() <= 2e-4, rel.max()
+        assert rel.max() <= 1e-5, rel.max()
         lib = gpu_ctx.fulldist_build(gpu_ctx.bank(ws["filt"]), torch.from_numpy(patches).to(dev), torch.from_numpy(idx).to(dev))
         assert np.array_equal(lib.cpu().numpy(), d)
         dist[name] = (d, lab.ravel())
@@ -156,9 +155,9 @@ def test_pipeline(workspace, gpu_ctx):
         d = H5File(out).read("Distance")
         assert d.shape == (len(idx), 8 * len(sel)) and np.array_equal(H5File(out).read("Label").ravel(), O.pair_labels(idx))
         want = O.uprj_distances(sel, patches, idx[:48])
-        # differences of values clamped to [0, 1]; end to end against the oracle's own fp32 get_desc
-        # (descriptor conditioning; the pooling alone is held to 2e-6 in tests/test_gpu_learn.py)
-        assert np.abs(d[:48] - want).max() <= 1e-4
+        # differences of values clamped to [0, 1]; end to end against the oracle's own (cv2-pinned) fp32
+        # get_desc at north_star's 1e-5, relative to the row's largest entry
+        assert (np.abs(d[:48] - want).max(axis=1) / np.abs(want).max(axis=1)).max() <= 1e-5
         unproj[name] = (d, O.pair_labels(idx))
 
     # ---- pj-learn (workspace/08-pjlearn.sh:24-27) ------------------------------------------------

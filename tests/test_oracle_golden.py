@@ -134,6 +134,70 @@ def test_contour_area_matches_cv2():
     assert abs(abs(np.sum(xp * y - yp * x)) * 0.5 - float(z["area"])) <= 1e-12
 
 
+# ---- get_desc as a whole vs OpenCV itself (tests/golden/make_desc_golden.py drove cv2 4.13 through the
+# reference's call sequence, src/vgg-desc.cpp:41-152) ------------------------------------------------
+def load_desc_kat(variant="pt"):
+    """-> patches, v1, v2, bin1, T of the fixture variant (pt | pt_atan2f | pt_ipp), rows p = x*64 + y."""
+    z = np.load(os.path.join(G, "desc_kat.npz"))
+    v1, v2, b1 = z["pt_v1"].copy(), z["pt_v2"].copy(), z["pt_bin1"].copy()
+    if variant != "pt":
+        for fld, a in (("v1", v1), ("v2", v2), ("bin1", b1)):
+            a.reshape(-1)[z[variant + "_" + fld + "_idx"]] = z[variant + "_" + fld + "_val"]
+    return z["patches"], v1, v2, b1, z[variant + "_T"]
+
+
+def kat_patchtrans(v1, v2, b1):
+    """(n, 4096, 8) PatchTrans from the fixture's sparse form (Bin2 assignment second, :143-146)."""
+    n = v1.shape[0]
+    pt = np.zeros((n, 4096, 8), np.float32)
+    i, p = np.meshgrid(np.arange(n), np.arange(4096), indexing="ij")
+    pt[i, p, b1] = v1
+    pt[i, p, (b1 + 1) % 8] = v2
+    return pt
+
+
+@pytest.mark.parametrize("variant", ["pt", "pt_atan2f"])
+def test_get_desc_bit_exact_vs_cv2_driven_fixture(variant):
+    """The fp32 oracle reproduces OpenCV's get_desc to the bit: blur order, magnitude, angle, soft bins,
+    cv::sort quantile, Mat/=s scaling and the transposed flatten -- on smooth, flat, ramp, saturated,
+    single-pixel and noise patches."""
+    patches, v1, v2, b1, T = load_desc_kat(variant)
+    assert len(patches) >= 64
+    for i, patch in enumerate(patches):
+        o1, o2, ob1, ob2, t = O.get_desc_parts(patch, atan2_float=(variant == "pt_atan2f"))
+        assert t == T[i], i
+        assert np.array_equal(ob1.T.reshape(-1), b1[i]), i
+        assert np.array_equal(o1.T.reshape(-1).view(np.uint32), v1[i].view(np.uint32)), i
+        assert np.array_equal(o2.T.reshape(-1).view(np.uint32), v2[i].view(np.uint32)), i
+        assert np.array_equal(ob2, (ob1 + 1) % 8)
+    pt = kat_patchtrans(v1[:3], v2[:3], b1[:3])
+    for i in range(3):
+        assert np.array_equal(O.get_desc(patches[i], atan2_float=(variant == "pt_atan2f")), pt[i])
+
+
+def test_get_desc_ipp_magnitude_variant_is_ulps_away():
+    """With IPP (the cv2 wheel's default) cv::magnitude is an approximate kernel: the descriptor moves by
+    a few ulp, the bins and the structure do not."""
+    patches, v1, v2, b1, T = load_desc_kat("pt_ipp")
+    _, w1, w2, wb1, wT = load_desc_kat("pt")
+    assert np.array_equal(b1, wb1)
+    np.testing.assert_allclose(T, wT, rtol=4e-7)
+    for a, b in ((v1, w1), (v2, w2)):
+        assert np.abs(a - b).max() <= 6e-7 * max(np.abs(b).max(), 1.0)
+        np.testing.assert_allclose(a, b, rtol=1e-6, atol=1e-30)
+
+
+def test_get_desc_fp64_truth_close_to_fixture():
+    """Error budget of the reference's own fp32 arithmetic against exact arithmetic (fp64 mode)."""
+    patches, v1, v2, b1, _ = load_desc_kat("pt")
+    worst = 0.0
+    for i in range(0, 48, 4):                                              # the smooth synthetic patches
+        pt64 = O.get_desc(patches[i], dt=np.float64)
+        pt32 = kat_patchtrans(v1[i:i + 1], v2[i:i + 1], b1[i:i + 1])[0]
+        worst = max(worst, np.abs(pt32 - pt64).max() / pt64.max())
+    assert worst <= 2e-5, worst
+
+
 # ---- internal consistency of the oracle ----------------------------------------------------------
 def test_hinge_pairsum_sorted_equals_bruteforce(oracle_lib):
     import ctypes
