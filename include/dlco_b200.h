@@ -71,6 +71,20 @@ int dlco_profile_read(dlco_ctx *ctx, int which, double *h_ms, int64_t *h_count);
 int dlco_bank_create(dlco_ctx *ctx, const float *h_filters, int nF, dlco_bank **bank);
 int dlco_bank_create_dev(dlco_ctx *ctx, const float *d_filters, int nF, dlco_bank **bank);
 int dlco_bank_destroy(dlco_ctx *ctx, dlco_bank *bank);
+
+/* ---- gen-poolregion (src/gen-poolregion.cpp) ------------------------------------------
+ * dlco_ring_params: the ring grid of src/gen-poolregion.cpp:163-172,189-213 (host; loop variables accumulate
+ * in double as written): h_rings receives up to cap rows (r, phi, sigma) of doubles, *n = number of rings
+ * (5120 for the defaults patchSize 64, nr 32, nphi 5, nsigma 32).  h_rings may be NULL to query n.
+ * dlco_gen_pr_filters: "PRFilters" (nRings*8 x 4096 f32, src/gen-poolregion.cpp:51-80,241-275) generated on the
+ * device into d_filters, bit-identical to the reference's (elements whose float rounding hangs on the last
+ * ulp of exp() are regenerated with the host libm: *h_fixed filters, usually 0); h_params (optional) receives
+ * "PRParams" (nRings*8 x 3 f32).
+ * dlco_bank_create_analytic: the bank of those rings built entirely on the device. */
+int dlco_ring_params(int patchSize, int nr, int nphi, int nsigma, double *h_rings, int cap, int *n);
+int dlco_gen_pr_filters(dlco_ctx *ctx, const double *h_rings, int nRings, float *d_filters,
+                        float *h_params, int *h_fixed);
+int dlco_bank_create_analytic(dlco_ctx *ctx, const double *h_rings, int nRings, dlco_bank **bank);
 /* what the tensor-core kernel actually multiplies: distinct filters (rows), 128-row tiles and the
  * number of non-empty (tile, 64-wide K chunk) blocks -- 64 per tile when dense */
 int dlco_bank_info(const dlco_bank *bank, int *n_filters, int *n_rows, int *n_tiles, int64_t *k_chunks);

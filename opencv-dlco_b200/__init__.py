@@ -36,6 +36,9 @@ SIGNATURES = {
     "dlco_bank_create": (c_int, [c_void_p, c_void_p, c_int, P(c_void_p)]),
     "dlco_bank_create_dev": (c_int, [c_void_p, c_void_p, c_int, P(c_void_p)]),
     "dlco_bank_destroy": (c_int, [c_void_p, c_void_p]),
+    "dlco_ring_params": (c_int, [c_int, c_int, c_int, c_int, c_void_p, c_int, P(c_int)]),
+    "dlco_gen_pr_filters": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, P(c_int)]),
+    "dlco_bank_create_analytic": (c_int, [c_void_p, c_void_p, c_int, P(c_void_p)]),
     "dlco_bank_info": (c_int, [c_void_p, P(c_int), P(c_int), P(c_int), P(c_int64)]),
     "dlco_get_desc": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_int, c_void_p]),
     "dlco_fulldist_build": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int,
@@ -95,6 +98,17 @@ SIGNATURES = {
 
 class DlcoError(RuntimeError):
     pass
+
+
+def ring_params(patch_size=64, nr=32, nphi=5, nsigma=32):
+    """"RingParams" of src/gen-poolregion.cpp:163-213 -> (n, 3) float64 (host arithmetic inside the library)."""
+    import numpy as np
+    lib = load_library()
+    n = c_int()
+    _check(lib.dlco_ring_params(patch_size, nr, nphi, nsigma, None, 0, ctypes.byref(n)))
+    out = np.zeros((n.value, 3), np.float64)
+    _check(lib.dlco_ring_params(patch_size, nr, nphi, nsigma, out.ctypes.data_as(c_void_p), n.value, ctypes.byref(n)))
+    return out
 
 
 _lib = None
@@ -205,6 +219,29 @@ class Context:
         assert f.shape[1] == 4096
         _check(self.lib.dlco_bank_create(self.handle, f.ctypes.data_as(c_void_p), f.shape[0], ctypes.byref(h)))
         return Bank(self, h, f.shape[0])
+
+    # ---- gen-poolregion: src/gen-poolregion.cpp:51-80,163-295 -----------------------------
+    def gen_pr_filters(self, rings):
+        """rings: (n, 3) float64 (r, phi, sigma) -> (PRFilters (8n, 4096) f32 cuda tensor, PRParams (8n, 3) f32
+        numpy, number of filters the host libm had to regenerate)."""
+        import numpy as np
+        torch = self.torch
+        rings = np.ascontiguousarray(rings, np.float64).reshape(-1, 3)
+        out = torch.empty((len(rings) * 8, 4096), dtype=torch.float32, device=self.device)
+        prp = np.zeros((len(rings) * 8, 3), np.float32)
+        fixed = c_int()
+        _check(self.lib.dlco_gen_pr_filters(self.handle, rings.ctypes.data_as(c_void_p), len(rings), _ptr(out),
+                                            prp.ctypes.data_as(c_void_p), ctypes.byref(fixed)))
+        return out, prp, fixed.value
+
+    def bank_analytic(self, rings):
+        """The bank of the given rings generated on the device (no host filters, no upload)."""
+        import numpy as np
+        rings = np.ascontiguousarray(rings, np.float64).reshape(-1, 3)
+        h = c_void_p()
+        _check(self.lib.dlco_bank_create_analytic(self.handle, rings.ctypes.data_as(c_void_p), len(rings),
+                                                  ctypes.byref(h)))
+        return Bank(self, h, len(rings) * 8)
 
     # ---- get_desc: src/vgg-desc.cpp:41-152 -----------------------------------------------
     def get_desc(self, patches, ids, n_bins=8, sigma=1.4, b_norm=True):

@@ -7,7 +7,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libdlco_b200.so")
 SOURCES = ["api.cu", "desc.cu", "pool_simt.cu", "pool_tc.cu", "fulldist.cu", "hinge.cu",
-           "pr_learn.cu", "pj_learn.cu", "stats.cu", "gemm_tc.cu", "sqnorm_tc.cu", "pj_sign.cu"]
+           "pr_learn.cu", "pj_learn.cu", "stats.cu", "gemm_tc.cu", "sqnorm_tc.cu", "pj_sign.cu", "gen_bank.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
 
@@ -55,7 +55,8 @@ if __name__ == "__main__":
     print(build(force="--force" in sys.argv, verbose=True))
 
 
-TOOLS = ["comp-fulldists", "comp-uprjdists", "pr-learn", "pj-learn", "pj-sweep", "pr-stats", "pj-stats", "h5tool"]
+TOOLS = ["comp-fulldists", "comp-uprjdists", "pr-learn", "pj-learn", "pj-sweep", "pr-stats", "pj-stats", "h5tool",
+         "gen-poolregion", "export-opencv", "conv-impatches"]
 
 
 def build_tools(force=False, verbose=False):
@@ -75,7 +76,7 @@ def build_tools(force=False, verbose=False):
         if not (force or _stale(exe, [src] + headers)):
             continue
         cmd = ["g++", "-O2", "-std=c++17", "-Wall", "-I", os.path.join(cuda, "include"), src, "-o", exe]
-        if t != "h5tool":
+        if t not in ("h5tool", "export-opencv", "conv-impatches"):
             cmd += ["-L", HERE, "-ldlco_b200", "-L", os.path.join(cuda, "lib64"), "-lcudart",
                     "-Wl,-rpath,$ORIGIN/../opencv-dlco_b200", "-Wl,-rpath," + os.path.join(cuda, "lib64")]
         cmd += ["-lz", "-lpthread"]

@@ -367,12 +367,6 @@ __global__ void k_bank_planes(const float *__restrict__ src, const int32_t *__re
     }
 }
 
-static inline uint64_t mix64(uint64_t h, uint64_t v)
-{
-    h ^= v + 0x9e3779b97f4a7c15ULL + (h << 6) + (h >> 2);
-    return h * 0xff51afd7ed558ccdULL;
-}
-
 struct BankKey {
     uint64_t mask, hash;     // mask: bit (x/8)*8 + y/8 set <=> the filter is non-zero somewhere in that pixel block
     int idx;
@@ -421,29 +415,73 @@ static void bank_cluster(const std::vector<BankKey> &keys, std::vector<int> &row
     }
 }
 
-static int bank_finish(dlco_ctx *ctx, dlco_bank *b, const float *h_filters)
+// per filter: mask of the 8 x 8 pixel blocks that hold a non-zero, and an order-independent 64-bit hash of
+// (position, bits) pairs -- the bank never has to exist on the host (dlco_bank_create_analytic / _dev)
+__global__ void __launch_bounds__(256)
+k_bank_keys(const float *__restrict__ f32, int nF, unsigned long long *__restrict__ mask, unsigned long long *__restrict__ hash)
+{
+    __shared__ unsigned long long s_mask, s_hash;
+    const int i = blockIdx.x;
+    if (threadIdx.x == 0) { s_mask = 0ULL; s_hash = 0ULL; }
+    __syncthreads();
+    const uint32_t *p = reinterpret_cast<const uint32_t *>(f32) + (size_t)i * (DLCO_PATCH * DLCO_PATCH);
+    unsigned long long m = 0ULL, h = 0ULL;
+    for (int e = threadIdx.x; e < DLCO_PATCH * DLCO_PATCH; e += 256) {
+        const uint32_t v = p[e];
+        if (v << 1) m |= 1ULL << (((e >> 6) >> 3) * 8 + ((e & 63) >> 3));      // -0.0f counts as zero
+        unsigned long long z = ((unsigned long long)e << 32 | v) + 0x9e3779b97f4a7c15ULL;
+        z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ULL;
+        z = (z ^ (z >> 27)) * 0x94d049bb133111ebULL;
+        h += z ^ (z >> 31);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        m |= __shfl_xor_sync(0xffffffffu, m, o);
+        h += __shfl_xor_sync(0xffffffffu, h, o);
+    }
+    if ((threadIdx.x & 31) == 0) { atomicOr(&s_mask, m); atomicAdd(&s_hash, h); }
+    __syncthreads();
+    if (threadIdx.x == 0) { mask[i] = s_mask; hash[i] = s_hash; }
+}
+
+// eq[q] = filters pairs[2q] and pairs[2q+1] are identical bit for bit (the memcmp behind the de-duplication)
+__global__ void __launch_bounds__(256)
+k_rows_equal(const float *__restrict__ f32, const int32_t *__restrict__ pairs, uint8_t *__restrict__ eq)
+{
+    const uint4 *a = reinterpret_cast<const uint4 *>(f32 + (size_t)pairs[2 * blockIdx.x] * (DLCO_PATCH * DLCO_PATCH));
+    const uint4 *c = reinterpret_cast<const uint4 *>(f32 + (size_t)pairs[2 * blockIdx.x + 1] * (DLCO_PATCH * DLCO_PATCH));
+    int same = 1;
+    for (int e = threadIdx.x; e < DLCO_PATCH * DLCO_PATCH / 4; e += 256) {
+        const uint4 x = a[e], y = c[e];
+        same &= (x.x == y.x) & (x.y == y.y) & (x.z == y.z) & (x.w == y.w);
+    }
+    same = __syncthreads_and(same);
+    if (threadIdx.x == 0) eq[blockIdx.x] = (uint8_t)same;
+}
+
+// b->d_f32 holds the nF x 4096 bank on the device; everything else of the bank is derived from it here
+static int bank_finish(dlco_ctx *ctx, dlco_bank *b)
 {
     const int K = DLCO_PATCH * DLCO_PATCH, nF = b->nF;
     std::vector<BankKey> keys(nF);
-    for (int i = 0; i < nF; i++) {
-        const uint32_t *p = (const uint32_t *)(h_filters + (size_t)i * K);
-        uint64_t mask = 0, hash = 0x1234567ULL;
-        for (int x = 0; x < 64; x++) {
-            for (int yb = 0; yb < 8; yb++) {
-                uint32_t any = 0;
-                for (int y = 8 * yb; y < 8 * yb + 8; y++) {
-                    const uint32_t v = p[x * 64 + y];
-                    any |= (v << 1);                      // -0.0f counts as zero
-                    hash = mix64(hash, v);
-                }
-                if (any) mask |= 1ULL << ((x >> 3) * 8 + yb);
-            }
+    {
+        unsigned long long *d_keys = nullptr;
+        DLCO_CUDA(cudaMalloc(&d_keys, (size_t)nF * 16));
+        k_bank_keys<<<nF, 256, 0, ctx->stream>>>(b->d_f32, nF, d_keys, d_keys + nF);
+        ctx->launches++;
+        std::vector<unsigned long long> h_keys((size_t)nF * 2);
+        cudaError_t e = cudaMemcpyAsync(h_keys.data(), d_keys, (size_t)nF * 16, cudaMemcpyDeviceToHost, ctx->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+        cudaFree(d_keys);
+        if (e != cudaSuccess) { dlco_set_error("dlco_bank_create: filter keys: %s", cudaGetErrorString(e)); return DLCO_ECUDA; }
+        for (int i = 0; i < nF; i++) {
+            keys[i].mask = h_keys[i];
+            keys[i].hash = h_keys[nF + i];
+            keys[i].idx = i;
         }
-        keys[i].mask = mask;
-        keys[i].hash = hash;
-        keys[i].idx = i;
     }
-    // identical filters: equal (hash, mask) neighbours compared byte by byte; the first in bank order is kept
+    // identical filters: neighbours with equal (hash, mask) are compared bit for bit on the device; the first in
+    // bank order is kept
     std::vector<int> order(nF);
     for (int i = 0; i < nF; i++) order[i] = i;
     std::sort(order.begin(), order.end(), [&](int a, int c) {
@@ -452,18 +490,39 @@ static int bank_finish(dlco_ctx *ctx, dlco_bank *b, const float *h_filters)
         if (x.mask != y.mask) return x.mask < y.mask;
         return x.idx < y.idx;
     });
+    std::vector<int32_t> cand;                // (previous, this) for every neighbour pair with equal keys
+    std::vector<int> cand_at(nF, -1);
+    for (int o = 1; o < nF; o++) {
+        const int i = order[o], j = order[o - 1];
+        if (keys[i].hash == keys[j].hash && keys[i].mask == keys[j].mask) {
+            cand_at[o] = (int)cand.size() / 2;
+            cand.push_back(j);
+            cand.push_back(i);
+        }
+    }
+    std::vector<uint8_t> eq(cand.size() / 2 + 1, 0);
+    if (!cand.empty()) {
+        int32_t *d_pairs = nullptr;
+        uint8_t *d_eq = nullptr;
+        const int nq = (int)cand.size() / 2;
+        DLCO_CUDA(cudaMalloc(&d_pairs, cand.size() * 4));
+        if (cudaMalloc(&d_eq, nq) != cudaSuccess) { cudaFree(d_pairs); dlco_set_error("dlco_bank_create: out of device memory"); return DLCO_ENOMEM; }
+        cudaError_t e = cudaMemcpyAsync(d_pairs, cand.data(), cand.size() * 4, cudaMemcpyHostToDevice, ctx->stream);
+        k_rows_equal<<<nq, 256, 0, ctx->stream>>>(b->d_f32, d_pairs, d_eq);
+        ctx->launches++;
+        if (e == cudaSuccess) e = cudaMemcpyAsync(eq.data(), d_eq, nq, cudaMemcpyDeviceToHost, ctx->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+        cudaFree(d_pairs);
+        cudaFree(d_eq);
+        if (e != cudaSuccess) { dlco_set_error("dlco_bank_create: filter compare: %s", cudaGetErrorString(e)); return DLCO_ECUDA; }
+    }
     std::vector<int> rep(nF);                 // representative (first identical filter) of every filter
     std::vector<int> distinct;
     for (int o = 0; o < nF; o++) {
         const int i = order[o];
-        bool dup = false;
-        if (o > 0) {
-            const int j = order[o - 1];
-            dup = keys[i].hash == keys[j].hash && keys[i].mask == keys[j].mask &&
-                  memcmp(h_filters + (size_t)i * K, h_filters + (size_t)j * K, (size_t)K * 4) == 0;
-            if (dup) rep[i] = rep[j];
-        }
-        if (!dup) { rep[i] = i; distinct.push_back(i); }
+        const bool dup = cand_at[o] >= 0 && eq[cand_at[o]];
+        if (dup) rep[i] = rep[order[o - 1]];
+        else { rep[i] = i; distinct.push_back(i); }
     }
     std::sort(distinct.begin(), distinct.end());
     bank_cluster(keys, distinct);
@@ -528,7 +587,7 @@ extern "C" int dlco_bank_create(dlco_ctx *ctx, const float *h_filters, int nF, d
         dlco_set_error("dlco_bank_create: upload failed: %s", cudaGetErrorString(e));
         return DLCO_ECUDA;
     }
-    int r = bank_finish(ctx, b, h_filters);
+    int r = bank_finish(ctx, b);
     if (r != DLCO_OK) { dlco_bank_destroy(ctx, b); return r; }
     *out = b;
     return DLCO_OK;
@@ -538,19 +597,48 @@ extern "C" int dlco_bank_create_dev(dlco_ctx *ctx, const float *d_filters, int n
 {
     DLCO_REQUIRE(ctx && d_filters && out, "dlco_bank_create: bad arguments");
     DLCO_REQUIRE(nF > 0, "dlco_bank_create: nF=%d must be positive", nF);
-    // the de-duplication / support analysis runs on the host: bring the bank over once
+    DLCO_CUDA(cudaSetDevice(ctx->device));
+    dlco_bank *b = (dlco_bank *)calloc(1, sizeof(dlco_bank));
+    if (!b) return DLCO_ENOMEM;
+    b->nF = nF;
     const size_t bytes = (size_t)nF * DLCO_PATCH * DLCO_PATCH * 4;
-    float *h = (float *)malloc(bytes);
-    if (!h) { dlco_set_error("dlco_bank_create_dev: out of host memory"); return DLCO_ENOMEM; }
-    cudaError_t e = cudaMemcpy(h, d_filters, bytes, cudaMemcpyDeviceToHost);
+    if (cudaMalloc(&b->d_f32, bytes) != cudaSuccess) {
+        free(b);
+        dlco_set_error("dlco_bank_create_dev: out of device memory");
+        return DLCO_ENOMEM;
+    }
+    cudaError_t e = cudaMemcpyAsync(b->d_f32, d_filters, bytes, cudaMemcpyDeviceToDevice, ctx->stream);
     if (e != cudaSuccess) {
-        free(h);
-        dlco_set_error("dlco_bank_create_dev: download failed: %s", cudaGetErrorString(e));
+        dlco_bank_destroy(ctx, b);
+        dlco_set_error("dlco_bank_create_dev: copy failed: %s", cudaGetErrorString(e));
         return DLCO_ECUDA;
     }
-    int r = dlco_bank_create(ctx, h, nF, out);
-    free(h);
-    return r;
+    int r = bank_finish(ctx, b);
+    if (r != DLCO_OK) { dlco_bank_destroy(ctx, b); return r; }
+    *out = b;
+    return DLCO_OK;
+}
+
+// the gen-poolregion bank of the given rings (nRings x 3 doubles: r, phi, sigma; dlco_ring_params) generated on
+// the device (gen_bank.cu): no filters.h5 read, no 671 MB upload.  Bit-identical to dlco_bank_create on the
+// reference's PRFilters.
+extern "C" int dlco_bank_create_analytic(dlco_ctx *ctx, const double *h_rings, int nRings, dlco_bank **out)
+{
+    DLCO_REQUIRE(ctx && h_rings && out && nRings > 0, "dlco_bank_create_analytic: bad arguments");
+    DLCO_CUDA(cudaSetDevice(ctx->device));
+    dlco_bank *b = (dlco_bank *)calloc(1, sizeof(dlco_bank));
+    if (!b) return DLCO_ENOMEM;
+    b->nF = nRings * 8;
+    if (cudaMalloc(&b->d_f32, (size_t)b->nF * DLCO_PATCH * DLCO_PATCH * 4) != cudaSuccess) {
+        free(b);
+        dlco_set_error("dlco_bank_create_analytic: out of device memory");
+        return DLCO_ENOMEM;
+    }
+    int r = dlco_gen_pr_filters(ctx, h_rings, nRings, b->d_f32, nullptr, nullptr);
+    if (r == DLCO_OK) r = bank_finish(ctx, b);
+    if (r != DLCO_OK) { dlco_bank_destroy(ctx, b); return r; }
+    *out = b;
+    return DLCO_OK;
 }
 
 extern "C" int dlco_bank_destroy(dlco_ctx *ctx, dlco_bank *b)

@@ -215,6 +215,46 @@ def test_pair_labels(gpu_ctx, synth):
 
 
 # ------------------------------------------------------------------------------------------
+# gen-poolregion on the device: src/gen-poolregion.cpp:51-80,163-295
+# ------------------------------------------------------------------------------------------
+def test_gen_pr_filters_bit_exact_full_bank(gpu_ctx, full_bank):
+    """All 40 960 filters generated on the device equal the C oracle's (pinned to workspace/opencv/*.i) bit for
+    bit; PRParams likewise; the ring grid from the library's host loops equals the oracle's."""
+    import dlco_b200
+    rings, filt, prp = full_bank
+    assert np.array_equal(dlco_b200.ring_params(), rings)
+    d, p, fixed = gpu_ctx.gen_pr_filters(rings)
+    got = d.cpu().numpy()
+    assert fixed <= 64, fixed                                  # host-libm regenerations: rounding ties only
+    assert np.array_equal(p, prp)
+    bad = np.nonzero((got.view(np.uint32) != filt.view(np.uint32)).any(axis=1))[0]
+    assert len(bad) == 0, (len(bad), bad[:8])
+
+
+def test_bank_analytic_matches_uploaded_bank(gpu_ctx, synth, full_bank):
+    patches, _, idx = synth
+    rings, filt, _ = full_bank
+    d_p, d_i = dev_t(gpu_ctx, patches), dev_t(gpu_ctx, idx)
+    up = gpu_ctx.bank(filt)
+    an = gpu_ctx.bank_analytic(rings)
+    assert an.info() == up.info()
+    a = gpu_ctx.fulldist_build(up, d_p, d_i).cpu().numpy()
+    b = gpu_ctx.fulldist_build(an, d_p, d_i).cpu().numpy()
+    up.close()
+    an.close()
+    assert np.array_equal(a, b)
+    # a device-resident bank (dlco_bank_create_dev) goes the same way: no host copy of the filters
+    sub = gpu_ctx.bank(torch.from_numpy(filt[:512]).to(gpu_ctx.device))
+    sub2 = gpu_ctx.bank(filt[:512])
+    assert sub.info() == sub2.info()
+    a = gpu_ctx.fulldist_build(sub, d_p, d_i).cpu().numpy()
+    b = gpu_ctx.fulldist_build(sub2, d_p, d_i).cpu().numpy()
+    sub.close()
+    sub2.close()
+    assert np.array_equal(a, b)
+
+
+# ------------------------------------------------------------------------------------------
 # BASELINE configs[0]: 10 000 pairs x the full gen-poolregion bank, end to end at north_star's 1e-5
 # ------------------------------------------------------------------------------------------
 def _pool_fp64_torch(filt64, pt1, pt2, uprj=False):
