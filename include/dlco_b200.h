@@ -222,11 +222,12 @@ int dlco_pj_rda_step_grid_sign(dlco_ctx *ctx, const float *d_dists, int64_t ld, 
                                int32_t nNegTrn, int szBatch, uint64_t *d_rng_state, int nCfg,
                                const float *d_mu, const float *d_gamma, uint64_t t, float *d_A,
                                float *d_dfavg, int32_t *d_rank, float *d_work);
-/* W of src/pj-learn.cpp:472-490 from already projected matrices: rows sqrt(l_k) v_k^T of the d_rank[g]
- * largest eigenpairs of A_g, ascending (library eigensolver).  For the points where a sign-prox run
- * needs W: validation, statistics, saving the model.  d_work >= nCfg * (D * D + D) floats.
- * Synchronises and checks the solver's info words. */
-int dlco_pj_factor_grid(dlco_ctx *ctx, int D, int nCfg, const float *d_A, const int32_t *d_rank,
+/* W of src/pj-learn.cpp:472-490 from already projected matrices: rows sqrt(l_k) v_k^T of the positive eigenpairs
+ * of A_g, ascending (library eigensolver).  For the points where a sign-prox run needs W: validation, statistics,
+ * saving the model.  d_rank[g] is REPLACED by the number of eigenvalues above 2e-5 of the largest (the projection's
+ * own rank comes from a trace and is off by the eigenvalues near 0 it leaves unconverged; the logged Rank / Dim and
+ * the rows of W follow this count).  d_work >= nCfg * (D * D + D) floats.  Synchronises and checks the solver. */
+int dlco_pj_factor_grid(dlco_ctx *ctx, int D, int nCfg, const float *d_A, int32_t *d_rank,
                         float *d_W, int64_t w_stride, float *d_work);
 /* The prox's projection alone, without an eigen-decomposition (src/pj-learn.cpp:434-470 computes
  * V max(L,0) V^T through LAPACKE_ssyevr): nCfg symmetric D x D matrices at d_A are replaced by their

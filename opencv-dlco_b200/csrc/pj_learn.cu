@@ -885,15 +885,41 @@ extern "C" int dlco_pj_rda_step_grid_sign(dlco_ctx *ctx, const float *d_dists, i
     return r;
 }
 
-// W_g = rows sqrt(l_k) v_k^T of the d_rank[g] largest eigenpairs of the (already projected) A_g, in the
-// reference's ascending order (src/pj-learn.cpp:472-490); cusolverDnXsyevBatched.  d_work >= nCfg * (D D + D).
-extern "C" int dlco_pj_factor_grid(dlco_ctx *ctx, int D, int nCfg, const float *d_A, const int32_t *d_rank,
+// rank of an (approximately) projected matrix from its eigenvalues: the eigenvalues the projection zeroed come
+// back as rounding noise around 0 (|e| <~ 4e-6 e_max, the accuracy of the sign iteration), the kept
+// ones are untouched, so "e_k > 0" (src/pj-learn.cpp:452-456) becomes e_k > DLCO_RANK_EPS * e_max.
+#define DLCO_RANK_EPS 2e-5f
+__global__ void __launch_bounds__(256) k_pj_rank_eps(int D, const float *__restrict__ eval, int32_t *__restrict__ rank)
+{
+    __shared__ int s_cnt[8];
+    const float *e = eval + (size_t)blockIdx.x * D;
+    const float thr = DLCO_RANK_EPS * fmaxf(e[D - 1], 0.0f);          // eigenvalues ascend
+    int c = 0;
+    for (int k = threadIdx.x; k < D; k += 256) c += e[k] > thr;
+    for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+    if ((threadIdx.x & 31) == 0) s_cnt[threadIdx.x >> 5] = c;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int t = 0;
+        for (int i = 0; i < 8; i++) t += s_cnt[i];
+        rank[blockIdx.x] = e[D - 1] > 0.0f ? t : 0;
+    }
+}
+
+// W_g = rows sqrt(l_k) v_k^T of the positive eigenpairs of the (already projected) A_g, in the reference's
+// ascending order (src/pj-learn.cpp:472-490); cusolverDnXsyevBatched.  d_rank[g] is REPLACED by the number of those
+// eigenpairs (k_pj_rank_eps): the sign iteration's own rank, (D + trace sign(A)) / 2, is off by the eigenvalues it
+// has not driven to +-1 (|l| < 1e-4 ||A||_F), and this count is what the "Rank:" / "Dim [..]" log lines and the rows
+// of the saved W must agree with.  d_work >= nCfg * (D D + D).
+extern "C" int dlco_pj_factor_grid(dlco_ctx *ctx, int D, int nCfg, const float *d_A, int32_t *d_rank,
                                    float *d_W, int64_t w_stride, float *d_work)
 {
     DLCO_REQUIRE(ctx && d_A && d_rank && d_W && d_work && D > 0 && nCfg > 0, "dlco_pj_factor_grid: bad arguments");
     float *evec = d_work, *eval = d_work + (size_t)nCfg * D * D;
     int r = pj_eig_batched_async(ctx, D, nCfg, d_A, eval, evec);
     if (r != DLCO_OK) return r;
+    k_pj_rank_eps<<<nCfg, 256, 0, ctx->stream>>>(D, eval, d_rank);
+    DLCO_CHECK_LAUNCH(ctx);
     k_pj_prox_w_grid<<<dim3(D, nCfg), 256, 0, ctx->stream>>>(D, d_rank, eval, evec, d_W, w_stride);
     DLCO_CHECK_LAUNCH(ctx);
     return pj_eig_batched_check(ctx, nCfg);

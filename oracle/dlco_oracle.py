@@ -267,7 +267,8 @@ def get_desc_parts(patch, n_bins=8, init_sigma=1.4, b_norm=True, dt=f32, atan2_f
       * GAngle / AngleStep - 0.5f and GMag /= s are scaled convertTo's: x * float(1/s) + b, fused."""
     dt = np.dtype(dt).type
     img = np.asarray(patch).astype(dt)
-    img = _sep_blur_replicate(img, gaussian_kernel_1d(init_sigma, dt))       # :46
+    # `float InitSigma` (:41) is promoted to GaussianBlur's double sigma: 1.4f = 1.39999997615..., not 1.4
+    img = _sep_blur_replicate(img, gaussian_kernel_1d(float(f32(init_sigma)), dt))       # :46
     px = np.pad(img, ((0, 0), (1, 1)), mode="edge")
     py = np.pad(img, ((1, 1), (0, 0)), mode="edge")
     ix = px[:, 2:] - px[:, :-2]                                              # :50-53

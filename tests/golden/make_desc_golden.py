@@ -66,8 +66,8 @@ def _convert_scale(cv2, src, alpha, beta):
 def get_desc_cv2(cv2, patch, n_bins=8, init_sigma=1.4, b_norm=True, atan2_float=False):
     """-> v1, v2 (f32 [4096]), bin1 (u8 [4096]), T; row order p = x*64 + y."""
     img = patch.astype(f32)                                                             # :44 convertTo CV_32F
-    img = cv2.GaussianBlur(img, (0, 0), init_sigma, sigmaY=init_sigma,
-                           borderType=cv2.BORDER_REPLICATE)                             # :46
+    sig = float(f32(init_sigma))            # `float InitSigma` (:41) promoted to double: 1.39999997615814...
+    img = cv2.GaussianBlur(img, (0, 0), sig, sigmaY=sig, borderType=cv2.BORDER_REPLICATE)   # :46
     kern = np.array([[-1, 0, 1]], f32)                                                  # :50-51
     ix = cv2.filter2D(img, cv2.CV_32F, kern, anchor=(-1, -1), delta=0,
                       borderType=cv2.BORDER_REPLICATE)                                  # :52

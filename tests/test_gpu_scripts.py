@@ -1,0 +1,256 @@
+"""The reference's workspace scripts 01 .. 10, UNCHANGED except the (mu, gamma) grid lists, run against bin/ on a
+GPU box in a temporary workspace with three small synthetic data sets named like the reference's
+(yosemite / notredame / liberty).  north_star: "drops into the workspace scripts unchanged".
+
+The scripts come byte for byte from tests/golden/workspace_scripts.json (sha256-checked).  The only edits, made by
+`shorten_grid` below and asserted to touch nothing else:
+    04-prlearn.sh line 10  `for mu in 0.001 ... 0.060`      -> `for mu in 0.035`
+    04-prlearn.sh line 13  `for gamma in 0.005 ... 0.250`   -> `for gamma in 0.250`
+    08-pjlearn.sh line 10  `for mu in 0.0001 ... 0.0030`    -> `for mu in 0.0010`
+    08-pjlearn.sh line 13  `for gamma in 0.025 ... 1.000`   -> `for gamma in 0.100 0.200`
+(256 x 3 runs of 5 M steps and 405 runs of 50 000 iterations are the reference's week of GTX-970 time.)
+pr-learn is launched by the script with `-iters 50000000` and counts as complete when its log holds the
+step-5 000 000 line: DLCO_MAX_ITERS=5000000 (tools/common.hpp) ends it at exactly that line.  bc(1) is missing from
+this image: tests/golden/bc stands in (pinned to the reference's pj-top10.log by tests/test_workspace_scripts.py).
+"""
+import os
+import re
+import shutil
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+from oracle import dlco_oracle as O  # noqa: E402
+from oracle.h5lite import H5File  # noqa: E402
+from test_workspace_scripts import _write_bmp8, h5pack, make_workspace  # noqa: E402
+
+DATASETS = ("yosemite", "notredame", "liberty")
+PJ_FULL_ITERS = 50000          # what 08-pjlearn.sh asks for; one run goes all the way (resume-by-grep check)
+PJ_SHORT_ITERS = 300           # DLCO_MAX_ITERS for the other runs
+
+
+def shorten_grid(ws, script, mu, gamma):
+    path = os.path.join(ws, script)
+    lines = open(path).read().split("\n")
+    changed = []
+    for i, ln in enumerate(lines):
+        if re.match(r"\s*for mu in [0-9. ]+$", ln):
+            lines[i] = re.sub(r"in [0-9. ]+$", "in " + mu, ln)
+            changed.append(i + 1)
+        elif re.match(r"\s*for gamma in [0-9. ]+$", ln):
+            lines[i] = re.sub(r"in [0-9. ]+$", "in " + gamma, ln)
+            changed.append(i + 1)
+    assert changed == [10, 13], (script, changed)
+    open(path, "w").write("\n".join(lines))
+
+
+def sh(ws, env, script, **extra):
+    e = dict(env)
+    e.update({k: str(v) for k, v in extra.items()})
+    r = subprocess.run(["bash", script], cwd=ws, env=e, stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+    assert r.returncode == 0, (script, r.stderr.decode()[-2000:])
+    return r.stdout.decode(), r.stderr.decode()
+
+
+@pytest.fixture(scope="module")
+def ws_env(tmp_path_factory, gpu_ctx):
+    import __graft_entry__
+    __graft_entry__.build()
+    tmp = str(tmp_path_factory.mktemp("scripts"))
+    ws, env = make_workspace(tmp)
+    for d in ("dataset", "distances", "pr-learn/logging", "pr-learn/olderbest", "pr-learn/originals", "pj-learn/logging", "opencv"):
+        os.makedirs(os.path.join(ws, d))
+    data = {}
+    for k, ds in enumerate(DATASETS):                        # Brown-layout directories for 01-export.sh
+        patches, pid = O.synth_patches(170, per_point=3, seed=100 + k)          # 510 patches = 2 bitmaps
+        idx = O.synth_pairs(pid, 1200, seed=200 + k)
+        d = os.path.join(ws, "dataset", ds)
+        os.makedirs(d)
+        pad = np.zeros((512, 64, 64), np.uint8)
+        pad[:len(patches)] = patches
+        for b in range(2):
+            img = pad[256 * b:256 * b + 256].reshape(16, 16, 64, 64).transpose(0, 2, 1, 3).reshape(1024, 1024)
+            _write_bmp8(os.path.join(d, "patches%04d.bmp" % b), img)
+        idx[0, 0] = len(patches) - 1                          # conv-impatches sizes Patches by the largest id
+        with open(os.path.join(d, "m50_500000_500000_0.txt"), "w") as f:
+            for r in idx:
+                f.write("%d %d 0 %d %d 0\n" % tuple(r))
+        data[ds] = (patches, idx)
+    return ws, env, data
+
+
+def test_scripts_01_to_10(ws_env, gpu_ctx):
+    ws, env, data = ws_env
+    # ---- 01-export.sh: conv-impatches ---------------------------------------------------------------------------
+    so, _ = sh(ws, env, "01-export.sh")
+    assert so.count("Export [") == 3 and so.count("Done.") == 3
+    for ds in DATASETS:
+        f = H5File(os.path.join(ws, "dataset", ds + ".h5"))
+        assert np.array_equal(f.read("Patches"), data[ds][0]) and np.array_equal(f.read("Indices"), data[ds][1])
+    so, _ = sh(ws, env, "01-export.sh")
+    assert so.count("already done.") == 3
+    # ---- 02-genpoolregs.sh: the full default bank, generated on the device ------------------------------------------
+    so, _ = sh(ws, env, "02-genpoolregs.sh")
+    assert "Export RingParams: #5120\n" in so and "Export Projection: #40960\n" in so and so.endswith("Done.\n\n")
+    f = H5File(os.path.join(ws, "filters.h5"))
+    assert f.info("PRFilters")["shape"] == (40960, 64, 64) and f.info("PRParams")["shape"] == (40960, 3)
+    rings = f.read("RingParams")
+    assert np.array_equal(rings, O.ring_params())
+    assert "PR Filters already done." in sh(ws, env, "02-genpoolregs.sh")[0]
+    # ---- 03-compdist.sh ---------------------------------------------------------------------------------------------
+    so, _ = sh(ws, env, "03-compdist.sh")
+    assert so.count("Compute dataset [") == 3 and so.count("Start Compute L2 distances.") == 3
+    dist = {}
+    for ds in DATASETS:
+        f = H5File(os.path.join(ws, "distances", ds + "-dist.h5"))
+        d, lab = f.read("Distance"), f.read("Label").ravel()
+        assert d.shape == (1200, 5120) and np.array_equal(lab, O.pair_labels(data[ds][1]))
+        dist[ds] = (d, lab)
+    sel_rings = np.r_[0:5120:411]
+    filt, prp_sel = O.pr_filters_for_rings(rings[sel_rings])
+    want = O.full_distances(filt, data["liberty"][0], data["liberty"][1][:24])
+    got = dist["liberty"][0][:24]
+    assert (np.abs(got[:, sel_rings] - want).max(axis=1) / got.max(axis=1)).max() <= 1e-5
+    # ---- 04-prlearn.sh: grid shortened to one (mu, gamma); -iters 50000000 capped at the script's own finish line ----
+    shorten_grid(ws, "04-prlearn.sh", "0.035", "0.250")
+    so, _ = sh(ws, env, "04-prlearn.sh", DLCO_MAX_ITERS=5000000)
+    assert so.count("Compute dataset [") == 3
+    for ds in DATASETS:
+        log = open(os.path.join(ws, "pr-learn", "logging", ds + "-0.035-0.250-pr.log")).read()
+        assert log.startswith("mu: 0.035 gamma: 0.25 maxdim: 640 nIters: 50000000\n")
+        steps = [int(m.group(2)) for m in re.finditer(r"^(Best|Step): (\d+)  Loss: ", log, re.M)]
+        assert steps == list(range(100000, 5000001, 100000))
+        assert re.search(r": 5000000  Loss: ", log)                              # the script's completion test
+    so, _ = sh(ws, env, "04-prlearn.sh", DLCO_MAX_ITERS=5000000)                  # resume-by-grep: nothing to do
+    assert so.count("already done.") == 3 and "Compute dataset" not in so
+    # an interrupted run (log without the finish line) is removed and recomputed, the others are left alone
+    log = os.path.join(ws, "pr-learn", "logging", "notredame-0.035-0.250-pr.log")
+    full_log = open(log).read()
+    open(log, "w").write(full_log[:full_log.index(": 5000000  Loss:") - 5])
+    so, _ = sh(ws, env, "04-prlearn.sh", DLCO_MAX_ITERS=5000000)
+    assert so.count("already done.") == 2 and so.count("Compute dataset [notredame]") == 1
+    strip = lambda s: re.sub(r"  Ttime: .*$", "", s, flags=re.M)                  # noqa: E731
+    assert strip(open(log).read()) == strip(full_log)                            # deterministic rerun
+    w = {ds: H5File(os.path.join(ws, "pr-learn", ds + "-0.035-0.250-pr.h5")).read("w") for ds in DATASETS}
+    for ds in DATASETS:
+        saved = [ln for ln in open(os.path.join(ws, "pr-learn", "logging", ds + "-0.035-0.250-pr.log")) if "[saved]" in ln]
+        assert len(saved) == len(w[ds]) >= 1
+    # ---- 05-prstats.sh / 06-pr-top.sh -------------------------------------------------------------------------------------
+    so, _ = sh(ws, env, "05-prstats.sh")
+    prp = H5File(os.path.join(ws, "filters.h5")).read("PRParams")
+    for ds in DATASETS:
+        log = open(os.path.join(ws, "pr-select-%s.log" % ds)).read()
+        assert log.count("BestModel:") == 3
+        ms = re.findall(r"^  ModelStat: AUC #(\S+)  FPR95: (\d+\.\d\d) Dim/MaxDim \[(\d+)/640\] nPR: (\d+) \(#(\d+)\) "
+                        r"\[pr-learn/%s-0.035-0.250-pr.h5\]\(#(\d+)\)->\[distances/(\w+)-dist.h5\]$" % ds, log, re.M)
+        assert len(ms) == 3 * len(w[ds])
+        for m in ms[::max(1, len(ms) // 6)]:
+            n_pr, dim, nz, fpr95, auc = O.pr_stats(prp, dist[m[6]][0], dist[m[6]][1], w[ds][int(m[5])])
+            assert (int(m[3]), int(m[2]), int(m[4])) == (n_pr, dim, nz)
+            assert abs(float(m[1]) - float(fpr95) * 100) <= 0.1 + 0.005 and abs(float(m[0]) - auc) <= 1e-5
+    assert sh(ws, env, "05-prstats.sh")[0].count("already done.") == 3
+    so, _ = sh(ws, env, "06-pr-top.sh")
+    top = open(os.path.join(ws, "pr-top10.log")).read()
+    for ds in DATASETS:
+        assert "TOP 10 learnt over [%s]:" % ds in top
+    rows = re.findall(r"^ mean: (\S+) \[(\d+)/640\] YO:(\S+) ND:(\S+) LY:(\S+) pr-learn/(\w+)-0.035-0.250-pr.h5#(\d+)$", top, re.M)
+    assert rows, top
+    for mean, dim, yo, nd, ly, ds, k in rows:                                    # awk columns $5 / $7 / $11 line up
+        assert abs(float(mean) - (float(yo) + float(nd) + float(ly)) / 3) <= 1e-4 + 1e-9
+        log = open(os.path.join(ws, "pr-select-%s.log" % ds)).read()
+        m = re.search(r"FPR95: (\S+) Dim/MaxDim \[%s/640\] .*\(#%s\)->\[distances/yosemite-dist.h5\]" % (dim, k), log)
+        assert m and m.group(1) == yo
+    # ---- 07-compunproj.sh: its model list is hard-coded (the author's earlier runs); supply those files from the
+    # models just learnt, 8 rows each so that `#7` exists -----------------------------------------------------------------
+    def model8(ds):
+        rows8 = np.concatenate([w[ds], np.repeat(w[ds][-1:], max(0, 8 - len(w[ds])), axis=0)])[-8:]
+        return np.ascontiguousarray(rows8, np.float32)
+    h5pack(os.path.join(ws, "pr-learn/olderbest/yosemite-0.025-0.075-pr.h5"), ("w", model8("yosemite"), 1, 9))
+    h5pack(os.path.join(ws, "pr-learn/notredame-0.003-0.040-pr.h5"), ("w", model8("notredame"), 1, 9))
+    if len(w["liberty"]) < 8:
+        h5pack(os.path.join(ws, "pr-learn/liberty-0.035-0.250-pr.h5"), ("w", model8("liberty"), 1, 9))
+    so, se = sh(ws, env, "07-compunproj.sh")
+    assert so.count("Start Compute L1 distances.") == 9          # 3 data sets x 3 models; the `originals` are absent
+    unproj = sorted(f for f in os.listdir(os.path.join(ws, "distances")) if f.endswith("-unproj.h5"))
+    assert len(unproj) == 9 and "liberty-liberty-0.035-0.250-pr#7-unproj.h5" in unproj
+    flt = H5File(os.path.join(ws, "filters.h5"))
+    w7 = H5File(os.path.join(ws, "pr-learn/liberty-0.035-0.250-pr.h5")).read("w")[7]
+    full = np.zeros((40960, 4096), np.float32)
+    nzr = np.nonzero(w7 > 0)[0]
+    f_sel, _ = O.pr_filters_for_rings(rings[nzr])
+    for j, r in enumerate(nzr):
+        full[8 * r:8 * r + 8] = f_sel[8 * j:8 * j + 8]
+    sel = O.select_pr_filters(full, w7)
+    del full, flt
+    d = H5File(os.path.join(ws, "distances", "notredame-liberty-0.035-0.250-pr#7-unproj.h5")).read("Distance")
+    assert d.shape == (1200, 8 * len(sel))
+    want = O.uprj_distances(sel, data["notredame"][0], data["notredame"][1][:32])
+    assert (np.abs(d[:32] - want).max(axis=1) / np.abs(want).max(axis=1)).max() <= 1e-5
+    assert sh(ws, env, "07-compunproj.sh")[0].count("already done.") == 9
+    # ---- 08-pjlearn.sh: one model family (the three data sets of liberty-0.035-0.250-pr#7), grid 1 x 2 ------------------
+    aside = os.path.join(os.path.dirname(ws), "aside")       # outside the workspace: 08 looks for *-unproj.h5 with find
+    os.makedirs(aside)
+    keep = [f for f in unproj if f.endswith("-liberty-0.035-0.250-pr#7-unproj.h5")]
+    assert len(keep) == 3
+    for f in unproj:
+        if f not in keep:
+            shutil.move(os.path.join(ws, "distances", f), aside)
+    # (a) one run all the way to the script's finish line (": 50000  Loss:"), the others held back
+    for f in keep[1:]:
+        shutil.move(os.path.join(ws, "distances", f), aside)
+    shorten_grid(ws, "08-pjlearn.sh", "0.0010", "0.100")
+    so, _ = sh(ws, env, "08-pjlearn.sh", DLCO_PJ_PROX="sign")
+    first = keep[0].replace("-unproj.h5", "")
+    log0 = open(os.path.join(ws, "pj-learn/logging/%s-0.0010-0.100-pj.log" % first)).read()
+    assert log0.startswith("mu: 0.001 gamma: 0.1 nIters: 50000\n") and re.search(r": 50000  Loss: ", log0)
+    # (b) everything else, capped; the finished run is recognised by the script's grep and skipped
+    for f in keep[1:]:
+        shutil.move(os.path.join(aside, f), os.path.join(ws, "distances"))
+    shorten_grid(ws, "08-pjlearn.sh", "0.0010", "0.100 0.200")
+    so, _ = sh(ws, env, "08-pjlearn.sh", DLCO_MAX_ITERS=PJ_SHORT_ITERS)
+    assert so.count("already done.") == 1 and so.count("Compute dataset [") == 5
+    logs = sorted(os.listdir(os.path.join(ws, "pj-learn/logging")))
+    assert len(logs) == 6
+    for name in logs:
+        txt = open(os.path.join(ws, "pj-learn/logging", name)).read()
+        assert "[saved]" in txt, name
+        m = H5File(os.path.join(ws, "pj-learn", name.replace(".log", ".h5")))
+        W, A = m.read("W"), m.read("A")
+        last = [ln for ln in txt.splitlines() if "[saved]" in ln][-1]
+        dim = int(re.match(r"Stat: Dim \[(\d+)\]", last).group(1))
+        assert W.shape == (dim, A.shape[0]) or (dim == 0 and W.shape == A.shape)
+        assert np.abs(W.T.astype(np.float64) @ W - A).max() <= 2e-4 * max(np.abs(A).max(), 1e-30)
+    # ---- 09-pjstats.sh / 10-pj-top.sh ------------------------------------------------------------------------------------
+    sh(ws, env, "09-pjstats.sh")
+    stats = {}
+    for ds in DATASETS:
+        sel_log = open(os.path.join(ws, "pj-select-%s.log" % ds)).read()
+        ms = re.findall(r"^  ModelStat: FPR95: (\S+) AUC #(\S+) DIM: \[(\d+)\] \[pj-learn/(\S+)\.h5\]$", sel_log, re.M)
+        assert len(ms) == 2, sel_log
+        for fpr, auc, dim, name in ms:                     # awk fields $6 / $9 / $3 of the LAST "[saved]" line
+            txt = open(os.path.join(ws, "pj-learn/logging", name + ".log")).read()
+            last = [ln for ln in txt.splitlines() if "[saved]" in ln][-1]
+            g = re.match(r"Stat: Dim \[(\d+)\] AUC: (\S+) \((\S+)\) FPR95: (\S+) \((\S+)\) \[saved\]", last)
+            assert (g.group(4), g.group(2), g.group(1)) == (fpr, auc, dim)
+            stats[name] = (float(fpr), int(dim))
+        # the script's "best" is `sort -n | sed -n 1p` over lines that start with text: a bytewise sort (LC_ALL=C)
+        lines = sorted(ln for ln in sel_log.splitlines() if "ModelStat" in ln)
+        best = re.search(r"^  BestModel:(.*)$", sel_log, re.M)
+        assert best and best.group(1) == lines[0].replace("  ModelStat:", "")
+    so, _ = sh(ws, env, "10-pj-top.sh")
+    top = open(os.path.join(ws, "pj-top10.log")).read()
+    for maxdim in (48, 64, 80, 120):
+        assert "TOP maxdim #%d minimisers:" % maxdim in top
+    rows = re.findall(r"^ mean: (\S+)  YO:(\S+) ND:(\S+) LY:(\S+) dim #\[(\d+)/(\d+)/(\d+)\] AUC\[\S+\] (\S+)$", top, re.M)
+    for mean, yo, nd, ly, d1, d2, d3, label in rows:
+        assert abs(float(mean) - (float(yo) + float(nd) + float(ly)) / 3) <= 1e-4 + 1e-9
+        for ds, fpr, dim in zip(DATASETS, (yo, nd, ly), (d1, d2, d3)):
+            assert stats["%s-%s" % (ds, label)] == (float(fpr), int(dim))

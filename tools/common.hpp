@@ -61,6 +61,20 @@ inline int deflate_level()
     return e ? std::max(0, std::min(9, atoi(e))) : 1;
 }
 
+// DLCO_MAX_ITERS caps the iteration count of pr-learn / pj-learn / pj-sweep: the workspace
+// scripts hard-code -iters; the cap ends a run early at a whole number of steps, logged lines unchanged.
+inline unsigned int max_iters_cap(unsigned int n_iter)
+{
+    const char *e = getenv("DLCO_MAX_ITERS");
+    if (!e || !*e) return n_iter;
+    const unsigned long long cap = strtoull(e, nullptr, 10);
+    if (cap < n_iter) {
+        fprintf(stderr, "DLCO_MAX_ITERS=%llu: stopping after %llu of %u iterations\n", cap, cap, n_iter);
+        return (unsigned int)cap;
+    }
+    return n_iter;
+}
+
 // ---- cv::RNG (multiply-with-carry) and cv::randShuffle (src/pr-learn.cpp:241-243) -------------
 struct CvRng {
     uint64_t state;

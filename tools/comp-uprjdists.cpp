@@ -41,13 +41,14 @@ int main(int argc, char **argv)
         const h5mini::DatasetInfo &fi = rflt.info("PRFilters");
         if (fi.dtype != h5mini::F32 || fi.row_elems() != 4096) throw h5mini::Error("PRFilters must be f32 nF x 64 x 64");
         const int n_filters = (int)fi.dims[0];
-        std::vector<float> filters((size_t)n_filters * 4096);
+        // only the rings the learnt w row selects are needed (SelectPRFilters looks at nothing else): read w first
+        // (a missing model file fails here, before any bulk I/O), then those rows of the 671 MB bank
+        std::vector<float> filters((size_t)n_filters * 4096, 0.f);
         {
             Progress bar;
-            const int blk = 2048;
-            for (int i = 0; i < n_filters; i += blk) {
-                rflt.read_rows("PRFilters", i, std::min(n_filters, i + blk), &filters[(size_t)i * 4096], io_threads);
-                bar.update((double)i / (double)n_filters);
+            for (int i = 0; i < n_filters / 8; i++) {
+                if (w[i] > 0.0f) rflt.read_rows("PRFilters", (uint64_t)8 * i, (uint64_t)8 * i + 8, &filters[(size_t)8 * i * 4096], io_threads);
+                if ((i & 63) == 0) bar.update((double)(8 * i) / (double)n_filters);
             }
             bar.update(1.0);
         }
@@ -84,16 +85,6 @@ int main(int argc, char **argv)
 
         // ---- the learnt w row and SelectPRFilters (src/comp-uprjdists.cpp:222-244) --------------
         printf("Load Learnt Filters: [%s]#%i\n", prj, widx);
-        std::vector<float> w;
-        {
-            h5mini::Reader rw(prj);
-            const h5mini::DatasetInfo &wi = rw.info("w");
-            if (wi.dtype != h5mini::F32 || wi.dims.size() != 2 || (int)wi.dims[1] * 8 != n_filters)
-                throw h5mini::Error("w must be f32 k x (nFilters / 8)");
-            if (widx < 0 || (uint64_t)widx >= wi.dims[0]) throw h5mini::Error("-id is outside the rows of w");
-            w.resize(wi.dims[1]);
-            rw.read_rows("w", (uint64_t)widx, (uint64_t)widx + 1, w.data());
-        }
         int n_sel = 0;
         std::vector<float> sel = select_pr_filters(filters.data(), n_filters, 4096, w.data(), &n_sel);
         std::vector<float>().swap(filters);

@@ -47,6 +47,7 @@ int main(int argc, char **argv)
         return 1;
     }
     printf("mu: %g gamma: %g nIters: %u\n", mu, gamma, n_iter);
+    n_iter = max_iters_cap(n_iter);                        // DLCO_MAX_ITERS, see tools/common.hpp
     try {
         Ctx ctx(0);
         DevBuf<float> d_dists;

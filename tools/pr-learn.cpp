@@ -43,6 +43,10 @@ int main(int argc, char **argv)
         return 1;
     }
     printf("mu: %g gamma: %g maxdim: %d nIters: %u\n", mu, gamma, max_dim, n_iter);
+    // DLCO_MAX_ITERS: stop after that many steps whatever -iters asks for.  workspace/04-prlearn.sh launches
+    // `-iters 50000000` and calls a run complete once its log holds the step-5 000 000 line; DLCO_MAX_ITERS=5000000
+    // ends a run at exactly that line without touching the script.
+    n_iter = max_iters_cap(n_iter);
     try {
         std::vector<float> pr_params;
         {
@@ -79,11 +83,14 @@ int main(int argc, char **argv)
         std::vector<float> old_rows;
         if (FILE *f = fopen(outp, "rb")) {
             fclose(f);
-            try {
-                h5mini::Reader ro(outp);
-                if (ro.exists("w") && (int)ro.info("w").row_elems() == F) old_rows = ro.read_all<float>("w");
-            } catch (const h5mini::Error &) {
-            }
+            // the reference appends in place (dsinsert); this writer re-creates the file with the old rows in front:
+            // anything it cannot carry over is an error, not something to drop silently
+            h5mini::Reader ro(outp);
+            if (ro.names().size() != 1 || !ro.exists("w"))
+                throw h5mini::Error(std::string("existing output holds other datasets than `w` (would be lost): ") + outp);
+            if ((int)ro.info("w").row_elems() != F || ro.info("w").dtype != h5mini::F32)
+                throw h5mini::Error(std::string("existing output has a `w` of another width: ") + outp);
+            old_rows = ro.read_all<float>("w");
         }
         std::unique_ptr<h5mini::Writer> out;
         int hw = -1;
