@@ -43,6 +43,16 @@ int main(int argc, char **argv)
         const int n_filters = (int)fi.dims[0];
         // only the rings the learnt w row selects are needed (SelectPRFilters looks at nothing else): read w first
         // (a missing model file fails here, before any bulk I/O), then those rows of the 671 MB bank
+        std::vector<float> w;
+        {
+            h5mini::Reader rw(prj);
+            const h5mini::DatasetInfo &wi = rw.info("w");
+            if (wi.dtype != h5mini::F32 || wi.dims.size() != 2 || (int)wi.dims[1] * 8 != n_filters)
+                throw h5mini::Error("w must be f32 k x (nFilters / 8)");
+            if (widx < 0 || (uint64_t)widx >= wi.dims[0]) throw h5mini::Error("-id is outside the rows of w");
+            w.resize(wi.dims[1]);
+            rw.read_rows("w", (uint64_t)widx, (uint64_t)widx + 1, w.data());
+        }
         std::vector<float> filters((size_t)n_filters * 4096, 0.f);
         {
             Progress bar;
