@@ -20,19 +20,66 @@ import subprocess
 import sys
 import time
 
-import numpy as np
+# The CPU legs (cpu_baseline, --impl reference) use every host thread the box has: torch.distributed.run exports
+# OMP_NUM_THREADS=1 to its workers, which would leave OpenBLAS single-threaded (round-1 SCALE record).  Set the
+# thread counts before numpy / OpenBLAS load; `threads_in_use()` reports what the BLAS pool really has.
+HOST_THREADS = os.cpu_count() or 1
+for _v in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS"):
+    os.environ[_v] = str(HOST_THREADS)
+
+import numpy as np  # noqa: E402
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 RINGS, NFILT, K = 5120, 40960, 4096
 FLOP_PER_PAIR = 2.0 * 2 * NFILT * K * 8          # dense-equivalent fp32 flops
-NCU_POOL_TRAFFIC_BYTES = 1.492e9 + 42.0e6        # ncu --set full, k_pool_fulldist, per launch (round 1)
 GTX970_PAIRS_PER_S = 35.5                        # reference's own GPU path, derived from mtimes
 
 
 def log(*a):
     print(*a, file=sys.stderr, flush=True)
+
+
+def threads_in_use():
+    """Threads of the BLAS pool numpy will use (threadpoolctl), and OpenMP's view."""
+    try:
+        from threadpoolctl import threadpool_info
+        info = threadpool_info()
+        blas = [i["num_threads"] for i in info if i.get("user_api") == "blas"]
+        return max(blas) if blas else HOST_THREADS
+    except Exception:
+        return HOST_THREADS
+
+
+def ncu_traffic(kernel_substr, profiles=None):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the first kernel whose name contains
+    `kernel_substr`, from the newest `ncu --set full --page raw --csv` export under profiles/ that has it.
+    -> (bytes, file name) or (None, None)."""
+    import csv
+    import glob
+    unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
+    files = sorted(glob.glob(os.path.join(profiles or os.path.join(ROOT, "profiles"), "r*_ncu_full.csv")), reverse=True)
+    for path in files:
+        try:
+            rows = list(csv.reader(open(path, newline="")))
+            head = rows[0]
+            ki = head.index("Kernel Name")
+            cols = {}
+            for want in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+                cols[want] = [i for i, h in enumerate(head) if h == want or h.endswith("." + want)]
+            if not all(cols.values()):
+                continue
+            for row in rows[2:]:
+                if len(row) > ki and kernel_substr in row[ki]:
+                    tot = 0.0
+                    for want, idxs in cols.items():
+                        i = idxs[0]
+                        tot += float(row[i].replace(",", "")) * unit.get(rows[1][i], 1.0)
+                    return tot, os.path.basename(path)
+        except (OSError, ValueError, IndexError):
+            continue
+    return None, None
 
 
 # --------------------------------------------------------------------------------------------
@@ -204,7 +251,7 @@ def cpu_time_sample(filt, patches, pid, n_pairs, pool, seed):
 
 def run_cpu_baseline(target_s=12.0):
     import multiprocessing as mp
-    cores = os.cpu_count() or 1
+    cores = HOST_THREADS
     filt, patches, pid = cpu_arm_setup()
     pool = mp.get_context("fork").Pool(min(cores, 32))
     try:
@@ -213,17 +260,18 @@ def run_cpu_baseline(target_s=12.0):
         dt = cpu_time_sample(filt, patches, pid, n, pool, 2)
     finally:
         pool.close()
-    return {"value": n / dt, "unit": "pairs/s", "cores": cores, "kind": "port",
-            "sample": "%d pairs x 5120 rings (get_desc on %d procs + OpenBLAS SGEMM 40960x4096x%d), %.1f s"
-                      % (n, min(cores, 32), 16 * n, dt)}
+    return {"value": n / dt, "unit": "pairs/s", "cores": threads_in_use(), "kind": "port",
+            "sample": "%d pairs x 5120 rings (get_desc on %d procs + OpenBLAS SGEMM 40960x4096x%d on %d threads), %.1f s"
+                      % (n, min(cores, 32), 16 * n, threads_in_use(), dt)}
 
 
 def run_reference_arm(args, rank):
-    """--impl reference: the CPU implementation timed alone (rank 0 only)."""
+    """--impl reference: the CPU implementation timed alone (rank 0 only), all host threads whatever the launcher
+    exported (see HOST_THREADS above)."""
     if rank != 0:
         return
     import multiprocessing as mp
-    cores = os.cpu_count() or 1
+    cores = HOST_THREADS
     filt, patches, pid = cpu_arm_setup()
     pool = mp.get_context("fork").Pool(min(cores, 32))
     try:
@@ -237,6 +285,8 @@ def run_reference_arm(args, rank):
     finally:
         pool.close()
     v = n * args.steps / tt
+    thr = threads_in_use()
+    log("[bench] reference arm: %d BLAS threads, %d get_desc processes, %d host cores" % (thr, min(cores, 32), cores))
     line = {
         "impl": "reference", "metric": "full-dist pairs/s", "value": v, "unit": "pairs/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
@@ -244,12 +294,119 @@ def run_reference_arm(args, rank):
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": "comp-fulldists full build, 500k pairs x 5120 rings (40960 filters) per GPU; "
                                "CPU arm timed on a bounded sample of %d pairs per step" % n},
-        "cpu_baseline": {"value": v, "unit": "pairs/s", "cores": cores, "kind": "port",
-                         "sample": "%d pairs/step: oracle get_desc + OpenBLAS SGEMM pooling, all host threads" % n},
+        "cpu_baseline": {"value": v, "unit": "pairs/s", "cores": thr, "kind": "port",
+                         "sample": "%d pairs/step: oracle get_desc (%d processes) + OpenBLAS SGEMM pooling (%d threads)"
+                                   % (n, min(cores, 32), thr)},
         "e2e": {"value": v, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
+
+
+def strong_scaling_leg(torch, dist, ctx, bank, dev, rank, world, n_pairs, steps, barrier):
+    """ONE n_pairs job split over the ranks by shard.pair_range (weak scaling above gives every rank its own job):
+    every rank builds its row range through the host entry point straight into ONE host buffer shared by all ranks
+    (POSIX shared memory, each rank page-locks the slice it writes) -- the gather a single-process multi-GPU tool does
+    with threads (tools/comp-fulldists.cpp).  Inputs: the same patches / pairs on every rank (seeded alike)."""
+    from dlco_b200 import shard
+    import shutil
+    nbytes = n_pairs * RINGS * 4
+    path = "/dev/shm/dlco_bench_strong_%s.f32" % os.environ.get("MASTER_PORT", "0")
+    free = shutil.disk_usage("/dev/shm").free if os.path.isdir("/dev/shm") else 0
+    if free < nbytes + (1 << 30):
+        return {"skipped": "/dev/shm has %.1f GB free, the gathered matrix needs %.1f GB" % (free / 1e9, nbytes / 1e9)}
+    per_point = 3
+    n_points = max(64, int(n_pairs * 0.9) // per_point)
+    patches = synth_patches(torch, dev, n_points, per_point, seed=20240601)
+    idx = synth_pairs(torch, dev, n_points, per_point, n_pairs, seed=20240602)
+    h_patches, h_idx = patches.cpu().pin_memory(), idx.cpu().pin_memory()
+    del patches, idx
+    if rank == 0:
+        with open(path, "wb") as f:
+            f.truncate(nbytes)
+    barrier()
+    whole = torch.from_file(path, shared=True, size=n_pairs * RINGS, dtype=torch.float32).view(n_pairs, RINGS)
+    lo, hi = shard.pair_range(n_pairs, rank, world)
+    mine = whole[lo:hi]
+    cudart = torch.cuda.cudart()
+    reg = cudart.cudaHostRegister(mine.data_ptr(), mine.numel() * 4, 0)
+    try:
+        ctx.fulldist_build_host(bank, h_patches, h_idx, lo, min(hi, lo + 2048), out=mine[:min(hi - lo, 2048)])   # warm-up
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            ctx.fulldist_build_host(bank, h_patches, h_idx, lo, hi, out=mine)
+        torch.cuda.synchronize(dev)
+        dt = time.perf_counter() - t0
+        te = torch.tensor([dt], dtype=torch.float64, device=dev)
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+        barrier()
+        res = {"pairs_total": n_pairs, "pairs_per_rank": hi - lo, "steps": steps, "pairs_per_s": n_pairs * steps / float(te.item()),
+               "ms_per_step": float(te.item()) / steps * 1e3, "gather": "ranks write their row range of one /dev/shm host matrix (page-locked slice)",
+               "host_register_rc": str(reg)}
+        if rank == 0:        # the gathered matrix is complete and finite: sample rows of every rank's range
+            probe = whole[:: max(1, n_pairs // 997)]
+            res["gathered_checksum"] = float(probe.double().sum().item())
+            res["gathered_finite"] = bool(torch.isfinite(probe).all().item())
+    finally:
+        cudart.cudaHostUnregister(mine.data_ptr())
+        del mine, whole
+        barrier()
+        if rank == 0:
+            try:
+                os.remove(path)
+            except OSError:
+                pass
+    return res
+
+
+def collective_leg(torch, dist, ctx, dev, rank, world):
+    """The exchange steps of a pair-sharded pj-learn iteration (opencv-dlco_b200/shard.py: every rank owns a row range
+    of "Distance"; margins all-reduce of 2 x 200 floats, then the D x D gradient all-reduce) over NCCL / NVLink, checked
+    against the single-GPU gradient, plus the bare all-reduce of the D x D matrix."""
+    from dlco_b200 import learn, shard
+    n, D, r, b = 200000, 544, 64, 200
+    g = torch.Generator(device="cpu").manual_seed(1)
+    lab = (torch.arange(n) % 2 == 0).to(torch.uint8)
+    x = torch.randn((n, D), generator=g) * 0.1 * (1.0 + (1 - lab.float())[:, None])
+    W = (torch.randn((r, D), generator=g) * 0.03).to(dev)
+    ip, ineg, npt, nnt = learn.split_train_val(lab.numpy())
+    rng = learn.CvRNG(2215)
+    rp = np.array([ip[rng.uniform(0, npt)] for _ in range(b)], np.int32)
+    rn = np.array([ineg[rng.uniform(0, nnt)] for _ in range(b)], np.int32)
+    coll = shard.Collective()
+    lo, hi = shard.pair_range(n, rank, world)
+    sp = shard.ShardedPj(ctx, coll, x[lo:hi].to(dev), lab[lo:hi].to(dev), lo, n)
+    grad = sp.grad(rp, rn, W, r)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize(dev)
+    dist.barrier()
+    e0.record()
+    for _ in range(20):
+        grad = sp.grad(rp, rn, W, r)
+    e1.record()
+    torch.cuda.synchronize(dev)
+    ms = torch.tensor([e0.elapsed_time(e1) / 20], dtype=torch.float64, device=dev)
+    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    buf = torch.zeros((D, D), dtype=torch.float32, device=dev)
+    for _ in range(5):
+        dist.all_reduce(buf)
+    torch.cuda.synchronize(dev)
+    dist.barrier()
+    e0.record()
+    for _ in range(100):
+        dist.all_reduce(buf)
+    e1.record()
+    torch.cuda.synchronize(dev)
+    us = torch.tensor([e0.elapsed_time(e1) * 10.0], dtype=torch.float64, device=dev)
+    dist.all_reduce(us, op=dist.ReduceOp.MAX)
+    res = {"op": "ncclAllReduce sum f32", "bytes": D * D * 4, "allreduce_us": float(us.item()),
+           "allreduce_busbw_gbs": 2.0 * (world - 1) / world * D * D * 4 / (float(us.item()) * 1e-6) / 1e9,
+           "sharded_pj_grad_ms": float(ms.item()), "rows_per_rank": hi - lo, "D": D, "batch": 2 * b}
+    if rank == 0:
+        g1 = ctx.pj_rda_grad(x.to(dev), torch.from_numpy(rp).to(dev), torch.from_numpy(rn).to(dev), W, r)
+        res["grad_rel_err_vs_single_gpu"] = float((grad - g1).abs().max() / g1.abs().max().clamp_min(1e-30))
+    return res
 
 
 # --------------------------------------------------------------------------------------------
@@ -294,9 +451,8 @@ def main():
     per_point = 3
     n_points = max(64, int(n_pairs * 0.9) // per_point)      # ~Liberty: 450k patches for 500k pairs
     t_setup = time.time()
-    bank_t = synth_bank(torch, dev)
-    bank = ctx.bank(bank_t)
-    del bank_t
+    # the reference's own candidate set, bit-exact (gen-poolregion restated on the device: no filters.h5, no upload)
+    bank = ctx.bank_analytic(dlco_b200.ring_params())
     patches = synth_patches(torch, dev, n_points, per_point, seed=20240601 + rank)
     idx = synth_pairs(torch, dev, n_points, per_point, n_pairs, seed=20240602 + rank)
     out = torch.empty((n_pairs, RINGS), dtype=torch.float32, device=dev)
@@ -312,7 +468,6 @@ def main():
     clocks = Clocks(local)
     if rank == 0:
         clocks.start()
-    ctx.profile(True)
     l0 = ctx.launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
@@ -323,14 +478,25 @@ def main():
     barrier()
     ms = e0.elapsed_time(e1)
     launches = ctx.launch_count() - l0
-    pool_ms, pool_n = ctx.profile_read(1)
-    desc_ms, desc_n = ctx.profile_read(0)
-    red_ms, red_n = ctx.profile_read(6)
-    ctx.profile(False)
     clk = clocks.stop() if rank == 0 else None
     checksum = float(out[:: max(1, n_pairs // 1000)].double().sum().item())
     if not np.isfinite(checksum):
         raise SystemExit("bench.py: non-finite distances")
+    # per-kernel split and the dominant kernel's average launch time: a separate pass over the same workload with
+    # an event pair around every launch (the timed region above runs without them)
+    prof_steps = 1 if n_pairs >= 100000 else min(args.steps, 3)
+    ctx.profile(True)
+    p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    p0.record()
+    for _ in range(prof_steps):
+        step()
+    p1.record()
+    torch.cuda.synchronize(dev)
+    prof_ms = p0.elapsed_time(p1)
+    pool_ms, pool_n = ctx.profile_read(1)
+    desc_ms, desc_n = ctx.profile_read(0)
+    red_ms, red_n = ctx.profile_read(6)
+    ctx.profile(False)
 
     tmax = torch.tensor([ms], dtype=torch.float64, device=dev)
     if world > 1:
@@ -346,7 +512,7 @@ def main():
         del out
         torch.cuda.empty_cache()
         h_out = torch.empty((n_pairs, RINGS), dtype=torch.float32).pin_memory()
-        e2e_steps = max(1, min(args.steps, 2))
+        e2e_steps = max(1, args.steps)
         ctx.fulldist_build_host(bank, h_patches, h_idx, 0, min(n_pairs, 4096), out=h_out)   # warm-up
         barrier()
         t0 = time.perf_counter()
@@ -360,6 +526,21 @@ def main():
         e2e = {"value": world * n_pairs * e2e_steps / float(te.item()), "unit": "pairs/s",
                "h2d_bytes_per_step": n_pairs * (2 * 4096 + 16), "d2h_bytes_per_step": n_pairs * RINGS * 4,
                "steps": e2e_steps, "host_checksum": float(h_out[:: max(1, n_pairs // 1000)].double().sum().item())}
+
+    # ---- N > 1: one n_pairs job split over the ranks (strong scaling, gathered on the host), and the collective steps
+    strong, collective = None, None
+    if world > 1 and not args.no_e2e:
+        try:
+            del h_out
+            strong = strong_scaling_leg(torch, dist, ctx, bank, dev, rank, world, n_pairs, max(1, min(args.steps, 3)), barrier)
+        except Exception as ex:
+            strong = {"failed": repr(ex)}
+        h_out = None
+    if world > 1 and not args.no_rows:
+        try:
+            collective = collective_leg(torch, dist, ctx, dev, rank, world)
+        except Exception as ex:
+            collective = {"failed": repr(ex)}
 
     # ---- N > 1: the 5 x 9 (mu, gamma) pj-learn sweep of one data set sharded over the ranks by configuration
     # (c % world == rank, as `pj-sweep -shard r/n`), unprojected distances replicated, no collective
@@ -436,21 +617,25 @@ def main():
     issued_flop_per_pair_slot = 2.0 * 3 * info["k_chunks"] * 128 * 64 * 16
     issued_per_step = issued_flop_per_pair_slot * pairs_issued
     avg_ms = pool_ms / max(pool_n, 1)
-    issued_tflops = issued_per_step * args.steps / (pool_ms * 1e-3) / 1e12 if pool_n else None
-    dense_equiv_tflops = FLOP_PER_PAIR * n_pairs * args.steps / (pool_ms * 1e-3) / 1e12 if pool_n else None
+    issued_tflops = issued_per_step * prof_steps / (pool_ms * 1e-3) / 1e12 if pool_n else None
+    dense_equiv_tflops = FLOP_PER_PAIR * n_pairs * prof_steps / (pool_ms * 1e-3) / 1e12 if pool_n else None
+    traffic, traffic_src = ncu_traffic("k_pool_fulldist<0>")
     roofline = {
         "bound": "tensor", "kernel": "k_pool_fulldist (tcgen05 kind::f16, 3 fp16 passes = fp32-equivalent)",
         "achieved": issued_tflops, "peak": bf16, "unit": "TFLOP/s",
         "frac": (issued_tflops / bf16) if issued_tflops else None,
-        # dram__bytes_read.sum + dram__bytes_write.sum of one 256-pair launch, profiles/r01_pool_fulldist_ncu_full.csv
-        "traffic": NCU_POOL_TRAFFIC_BYTES if batch == 256 else None,
+        # dram__bytes_read.sum + dram__bytes_write.sum of one 256-pair launch, read from the ncu export under profiles/
+        "traffic": traffic if batch == 256 else None, "traffic_source": traffic_src,
+        "algorithmic_bytes_per_launch": batch * (8192 + RINGS * 4),
+        "timed_in": "separate pass of %d step(s) with an event pair around every launch, right after the timed region "
+                    "(which runs without them); %.1f ms per profiled step vs %.1f ms timed" % (prof_steps, prof_ms / prof_steps, ms / args.steps),
         "peak_source": peak_src, "launches": pool_n, "avg_launch_ms": avg_ms,
         "achieved_is": "fp16 tensor flops the kernel issues (non-empty tile x K-chunk blocks x 3 passes)",
         "issued_gflop_per_pair": issued_flop_per_pair_slot / 1e9,
         "algorithmic_gflop_per_pair_dense_fp32": FLOP_PER_PAIR / 1e9,
         "algorithmic_tflops_dense_equiv": dense_equiv_tflops,
         "bank": info, "launches_per_step": launches_per_step,
-        "kernel_share_of_step": pool_ms / ms if ms else None,
+        "kernel_share_of_step": pool_ms / prof_ms if prof_ms else None,
         "desc_kernel_ms_total": desc_ms, "desc_launches": desc_n,
         "reduce_kernel_ms_total": red_ms, "reduce_launches": red_n,
         "out_stream_gbs": n_pairs * args.steps * (RINGS * 4 + 8192) / (ms * 1e-3) / 1e9,
@@ -463,7 +648,7 @@ def main():
             import bench_paths
             del patches, idx
             if e2e is not None:
-                del h_out, h_patches, h_idx
+                h_out = h_patches = h_idx = None
             bank.close()
             torch.cuda.empty_cache()
             r = bench_paths.run(ctx, quick=True)
@@ -488,7 +673,14 @@ def main():
             }
         except Exception as ex:   # the headline line must still be printed
             rows = {"failed": repr(ex)}
-    cpu = None
+    cpu, rows_cpu = None, None
+    if world == 1 and not args.no_cpu and not args.no_rows:
+        try:
+            import bench_paths
+            rows_cpu = bench_paths.cpu_leg(quick=True)
+            rows_cpu["threads"] = threads_in_use()
+        except Exception as ex:
+            rows_cpu = {"failed": repr(ex)}
     if world == 1 and not args.no_cpu:
         try:
             cpu = run_cpu_baseline()
@@ -503,10 +695,12 @@ def main():
         "config": {"workload": "comp-fulldists full build: %d synthetic 64x64 patch pairs x 5120 rings "
                                "(40960 filters) per GPU, pair-sharded" % n_pairs,
                    "pairs_per_gpu": n_pairs, "filters": NFILT, "arith": "3 fp16 products per fp32 product on tcgen05 (22 mantissa bits), fp32 accumulate",
+                   "bank": "gen-poolregion defaults (nr 32, nphi 5, nsigma 32), bit-exact, generated on the device",
                    "l2": "inputs larger than L2 (1.04 GB of filter planes streamed per 256-pair batch, 10 GB of output per step)",
                    "reference_gtx970_pairs_per_s": GTX970_PAIRS_PER_S},
         "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
-        "cpu_baseline": cpu, "rows": rows, "pj_sweep_sharded": sweep_sharded, "checksum": checksum,
+        "cpu_baseline": cpu, "rows": rows, "rows_cpu_baseline": rows_cpu, "strong_scaling": strong,
+        "collective": collective, "pj_sweep_sharded": sweep_sharded, "checksum": checksum,
     }
     print(json.dumps(line), flush=True)
     if world > 1:

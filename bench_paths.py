@@ -96,6 +96,25 @@ def run(ctx, n_train=500000, n_test=100000, quick=False, D=544, n_pj_cfg=45, n_p
                                   "sector_gbs": sect / (mean_ms * 1e-3), "frac_hbm_sectors": sect / (mean_ms * 1e-3) / hbm,
                                   "dense_equiv_gbs": gb / (mean_ms * 1e-3)}
 
+    # ---- (d1) ComputePRStats end to end from a HOST matrix: n_test x 5120 pinned floats in, FPR95 / AUC out --------
+    import time
+    h_d = dists[:n_test].cpu().pin_memory()
+    d_d = torch.empty_like(dists[:n_test])
+    d_lab_t = torch.from_numpy(labels[:n_test]).to(dev)
+
+    def stats_e2e():
+        d_d.copy_(h_d, non_blocking=True)
+        return ctx.roc_stats(ctx.pr_patchdist(d_d, w), d_lab_t)
+    stats_e2e()
+    t0 = time.perf_counter()
+    for _ in range(3):
+        stats_e2e()
+    dt = (time.perf_counter() - t0) / 3
+    res["pr_stats_e2e_host"] = {"rows": n_test, "cols": F, "ms": dt * 1e3, "models_per_s": 1.0 / dt,
+                                "h2d_bytes": int(h_d.numel() * 4), "d2h_bytes": 12,
+                                "note": "PCIe-bound: the matrix upload is the whole cost; a -prj list amortises it"}
+    del h_d, d_d
+
     # ---- (d1) ROC / FPR95 on n_test pairs -----------------------------------------------
     pd = ctx.pr_patchdist(dists[:n_test], w)
     d_lab = torch.from_numpy(labels[:n_test]).to(dev)
@@ -271,8 +290,26 @@ def run_uprj_builder(ctx, n_pairs, n_sel, hbm):
     pool_ms, pool_n = ctx.profile_read(1)
     fin_ms, fin_n = ctx.profile_read(6)
     ctx.profile(False)
+    # end to end with host buffers: pinned patches / pairs in, the N x 8 nSel matrix out to pinned host memory
+    import time
+    h_p, h_i = patches.cpu().pin_memory(), idx.cpu().pin_memory()
+    h_o = torch.empty((n_pairs, 8 * n_sel), dtype=torch.float32).pin_memory()
+    d_p, d_i = torch.empty_like(patches), torch.empty_like(idx)
+
+    def e2e_once():
+        d_p.copy_(h_p, non_blocking=True)
+        d_i.copy_(h_i, non_blocking=True)
+        h_o.copy_(ctx.uprjdist_build(bank, d_p, d_i), non_blocking=True)
+        torch.cuda.synchronize()
+    e2e_once()
+    t0 = time.perf_counter()
+    for _ in range(3):
+        e2e_once()
+    e2e_s = (time.perf_counter() - t0) / 3
     by = n_pairs * (8192 + 32 * n_sel)
     out = {"pairs": n_pairs, "n_sel": n_sel, "ms": mean_ms, "best_ms": best_ms,
+           "e2e_host": {"pairs_per_s": n_pairs / e2e_s, "ms": e2e_s * 1e3, "h2d_bytes": int(h_p.numel() + h_i.numel() * 4),
+                        "d2h_bytes": int(h_o.numel() * 4)},
            "pairs_per_s": n_pairs / (mean_ms * 1e-3), "desc_per_s": 2 * n_pairs / (mean_ms * 1e-3),
            "algorithmic_bytes_per_pair": 8192 + 32 * n_sel,
            "achieved_gbs": by / (mean_ms * 1e-3) / 1e9, "frac_hbm": by / (mean_ms * 1e-3) / 1e9 / hbm,
@@ -281,6 +318,13 @@ def run_uprj_builder(ctx, n_pairs, n_sel, hbm):
            "pool_gflops": 2.0 * 2 * n_sel * 4096 * 8 * n_pairs / (mean_ms * 1e-3) / 1e9}
     bank.close()
     return out
+
+
+def _uprj_chunk(sel, patches, idx):
+    from oracle import dlco_oracle as O
+    from threadpoolctl import threadpool_limits
+    with threadpool_limits(1):          # one pair per process, as the reference's OMP loop: no nested BLAS threads
+        return O.uprj_distances(sel, patches, idx, dt=np.float32)
 
 
 def cpu_leg(D=544, quick=False):
@@ -319,6 +363,23 @@ def cpu_leg(D=544, quick=False):
     pd = (dists @ w).astype(np.float32)
     dt = best(lambda: O.roc_stats(pd, labels))
     res["roc_stats"] = {"n": n, "ms": dt * 1e3, "sample": "sort + ROC + polygon area on %d pairs (numpy)" % n}
+    t = time.perf_counter()
+    O.pr_stats(O.pr_params(O.ring_params()), dists, labels, w, dt=np.float32)
+    dt = time.perf_counter() - t
+    res["pr_stats_e2e_host"] = {"rows": n, "ms": dt * 1e3, "models_per_s": 1.0 / dt,
+                                "sample": "ComputePRStats on %d x %d (bookkeeping + sgemv + sort + ROC)" % (n, F)}
+    # (b1) comp-uprjdists: get_desc x 2 + (nSel x 4096)(4096 x 8) x 2 per pair, the reference's OMP-over-pairs loop
+    import multiprocessing as mp
+    n_sel = D // 8
+    pt_patches, pid = O.synth_patches(40, per_point=3, seed=5)
+    sel = O.pr_filters_for_rings(O.ring_params()[np.arange(n_sel // 8 + 1) * 601 % 5120])[0][:n_sel]
+    idxu = O.synth_pairs(pid, 256 if quick else 1024, seed=9)
+    with mp.get_context("fork").Pool(min(cores, 32)) as pool:
+        t = time.perf_counter()
+        pool.starmap(_uprj_chunk, [(sel, pt_patches, idxu[c:c + 16]) for c in range(0, len(idxu), 16)])
+        dt = time.perf_counter() - t
+    res["uprjdist_build"] = {"pairs": len(idxu), "n_sel": n_sel, "ms": dt * 1e3, "pairs_per_s": len(idxu) / dt,
+                             "sample": "%d pairs x %d filters, oracle get_desc + sgemm per pair on %d processes" % (len(idxu), n_sel, min(cores, 32))}
     # (c1) the serial RDA chain
     ip, ineg, npt, nnt = O.split_train_val(labels)
     ip, ineg = np.asarray(ip, np.int32), np.asarray(ineg, np.int32)

@@ -177,10 +177,16 @@ def test_scripts_01_to_10(ws_env, gpu_ctx):
     h5pack(os.path.join(ws, "pr-learn/notredame-0.003-0.040-pr.h5"), ("w", model8("notredame"), 1, 9))
     if len(w["liberty"]) < 8:
         h5pack(os.path.join(ws, "pr-learn/liberty-0.035-0.250-pr.h5"), ("w", model8("liberty"), 1, 9))
+    # the `originals` (MATLAB-converted models: one row, chunked, unfiltered; no `#id` -> -id 0)
+    for ds, name in (("liberty", "liberty-rank_m0.5_g8-pr.h5"), ("notredame", "notredame-rank_m0.15_g0.5-pr.h5"),
+                     ("yosemite", "yosemite-rank_m0.25_g4-pr.h5")):
+        h5pack(os.path.join(ws, "pr-learn/originals", name), ("w", np.ascontiguousarray(w[ds][-1:]), 1, 0))
     so, se = sh(ws, env, "07-compunproj.sh")
-    assert so.count("Start Compute L1 distances.") == 9          # 3 data sets x 3 models; the `originals` are absent
+    assert so.count("Start Compute L1 distances.") == 18         # 3 data sets x 6 models
     unproj = sorted(f for f in os.listdir(os.path.join(ws, "distances")) if f.endswith("-unproj.h5"))
-    assert len(unproj) == 9 and "liberty-liberty-0.035-0.250-pr#7-unproj.h5" in unproj
+    assert len(unproj) == 18 and "liberty-liberty-0.035-0.250-pr#7-unproj.h5" in unproj
+    unproj = [f for f in unproj if "rank" not in f]              # 08-pjlearn.sh: `grep -v rank`
+    assert len(unproj) == 9
     flt = H5File(os.path.join(ws, "filters.h5"))
     w7 = H5File(os.path.join(ws, "pr-learn/liberty-0.035-0.250-pr.h5")).read("w")[7]
     full = np.zeros((40960, 4096), np.float32)
@@ -194,7 +200,7 @@ def test_scripts_01_to_10(ws_env, gpu_ctx):
     assert d.shape == (1200, 8 * len(sel))
     want = O.uprj_distances(sel, data["notredame"][0], data["notredame"][1][:32])
     assert (np.abs(d[:32] - want).max(axis=1) / np.abs(want).max(axis=1)).max() <= 1e-5
-    assert sh(ws, env, "07-compunproj.sh")[0].count("already done.") == 9
+    assert sh(ws, env, "07-compunproj.sh")[0].count("already done.") == 18
     # ---- 08-pjlearn.sh: one model family (the three data sets of liberty-0.035-0.250-pr#7), grid 1 x 2 ------------------
     aside = os.path.join(os.path.dirname(ws), "aside")       # outside the workspace: 08 looks for *-unproj.h5 with find
     os.makedirs(aside)
