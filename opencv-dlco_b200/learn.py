@@ -319,6 +319,8 @@ class PjSweep:
         self.t += 1
 
     def ranks(self):
+        """Ranks of the current A (prox="sign": call refresh_w() first for the eigenvalue-based count that the
+        log lines and W follow; between refreshes d_rank holds the sign iteration's trace-based estimate)."""
         if self.prox == "eig":
             self.ctx.pj_grid_check(self.n_cfg)                   # synchronises; raises on a failed eig
         return self.d_rank.cpu().numpy().astype(int)
@@ -345,6 +347,7 @@ class PjSweep:
         while self.t <= n_iter:
             self.step()
             if step == self.log_step:
+                self.refresh_w()                 # prox="sign": W and the eigenvalue-based ranks of the projected A
                 ranks = self.ranks()
                 ttime = time.perf_counter() - t_train
                 for c in range(self.n_cfg):

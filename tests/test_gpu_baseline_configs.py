@@ -1,0 +1,262 @@
+"""Learner parity at the configurations BASELINE.json names (configs[2], [3]):
+
+  * pj-learn at D = 544 / 480, batch 200 + 200, 500 steps, the four (mu, gamma) picks of
+    workspace/11-opencv-export.sh:3-6, both prox routes: teacher-forced per iteration (A and dfAvg within
+    1e-4 of the fp64 oracle started from the GPU's own state), the free-run drift reported next to the fp32
+    oracle's own drift, rank equal, FPR95 within 0.1 pp on a 100k-pair test matrix;
+  * the sign route over 5 000 iterations of one D = 544 configuration: its "Best:/Stat:" lines (Rank, AUC,
+    FPR95) track the eig route's (the scripts run 50 000);
+  * pr-learn + pr-stats on a "Distance" matrix produced by dlco_fulldist_build (not a noise matrix):
+    200 000 steps against the C oracle's chain, FPR95 on 100 000 test pairs.
+
+The fp64 / fp32 free-running oracle of the 500-step runs is oracle.pj_rda_steps restated with torch on the GPU
+(`pj_rda_steps_torch`: 4 000 eigen-decompositions of 544 x 544 would take the numpy oracle 20 minutes); the
+restatement is held to the numpy oracle on its first steps inside the test."""
+import ctypes
+import os
+import re
+import sys
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+from oracle import dlco_oracle as O  # noqa: E402
+
+# (D, mu, gamma): workspace/11-opencv-export.sh -- the 48-D model is learnt on the 60-PR (480-D) yosemite
+# descriptors, the 64 / 80 / 120-D ones on the 68-PR (544-D) liberty descriptors
+PICKS = [(480, 0.0020, 0.200), (544, 0.0010, 0.100), (544, 0.0005, 0.100), (544, 0.0001, 0.025)]
+
+
+def synth_uprj(n, D, seed):
+    """Unprojected-distance-like rows: differences of pooled values clamped to [0, 1] (|x| <= 1), positives
+    (even rows) closer; low-rank structure plus noise so that the learnt rank settles well below D."""
+    rng = np.random.default_rng(seed)
+    lab = (np.arange(n) % 2 == 0).astype(np.uint8)
+    basis = rng.standard_normal((24, D)) / np.sqrt(D)
+    z = rng.standard_normal((n, 24)) * (0.35 + 0.9 * (1 - lab[:, None]))
+    x = z @ basis + rng.standard_normal((n, D)) * 0.05
+    return np.clip(x, -1, 1).astype(np.float32), lab
+
+
+def pj_prox_torch(A):
+    """oracle.pj_prox: eigh, clip, V L V^T; W rows sqrt(l_k) v_k for l_k > 0, ascending."""
+    e, V = torch.linalg.eigh(A)
+    keep = e > 0
+    ep, Vp = e[keep], V[:, keep]
+    W = (Vp * torch.sqrt(ep)).T.contiguous()
+    if W.shape[0] == 0:                                  # an empty W becomes a D x D zero matrix (:487-490)
+        W = torch.zeros_like(A)
+    return (Vp * ep) @ Vp.T, W
+
+
+def pj_rda_steps_torch(x, ip, ineg, npt, nnt, mu, gamma, n_steps, dt, state=None, sz_batch=200):
+    """oracle.pj_rda_steps (src/pj-learn.cpp:305-490) with torch tensors of dtype dt on the GPU."""
+    D = x.shape[1]
+    dev = x.device
+    if state is None:
+        z = lambda: torch.zeros((D, D), dtype=dt, device=dev)              # noqa: E731
+        state = dict(W=z(), A=z(), dfAvg=z(), t=0, rng=O.CvRNG(2215))
+    W, A, df, t, rng = state["W"], state["A"], state["dfAvg"], state["t"], state["rng"]
+    mu, gamma = float(np.float32(mu)), float(np.float32(gamma))
+    eye = torch.eye(D, dtype=dt, device=dev)
+    for _ in range(n_steps):
+        rp, rn = O.pj_sample_batch(rng, npt, nnt, sz_batch)
+        pos = x[torch.from_numpy(ip[rp]).to(dev)].to(dt)
+        neg = x[torch.from_numpy(ineg[rn]).to(dev)].to(dt)
+        pd = ((pos @ W.T) ** 2).sum(1).float()
+        nd = ((neg @ W.T) ** 2).sum(1).float()
+        viol = (pd[:, None] + 1.0) > nd[None, :]                            # :373-410
+        cp = viol.sum(1).to(dt)
+        cn = viol.sum(0).to(dt)
+        dloss = (pos.T * cp) @ pos - (neg.T * cn) @ neg
+        beta = float(np.float32(1.0) / np.float32(sz_batch * sz_batch * (t + 1)))
+        if dt == torch.float32:
+            df = df * float(np.float32(t / (t + 1))) + dloss * beta
+        else:
+            df = df * (t / (t + 1)) + dloss * beta
+        A = (df + mu * eye) * (-np.sqrt(t + 1.0) / gamma)
+        A = 0.5 * (A + A.T)
+        A, W = pj_prox_torch(A)
+        t += 1
+    return dict(W=W, A=A, dfAvg=df, t=t, rng=rng)
+
+
+def rel(a, b):
+    return float((a.double() - b.double()).abs().max() / b.double().abs().max().clamp_min(1e-300))
+
+
+_ORACLE_RUNS = {}
+
+
+def oracle_runs(dev, D, mu, gamma, steps):
+    """The free-running fp64 and fp32 oracles of one pick (shared by both prox routes): A of the fp64 run and the
+    fp32 run's drift from it at t = 100, 200, ..; final W of both."""
+    key = (D, mu, gamma, steps)
+    if key not in _ORACLE_RUNS:
+        x, lab = synth_uprj(40000, D, 100 + D)
+        d_x = torch.from_numpy(x).to(dev)
+        ip, ineg, npt, nnt = O.split_train_val(lab)
+        # the torch restatement == the numpy oracle on its first steps
+        a = pj_rda_steps_torch(d_x, ip, ineg, npt, nnt, mu, gamma, 2, torch.float64)
+        b = O.pj_rda_steps(x, ip, ineg, npt, nnt, mu, gamma, 2, dt=np.float64)
+        assert np.abs(a["A"].cpu().numpy() - b["A"]).max() <= 1e-9 * np.abs(b["A"]).max()
+        assert a["W"].shape[0] == b["W"].shape[0]
+        st64 = st32 = None
+        cps = {}
+        for t in range(0, steps, 100):
+            st64 = pj_rda_steps_torch(d_x, ip, ineg, npt, nnt, mu, gamma, 100, torch.float64, state=st64)
+            st32 = pj_rda_steps_torch(d_x, ip, ineg, npt, nnt, mu, gamma, 100, torch.float32, state=st32)
+            cps[t + 100] = (st64["A"].clone(), rel(st32["A"], st64["A"]))
+        _ORACLE_RUNS[key] = dict(cps=cps, W64=st64["W"].cpu().numpy(), rank64=st64["W"].shape[0], rank32=st32["W"].shape[0],
+                                 rng_state=st64["rng"].state)
+    return _ORACLE_RUNS[key]
+
+
+@pytest.mark.parametrize("prox", ["eig", "sign"])
+@pytest.mark.parametrize("D,mu,gamma", PICKS)
+def test_pj_learn_500_steps_at_baseline_configs(gpu_ctx, D, mu, gamma, prox):
+    import dlco_b200
+    dev = gpu_ctx.device
+    steps = 500
+    x, lab = synth_uprj(40000, D, 100 + D)
+    xt, labt = synth_uprj(100000, D, 900 + D)                               # the 100k-pair test matrix
+    d_x = torch.from_numpy(x).to(dev)
+    ip, ineg, npt, nnt = O.split_train_val(lab)
+    S = dlco_b200.learn.PjSweep(gpu_ctx, d_x, lab, [mu], [gamma], prox=prox)
+    ora = oracle_runs(dev, D, mu, gamma, steps)
+    worst_df = worst_a = 0.0
+    drift = []
+    for t in range(steps):
+        forced = t % 25 == 24 or t < 3                                       # 23 teacher-forced iterations
+        if forced:
+            rng = O.CvRNG(2215)
+            rng.state = int(S.rng_state.cpu().numpy().view(np.uint64)[0])
+            S.refresh_w()
+            rank0 = int(S.ranks()[0]) if t else 0
+            W0 = S.W[0, :rank0].double() if rank0 else torch.zeros((D, D), dtype=torch.float64, device=dev)
+            snap = dict(W=W0, A=S.A[0].double(), dfAvg=S.dfavg[0].double(), t=t, rng=rng)
+        S.step()
+        if forced:
+            tf = pj_rda_steps_torch(d_x, ip, ineg, npt, nnt, mu, gamma, 1, torch.float64, state=snap)
+            worst_df = max(worst_df, rel(S.dfavg[0], tf["dfAvg"]))
+            worst_a = max(worst_a, rel(S.A[0], tf["A"]))
+            assert int(S.rng_state.cpu().numpy().view(np.uint64)[0]) == tf["rng"].state
+        if (t + 1) in ora["cps"]:
+            a64, d32 = ora["cps"][t + 1]
+            drift.append((t + 1, rel(S.A[0], a64), d32))
+    assert int(S.rng_state.cpu().numpy().view(np.uint64)[0]) == ora["rng_state"]
+    assert worst_df <= 1e-4 and worst_a <= 1e-4, (worst_df, worst_a)
+    S.refresh_w()
+    rank_g, rank_o, rank_o32 = int(S.ranks()[0]), ora["rank64"], ora["rank32"]
+    gpu_drift, ref_drift = drift[-1][1], drift[-1][2]
+    print("pj-learn D=%d mu=%g gamma=%g prox=%s: teacher-forced worst dfAvg %.2e A %.2e; free-run drift of A after "
+          "(100..500) steps, GPU vs fp64 | fp32 oracle vs fp64: %s; rank GPU %d, fp64 oracle %d, fp32 oracle %d"
+          % (D, mu, gamma, prox, worst_df, worst_a, " ".join("%d: %.1e | %.1e" % d for d in drift), rank_g, rank_o, rank_o32))
+    # learnt A within 1e-4 of the exact recursion, or -- where the recursion itself is ill-conditioned (a hinge
+    # decision within rounding of a tie flips) -- as close to it as the reference's own fp32 arithmetic gets
+    assert gpu_drift <= max(1e-4, 4 * ref_drift), (gpu_drift, ref_drift)
+    assert abs(rank_g - rank_o) <= max(1, abs(rank_o32 - rank_o)), (rank_g, rank_o, rank_o32)
+    # FPR95 on the 100k-pair test matrix: GPU model through the GPU statistics vs the oracle's model through the oracle's
+    d_xt = torch.from_numpy(xt).to(dev)
+    pd = gpu_ctx.pj_patchdist(d_xt, S.W[0], rank_g)
+    fpr_g, auc_g = gpu_ctx.roc_stats(pd, torch.from_numpy(labt).to(dev))
+    dim_o, fpr_o, auc_o = O.pj_stats(ora["W64"], xt, labt)
+    print("   FPR95 on 100k test pairs: GPU %.4f, oracle %.4f; AUC %.6f / %.6f" % (fpr_g, float(fpr_o), auc_g, auc_o))
+    assert abs(float(fpr_g) - float(fpr_o)) <= 1e-3                          # 0.1 percentage points
+    assert abs(auc_g - auc_o) <= 1e-4
+
+
+def test_pj_sign_route_tracks_eig_route_over_5000_iterations(gpu_ctx):
+    """workspace/08-pjlearn.sh runs 50 000 iterations; the sign-iteration prox approximates the projection for
+    eigenvalues within 1e-4 ||A||_F of zero.  Over 5 000 iterations of one D = 544 configuration the
+    logged Rank / AUC / FPR95 of both routes must stay together."""
+    import dlco_b200
+    D, mu, gamma, iters = 544, 0.0010, 0.100, 5000
+    x, lab = synth_uprj(60000, D, 7)
+    d_x = torch.from_numpy(x).to(gpu_ctx.device)
+    logs = {}
+    for prox in ("eig", "sign"):
+        lines = []
+        S = dlco_b200.learn.PjSweep(gpu_ctx, d_x, lab, [mu], [gamma], prox=prox, emit=lines.append)
+        S.train(iters)
+        logs[prox] = lines
+        del S
+    pat = re.compile(r"^\[\S+\] (Best|Step): (\d+)  Loss: (\S+) Regul: (\S+) Obj: (\S+) \((\S+)\) Rank: (\d+) \((\d+)\)")
+    spat = re.compile(r"^\[\S+\] Stat: Dim \[(\d+)\] AUC: (\S+) \((\S+)\) FPR95: (\S+) \((\S+)\)( \[saved\])?$")
+    rows = {}
+    for prox, lines in logs.items():
+        steps = [pat.match(ln) for ln in lines]
+        rows[prox] = {int(m.group(2)): (float(m.group(3)), float(m.group(4)), int(m.group(7))) for m in steps if m}
+        assert sorted(rows[prox]) == list(range(100, iters + 1, 100))
+    worst_rank = worst_loss = 0.0
+    for t in rows["eig"]:
+        le, re_, rke = rows["eig"][t]
+        ls, rs, rks = rows["sign"][t]
+        worst_rank = max(worst_rank, abs(rke - rks))
+        worst_loss = max(worst_loss, abs(le - ls) / max(le, 1e-12), abs(re_ - rs) / max(re_, 1e-12))
+    st = {p: [spat.match(ln) for ln in logs[p] if " Stat: " in ln] for p in logs}
+    last = {p: [m for m in st[p] if m and m.group(6)][-1] for p in logs}
+    print("sign vs eig over %d iterations: worst |rank diff| %d, worst rel. loss/regul diff %.2e; last saved: eig Dim %s AUC %s "
+          "FPR95 %s | sign Dim %s AUC %s FPR95 %s" % (iters, worst_rank, worst_loss, last["eig"].group(1), last["eig"].group(2),
+                                                      last["eig"].group(4), last["sign"].group(1), last["sign"].group(2),
+                                                      last["sign"].group(4)))
+    assert worst_rank <= 2 and worst_loss <= 2e-3
+    assert abs(int(last["eig"].group(1)) - int(last["sign"].group(1))) <= 2
+    assert abs(float(last["eig"].group(2)) - float(last["sign"].group(2))) <= 1e-4
+    assert abs(float(last["eig"].group(4)) - float(last["sign"].group(4))) <= 0.1          # FPR95 in percent: 0.1 pp
+
+
+def test_pr_learn_on_built_distances_200k_steps_and_fpr95_on_100k(gpu_ctx, oracle_lib):
+    """BASELINE configs[2]: pr-learn over a full-distance matrix that dlco_fulldist_build produced (all 5120 rings,
+    the bit-exact bank), (mu, gamma) = (0.035, 0.25), 200 000 steps against the C oracle's chain; then pr-stats'
+    FPR95 of the learnt w on 100 000 test pairs against the oracle's ComputePRStats."""
+    import bench as B
+    import dlco_b200
+    dev = gpu_ctx.device
+    bank = gpu_ctx.bank_analytic(dlco_b200.ring_params())
+    n_tr, n_te = 20000, 100000
+    patches = B.synth_patches(torch, dev, 12000, 3, seed=31)
+    idx_tr = B.synth_pairs(torch, dev, 12000, 3, n_tr, seed=32)
+    d_tr = gpu_ctx.fulldist_build(bank, patches, idx_tr)
+    patches_te = B.synth_patches(torch, dev, 40000, 3, seed=33)
+    idx_te = B.synth_pairs(torch, dev, 40000, 3, n_te, seed=34)
+    d_te = gpu_ctx.fulldist_build(bank, patches_te, idx_te)
+    bank.close()
+    torch.cuda.synchronize()
+    lab_tr = gpu_ctx.pair_labels(idx_tr).cpu().numpy()
+    lab_te = gpu_ctx.pair_labels(idx_te).cpu().numpy()
+    mu, gamma, steps, F = 0.035, 0.25, 200000, 5120
+    L = dlco_b200.learn.PrLearner(gpu_ctx, d_tr, lab_tr, mu, gamma)
+    L.run_steps(steps)
+    w_g = L.w[0].cpu().numpy()
+    h_tr = d_tr.cpu().numpy()
+    ip, ineg, npt, nnt = O.split_train_val(lab_tr)
+    ip, ineg = np.asarray(ip, np.int32), np.asarray(ineg, np.int32)
+    w = np.zeros(F, np.float32)
+    df = np.zeros(F, np.float32)
+    stt = ctypes.c_ulonglong(2215)
+    vp = ctypes.c_void_p
+    oracle_lib.dlco_oracle_pr_rda.restype = None
+    oracle_lib.dlco_oracle_pr_rda.argtypes = [vp, ctypes.c_long, ctypes.c_int, vp, ctypes.c_int, vp, ctypes.c_int,
+                                              ctypes.c_float, ctypes.c_float, ctypes.c_ulonglong, ctypes.c_ulonglong,
+                                              ctypes.POINTER(ctypes.c_ulonglong), vp, vp]
+    oracle_lib.dlco_oracle_pr_rda(h_tr.ctypes.data, F, F, ip.ctypes.data, npt, ineg.ctypes.data, nnt, mu, gamma, 0, steps,
+                                  ctypes.byref(stt), w.ctypes.data, df.ctypes.data)
+    assert stt.value == L.rng_state
+    nnz = int((w > 0).sum())
+    assert nnz >= 2 and np.array_equal(w_g > 0, w > 0), (nnz, int((w_g > 0).sum()))
+    assert np.abs(w_g - w).max() <= 1e-4 * np.abs(w).max()
+    assert np.abs(L.dfavg[0].cpu().numpy() - df).max() <= 1e-4 * np.abs(df).max()
+    # pr-stats: FPR95 / AUC of the learnt w on the 100k test pairs
+    pd = gpu_ctx.pr_patchdist(d_te, L.w[0])
+    fpr_g, auc_g = gpu_ctx.roc_stats(pd, torch.from_numpy(lab_te).to(dev))
+    fpr_o, auc_o = O.roc_stats((d_te.cpu().numpy().astype(np.float64) @ w.astype(np.float64)).astype(np.float32), lab_te)
+    print("pr-learn on built distances: NNZ %d, FPR95 on 100k test pairs GPU %.4f oracle %.4f, AUC %.6f / %.6f"
+          % (nnz, fpr_g, float(fpr_o), auc_g, auc_o))
+    assert abs(float(fpr_g) - float(fpr_o)) <= 1e-3 and abs(auc_g - auc_o) <= 1e-5

@@ -171,6 +171,7 @@ int main(int argc, char **argv)
         unsigned int step = 0;
         double t_train = now_sec();
         const double t_all = now_sec();
+        n_iter = max_iters_cap(n_iter);                    // DLCO_MAX_ITERS, see tools/common.hpp
         for (unsigned int t = 0; t <= n_iter; t++) {
             if (prox_sign)
                 check(dlco_pj_rda_step_grid_sign(ctx.h, d_dists.p, D, D, d_pos.p, (int32_t)sp.n_pos_trn, d_neg.p,
