@@ -107,6 +107,16 @@ int dlco_fulldist_build_host(dlco_ctx *ctx, const dlco_bank *bank, const uint8_t
                              int64_t nPatches, const int32_t *h_indices, int64_t lo, int64_t hi,
                              int nAngleBins, float sigma, int bNorm, float *h_out,
                              int64_t ld_out);
+/* the same without waiting: uploads, kernels and downloads are queued on the context's three streams (created once
+ * per context) and the double-buffered staging slots keep alternating across calls, so block after block can be
+ * issued back to back; h_out rows are complete after dlco_sync(), or after dlco_fulldist_host_wait(*h_ticket) while
+ * later calls are still in flight (h_ticket may be NULL).  h_patches / h_indices / h_out must stay valid (and h_out
+ * unread) until then. */
+int dlco_fulldist_build_host_async(dlco_ctx *ctx, const dlco_bank *bank, const uint8_t *h_patches,
+                                   int64_t nPatches, const int32_t *h_indices, int64_t lo, int64_t hi,
+                                   int nAngleBins, float sigma, int bNorm, float *h_out,
+                                   int64_t ld_out, int64_t *h_ticket);
+int dlco_fulldist_host_wait(dlco_ctx *ctx, int64_t ticket);
 /* Label = (point1 == point2): src/comp-fulldists.cpp:247-251 */
 int dlco_pair_labels(dlco_ctx *ctx, const int32_t *d_indices, int64_t n, uint8_t *d_label);
 

@@ -45,6 +45,9 @@ SIGNATURES = {
                                     c_float, c_int, c_void_p, c_int64]),
     "dlco_fulldist_build_host": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int64,
                                          c_int64, c_int, c_float, c_int, c_void_p, c_int64]),
+    "dlco_fulldist_build_host_async": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int64,
+                                               c_int64, c_int, c_float, c_int, c_void_p, c_int64, P(c_int64)]),
+    "dlco_fulldist_host_wait": (c_int, [c_void_p, c_int64]),
     "dlco_pair_labels": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
     "dlco_uprjdist_build": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int,
                                     c_float, c_int, c_void_p, c_int64]),
@@ -275,6 +278,18 @@ class Context:
                                                  _ptr(indices), lo, hi, n_bins, sigma, int(b_norm),
                                                  _ptr(out), out.stride(0)))
         return out
+
+    def fulldist_build_host_async(self, bank, patches, indices, lo, hi, out, n_bins=8, sigma=1.4, b_norm=True):
+        """Queues rows [lo, hi) into the HOST tensor `out` (hi - lo rows) without waiting; complete after sync() or
+        fulldist_host_wait(ticket).  -> ticket"""
+        t = c_int64()
+        _check(self.lib.dlco_fulldist_build_host_async(self.handle, bank.handle, _ptr(patches), patches.shape[0],
+                                                       _ptr(indices), lo, hi, n_bins, sigma, int(b_norm),
+                                                       _ptr(out), out.stride(0), ctypes.byref(t)))
+        return t.value
+
+    def fulldist_host_wait(self, ticket):
+        _check(self.lib.dlco_fulldist_host_wait(self.handle, ticket))
 
     def pair_labels(self, indices):
         out = self.torch.empty((indices.shape[0],), dtype=self.torch.uint8, device=self.device)

@@ -64,6 +64,22 @@ int dlco_side_stream(dlco_ctx *ctx)
     return DLCO_OK;
 }
 
+int dlco_host_pipe(dlco_ctx *ctx)
+{
+    if (ctx->pipe_ready) return DLCO_OK;
+    DLCO_CUDA(cudaStreamCreateWithFlags(&ctx->pipe_in, cudaStreamNonBlocking));
+    DLCO_CUDA(cudaStreamCreateWithFlags(&ctx->pipe_out, cudaStreamNonBlocking));
+    for (int s = 0; s < 2; s++) {
+        DLCO_CUDA(cudaEventCreateWithFlags(&ctx->pipe_ev_in[s], cudaEventDisableTiming));
+        DLCO_CUDA(cudaEventCreateWithFlags(&ctx->pipe_ev_k[s], cudaEventDisableTiming));
+        DLCO_CUDA(cudaEventCreateWithFlags(&ctx->pipe_ev_out[s], cudaEventDisableTiming));
+    }
+    DLCO_CUDA(cudaEventCreateWithFlags(&ctx->pipe_ev_join, cudaEventDisableTiming));
+    ctx->pipe_bi = 0;
+    ctx->pipe_ready = 1;
+    return DLCO_OK;
+}
+
 extern "C" int dlco_init(int device, dlco_ctx **out)
 {
     DLCO_REQUIRE(out != nullptr, "dlco_init: ctx is NULL");
@@ -106,6 +122,18 @@ extern "C" int dlco_shutdown(dlco_ctx *ctx)
         for (int i = 0; i < 6; i++) cudaEventDestroy(ctx->side_ev[i]);
         cudaStreamDestroy(ctx->side_stream);
     }
+    if (ctx->pipe_ready) {
+        cudaStreamSynchronize(ctx->pipe_in);
+        cudaStreamSynchronize(ctx->pipe_out);
+        for (int i = 0; i < 2; i++) {
+            cudaEventDestroy(ctx->pipe_ev_in[i]);
+            cudaEventDestroy(ctx->pipe_ev_k[i]);
+            cudaEventDestroy(ctx->pipe_ev_out[i]);
+        }
+        cudaEventDestroy(ctx->pipe_ev_join);
+        cudaStreamDestroy(ctx->pipe_in);
+        cudaStreamDestroy(ctx->pipe_out);
+    }
     for (int i = 0; i < 48; i++)
         if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
     for (int i = 0; i < 8; i++)
@@ -134,7 +162,10 @@ extern "C" int dlco_device_name(dlco_ctx *ctx, char *buf, int len, int *maj, int
 extern "C" int dlco_sync(dlco_ctx *ctx)
 {
     DLCO_REQUIRE(ctx, "dlco_sync: ctx is NULL");
+    // the host-buffer pipeline's copy streams run ahead of / behind the context stream: drain them as well
+    if (ctx->pipe_ready) DLCO_CUDA(cudaStreamSynchronize(ctx->pipe_in));
     DLCO_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (ctx->pipe_ready) DLCO_CUDA(cudaStreamSynchronize(ctx->pipe_out));
     return DLCO_OK;
 }
 

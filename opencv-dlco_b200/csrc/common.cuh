@@ -36,6 +36,13 @@ struct dlco_ctx {
     cudaStream_t side_stream;
     cudaEvent_t side_ev[6];
     int side_ready;
+    // host-buffer pipeline of dlco_fulldist_build_host[_async] (lazy, dlco_host_pipe): upload and download streams and
+    // the per-slot events (in = upload done, k = kernels done, out = download done); pipe_bi counts batches over the
+    // context's lifetime so that consecutive calls keep alternating the two staging slots without draining
+    cudaStream_t pipe_in, pipe_out;
+    cudaEvent_t pipe_ev_in[2], pipe_ev_k[2], pipe_ev_out[2], pipe_ev_join;
+    int pipe_ready;
+    int64_t pipe_bi;
     uint32_t attr_mask;   // which kernels had their dynamic-smem limit raised on THIS context's device
     void *cusolver;       // cusolverDnHandle_t (lazy)
     void *cusolver_lib;   // dlopen handle
@@ -62,6 +69,7 @@ void dlco_set_error(const char *fmt, ...);
 void *dlco_scratch(dlco_ctx *ctx, int slot, size_t bytes);
 void *dlco_pinned(dlco_ctx *ctx, int slot, size_t bytes);
 int dlco_side_stream(dlco_ctx *ctx);
+int dlco_host_pipe(dlco_ctx *ctx);
 void dlco_prof_begin(dlco_ctx *ctx, int which);
 void dlco_prof_end(dlco_ctx *ctx);
 

@@ -110,52 +110,52 @@ extern "C" int dlco_fulldist_build(dlco_ctx *ctx, const dlco_bank *bank, const u
     return DLCO_OK;
 }
 
-extern "C" int dlco_fulldist_build_host(dlco_ctx *ctx, const dlco_bank *bank, const uint8_t *h_patches,
-                                        int64_t nPatches, const int32_t *h_indices, int64_t lo,
-                                        int64_t hi, int nAngleBins, float sigma, int bNorm,
-                                        float *h_out, int64_t ld_out)
+// Rows [lo, hi) of "Distance" from HOST buffers into a HOST matrix, without waiting for them: uploads run ahead on the
+// context's upload stream, the kernels of each batch on the context stream, downloads behind on its download stream;
+// device staging and output blocks are double buffered and the slots keep alternating across calls, so a caller that
+// issues block after block (tools/comp-fulldists.cpp) keeps the GPU busy across call boundaries.  h_out rows are
+// complete after dlco_sync().  The staging copy of the patches is done by the calling thread.
+extern "C" int dlco_fulldist_build_host_async(dlco_ctx *ctx, const dlco_bank *bank, const uint8_t *h_patches,
+                                              int64_t nPatches, const int32_t *h_indices, int64_t lo,
+                                              int64_t hi, int nAngleBins, float sigma, int bNorm,
+                                              float *h_out, int64_t ld_out, int64_t *h_ticket)
 {
+    if (h_ticket) *h_ticket = -1;
     int r = check_common(ctx, bank, h_patches, h_indices, lo, hi, nAngleBins, h_out, "dlco_fulldist_build_host");
     if (r != DLCO_OK) return r;
     const int rings = bank->nF / 8;
     DLCO_REQUIRE(bank->nF % 8 == 0, "dlco_fulldist_build_host: bank has %d filters, need 8 per ring", bank->nF);
     DLCO_REQUIRE(ld_out >= rings, "dlco_fulldist_build_host: ld_out too small");
     DLCO_CUDA(cudaSetDevice(ctx->device));
+    r = dlco_host_pipe(ctx);
+    if (r != DLCO_OK) return r;
     const int nb = group_pairs();
     // staging: per slot, 2*nb patches (pair order) + nb index rows rewritten to local ids
     const size_t pbytes = (size_t)nb * 2 * 4096, ibytes = (size_t)nb * 4 * sizeof(int32_t);
+    const size_t obytes = (size_t)nb * rings * sizeof(float);
+    // growing a buffer frees the old one: nothing of an earlier call may still be in flight then
+    if (ctx->pinned_bytes[0] < pbytes + ibytes || ctx->scratch_bytes[23] < 2 * (pbytes + ibytes) || ctx->scratch_bytes[24] < 2 * obytes) {
+        r = dlco_sync(ctx);
+        if (r != DLCO_OK) return r;
+    }
     uint8_t *h_stage[2];
     for (int s = 0; s < 2; s++) {
         h_stage[s] = (uint8_t *)dlco_pinned(ctx, s, pbytes + ibytes);
         if (!h_stage[s]) return DLCO_ENOMEM;
     }
     uint8_t *d_stage = (uint8_t *)dlco_scratch(ctx, 23, 2 * (pbytes + ibytes));
-    const size_t obytes = (size_t)nb * rings * sizeof(float);
     uint8_t *d_o = (uint8_t *)dlco_scratch(ctx, 24, 2 * obytes);
     if (!d_stage || !d_o) return DLCO_ENOMEM;
-    // Three streams so that neither copy sits in front of the pooling GEMM: uploads run ahead on cs_in, the batch's
-    // kernels on the context stream, downloads behind on cs_out; device staging and the output block are double
-    // buffered.  Per slot s: ev_in = upload done, ev_k = kernels of the batch done, ev_out = download done.
-    cudaStream_t cs_in = nullptr, cs_out = nullptr;
-    cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_k[2] = {nullptr, nullptr}, ev_out[2] = {nullptr, nullptr};
-    cudaError_t e = cudaStreamCreateWithFlags(&cs_in, cudaStreamNonBlocking);
-    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&cs_out, cudaStreamNonBlocking);
-    for (int s = 0; s < 2 && e == cudaSuccess; s++) {
-        e = cudaEventCreateWithFlags(&ev_in[s], cudaEventDisableTiming);
-        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ev_k[s], cudaEventDisableTiming);
-        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ev_out[s], cudaEventDisableTiming);
-    }
+    cudaStream_t cs_in = ctx->pipe_in, cs_out = ctx->pipe_out;
+    cudaEvent_t *ev_in = ctx->pipe_ev_in, *ev_k = ctx->pipe_ev_k, *ev_out = ctx->pipe_ev_out;
     int rc = DLCO_OK;
-    if (e != cudaSuccess) { dlco_set_error("dlco_fulldist_build_host: %s", cudaGetErrorString(e)); rc = DLCO_ECUDA; }
     // the copy streams start after whatever the caller queued on the context stream
-    if (rc == DLCO_OK) {
-        e = cudaEventRecord(ev_k[0], ctx->stream);
-        if (e == cudaSuccess) e = cudaStreamWaitEvent(cs_in, ev_k[0], 0);
-        if (e == cudaSuccess) e = cudaStreamWaitEvent(cs_out, ev_k[0], 0);
-        if (e != cudaSuccess) { dlco_set_error("dlco_fulldist_build_host: %s", cudaGetErrorString(e)); rc = DLCO_ECUDA; }
-    }
-    int64_t bi = 0;
-    for (int64_t p = lo; p < hi && rc == DLCO_OK; p += nb, bi++) {
+    cudaError_t e = cudaEventRecord(ctx->pipe_ev_join, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamWaitEvent(cs_in, ctx->pipe_ev_join, 0);
+    if (e == cudaSuccess) e = cudaStreamWaitEvent(cs_out, ctx->pipe_ev_join, 0);
+    if (e != cudaSuccess) { dlco_set_error("dlco_fulldist_build_host: %s", cudaGetErrorString(e)); return DLCO_ECUDA; }
+    for (int64_t p = lo; p < hi && rc == DLCO_OK; p += nb) {
+        const int64_t bi = ctx->pipe_bi;
         const int s = (int)(bi & 1);
         const int n = (int)((hi - p) < nb ? (hi - p) : nb);
         if (bi >= 2) cudaEventSynchronize(ev_in[s]);     // the slot's previous upload has left the host staging buffer
@@ -186,31 +186,48 @@ extern "C" int dlco_fulldist_build_host(dlco_ctx *ctx, const dlco_bank *bank, co
         if (e == cudaSuccess) e = cudaStreamWaitEvent(ctx->stream, ev_in[s], 0);
         if (e == cudaSuccess && bi >= 2) e = cudaStreamWaitEvent(ctx->stream, ev_out[s], 0);   // its output block has been downloaded
         if (e != cudaSuccess) { dlco_set_error("upload failed: %s", cudaGetErrorString(e)); rc = DLCO_ECUDA; break; }
+        ctx->pipe_bi = bi + 1;                           // the slot's events are (re)recorded from here on
         rc = fulldist_batch(ctx, bank, dp, (const int32_t *)(dp + pbytes), n, nAngleBins, sigma, bNorm, dout, rings);
-        if (rc != DLCO_OK) break;
         e = cudaEventRecord(ev_k[s], ctx->stream);
         if (e == cudaSuccess) e = cudaStreamWaitEvent(cs_out, ev_k[s], 0);
-        if (e == cudaSuccess)
+        if (e == cudaSuccess && rc == DLCO_OK)
             e = cudaMemcpy2DAsync(h_out + (p - lo) * ld_out, (size_t)ld_out * sizeof(float), dout,
                                   (size_t)rings * sizeof(float), (size_t)rings * sizeof(float), n,
                                   cudaMemcpyDeviceToHost, cs_out);
         if (e == cudaSuccess) e = cudaEventRecord(ev_out[s], cs_out);
-        if (e != cudaSuccess) { dlco_set_error("download failed: %s", cudaGetErrorString(e)); rc = DLCO_ECUDA; }
+        if (rc == DLCO_OK && e != cudaSuccess) { dlco_set_error("download failed: %s", cudaGetErrorString(e)); rc = DLCO_ECUDA; }
     }
-    // drain all three streams whatever happened: the staging buffers belong to the context
-    cudaError_t e1 = cs_in ? cudaStreamSynchronize(cs_in) : cudaSuccess;
-    cudaError_t e2 = cudaStreamSynchronize(ctx->stream);
-    cudaError_t e3 = cs_out ? cudaStreamSynchronize(cs_out) : cudaSuccess;
-    e = e1 != cudaSuccess ? e1 : (e2 != cudaSuccess ? e2 : e3);
-    if (rc == DLCO_OK && e != cudaSuccess) { dlco_set_error("fulldist_build_host: %s", cudaGetErrorString(e)); rc = DLCO_ECUDA; }
-    for (int s = 0; s < 2; s++) {
-        if (ev_in[s]) cudaEventDestroy(ev_in[s]);
-        if (ev_k[s]) cudaEventDestroy(ev_k[s]);
-        if (ev_out[s]) cudaEventDestroy(ev_out[s]);
+    if (rc != DLCO_OK) {       // leave nothing in flight behind a failed call
+        cudaStreamSynchronize(cs_in);
+        cudaStreamSynchronize(ctx->stream);
+        cudaStreamSynchronize(cs_out);
     }
-    if (cs_in) cudaStreamDestroy(cs_in);
-    if (cs_out) cudaStreamDestroy(cs_out);
+    if (h_ticket) *h_ticket = ctx->pipe_bi - 1;
     return rc;
+}
+
+// blocks until the rows of the async call that returned `ticket` are in host memory (later calls may still be in
+// flight): the ticket is the call's last batch, the download stream is in order, and a slot's "download done" event
+// only ever moves forward
+extern "C" int dlco_fulldist_host_wait(dlco_ctx *ctx, int64_t ticket)
+{
+    DLCO_REQUIRE(ctx, "dlco_fulldist_host_wait: ctx is NULL");
+    if (ticket < 0 || !ctx->pipe_ready) return DLCO_OK;          // an empty range: nothing was queued
+    DLCO_REQUIRE(ticket < ctx->pipe_bi, "dlco_fulldist_host_wait: ticket %lld was never issued", (long long)ticket);
+    DLCO_CUDA(cudaEventSynchronize(ctx->pipe_ev_out[ticket & 1]));
+    return DLCO_OK;
+}
+
+// the same, complete on return (the call comp-fulldists made per block before the pipeline crossed call boundaries)
+extern "C" int dlco_fulldist_build_host(dlco_ctx *ctx, const dlco_bank *bank, const uint8_t *h_patches,
+                                        int64_t nPatches, const int32_t *h_indices, int64_t lo,
+                                        int64_t hi, int nAngleBins, float sigma, int bNorm,
+                                        float *h_out, int64_t ld_out)
+{
+    int rc = dlco_fulldist_build_host_async(ctx, bank, h_patches, nPatches, h_indices, lo, hi, nAngleBins, sigma, bNorm,
+                                            h_out, ld_out, nullptr);
+    if (rc != DLCO_OK) return rc;
+    return dlco_sync(ctx);
 }
 
 extern "C" int dlco_uprjdist_build(dlco_ctx *ctx, const dlco_bank *bank, const uint8_t *d_patches,

@@ -152,6 +152,31 @@ def test_fulldist_host_entry_point(gpu_ctx, synth, small_bank):
     assert np.array_equal(dev, host)
 
 
+def test_fulldist_host_async_blocks_in_flight(gpu_ctx, synth, small_bank):
+    """dlco_fulldist_build_host_async + dlco_fulldist_host_wait: several blocks queued back to back (the staging
+    slots keep alternating across calls), waited for one by one, bit-identical to the device entry point."""
+    patches, _, idx0 = synth
+    filt, _ = small_bank
+    rng = np.random.default_rng(5)
+    n = 1100
+    idx = np.zeros((n, 4), np.int32)
+    idx[:, 0] = rng.integers(0, patches.shape[0], n)
+    idx[:, 2] = rng.integers(0, patches.shape[0], n)
+    bank = gpu_ctx.bank(filt)
+    want = gpu_ctx.fulldist_build(bank, dev_t(gpu_ctx, patches), dev_t(gpu_ctx, idx)).cpu().numpy()
+    h_p, h_i = torch.from_numpy(patches).pin_memory(), torch.from_numpy(idx).pin_memory()
+    out = torch.zeros((n, filt.shape[0] // 8), dtype=torch.float32).pin_memory()
+    cuts = [0, 300, 301, 301, 900, n]                        # ragged blocks, an empty one in between
+    tickets = [gpu_ctx.fulldist_build_host_async(bank, h_p, h_i, lo, hi, out[lo:hi]) for lo, hi in zip(cuts[:-1], cuts[1:])]
+    assert tickets[2] == -1 or cuts[2] != cuts[3]            # the empty range queues nothing
+    for (lo, hi), t in zip(zip(cuts[:-1], cuts[1:]), tickets):
+        gpu_ctx.fulldist_host_wait(t)
+        assert np.array_equal(out[lo:hi].numpy(), want[lo:hi])           # complete although later blocks are in flight
+    gpu_ctx.sync()
+    bank.close()
+    assert np.array_equal(out.numpy(), want)
+
+
 def test_fulldist_full_bank_three_batches(gpu_ctx, synth, full_bank):
     """The gen-poolregion bank at full size and more pairs than two batches: exercises the block-sparse bank order
     (8 x 8 pixel-block K chunks, clustered rows), the cached work schedule of the pooling kernel and the

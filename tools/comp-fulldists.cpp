@@ -130,69 +130,89 @@ int main(int argc, char **argv)
         printf("Start Compute L2 distances.\n");
         const double t0 = now_sec();
 
-        // ---- the hot loop: blocks of pairs, double-buffered per GPU, written in order -----------
+        // ---- the hot loop: blocks of pairs, two in flight per GPU, written in order -----------------
+        // Each GPU's worker queues block k with the non-draining entry point and only then waits for block k-1, so the
+        // device never idles between blocks while the writer thread deflates and writes finished blocks in order.
         const int64_t block_pairs = 8192;
         const int64_t n_blocks = (n_pairs + block_pairs - 1) / block_pairs;
-        const int slots = 2 * n_gpus;
+        const int per_gpu = 3;                                   // computing, queued behind it, being written
+        const int slots = per_gpu * n_gpus;
         std::vector<Block> blk((size_t)slots);
         for (auto &b : blk)
             if (cudaMallocHost((void **)&b.host, (size_t)block_pairs * rings * sizeof(float)) != cudaSuccess)
                 throw AbiError("cudaMallocHost failed for the output staging buffers");
         std::atomic<bool> failed(false);
+        auto fail_all = [&](const std::string &why) {          // wake everybody; every wait predicate looks at `failed`
+            failed = true;
+            for (auto &x : blk) {
+                std::lock_guard<std::mutex> lk(x.m);
+                if (x.error.empty()) x.error = why;
+                x.cv.notify_all();
+            }
+        };
         std::vector<std::thread> workers;
         for (int g = 0; g < n_gpus; g++)
             workers.emplace_back([&, g]() {
+                int64_t prev_ticket = -1;
+                Block *prev = nullptr;
+                auto finish_prev = [&]() -> bool {
+                    if (!prev) return true;
+                    const int rc = dlco_fulldist_host_wait(ctxs[g]->h, prev_ticket);
+                    if (rc != DLCO_OK) { fail_all(dlco_last_error()); return false; }
+                    std::lock_guard<std::mutex> lk(prev->m);
+                    prev->ready = true;
+                    prev->cv.notify_all();
+                    prev = nullptr;
+                    return true;
+                };
                 for (int64_t b = g, k = 0; b < n_blocks && !failed; b += n_gpus, k++) {
-                    Block &s = blk[(size_t)(g * 2 + (k & 1))];
+                    Block &s = blk[(size_t)(g * per_gpu + (k % per_gpu))];
                     {
                         std::unique_lock<std::mutex> lk(s.m);
                         s.cv.wait(lk, [&] { return s.free_ || failed.load(); });
-                        if (failed) return;
+                        if (failed) break;
                         s.free_ = false;
                     }
                     s.lo = b * block_pairs;
                     s.hi = std::min(n_pairs, s.lo + block_pairs);
-                    const int rc = dlco_fulldist_build_host(ctxs[g]->h, banks[g], patches.data(), n_patches, indices.data(),
-                                                            s.lo, s.hi, n_bins, sigma, b_norm, s.host, rings);
-                    std::lock_guard<std::mutex> lk(s.m);
-                    if (rc != DLCO_OK) { s.error = dlco_last_error(); failed = true; }
-                    s.ready = true;
-                    s.cv.notify_all();
+                    int64_t ticket = -1;
+                    const int rc = dlco_fulldist_build_host_async(ctxs[g]->h, banks[g], patches.data(), n_patches, indices.data(),
+                                                                  s.lo, s.hi, n_bins, sigma, b_norm, s.host, rings, &ticket);
+                    if (rc != DLCO_OK) { fail_all(dlco_last_error()); break; }
+                    if (!finish_prev()) break;
+                    prev = &s;
+                    prev_ticket = ticket;
                 }
+                if (!failed) finish_prev();
+                dlco_sync(ctxs[g]->h);
             });
         std::string error;
         for (int64_t b = 0; b < n_blocks && error.empty(); b++) {
             const int g = (int)(b % n_gpus);
-            Block &s = blk[(size_t)(g * 2 + ((b / n_gpus) & 1))];
+            Block &s = blk[(size_t)(g * per_gpu + ((b / n_gpus) % per_gpu))];
             {
                 std::unique_lock<std::mutex> lk(s.m);
-                s.cv.wait(lk, [&] { return s.ready; });
+                s.cv.wait(lk, [&] { return s.ready || failed.load(); });
+                if (!s.ready) { error = s.error.empty() ? "a worker failed" : s.error; break; }
                 s.ready = false;
-                error = s.error;
             }
-            if (error.empty()) {
-                const size_t cnt = (size_t)(s.hi - s.lo) * rings;
-                bool bad = false;                                   // checkRange (:362-366)
-                for (size_t i = 0; i < cnt && !bad; i++) bad = !std::isfinite(s.host[i]);
-                if (bad) {
-                    printf("\nDist contains NaN\n");
-                    failed = true;
-                    for (auto &x : blk) x.cv.notify_all();
-                    for (auto &w : workers) w.join();
-                    return -1;
-                }
-                out.append_rows(hd, s.host, (uint64_t)(s.hi - s.lo), io_threads);
-                printf("\rStep: %lld / %lld", (long long)s.hi, (long long)n_pairs);
-                fflush(stdout);
+            const size_t cnt = (size_t)(s.hi - s.lo) * rings;
+            bool bad = false;                                   // checkRange (:362-366)
+            for (size_t i = 0; i < cnt && !bad; i++) bad = !std::isfinite(s.host[i]);
+            if (bad) {
+                printf("\nDist contains NaN\n");
+                fail_all("NaN");
+                for (auto &w : workers) w.join();
+                return -1;
             }
+            out.append_rows(hd, s.host, (uint64_t)(s.hi - s.lo), io_threads);
+            printf("\rStep: %lld / %lld", (long long)s.hi, (long long)n_pairs);
+            fflush(stdout);
             std::lock_guard<std::mutex> lk(s.m);
             s.free_ = true;
             s.cv.notify_all();
         }
-        if (!error.empty()) {
-            failed = true;
-            for (auto &x : blk) { std::lock_guard<std::mutex> lk(x.m); x.cv.notify_all(); }
-        }
+        if (!error.empty()) fail_all(error);
         for (auto &w : workers) w.join();
         if (!error.empty()) throw AbiError("dlco_fulldist_build_host: " + error);
         const double t_compute = now_sec() - t0;
