@@ -168,7 +168,6 @@ def test_fulldist_host_async_blocks_in_flight(gpu_ctx, synth, small_bank):
     out = torch.zeros((n, filt.shape[0] // 8), dtype=torch.float32).pin_memory()
     cuts = [0, 300, 301, 301, 900, n]                        # ragged blocks, an empty one in between
     tickets = [gpu_ctx.fulldist_build_host_async(bank, h_p, h_i, lo, hi, out[lo:hi]) for lo, hi in zip(cuts[:-1], cuts[1:])]
-    assert tickets[2] == -1 or cuts[2] != cuts[3]            # the empty range queues nothing
     for (lo, hi), t in zip(zip(cuts[:-1], cuts[1:]), tickets):
         gpu_ctx.fulldist_host_wait(t)
         assert np.array_equal(out[lo:hi].numpy(), want[lo:hi])           # complete although later blocks are in flight

@@ -60,6 +60,20 @@ inline int deflate_level()
     const char *e = getenv("DLCO_GZIP");
     return e ? std::max(0, std::min(9, atoi(e))) : 1;
 }
+inline int dist_deflate_level()
+{
+    // "Distance" (f32 distances): deflate buys 10 % on such data (measured: 10.24 GB -> 9.09 GB at level 1, 9.06 GB at
+    // level 9) and costs 15 s per GB and 4 threads at ANY level -- 21 s of a 24 s comp-fulldists run on 500k pairs,
+    // against 2.8 s of compute (profiles/r02_tool_comp_fulldists.json).  Default: chunked, no filter.  DLCO_GZIP=n
+    // (1..9) restores the reference's filter pipeline.
+    const char *e = getenv("DLCO_GZIP");
+    return e ? std::max(0, std::min(9, atoi(e))) : 0;
+}
+inline void announce_storage(const char *tool, int level)
+{
+    fprintf(stderr, "[%s] Distance chunks: %s (DLCO_GZIP=%d); host threads: %d\n", tool,
+            level ? "deflate" : "no filter", level, host_threads());
+}
 
 // DLCO_MAX_ITERS caps the iteration count of pr-learn / pj-learn / pj-sweep: the workspace
 // scripts hard-code -iters; the cap ends a run early at a whole number of steps, logged lines unchanged.

@@ -126,7 +126,8 @@ int main(int argc, char **argv)
         for (int g = 0; g < n_gpus; g++) check(dlco_bank_create(ctxs[g]->h, filters.data(), n_filters, &banks[g]), "dlco_bank_create");
         std::vector<float>().swap(filters);
 
-        const int hd = out.create_chunked("Distance", h5mini::F32, {(uint64_t)rings}, 128, deflate_level(), false);
+        const int hd = out.create_chunked("Distance", h5mini::F32, {(uint64_t)rings}, 128, dist_deflate_level(), false);
+        announce_storage("comp-fulldists", dist_deflate_level());
         printf("Start Compute L2 distances.\n");
         const double t0 = now_sec();
 

@@ -122,7 +122,8 @@ int main(int argc, char **argv)
         check(dlco_bank_create(ctx.h, sel.data(), n_sel, &bank), "dlco_bank_create");
         DevBuf<int32_t> d_idx(ctx, (size_t)n_pairs * 4);
         d_idx.upload(indices.data(), (size_t)n_pairs * 4);
-        const int hd = out.create_chunked("Distance", h5mini::F32, {(uint64_t)D}, 128, deflate_level(), false);
+        const int hd = out.create_chunked("Distance", h5mini::F32, {(uint64_t)D}, 128, dist_deflate_level(), false);
+        announce_storage("comp-uprjdists", dist_deflate_level());
 
         printf("Start Compute L1 distances.\n");
         const double t0 = now_sec();
