@@ -117,6 +117,7 @@ extern "C" int dlco_shutdown(dlco_ctx *ctx)
     if (!ctx) return DLCO_OK;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
+    dlco_pj_graph_release(ctx);
     if (ctx->side_ready) {
         cudaStreamSynchronize(ctx->side_stream);
         for (int i = 0; i < 6; i++) cudaEventDestroy(ctx->side_ev[i]);

@@ -44,6 +44,7 @@ struct dlco_ctx {
     int pipe_ready;
     int64_t pipe_bi;
     uint32_t attr_mask;   // which kernels had their dynamic-smem limit raised on THIS context's device
+    void *pj_graph;       // captured sign-route iteration (pj_learn.cu: PjGraph), released by dlco_pj_graph_release
     void *cusolver;       // cusolverDnHandle_t (lazy)
     void *cusolver_lib;   // dlopen handle
 };
@@ -70,6 +71,7 @@ void *dlco_scratch(dlco_ctx *ctx, int slot, size_t bytes);
 void *dlco_pinned(dlco_ctx *ctx, int slot, size_t bytes);
 int dlco_side_stream(dlco_ctx *ctx);
 int dlco_host_pipe(dlco_ctx *ctx);
+void dlco_pj_graph_release(dlco_ctx *ctx);
 void dlco_prof_begin(dlco_ctx *ctx, int which);
 void dlco_prof_end(dlco_ctx *ctx);
 

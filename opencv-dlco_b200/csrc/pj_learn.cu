@@ -618,10 +618,9 @@ extern "C" int dlco_pj_rda_grad_grid_dev(dlco_ctx *ctx, const float *d_dists, in
 
 // K_pj_update for configuration blockIdx.z: same arithmetic as k_pj_update, the per-configuration
 // scalar -sqrt(t+1)/gamma is formed in double and rounded once, as the host version does.
-__global__ void __launch_bounds__(256)
-k_pj_update_grid(int D, double t1, float a_avg, float beta, const float *__restrict__ mu,
-                 const float *__restrict__ gamma, const float *__restrict__ dLoss,
-                 float *__restrict__ dfavg, float *__restrict__ A)
+__device__ __forceinline__ void pj_update_body(int D, double t1, float a_avg, float beta, const float *__restrict__ mu,
+                                               const float *__restrict__ gamma, const float *__restrict__ dLoss,
+                                               float *__restrict__ dfavg, float *__restrict__ A)
 {
     const int j = blockIdx.x * 32 + (threadIdx.x & 31);
     const int i = blockIdx.y * 8 + (threadIdx.x >> 5);
@@ -641,6 +640,30 @@ k_pj_update_grid(int D, double t1, float a_avg, float beta, const float *__restr
     A[ij] = s;
     A[ji] = s;
 }
+
+__global__ void __launch_bounds__(256)
+k_pj_update_grid(int D, double t1, float a_avg, float beta, const float *__restrict__ mu,
+                 const float *__restrict__ gamma, const float *__restrict__ dLoss,
+                 float *__restrict__ dfavg, float *__restrict__ A)
+{
+    pj_update_body(D, t1, a_avg, beta, mu, gamma, dLoss, dfavg, A);
+}
+
+// the same with the iteration number read from device memory (the iteration replayed as a CUDA graph): the
+// host's scalars, formed the same way (IEEE double / float divisions)
+__global__ void __launch_bounds__(256)
+k_pj_update_grid_dev(int D, const unsigned long long *__restrict__ d_t, unsigned int b2, const float *__restrict__ mu,
+                     const float *__restrict__ gamma, const float *__restrict__ dLoss,
+                     float *__restrict__ dfavg, float *__restrict__ A)
+{
+    const unsigned long long t = *d_t;
+    const float a_avg = (float)((double)t / (double)(t + 1));
+    const unsigned int den = b2 * (unsigned int)(t + 1);
+    const float beta = 1.0f / (float)den;
+    pj_update_body(D, (double)t + 1.0, a_avg, beta, mu, gamma, dLoss, dfavg, A);
+}
+
+__global__ void k_set_u64(unsigned long long *p, unsigned long long v) { *p = v; }
 
 extern "C" int dlco_pj_rda_update_grid(dlco_ctx *ctx, int D, uint64_t t, int szBatch, int nCfg,
                                        const float *d_mu, const float *d_gamma, const float *d_dLoss,
@@ -866,6 +889,79 @@ extern "C" int dlco_pj_rda_step_grid(dlco_ctx *ctx, const float *d_dists, int64_
 // (pj_sign.cu) instead of an eigen-decomposition: margins are x^T A x, A is projected in place and
 // d_rank updated; d_W is NOT touched (dlco_pj_factor_grid rebuilds it when a caller needs W: the
 // validation / statistics / save points).  d_work >= nCfg * D * D floats.
+// the kernels of one sign-route iteration, queued on the context stream; d_t != NULL: the iteration number comes
+// from device memory (graph capture), else from `t`
+static int pj_step_sign_enqueue(dlco_ctx *ctx, const float *d_dists, int64_t ld, int D, const int32_t *d_idx_pos,
+                                int32_t nPosTrn, const int32_t *d_idx_neg, int32_t nNegTrn, int szBatch,
+                                uint64_t *d_rng_state, int nCfg, const float *d_mu, const float *d_gamma, uint64_t t,
+                                const unsigned long long *d_t, float *d_A, float *d_dfavg, int32_t *d_rank, float *d_work)
+{
+    float *dLoss = d_work;
+    int32_t *rows = (int32_t *)dlco_scratch(ctx, 25, (size_t)2 * szBatch * sizeof(int32_t));
+    if (!rows) return DLCO_ENOMEM;
+    int r = dlco_pj_sample_batch(ctx, d_idx_pos, nPosTrn, d_idx_neg, nNegTrn, szBatch, d_rng_state, rows, rows + szBatch);
+    if (r == DLCO_OK) r = pj_grad_core(ctx, d_dists, ld, D, rows, rows + szBatch, szBatch, nCfg, nullptr, 0, nullptr, d_rank, dLoss, d_A);
+    if (r != DLCO_OK) return r;
+    if (d_t) {
+        dim3 grid((D + 31) / 32, (D + 7) / 8, nCfg);
+        k_pj_update_grid_dev<<<grid, 256, 0, ctx->stream>>>(D, d_t, (unsigned int)szBatch * (unsigned int)szBatch, d_mu, d_gamma,
+                                                            dLoss, d_dfavg, d_A);
+        DLCO_CHECK_LAUNCH(ctx);
+    } else {
+        r = dlco_pj_rda_update_grid(ctx, D, t, szBatch, nCfg, d_mu, d_gamma, dLoss, d_dfavg, d_A);
+    }
+    if (r == DLCO_OK) r = dlco_pj_psd_sign(ctx, D, nCfg, d_A, d_rank, nullptr);
+    return r;
+}
+
+// One iteration is ~67 small launches (29 GEMMs of the sign iteration with their plane passes): launch-bound for
+// one or a few configurations.  The launch sequence depends on nothing but the arguments, so the second call with
+// the same arguments captures it into a CUDA graph (the iteration number moves to device memory) and every later
+// call replays it: one tiny launch that sets the iteration number + one cudaGraphLaunch.  DLCO_PJ_GRAPH=0 or
+// per-kernel profiling turn it off; any change of an argument (or of the context stream) re-captures.
+struct PjGraphKey {
+    const void *p[9];
+    int64_t ld;
+    int D, nPos, nNeg, szBatch, nCfg;
+    cudaStream_t stream;
+    uint32_t env;
+};
+struct PjGraph {
+    PjGraphKey key, pending;
+    cudaGraphExec_t exec;
+    unsigned long long *d_t;
+    int have_pending;
+    int64_t nodes;
+};
+static uint32_t pj_env_hash()
+{
+    uint32_t h = 2166136261u;
+    for (const char *name : {"DLCO_SIGN_FUSED", "DLCO_SIGN_PLANES", "DLCO_SYRK_PLANES", "DLCO_GEMM_FLUSH"}) {
+        const char *e = getenv(name);
+        for (const char *c = e ? e : "-"; *c; c++) h = (h ^ (uint8_t)*c) * 16777619u;
+        h = (h ^ 0xffu) * 16777619u;
+    }
+    return h;
+}
+static bool pj_graph_enabled()
+{
+    const char *e = getenv("DLCO_PJ_GRAPH");
+    return !(e && e[0] == '0');
+}
+void dlco_pj_graph_release(dlco_ctx *ctx)
+{
+    PjGraph *g = (PjGraph *)ctx->pj_graph;
+    if (!g) return;
+    if (g->exec) cudaGraphExecDestroy(g->exec);
+    if (g->d_t) cudaFree(g->d_t);
+    free(g);
+    ctx->pj_graph = nullptr;
+}
+
+// The same iteration with the prox's projection done by the tensor-core matrix-sign iteration
+// (pj_sign.cu) instead of an eigen-decomposition: margins are x^T A x, A is projected in place and
+// d_rank updated; d_W is NOT touched (dlco_pj_factor_grid rebuilds it when a caller needs W: the
+// validation / statistics / save points).  d_work >= nCfg * D * D floats.
 extern "C" int dlco_pj_rda_step_grid_sign(dlco_ctx *ctx, const float *d_dists, int64_t ld, int D,
                                           const int32_t *d_idx_pos, int32_t nPosTrn, const int32_t *d_idx_neg,
                                           int32_t nNegTrn, int szBatch, uint64_t *d_rng_state, int nCfg,
@@ -875,14 +971,64 @@ extern "C" int dlco_pj_rda_step_grid_sign(dlco_ctx *ctx, const float *d_dists, i
     DLCO_REQUIRE(ctx && d_dists && d_idx_pos && d_idx_neg && d_rng_state && d_mu && d_gamma && d_A && d_dfavg &&
                  d_rank && d_work, "dlco_pj_rda_step_grid_sign: NULL argument");
     DLCO_REQUIRE(D > 0 && szBatch > 0 && szBatch <= 4096 && nCfg > 0 && ld >= D, "dlco_pj_rda_step_grid_sign: bad shapes");
-    float *dLoss = d_work;
-    int32_t *rows = (int32_t *)dlco_scratch(ctx, 25, (size_t)2 * szBatch * sizeof(int32_t));
-    if (!rows) return DLCO_ENOMEM;
-    int r = dlco_pj_sample_batch(ctx, d_idx_pos, nPosTrn, d_idx_neg, nNegTrn, szBatch, d_rng_state, rows, rows + szBatch);
-    if (r == DLCO_OK) r = pj_grad_core(ctx, d_dists, ld, D, rows, rows + szBatch, szBatch, nCfg, nullptr, 0, nullptr, d_rank, dLoss, d_A);
-    if (r == DLCO_OK) r = dlco_pj_rda_update_grid(ctx, D, t, szBatch, nCfg, d_mu, d_gamma, dLoss, d_dfavg, d_A);
-    if (r == DLCO_OK) r = dlco_pj_psd_sign(ctx, D, nCfg, d_A, d_rank, nullptr);
-    return r;
+    if (!pj_graph_enabled() || ctx->profile_on)
+        return pj_step_sign_enqueue(ctx, d_dists, ld, D, d_idx_pos, nPosTrn, d_idx_neg, nNegTrn, szBatch, d_rng_state, nCfg,
+                                    d_mu, d_gamma, t, nullptr, d_A, d_dfavg, d_rank, d_work);
+    PjGraphKey key;
+    memset(&key, 0, sizeof(key));
+    const void *ptrs[9] = {d_dists, d_idx_pos, d_idx_neg, d_rng_state, d_mu, d_gamma, d_A, d_dfavg, d_rank};
+    memcpy(key.p, ptrs, sizeof(ptrs));
+    key.ld = ld; key.D = D; key.nPos = nPosTrn; key.nNeg = nNegTrn; key.szBatch = szBatch; key.nCfg = nCfg;
+    key.stream = nullptr; key.env = pj_env_hash() ^ (uint32_t)(uintptr_t)d_work;
+    PjGraph *g = (PjGraph *)ctx->pj_graph;
+    if (!g) {
+        g = (PjGraph *)calloc(1, sizeof(PjGraph));
+        if (!g) return DLCO_ENOMEM;
+        if (cudaMalloc(&g->d_t, 8) != cudaSuccess) { free(g); dlco_set_error("dlco_pj_rda_step_grid_sign: out of device memory"); return DLCO_ENOMEM; }
+        ctx->pj_graph = g;
+    }
+    if (g->exec && memcmp(&g->key, &key, sizeof(key)) != 0) {       // other arguments: start over
+        cudaGraphExecDestroy(g->exec);
+        g->exec = nullptr;
+        g->have_pending = 0;
+    }
+    if (!g->exec) {
+        if (!g->have_pending || memcmp(&g->pending, &key, sizeof(key)) != 0) {
+            // first call with these arguments: run it plainly (scratch buffers grow here, not under capture)
+            g->pending = key;
+            g->have_pending = 1;
+            return pj_step_sign_enqueue(ctx, d_dists, ld, D, d_idx_pos, nPosTrn, d_idx_neg, nNegTrn, szBatch, d_rng_state,
+                                        nCfg, d_mu, d_gamma, t, nullptr, d_A, d_dfavg, d_rank, d_work);
+        }
+        cudaGraph_t graph = nullptr;
+        const int64_t l0 = ctx->launches;
+        // captured on the context's own stream (the caller's may be the legacy default stream, which cannot
+        // capture); a graph is not tied to the stream it was captured on
+        cudaStream_t user_stream = ctx->stream;
+        DLCO_CUDA(cudaStreamBeginCapture(ctx->own_stream, cudaStreamCaptureModeThreadLocal));
+        ctx->stream = ctx->own_stream;
+        int r = pj_step_sign_enqueue(ctx, d_dists, ld, D, d_idx_pos, nPosTrn, d_idx_neg, nNegTrn, szBatch, d_rng_state, nCfg,
+                                     d_mu, d_gamma, t, g->d_t, d_A, d_dfavg, d_rank, d_work);
+        ctx->stream = user_stream;
+        cudaError_t e = cudaStreamEndCapture(ctx->own_stream, &graph);
+        g->nodes = ctx->launches - l0;
+        ctx->launches = l0;
+        if (r != DLCO_OK || e != cudaSuccess || !graph) {
+            if (graph) cudaGraphDestroy(graph);
+            if (r == DLCO_OK) { dlco_set_error("dlco_pj_rda_step_grid_sign: graph capture failed: %s", cudaGetErrorString(e)); r = DLCO_ECUDA; }
+            g->have_pending = 0;
+            return r;
+        }
+        e = cudaGraphInstantiate(&g->exec, graph, 0);
+        cudaGraphDestroy(graph);
+        if (e != cudaSuccess) { g->exec = nullptr; dlco_set_error("cudaGraphInstantiate: %s", cudaGetErrorString(e)); return DLCO_ECUDA; }
+        g->key = key;
+    }
+    k_set_u64<<<1, 1, 0, ctx->stream>>>(g->d_t, (unsigned long long)t);
+    DLCO_CHECK_LAUNCH(ctx);
+    DLCO_CUDA(cudaGraphLaunch(g->exec, ctx->stream));
+    ctx->launches += g->nodes;
+    return DLCO_OK;
 }
 
 // rank of an (approximately) projected matrix from its eigenvalues: the eigenvalues the projection zeroed come
