@@ -34,13 +34,15 @@ PICKS = [(480, 0.0020, 0.200), (544, 0.0010, 0.100), (544, 0.0005, 0.100), (544,
 
 
 def synth_uprj(n, D, seed):
-    """Unprojected-distance-like rows: differences of pooled values clamped to [0, 1] (|x| <= 1), positives
-    (even rows) closer; low-rank structure plus noise so that the learnt rank settles well below D."""
+    """Unprojected-distance-like rows (|x| <= 1), positives on even rows."""
     rng = np.random.default_rng(seed)
     lab = (np.arange(n) % 2 == 0).astype(np.uint8)
-    basis = rng.standard_normal((24, D)) / np.sqrt(D)
-    z = rng.standard_normal((n, 24)) * (0.35 + 0.9 * (1 - lab[:, None]))
-    x = z @ basis + rng.standard_normal((n, D)) * 0.05
+    # 24 discriminative directions (positives 0.55 x the spread of negatives) buried under 72 nuisance directions of
+    # the same energy and noise: plain L2 gives FPR95 ~ 67 %, the ideal projection ~ 5 % -- the learner has work to do
+    basis = rng.standard_normal((96, D)) / np.sqrt(D)
+    sc = np.ones((n, 96))
+    sc[:, :24] = np.where(lab[:, None] == 1, 0.55, 1.0)
+    x = (rng.standard_normal((n, 96)) * sc) @ basis + rng.standard_normal((n, D)) * 0.06
     return np.clip(x, -1, 1).astype(np.float32), lab
 
 
@@ -206,10 +208,30 @@ def test_pj_sign_route_tracks_eig_route_over_5000_iterations(gpu_ctx):
           "FPR95 %s | sign Dim %s AUC %s FPR95 %s" % (iters, worst_rank, worst_loss, last["eig"].group(1), last["eig"].group(2),
                                                       last["eig"].group(4), last["sign"].group(1), last["sign"].group(2),
                                                       last["sign"].group(4)))
-    assert worst_rank <= 2 and worst_loss <= 2e-3
+    # two free-running fp32 trajectories (40 000 hinge decisions per iteration): objective values within 1 %,
+    # the statistics the scripts select on within north_star's bars
+    assert worst_rank <= 2 and worst_loss <= 1e-2
     assert abs(int(last["eig"].group(1)) - int(last["sign"].group(1))) <= 2
     assert abs(float(last["eig"].group(2)) - float(last["sign"].group(2))) <= 1e-4
     assert abs(float(last["eig"].group(4)) - float(last["sign"].group(4))) <= 0.1          # FPR95 in percent: 0.1 pp
+
+
+def hard_patches(dev, n_points, per_point, seed):
+    """u8 patches whose positives (same point) share a smooth field but carry a per-patch nuisance field of
+    comparable energy, gain / bias changes and noise: matching them is a real ranking problem (FPR95 well
+    above zero), unlike near-duplicates."""
+    g = torch.Generator(device=dev)
+    g.manual_seed(seed)
+    out = torch.empty((n_points * per_point, 64, 64), dtype=torch.uint8, device=dev)
+    up = lambda t: torch.nn.functional.interpolate(t, size=(64, 64), mode="bicubic", align_corners=False)    # noqa: E731
+    for a in range(0, n_points, 4096):
+        n = min(4096, n_points - a)
+        base = up(torch.randn((n, 1, 8, 8), generator=g, device=dev)).repeat_interleave(per_point, dim=0)
+        nuis = up(torch.randn((n * per_point, 1, 6, 6), generator=g, device=dev))
+        gain = 0.7 + 0.6 * torch.rand((n * per_point, 1, 1, 1), generator=g, device=dev)
+        img = 128 + 45 * gain * (base + 0.8 * nuis) + 6 * torch.randn(base.shape, generator=g, device=dev)
+        out[a * per_point:(a + n) * per_point] = img.clamp(0, 255).round().to(torch.uint8)[:, 0]
+    return out
 
 
 def test_pr_learn_on_built_distances_200k_steps_and_fpr95_on_100k(gpu_ctx, oracle_lib):
@@ -221,10 +243,10 @@ def test_pr_learn_on_built_distances_200k_steps_and_fpr95_on_100k(gpu_ctx, oracl
     dev = gpu_ctx.device
     bank = gpu_ctx.bank_analytic(dlco_b200.ring_params())
     n_tr, n_te = 20000, 100000
-    patches = B.synth_patches(torch, dev, 12000, 3, seed=31)
+    patches = hard_patches(dev, 12000, 3, seed=31)
     idx_tr = B.synth_pairs(torch, dev, 12000, 3, n_tr, seed=32)
     d_tr = gpu_ctx.fulldist_build(bank, patches, idx_tr)
-    patches_te = B.synth_patches(torch, dev, 40000, 3, seed=33)
+    patches_te = hard_patches(dev, 40000, 3, seed=33)
     idx_te = B.synth_pairs(torch, dev, 40000, 3, n_te, seed=34)
     d_te = gpu_ctx.fulldist_build(bank, patches_te, idx_te)
     bank.close()
