@@ -936,7 +936,7 @@ struct PjGraph {
 static uint32_t pj_env_hash()
 {
     uint32_t h = 2166136261u;
-    for (const char *name : {"DLCO_SIGN_FUSED", "DLCO_SIGN_PLANES", "DLCO_SYRK_PLANES", "DLCO_GEMM_FLUSH"}) {
+    for (const char *name : {"DLCO_SIGN_FUSED", "DLCO_SIGN_PLANES", "DLCO_SYRK_PLANES", "DLCO_GEMM_FLUSH", "DLCO_SIGN_LO"}) {
         const char *e = getenv(name);
         for (const char *c = e ? e : "-"; *c; c++) h = (h ^ (uint8_t)*c) * 16777619u;
         h = (h ^ 0xffu) * 16777619u;

@@ -21,20 +21,58 @@
 
 namespace {
 
-constexpr int SIGN_STEPS = 9;
-// tools/sign_poly.py 1e-4  (a, b, c) per step
-__constant__ float c_sign_coef[SIGN_STEPS + 1][3] = {
-    {8.509885880f, -25.264305658f, 18.753568789f},
-    {4.228659615f, -3.108344126f, 0.571498694f},
-    {4.205812483f, -3.092890486f, 0.569812591f},
-    {4.114157757f, -3.030669974f, 0.563027579f},
-    {3.782556611f, -2.802261125f, 0.538186614f},
-    {2.943282063f, -2.192549912f, 0.472857879f},
-    {2.077505958f, -1.466020591f, 0.400932419f},
-    {1.891149032f, -1.279511400f, 0.388326974f},
-    {1.875000000f, -1.250000000f, 0.375000000f},
-    {1.5f, -0.5f, 0.f},       // Newton-Schulz cubic: the last step uses this one (2 GEMMs; 9e-4 -> 1e-6)
+// Two designs of the minimax sequence (tools/sign_poly.py, (a, b, c) per quintic step), both closed by one
+// Newton-Schulz cubic (the last row of a table):
+//   accurate (default): start interval [1e-5, 1], 10 quintics -- eigenvalues with |l| >= 1e-5 ||A||_F reach +-1 to 1e-6
+//   fast (DLCO_SIGN_LO=1e-4): start interval [1e-4, 1], 8 quintics (6 GEMMs fewer of 33)
+// An eigenvalue below the start interval contributes at most |l| / 2 of error to A+: the accurate design keeps the
+// projected A within ~1e-5 of the eigen-decomposition route per iteration (the fast one 9e-5, which on weakly
+// regularised configurations flips enough near-tie hinge decisions to move a 500-step run by 2e-3).
+constexpr int SIGN_MAX_STEPS = 11;            // quintics + the cubic polish
+constexpr int SIGN_CUBIC = SIGN_MAX_STEPS;    // row of the Newton-Schulz cubic in each table
+__constant__ float c_sign_coef[2][SIGN_MAX_STEPS + 1][3] = {
+    {   // tools/sign_poly.py 1e-5
+        {8.513860688f, -25.280005851f, 18.766060024f},
+        {4.235238769f, -3.112790494f, 0.571983984f},
+        {4.232931323f, -3.111231250f, 0.571813806f},
+        {4.223381004f, -3.104775470f, 0.571109226f},
+        {4.184294522f, -3.078315990f, 0.568222867f},
+        {4.031279114f, -2.974083769f, 0.556862602f},
+        {3.526038466f, -2.621450564f, 0.518625856f},
+        {2.547438779f, -1.879771375f, 0.440507919f},
+        {1.944437468f, -1.333945503f, 0.390465189f},
+        {1.889027073f, -1.277857301f, 0.388825486f},
+        {1.875000000f, -1.250000000f, 0.375000000f},      // (spare row: the 15/8, -10/8, 3/8 Newton-Schulz quintic)
+        {1.5f, -0.5f, 0.f},                                 // Newton-Schulz cubic: the last step (2 GEMMs; 2e-3 -> 1e-6)
+    },
+    {   // tools/sign_poly.py 1e-4
+        {8.509885880f, -25.264305658f, 18.753568789f},
+        {4.228659615f, -3.108344126f, 0.571498694f},
+        {4.205812483f, -3.092890486f, 0.569812591f},
+        {4.114157757f, -3.030669974f, 0.563027579f},
+        {3.782556611f, -2.802261125f, 0.538186614f},
+        {2.943282063f, -2.192549912f, 0.472857879f},
+        {2.077505958f, -1.466020591f, 0.400932419f},
+        {1.891149032f, -1.279511400f, 0.388326974f},
+        {1.875000000f, -1.250000000f, 0.375000000f},
+        {0.f, 0.f, 0.f},
+        {0.f, 0.f, 0.f},
+        {1.5f, -0.5f, 0.f},
+    },
 };
+// host copies (the fused-epilogue path passes the coefficients as kernel arguments)
+static const float h_sign_coef[2][SIGN_MAX_STEPS][3] = {
+    {{8.513860688f, -25.280005851f, 18.766060024f}, {4.235238769f, -3.112790494f, 0.571983984f},
+     {4.232931323f, -3.111231250f, 0.571813806f},   {4.223381004f, -3.104775470f, 0.571109226f},
+     {4.184294522f, -3.078315990f, 0.568222867f},   {4.031279114f, -2.974083769f, 0.556862602f},
+     {3.526038466f, -2.621450564f, 0.518625856f},   {2.547438779f, -1.879771375f, 0.440507919f},
+     {1.944437468f, -1.333945503f, 0.390465189f},   {1.889027073f, -1.277857301f, 0.388825486f},
+     {1.875000000f, -1.250000000f, 0.375000000f}},
+    {{8.509885880f, -25.264305658f, 18.753568789f}, {4.228659615f, -3.108344126f, 0.571498694f},
+     {4.205812483f, -3.092890486f, 0.569812591f},   {4.114157757f, -3.030669974f, 0.563027579f},
+     {3.782556611f, -2.802261125f, 0.538186614f},   {2.943282063f, -2.192549912f, 0.472857879f},
+     {2.077505958f, -1.466020591f, 0.400932419f},   {1.891149032f, -1.279511400f, 0.388326974f},
+     {1.875000000f, -1.250000000f, 0.375000000f},   {0.f, 0.f, 0.f}, {0.f, 0.f, 0.f}}};
 
 constexpr int NORM_BLOCKS = 32;
 
@@ -125,7 +163,10 @@ k_sign_prep(int D, int rows_pad, int k_pad, const float *__restrict__ in0, const
     float inv_alpha = 0.f, alpha = 0.f, ca = 0.f, cb = 0.f, cc = 0.f;
     if (MODE == PREP_INIT) inv_alpha = sign_inv_alpha(partial, g);
     if (MODE == PREP_FINAL) alpha = sign_alpha(partial, g);
-    if (MODE == PREP_POLY) { ca = c_sign_coef[step][0]; cb = c_sign_coef[step][1]; cc = c_sign_coef[step][2]; }
+    if (MODE == PREP_POLY) {
+        const float *co = &c_sign_coef[0][0][0] + 3 * step;       // step = design * (SIGN_MAX_STEPS + 1) + row
+        ca = co[0]; cb = co[1]; cc = co[2];
+    }
     // output: thread = (row r, group of 4 consecutive columns): 16-byte fp32 stores, 8-byte plane stores
     const int r = threadIdx.x >> 3, c4 = (threadIdx.x & 7) * 4;
     const int i = i0 + r;
@@ -258,12 +299,12 @@ int dlco_pj_psd_sign(dlco_ctx *ctx, int D, int nCfg, float *d_A, int32_t *d_rank
     k_sign_norm<<<dim3(NORM_BLOCKS, nCfg), 256, 0, ctx->stream>>>(d_A, dd, partial);
     DLCO_CHECK_LAUNCH(ctx);
     r = sign_prep<PREP_INIT>(ctx, f16, D, nCfg, rows_pad, k_pad, d_A, nullptr, partial, 0, 0, sx, nullptr, p1h, p1l);   // X lives in its planes
-    static const float h_coef[SIGN_STEPS][3] = {
-        {8.509885880f, -25.264305658f, 18.753568789f}, {4.228659615f, -3.108344126f, 0.571498694f},
-        {4.205812483f, -3.092890486f, 0.569812591f},   {4.114157757f, -3.030669974f, 0.563027579f},
-        {3.782556611f, -2.802261125f, 0.538186614f},   {2.943282063f, -2.192549912f, 0.472857879f},
-        {2.077505958f, -1.466020591f, 0.400932419f},   {1.891149032f, -1.279511400f, 0.388326974f},
-        {1.875000000f, -1.250000000f, 0.375000000f}};      // = c_sign_coef
+    // design 0: [1e-5, 1], 10 quintics + cubic; design 1 (DLCO_SIGN_LO=1e-4): [1e-4, 1], 8 quintics + cubic
+    const char *lo_env = getenv("DLCO_SIGN_LO");
+    const int design = (lo_env && strcmp(lo_env, "1e-4") == 0) ? 1 : 0;
+    const int SIGN_STEPS = design ? 9 : 11;                            // quintic steps + the closing cubic
+    const int row0 = design * (SIGN_MAX_STEPS + 1);
+    const float (*h_coef)[3] = h_sign_coef[design];
     const char *fe = getenv("DLCO_SIGN_FUSED");
     // DLCO_SIGN_FUSED=1: Y and Z planes written by the GEMM epilogues (direct + mirrored) instead of prep passes.
     // Bitwise the same result; measured equal at 45 configurations and slower at one: opt-in.
@@ -277,7 +318,7 @@ int dlco_pj_psd_sign(dlco_ctx *ctx, int D, int nCfg, float *d_A, int32_t *d_rank
         const float inv = 1.0f / (sx * sx);
         if (k == SIGN_STEPS - 1) {                      // cubic polish: Z = 1.5 I - 0.5 Y needs no second product
             r = gemm(p1h, p1l, p1h, p1l, sx, sx, Y);
-            if (r == DLCO_OK) r = sign_prep<PREP_POLY>(ctx, f16, D, nCfg, rows_pad, k_pad, Y, Y, partial, SIGN_STEPS, 1, sz, nullptr, p3h, p3l);
+            if (r == DLCO_OK) r = sign_prep<PREP_POLY>(ctx, f16, D, nCfg, rows_pad, k_pad, Y, Y, partial, row0 + SIGN_CUBIC, 1, sz, nullptr, p3h, p3l);
             if (r == DLCO_OK) r = gemm(p1h, p1l, p3h, p3l, sx, sz, T);
             if (r == DLCO_OK) r = sign_prep<PREP_SYM>(ctx, f16, D, nCfg, rows_pad, k_pad, T, nullptr, partial, k, 1, sx, X, p1h, p1l);
             break;
@@ -298,7 +339,7 @@ int dlco_pj_psd_sign(dlco_ctx *ctx, int D, int nCfg, float *d_A, int32_t *d_rank
         r = gemm(p1h, p1l, p1h, p1l, sx, sx, Y);                       // Y = X X^T (= X^2: X is kept symmetric)
         if (r == DLCO_OK && !last) r = sign_prep<PREP_COPY>(ctx, f16, D, nCfg, rows_pad, k_pad, Y, nullptr, partial, k, 1, sx, nullptr, p2h, p2l);
         if (r == DLCO_OK && !last) r = gemm(p2h, p2l, p2h, p2l, sx, sx, T);     // T = Y Y^T = X^4
-        if (r == DLCO_OK) r = sign_prep<PREP_POLY>(ctx, f16, D, nCfg, rows_pad, k_pad, Y, last ? Y : T, partial, last ? SIGN_STEPS : k, 1, sz, nullptr, p2h, p2l);
+        if (r == DLCO_OK) r = sign_prep<PREP_POLY>(ctx, f16, D, nCfg, rows_pad, k_pad, Y, last ? Y : T, partial, row0 + (last ? SIGN_CUBIC : k), 1, sz, nullptr, p2h, p2l);
         if (r == DLCO_OK) r = gemm(p1h, p1l, p2h, p2l, sx, sz, T);     // T = X Z^T, Z = a I + b Y + c Y^2
         // fp32 X is only read after the last step (trace, optional d_S)
         if (r == DLCO_OK) r = sign_prep<PREP_SYM>(ctx, f16, D, nCfg, rows_pad, k_pad, T, nullptr, partial, k, 1, sx, last ? X : nullptr, p1h, p1l);
