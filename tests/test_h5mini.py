@@ -185,3 +185,79 @@ def test_missing_dataset_and_bad_file_fail_loudly(h5tool, tmp_path):
     bad.write_bytes(b"not hdf5" * 100)
     assert subprocess.call([h5tool, "ls", str(bad)], stderr=subprocess.DEVNULL) == 2
     assert subprocess.call([h5tool, "raw", GOLDEN, "nope", str(tmp_path / "x.bin")], stderr=subprocess.DEVNULL) == 2
+
+
+# ---- structure of what h5mini writes against what libhdf5 wrote -----------------------------------------------------
+def _structure(path, name):
+    """Low-level facts of one dataset, byte-parsed independently of both readers: superblock, object header,
+    the messages with their raw bytes (addresses masked), the chunk B-tree's node type / key layout and the zlib
+    framing of every chunk."""
+    f = H5File(path)
+    b = f.b
+    out = {"superblock": (b[8], b[13], b[14]),                          # version, offset size, length size
+           "group_leaf_k": struct.unpack_from("<H", b, 16)[0], "group_internal_k": struct.unpack_from("<H", b, 18)[0],
+           "root_cache_type": struct.unpack_from("<I", b, 56 + 16)[0]}
+    addr = f.datasets[name]
+    ver, _, nmsg, refc, hsize = struct.unpack_from("<BBHII", b, addr)
+    out["ohdr"] = (ver, refc)
+    msgs = {}
+    for mtype, data in f._messages(addr):
+        if mtype in (0x00, 0x10):                                       # NIL padding / continuation: layout detail
+            continue
+        msgs[mtype] = bytes(data)
+    out["msg_types"] = sorted(msgs)
+    sp = msgs[0x01]
+    out["dataspace"] = (sp[0], sp[1], sp[2], struct.unpack_from("<%dQ" % (2 * sp[1]), sp, 8))
+    out["datatype"] = msgs[0x03][:8 + 12]
+    lay = msgs[0x08]
+    nd = lay[2]
+    out["layout"] = (lay[0], lay[1], nd, struct.unpack_from("<%dI" % nd, lay, 11))
+    out["filter"] = msgs.get(0x0B)
+    out["fill"] = msgs.get(0x05)
+    btree = struct.unpack_from("<Q", lay, 3)[0]
+    assert b[btree:btree + 4] == b"TREE"
+    ntype, level, used = struct.unpack_from("<BBH", b, btree + 4)
+    left, right = struct.unpack_from("<QQ", b, btree + 8)
+    out["btree"] = (ntype, level, used, left == UNDEF, right == UNDEF)
+    ksz = 8 + 8 * nd
+    keys, zhdr = [], set()
+    p = btree + 24
+    for i in range(used):
+        csize, fmask = struct.unpack_from("<II", b, p)
+        offs = struct.unpack_from("<%dQ" % nd, b, p + 8)
+        child = struct.unpack_from("<Q", b, p + ksz)[0]
+        keys.append((fmask, offs))
+        zhdr.add(bytes(b[child:child + 2]))
+        assert len(zlib.decompress(b[child:child + csize])) == 5120 * 4
+        p += ksz + 8
+    out["keys"] = keys
+    out["final_key"] = struct.unpack_from("<%dQ" % nd, b, p + 8)          # the key behind the last child
+    out["zlib_header"] = sorted(zhdr)
+    return out
+
+
+def test_writer_structure_matches_libhdf5_written_file(h5tool, tmp_path):
+    """The reference's own `w` file was written by libhdf5 (through OpenCV's hdf module).  h5mini re-writes the same
+    dataset (unlimited rows, chunk 1 x 5120, deflate 9); every structural element a libhdf5 reader walks must be the
+    same kind of object with the same field values -- only addresses, sizes of the compressed chunks, the
+    modification time and the allocation order of the blocks may differ.  No libhdf5 exists in this image, so this
+    is the strongest available check that libhdf5 can read h5mini's files (INTEGRATION.md says so)."""
+    out = str(tmp_path / "rewritten.h5")
+    subprocess.check_call([h5tool, "copy", GOLDEN, out, "1", "9", "2"])
+    ref, got = _structure(GOLDEN, "w"), _structure(out, "w")
+    assert got["superblock"] == ref["superblock"] == (0, 8, 8)
+    assert got["ohdr"] == ref["ohdr"] == (1, 1)
+    assert got["root_cache_type"] == ref["root_cache_type"] == 1            # symbol table cached in the root entry
+    assert got["dataspace"] == ref["dataspace"]                              # v1, rank 2, max-dims flag, dims, unlimited
+    assert got["datatype"] == ref["datatype"]                                # IEEE f32 LE: class, bit fields, properties
+    assert got["layout"] == ref["layout"] == (3, 2, 3, (1, 5120, 4))         # v3, chunked, chunk dims + element size
+    assert got["filter"] == ref["filter"]                                    # pipeline v1: deflate, client value 9
+    assert got["btree"][:2] == ref["btree"][:2] == (1, 0)                    # chunk B-tree, leaf
+    assert got["btree"][2:] == ref["btree"][2:]                              # entries used, no siblings
+    assert got["keys"] == ref["keys"] and got["final_key"] == ref["final_key"]
+    assert got["zlib_header"] == ref["zlib_header"]                          # same zlib framing (78 da)
+    # messages libhdf5 wrote that h5mini must write too (a reader may require them); extras are reported
+    assert set(ref["msg_types"]) <= set(got["msg_types"]) | {0x12}, (ref["msg_types"], got["msg_types"])
+    assert {0x01, 0x03, 0x08, 0x0B} <= set(got["msg_types"])
+    if ref["fill"] is not None and got["fill"] is not None:
+        assert got["fill"][:4] == ref["fill"][:4]                            # fill value message version / times / defined

@@ -584,8 +584,10 @@ private:
                 // final key: where the next subtree starts (one chunk past the end for the last node)
                 const uint64_t next_row = b < level.size() ? level[b].row : end_row;
                 w64(nb, o + 8, next_row);
-                if (b == level.size())
-                    for (size_t k = 1; k + 1 < nd; k++) w64(nb, o + 8 + 8 * k, s.dims[k]);
+                if (b == level.size()) {          // libhdf5's right-most key: one chunk past the end in EVERY dimension,
+                    for (size_t k = 1; k + 1 < nd; k++) w64(nb, o + 8 + 8 * k, s.dims[k]);      // element size included
+                    w64(nb, o + 8 + 8 * (nd - 1), dtype_size(s.t));
+                }
                 put(nb.data(), nb.size());
                 up.push_back({base + n * node_bytes, level[a].bytes, level[a].row});
             }
