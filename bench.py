@@ -411,6 +411,8 @@ def collective_leg(torch, dist, ctx, dev, rank, world):
 
 # --------------------------------------------------------------------------------------------
 def main():
+    import faulthandler
+    faulthandler.enable()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=3)
@@ -530,6 +532,7 @@ def main():
     # ---- N > 1: one n_pairs job split over the ranks (strong scaling, gathered on the host), and the collective steps
     strong, collective = None, None
     if world > 1 and not args.no_e2e:
+        log("[bench] rank %d: strong-scaling leg" % rank)
         try:
             del h_out
             strong = strong_scaling_leg(torch, dist, ctx, bank, dev, rank, world, n_pairs, max(1, min(args.steps, 3)), barrier)
@@ -537,6 +540,7 @@ def main():
             strong = {"failed": repr(ex)}
         h_out = None
     if world > 1 and not args.no_rows:
+        log("[bench] rank %d: collective leg (strong: %s)" % (rank, "ok" if strong and "pairs_per_s" in strong else strong))
         try:
             collective = collective_leg(torch, dist, ctx, dev, rank, world)
         except Exception as ex:
@@ -546,6 +550,7 @@ def main():
     # (c % world == rank, as `pj-sweep -shard r/n`), unprojected distances replicated, no collective
     sweep_sharded = None
     if world > 1 and not args.no_rows:
+        log("[bench] rank %d: sharded sweep leg (collective: %s)" % (rank, collective if collective and "failed" in collective else "ok"))
         try:
             import bench_paths
             from dlco_b200 import learn
@@ -592,6 +597,7 @@ def main():
         except Exception as ex:
             sweep_sharded = {"failed": repr(ex)}
 
+    log("[bench] rank %d: legs done (stdout closed: %s, isatty: %s)" % (rank, sys.stdout.closed, sys.stdout.isatty()))
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -702,7 +708,9 @@ def main():
         "cpu_baseline": cpu, "rows": rows, "rows_cpu_baseline": rows_cpu, "strong_scaling": strong,
         "collective": collective, "pj_sweep_sharded": sweep_sharded, "checksum": checksum,
     }
-    print(json.dumps(line), flush=True)
+    log("[bench] rank 0: printing the result line (%d keys)" % len(line))
+    sys.stdout.write(json.dumps(line) + "\n")
+    sys.stdout.flush()
     if world > 1:
         dist.destroy_process_group()
 
