@@ -268,6 +268,35 @@ int dlco_pj_patchdist(dlco_ctx *ctx, const float *d_dists, int64_t N, int64_t ld
 int dlco_roc_stats(dlco_ctx *ctx, const float *d_pd, const uint8_t *d_labels, int64_t N,
                    float *h_fpr95, double *h_auc);
 
+/* ---- pair-sharded runs over the GPUs of one box (north_star: "sharding training pairs, with an all-reduce over
+ *      NVLink of the per-step gradient") ----------------------------------------------------------------------------
+ * The reference is single-GPU; this is new.  Each rank owns a row range of "Distance"; a pj-learn iteration becomes:
+ * margins of the sampled rows a rank owns (dlco_pj_margins) -> dlco_scatter_f32 into the 2 x szBatch vector ->
+ * all-reduce (one owner per slot, the sum is exact) -> dlco_pj_hinge_weights -> dlco_gather_f32 of the owned weights ->
+ * dlco_pj_wsyrk over the owned rows -> all-reduce of the D x D gradient -> update / prox on every rank (identical bits).
+ * The all-reduce is ONE kernel per GPU reading the peers' partial sums over NVLink peer memory (csrc/comm.cu), summing in
+ * rank order (bit-identical results on every rank); no library collective.  A dlco_comm is bound to a ctx; every rank
+ * must make the same sequence of all-reduce calls.
+ *   one process, n GPUs (the C++ tools):  dlco_comm_create_local(ctxs, n, max_count, comms)
+ *   one process per GPU:  dlco_comm_create -> dlco_comm_export (64-byte CUDA IPC handle) -> exchange the handles ->
+ *                         dlco_comm_import for every peer
+ * dlco_make_current selects the ctx's device for the calling thread (a thread that drives several contexts calls it
+ * before each context's calls). */
+typedef struct dlco_comm dlco_comm;
+int dlco_make_current(dlco_ctx *ctx);
+int dlco_comm_create_local(dlco_ctx **ctxs, int n, size_t max_count, dlco_comm **comms);
+int dlco_comm_create(dlco_ctx *ctx, int n, int rank, size_t max_count, dlco_comm **comm);
+int dlco_comm_export(dlco_comm *comm, void *h_handle64);
+int dlco_comm_import(dlco_comm *comm, int peer, const void *h_handle64);
+int dlco_comm_destroy(dlco_comm *comm);
+/* d_out[i] = sum over ranks of d_in[i] (i < count <= max_count); asynchronous on the ctx stream; in place allowed */
+int dlco_comm_allreduce_f32(dlco_comm *comm, const float *d_in, float *d_out, size_t count);
+/* synchronises the stream; error if a wait for a peer timed out (~2 s without progress) */
+int dlco_comm_check(dlco_comm *comm);
+/* d_dst[0..n_dst) = 0 then d_dst[d_pos[i]] = d_src[i];   d_dst[i] = d_src[d_pos[i]] */
+int dlco_scatter_f32(dlco_ctx *ctx, const float *d_src, const int32_t *d_pos, int n, float *d_dst, int n_dst);
+int dlco_gather_f32(dlco_ctx *ctx, const float *d_src, const int32_t *d_pos, int n, float *d_dst);
+
 /* ---- utility: C (M x N) = A (M x K) . B (N x K)^T through the same tcgen05 3xTF32 kernel the
  * pj-learn SYRK uses (fp32 row-major in and out); exported so the tensor-core path can be
  * checked in isolation against an fp64 product. */

@@ -94,6 +94,16 @@ SIGNATURES = {
                                  c_void_p, c_int, c_void_p, c_float, P(c_float), P(c_float)]),
     "dlco_pr_patchdist": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int, c_void_p, c_void_p]),
     "dlco_pj_patchdist": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int, c_void_p, c_int, c_void_p]),
+    "dlco_make_current": (c_int, [c_void_p]),
+    "dlco_comm_create_local": (c_int, [P(c_void_p), c_int, c_size_t, P(c_void_p)]),
+    "dlco_comm_create": (c_int, [c_void_p, c_int, c_int, c_size_t, P(c_void_p)]),
+    "dlco_comm_export": (c_int, [c_void_p, c_void_p]),
+    "dlco_comm_import": (c_int, [c_void_p, c_int, c_void_p]),
+    "dlco_comm_destroy": (c_int, [c_void_p]),
+    "dlco_comm_allreduce_f32": (c_int, [c_void_p, c_void_p, c_void_p, c_size_t]),
+    "dlco_comm_check": (c_int, [c_void_p]),
+    "dlco_scatter_f32": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int]),
+    "dlco_gather_f32": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
     "dlco_gemm3x_nt_f32": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_int, c_void_p]),
     "dlco_roc_stats": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, P(c_float), P(c_double)]),
 }
@@ -146,6 +156,44 @@ def _check(rc):
 
 def _ptr(t):
     return c_void_p(t.data_ptr()) if t is not None else c_void_p(0)
+
+
+class PeerComm:
+    """dlco_comm for one-process-per-GPU launches (torch.distributed only carries the 64-byte IPC handles): the
+    all-reduce itself is the library's peer-memory kernel, not a collective of the process group."""
+
+    def __init__(self, ctx, max_count, group=None):
+        import torch
+        import torch.distributed as dist
+        self.ctx, self.lib = ctx, load_library()
+        self.rank, self.world = (dist.get_rank(group), dist.get_world_size(group)) if dist.is_initialized() else (0, 1)
+        h = c_void_p()
+        _check(self.lib.dlco_comm_create(ctx.handle, self.world, self.rank, max_count, ctypes.byref(h)))
+        self.handle = h
+        buf = ctypes.create_string_buffer(64)
+        _check(self.lib.dlco_comm_export(h, buf))
+        if self.world > 1:
+            mine = torch.frombuffer(bytearray(buf.raw), dtype=torch.uint8).to(ctx.device)
+            allh = [torch.empty_like(mine) for _ in range(self.world)]
+            dist.all_gather(allh, mine, group=group)
+            for p, t in enumerate(allh):
+                if p != self.rank:
+                    raw = bytes(t.cpu().numpy().tobytes())
+                    _check(self.lib.dlco_comm_import(h, p, ctypes.create_string_buffer(raw, 64)))
+            dist.barrier(group=group)
+
+    def allreduce(self, t_in, t_out=None):
+        t_out = t_in if t_out is None else t_out
+        _check(self.lib.dlco_comm_allreduce_f32(self.handle, _ptr(t_in), _ptr(t_out), t_in.numel()))
+        return t_out
+
+    def check(self):
+        _check(self.lib.dlco_comm_check(self.handle))
+
+    def close(self):
+        if self.handle:
+            self.lib.dlco_comm_destroy(self.handle)
+            self.handle = None
 
 
 class Bank:

@@ -7,7 +7,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libdlco_b200.so")
 SOURCES = ["api.cu", "desc.cu", "pool_simt.cu", "pool_tc.cu", "fulldist.cu", "hinge.cu",
-           "pr_learn.cu", "pj_learn.cu", "stats.cu", "gemm_tc.cu", "sqnorm_tc.cu", "pj_sign.cu", "gen_bank.cu"]
+           "pr_learn.cu", "pj_learn.cu", "stats.cu", "gemm_tc.cu", "sqnorm_tc.cu", "pj_sign.cu", "gen_bank.cu", "comm.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
 

@@ -170,6 +170,13 @@ extern "C" int dlco_sync(dlco_ctx *ctx)
     return DLCO_OK;
 }
 
+extern "C" int dlco_make_current(dlco_ctx *ctx)
+{
+    DLCO_REQUIRE(ctx, "dlco_make_current: ctx is NULL");
+    DLCO_CUDA(cudaSetDevice(ctx->device));
+    return DLCO_OK;
+}
+
 extern "C" int dlco_set_stream(dlco_ctx *ctx, void *s)
 {
     DLCO_REQUIRE(ctx, "dlco_set_stream: ctx is NULL");
