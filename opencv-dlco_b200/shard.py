@@ -49,11 +49,14 @@ def sweep_grid(mus, gammas):
 class Collective:
     """Thin wrapper over torch.distributed; a world of 1 is a no-op (no process group needed)."""
 
-    def __init__(self, group=None):
+    def __init__(self, group=None, peer=None):
+        """peer: a dlco_b200.PeerComm -- float32 CUDA sums then go through the library's own all-reduce (one kernel per
+        GPU over NVLink peer memory, bit-identical on every rank) instead of the process group's collective."""
         import torch
         self.torch = torch
         self.dist = None
         self.group = group
+        self.peer = peer
         self.rank, self.world = 0, 1
         try:
             import torch.distributed as dist
@@ -65,6 +68,8 @@ class Collective:
 
     def allreduce_sum(self, t):
         if self.world > 1:
+            if self.peer is not None and t.is_cuda and t.dtype == self.torch.float32 and t.is_contiguous():
+                return self.peer.allreduce(t)
             self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM, group=self.group)
         return t
 
