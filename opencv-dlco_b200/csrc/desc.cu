@@ -32,6 +32,47 @@ struct DescParams {
 
 __device__ __forceinline__ int clampi(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
 
+// float(atan2((double)y, (double)x) + CV_PI) as the reference computes it (src/vgg-desc.cpp:66: ::atan2 of the promoted
+// floats, + CV_PI in double, stored as float) -- branch-free, ~45 fp64 instructions instead of the ~180 of the generic
+// library atan2 (44 % of k_desc's instructions before).  min/max -> one division u = num / den with |u| <= tan(pi/8)
+// (u = t below tan(pi/8), (t - 1) / (t + 1) above), atan(u) = u + u^3 P(u^2) with a degree-10 near-minimax P
+// (1e-18 on the interval), then the octant fix-ups.  The result is within ~3e-16 of the correctly rounded double except
+// for pi - a, which is formed with a two-sum against pi = PI_HI + PI_LO: angles next to -pi end up next to 0 after
+// "+ CV_PI", where the float grid is as fine as the double error.  Checked against glibc on 1 000 000 float pairs: equal.
+__constant__ double c_atan[11] = {
+    -0x1.3a31b1c0fd3b7p-6, 0x1.4162c02b1dda3p-5, -0x1.a0999c632b6edp-5, 0x1.dfe6497e96323p-5,
+    -0x1.10fa77b1a6d57p-4, 0x1.3b1263064f6b9p-4, -0x1.745d0b28a7e37p-4, 0x1.c71c71853d7fap-4,
+    -0x1.2492492436201p-3, 0x1.999999999934cp-3, -0x1.5555555555555p-2};
+__device__ __forceinline__ float atan2_plus_pi(float yf, float xf)
+{
+    const double PI_HI = 0x1.921fb54442d18p+1, PI_LO = 0x1.1a62633145c07p-53;
+    const double ax = fabs((double)xf), ay = fabs((double)yf);
+    const double mx = fmax(ax, ay), mn = fmin(ax, ay);
+    const bool red = mn > 0x1.a827999fcef32p-2 * mx;                   // t > tan(pi / 8)
+    const double num = red ? mn - mx : mn;
+    double den = red ? mn + mx : mx;
+    den = mx == 0.0 ? 1.0 : den;                                        // atan2(0, 0) = 0
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(den));             // ~20 bits, two Newton steps, one residual fix
+    r = fma(r, fma(-den, r, 1.0), r);
+    r = fma(r, fma(-den, r, 1.0), r);
+    double u = num * r;
+    u = fma(r, fma(-den, u, num), u);
+    const double z = u * u;
+    double p = c_atan[0];
+#pragma unroll
+    for (int k = 1; k < 11; k++) p = fma(p, z, c_atan[k]);
+    double a = fma(u * z, p, u);
+    a = red ? a + 0x1.921fb54442d18p-1 : a;                             // + pi / 4
+    a = ay > ax ? 0x1.921fb54442d18p+0 - a : a;                          // pi / 2 - a
+    if (__float_as_uint(xf) >> 31) {                                     // x < 0 (or -0): pi - a, correctly rounded
+        const double hi = PI_HI - a, err = (PI_HI - hi) - a;
+        a = hi + (err + PI_LO);
+    }
+    a = (__float_as_uint(yf) >> 31) ? -a : a;
+    return (float)(a + PI_HI);
+}
+
 // ---- block-wide reductions over DESC_THREADS = 256 threads (8 warps): hardware redux inside a warp,
 // one 8-word shared buffer across warps.  Callers alternate between two buffers so that one
 // __syncthreads per reduction is enough (a writer of buffer A at step n+2 has passed the barrier of
@@ -198,7 +239,7 @@ k_desc(const uint8_t *__restrict__ patches, const int32_t *__restrict__ ids, int
         // floats + CV_PI in double, stored as float (src/vgg-desc.cpp:66); GAngle / AngleStep - 0.5f is a
         // scaled convertTo = one fused multiply-add (src/vgg-desc.cpp:70)
         float m = sqrtf(fmaf(ix, ix, __fmul_rn(iy, iy)));
-        float ang = (float)(atan2((double)iy, (double)ix) + 3.1415926535897932384626433832795);
+        float ang = atan2_plus_pi(iy, ix);
         float ratio = fmaf(ang, prm.inv_step, -0.5f);
         float fl = floorf(ratio);
         off1[i] = ratio - fl;
