@@ -1,10 +1,146 @@
 // FPR95 / AUC evaluation (reference ComputePRStats src/misc.cpp:227-263 and ComputePJStats
-// :292-332): ascending sort of the N patch distances (stable, ties keep index order), ROC
+// :292-332): ascending sort of the N patch distances (stable, ties keep index order; own radix sort below), ROC
 // sweep with the reference's float counters, FPR at the first TPR >= 0.95f, and the area of
 // the (FPR, TPR) polygon closed through (1, 0) (cv::contourArea = shoelace in double).
 #include "common.cuh"
 #include "kernels.h"
-#include <cub/device/device_radix_sort.cuh>
+
+// ---- stable LSD radix sort of (float key, u8 label), 4 passes of 8 bits -----------------------------------------
+// Hand-written (round 1 called CUB here).  Per pass: k_rs_count (digit histogram of every 4096-element tile) ->
+// k_rs_scan (exclusive offsets over (digit, tile), digit-major: one CTA) -> k_rs_scatter (every tile re-walks its
+// elements in order; a lane's rank among the earlier elements of the tile with the same digit comes from
+// __match_any_sync + per-warp running counters, so equal keys keep their index order through every pass -- the sort
+// is stable, ties resolve by index as the oracle's does).  Keys are the float bits mapped to an unsigned order
+// (sign flip; -0 sorts as +0).
+#define RS_THREADS 256
+#define RS_ITEMS 16
+#define RS_TILE (RS_THREADS * RS_ITEMS)
+
+__device__ __forceinline__ uint32_t rs_key(float f)
+{
+    uint32_t u = __float_as_uint(f);
+    if (u == 0x80000000u) u = 0u;
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+
+template <bool FIRST>
+__device__ __forceinline__ uint32_t rs_load(const void *keys, int64_t i)
+{
+    return FIRST ? rs_key(reinterpret_cast<const float *>(keys)[i]) : reinterpret_cast<const uint32_t *>(keys)[i];
+}
+
+// counts[digit * n_tiles + tile]
+template <bool FIRST>
+__global__ void __launch_bounds__(RS_THREADS)
+k_rs_count(const void *__restrict__ keys, int64_t n, int shift, int n_tiles, uint32_t *__restrict__ counts)
+{
+    __shared__ uint32_t h[256];
+    h[threadIdx.x] = 0;
+    __syncthreads();
+    const int64_t base = (int64_t)blockIdx.x * RS_TILE;
+    for (int k = 0; k < RS_ITEMS; k++) {
+        const int64_t i = base + k * RS_THREADS + threadIdx.x;
+        if (i < n) atomicAdd(&h[(rs_load<FIRST>(keys, i) >> shift) & 255u], 1u);
+    }
+    __syncthreads();
+    counts[(size_t)threadIdx.x * n_tiles + blockIdx.x] = h[threadIdx.x];
+}
+
+// in place exclusive scan of counts (256 * n_tiles entries, digit-major) by one CTA of 1024 threads
+__global__ void __launch_bounds__(1024) k_rs_scan(uint32_t *__restrict__ counts, int total)
+{
+    __shared__ uint32_t s_sum[1024];
+    const int per = (total + 1023) / 1024;
+    const int lo = min(threadIdx.x * per, total), hi = min(lo + per, total);
+    uint32_t acc = 0;
+    for (int i = lo; i < hi; i++) acc += counts[i];
+    s_sum[threadIdx.x] = acc;
+    __syncthreads();
+    for (int o = 1; o < 1024; o <<= 1) {
+        uint32_t a = threadIdx.x >= o ? s_sum[threadIdx.x - o] : 0u;
+        __syncthreads();
+        s_sum[threadIdx.x] += a;
+        __syncthreads();
+    }
+    uint32_t run = s_sum[threadIdx.x] - acc;
+    for (int i = lo; i < hi; i++) {
+        const uint32_t c = counts[i];
+        counts[i] = run;
+        run += c;
+    }
+}
+
+// warp w of a tile owns elements [w * 512, w * 512 + 512) of it, walked 32 at a time in index order
+template <bool FIRST>
+__global__ void __launch_bounds__(RS_THREADS)
+k_rs_scatter(const void *__restrict__ keys_in, const uint8_t *__restrict__ vals_in, int64_t n, int shift, int n_tiles,
+             const uint32_t *__restrict__ offsets, uint32_t *__restrict__ keys_out, uint8_t *__restrict__ vals_out)
+{
+    __shared__ uint32_t wh[RS_THREADS / 32][256];       // phase 1: per-warp digit counts; phase 2: running write positions
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int d = lane; d < 256; d += 32) wh[warp][d] = 0;
+    __syncwarp();
+    const int64_t wbase = (int64_t)blockIdx.x * RS_TILE + (int64_t)warp * (32 * RS_ITEMS);
+    uint32_t key[RS_ITEMS];
+#pragma unroll
+    for (int k = 0; k < RS_ITEMS; k++) {
+        const int64_t i = wbase + k * 32 + lane;
+        key[k] = i < n ? rs_load<FIRST>(keys_in, i) : 0xffffffffu;
+        if (i < n) atomicAdd(&wh[warp][(key[k] >> shift) & 255u], 1u);
+    }
+    __syncthreads();
+    {   // digit threadIdx.x: global offset of this tile, then the warps' bases in warp order
+        uint32_t run = offsets[(size_t)threadIdx.x * n_tiles + blockIdx.x];
+        for (int w = 0; w < RS_THREADS / 32; w++) {
+            const uint32_t c = wh[w][threadIdx.x];
+            wh[w][threadIdx.x] = run;
+            run += c;
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < RS_ITEMS; k++) {
+        const int64_t i = wbase + k * 32 + lane;
+        const bool ok = i < n;
+        const uint32_t d = (key[k] >> shift) & 255u;
+        // lanes of this step with the same digit, valid ones only (invalid lanes get a digit of their own: 256 + lane)
+        const uint32_t peers = __match_any_sync(0xffffffffu, ok ? d : 256u + lane);
+        const uint32_t before = __popc(peers & ((1u << lane) - 1u));
+        uint32_t pos = 0;
+        if (ok) pos = wh[warp][d] + before;
+        __syncwarp();
+        if (ok && before == __popc(peers) - 1u) wh[warp][d] = pos + 1;      // the last peer advances the digit's position
+        __syncwarp();
+        if (ok) {
+            keys_out[pos] = key[k];
+            vals_out[pos] = vals_in[i];
+        }
+    }
+}
+
+// sorted labels end up in vals_b; keys_a / keys_b, vals_a / vals_b: N elements each, counts: 256 * n_tiles words
+static int rs_sort_labels(dlco_ctx *ctx, const float *d_pd, const uint8_t *d_labels, int64_t N, uint32_t *keys_a,
+                          uint32_t *keys_b, uint8_t *vals_a, uint8_t *vals_b, uint32_t *counts)
+{
+    const int n_tiles = (int)((N + RS_TILE - 1) / RS_TILE);
+    const void *kin = d_pd;
+    const uint8_t *vin = d_labels;
+    for (int pass = 0; pass < 4; pass++) {
+        uint32_t *kout = (pass & 1) ? keys_b : keys_a;
+        uint8_t *vout = (pass & 1) ? vals_b : vals_a;
+        if (pass == 0) k_rs_count<true><<<n_tiles, RS_THREADS, 0, ctx->stream>>>(kin, N, 8 * pass, n_tiles, counts);
+        else k_rs_count<false><<<n_tiles, RS_THREADS, 0, ctx->stream>>>(kin, N, 8 * pass, n_tiles, counts);
+        DLCO_CHECK_LAUNCH(ctx);
+        k_rs_scan<<<1, 1024, 0, ctx->stream>>>(counts, 256 * n_tiles);
+        DLCO_CHECK_LAUNCH(ctx);
+        if (pass == 0) k_rs_scatter<true><<<n_tiles, RS_THREADS, 0, ctx->stream>>>(kin, vin, N, 8 * pass, n_tiles, counts, kout, vout);
+        else k_rs_scatter<false><<<n_tiles, RS_THREADS, 0, ctx->stream>>>(kin, vin, N, 8 * pass, n_tiles, counts, kout, vout);
+        DLCO_CHECK_LAUNCH(ctx);
+        kin = kout;
+        vin = vout;
+    }
+    return DLCO_OK;
+}
 
 #define ROC_THREADS 1024
 
@@ -80,16 +216,15 @@ extern "C" int dlco_roc_stats(dlco_ctx *ctx, const float *d_pd, const uint8_t *d
 {
     DLCO_REQUIRE(ctx && d_pd && d_labels && h_fpr95 && h_auc, "dlco_roc_stats: NULL argument");
     DLCO_REQUIRE(N > 0 && N < (1ll << 31), "dlco_roc_stats: N=%lld out of range", (long long)N);
-    float *keys = (float *)dlco_scratch(ctx, 12, (size_t)N * sizeof(float));
-    uint8_t *vals = (uint8_t *)dlco_scratch(ctx, 13, (size_t)N);
+    const int n_tiles = (int)((N + RS_TILE - 1) / RS_TILE);
+    uint32_t *keys = (uint32_t *)dlco_scratch(ctx, 12, (size_t)2 * N * sizeof(uint32_t));
+    uint8_t *vals2 = (uint8_t *)dlco_scratch(ctx, 13, (size_t)2 * N);
     double *res = (double *)dlco_scratch(ctx, 14, 64);
-    if (!keys || !vals || !res) return DLCO_ENOMEM;
-    size_t tmp_bytes = 0;
-    DLCO_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, d_pd, keys, d_labels, vals, (int)N, 0, 32, ctx->stream));
-    void *tmp = dlco_scratch(ctx, 15, tmp_bytes);
-    if (!tmp) return DLCO_ENOMEM;
-    DLCO_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, d_pd, keys, d_labels, vals, (int)N, 0, 32, ctx->stream));
-    ctx->launches += 4;
+    uint32_t *counts = (uint32_t *)dlco_scratch(ctx, 15, (size_t)256 * n_tiles * sizeof(uint32_t));
+    if (!keys || !vals2 || !res || !counts) return DLCO_ENOMEM;
+    uint8_t *vals = vals2 + N;                      // pass 3 (odd) writes the second halves
+    int rc = rs_sort_labels(ctx, d_pd, d_labels, N, keys, keys + N, vals2, vals, counts);
+    if (rc != DLCO_OK) return rc;
     k_roc<<<1, ROC_THREADS, 0, ctx->stream>>>(vals, N, (float *)(res + 1), res, (int64_t *)(res + 2));
     DLCO_CHECK_LAUNCH(ctx);
     double h[4];

@@ -202,6 +202,23 @@ def test_roc_stats(gpu_ctx, n):
     assert abs(a - ao) <= 1e-12
 
 
+@pytest.mark.parametrize("n", [1, 31, 4096, 4100, 500003])
+def test_roc_stats_sort_is_stable_and_total(gpu_ctx, n):
+    """The hand-written radix sort behind dlco_roc_stats (csrc/stats.cu): heavy ties (keys quantised to 64 levels),
+    negative keys, -0 / +0, tile and warp edges -- the ROC counters must equal the oracle's, whose argsort is stable."""
+    rng = np.random.default_rng(n)
+    lab = (rng.random(n) < 0.5).astype(np.uint8)
+    pd = (np.round(rng.normal(0, 4, n) + lab * -1.5) / 8).astype(np.float32)    # ~64 distinct values, both signs
+    pd[rng.random(n) < 0.05] = np.float32(-0.0)
+    pd[rng.random(n) < 0.05] = np.float32(0.0)
+    if lab.min() == lab.max():
+        lab[0] = 1 - lab[0] if n > 1 else lab[0]
+    f, a = gpu_ctx.roc_stats(dev_t(gpu_ctx, pd), dev_t(gpu_ctx, lab))
+    fo, ao = O.roc_stats(pd, lab)
+    if n > 1:
+        assert f == float(fo) and abs(a - ao) <= 1e-12, (f, float(fo), a, ao)
+
+
 def test_pr_patchdist_and_stats(gpu_ctx):
     dists, lab = synth_fulldist(5000, 256, 9)
     rng = np.random.default_rng(1)
