@@ -188,10 +188,10 @@ def test_pj_learn_500_steps_at_baseline_configs(gpu_ctx, D, mu, gamma, prox):
     assert int(S.rng_state.cpu().numpy().view(np.uint64)[0]) == ora["rng_state"]
     # dfAvg within 1e-4 (plus the outer products of the hinge pairs that sit within 1e-4 of a tie).  A per iteration:
     # within 1e-4 on the eigen-decomposition route (measured 2e-6 .. 4e-6).  The sign route forms A+ = (A + A sign(A)) / 2
-    # in fp32-equivalent arithmetic, so its error is relative to ||A||, not to ||A+||: 2e-5 .. 6e-5 on three of the
-    # picks, 1.3e-4 on the weakest regulariser (mu 1e-4, gamma 0.025), where the PSD part is a small fraction of A;
-    # its bar is 2e-4 -- the default route of the tools stays the eigen-decomposition.
-    assert worst_df <= 0.0 and worst_a <= (1e-4 if prox == "eig" else 2e-4), (worst_df, worst_a, n_ties)
+    # through 27 chained fp32-equivalent GEMMs, its error is relative to ||A||, not to ||A+||: measured 1.2e-5 .. 3.8e-5
+    # on three of the picks and 8.7e-5 on the weakest regulariser (mu 1e-4, gamma 0.025), where the PSD part is a small
+    # fraction of A; bar 1.5e-4 for that route -- the default route of the tools stays the eigen-decomposition.
+    assert worst_df <= 0.0 and worst_a <= (1e-4 if prox == "eig" else 1.5e-4), (worst_df, worst_a, n_ties)
     S.refresh_w()
     rank_g, rank_o, rank_o32 = int(S.ranks()[0]), ora["rank64"], ora["rank32"]
     gpu_drift, ref_drift = drift[-1][1], drift[-1][2]
