@@ -21,7 +21,11 @@ constexpr int STAGES = BN <= 128 ? 3 : 2;     // 64 KB / 80 KB stages: as many a
 constexpr int A_BYTES = BM * BK * 4;
 constexpr int B_BYTES = BN * BK * 4;
 constexpr int STAGE_BYTES = 2 * A_BYTES + 2 * B_BYTES;
-constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256;
+// per epilogue warp: a 16-column x 32-row block of packed (hi | lo << 16) plane words, row stride 33 words, for the
+// transposed ("mirror") plane stores of the symmetric products whose lower tiles are skipped
+constexpr int TSM_WORDS = 16 * 33;
+constexpr int TSM_BYTES = 8 * TSM_WORDS * 4;
+constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256 + TSM_BYTES;
 constexpr int EPI_WARPS = 8;
 constexpr int NTHREADS = 64 + EPI_WARPS * 32;
 constexpr int TMEM_COLS = 2 * BN <= 256 ? 256 : 512;   // two BN-column accumulators
@@ -210,42 +214,85 @@ k_gemm3x_nt(const __grid_constant__ GemmMaps maps, const __grid_constant__ GemmT
             }
             const int row = mt * BM + q * 32 + lane;
             const int col0 = nt * BN + half * EN;
-            if (F16 && epi.mode && row < M) {
-                const float *aux = epi.mode == 2 ? epi.aux + (size_t)g * c_batch_stride + (size_t)row * ldc : nullptr;
+            if (F16 && epi.mode) {
+                // planes of the result (mode 1) or of ca I + cb aux + cc result (mode 2) for the next GEMM.  Every lane
+                // walks the columns (rows >= M carry zeros): the direct plane rows are 16-byte stores; where the tile
+                // below the diagonal is never computed its planes come from here too, transposed through shared
+                // memory 16 columns at a time so that they leave as 32-byte runs per lane instead of 2-byte stores.
+                const bool rok = row < M;
+                const bool mirror = epi.mirror && mt != nt;
+                const float *aux = (epi.mode == 2 && rok) ? epi.aux + (size_t)g * c_batch_stride + (size_t)row * ldc : nullptr;
                 __half *ph = reinterpret_cast<__half *>(epi.phi) + ((size_t)g * epi.rows_pad + row) * epi.k_pad;
                 __half *pl = reinterpret_cast<__half *>(epi.plo) + ((size_t)g * epi.rows_pad + row) * epi.k_pad;
+                uint32_t *tsm = reinterpret_cast<uint32_t *>(smem + STAGES * STAGE_BYTES + 256) + (warp - 2) * TSM_WORDS;
 #pragma unroll
                 for (int e = 0; e < EN; e += 8) {
-                    if (col0 + e + 8 > epi.k_pad) break;
-                    uint32_t hw[4], lw[4];
+                    if (col0 + e + 8 > epi.k_pad) break;                 // warp-uniform
+                    uint32_t pk[8];                                       // hi | lo << 16 per column
+                    float ax[8];
+                    if (epi.mode == 2) {                                  // aux row: two 16-byte loads where they fit
+                        if (aux && col0 + e + 8 <= N && ((reinterpret_cast<uintptr_t>(aux + col0 + e) & 15) == 0)) {
+                            const float4 a0 = __ldg(reinterpret_cast<const float4 *>(aux + col0 + e));
+                            const float4 a1 = __ldg(reinterpret_cast<const float4 *>(aux + col0 + e) + 1);
+                            ax[0] = a0.x; ax[1] = a0.y; ax[2] = a0.z; ax[3] = a0.w;
+                            ax[4] = a1.x; ax[5] = a1.y; ax[6] = a1.z; ax[7] = a1.w;
+                        } else {
+#pragma unroll
+                            for (int u = 0; u < 8; u++) ax[u] = (aux && col0 + e + u < N) ? __ldg(aux + col0 + e + u) : 0.f;
+                        }
+                    }
 #pragma unroll
                     for (int u = 0; u < 8; u++) {
                         const int col = col0 + e + u;
                         float x = acc[e + u];
-                        if (epi.mode == 2) x = fmaf(epi.cc, x, fmaf(epi.cb, col < N ? __ldg(aux + col) : 0.f, col == row ? epi.ca : 0.f));
-                        if (col >= N) x = 0.f;
+                        if (epi.mode == 2) x = fmaf(epi.cc, x, fmaf(epi.cb, ax[u], col == row ? epi.ca : 0.f));
+                        if (col >= N || !rok) x = 0.f;
                         const float sv = x * epi.pscale;
                         const __half h = __float2half_rn(sv);
                         const __half l = __float2half_rn(sv - __half2float(h));
-                        if (u & 1) {
-                            hw[u >> 1] |= (uint32_t)__half_as_ushort(h) << 16;
-                            lw[u >> 1] |= (uint32_t)__half_as_ushort(l) << 16;
-                        } else {
-                            hw[u >> 1] = __half_as_ushort(h);
-                            lw[u >> 1] = __half_as_ushort(l);
-                        }
+                        pk[u] = (uint32_t)__half_as_ushort(h) | ((uint32_t)__half_as_ushort(l) << 16);
                     }
-                    *reinterpret_cast<uint4 *>(ph + col0 + e) = make_uint4(hw[0], hw[1], hw[2], hw[3]);
-                    *reinterpret_cast<uint4 *>(pl + col0 + e) = make_uint4(lw[0], lw[1], lw[2], lw[3]);
-                    if (epi.mirror && mt != nt) {            // the tile below the diagonal is never computed: write it too
+                    if (rok) {
+                        *reinterpret_cast<uint4 *>(ph + col0 + e) =
+                            make_uint4(__byte_perm(pk[0], pk[1], 0x5410), __byte_perm(pk[2], pk[3], 0x5410),
+                                       __byte_perm(pk[4], pk[5], 0x5410), __byte_perm(pk[6], pk[7], 0x5410));
+                        *reinterpret_cast<uint4 *>(pl + col0 + e) =
+                            make_uint4(__byte_perm(pk[0], pk[1], 0x7632), __byte_perm(pk[2], pk[3], 0x7632),
+                                       __byte_perm(pk[4], pk[5], 0x7632), __byte_perm(pk[6], pk[7], 0x7632));
+                    }
+                    if (mirror) {
 #pragma unroll
-                        for (int u = 0; u < 8; u++) {
-                            const int col = col0 + e + u;
+                        for (int u = 0; u < 8; u++) tsm[((e & 8) + u) * 33 + lane] = pk[u];
+                        if (e & 8) {                                      // 16 columns staged: lane = (column, row half)
+                            __syncwarp();
+                            const int c = lane & 15, hrow = (lane >> 4) * 16;
+                            const int col = col0 + (e & ~15) + c;
+                            const int r0 = mt * BM + q * 32 + hrow;
+                            uint32_t w[16];
+#pragma unroll
+                            for (int j = 0; j < 16; j++) w[j] = tsm[c * 33 + hrow + j];
                             if (col < N) {
-                                const size_t mo = ((size_t)g * epi.rows_pad + col) * epi.k_pad + row;
-                                reinterpret_cast<uint16_t *>(epi.phi)[mo] = (uint16_t)(hw[u >> 1] >> (16 * (u & 1)));
-                                reinterpret_cast<uint16_t *>(epi.plo)[mo] = (uint16_t)(lw[u >> 1] >> (16 * (u & 1)));
+                                const size_t mo = ((size_t)g * epi.rows_pad + col) * epi.k_pad + r0;
+                                __half *mh = reinterpret_cast<__half *>(epi.phi) + mo, *ml = reinterpret_cast<__half *>(epi.plo) + mo;
+                                if (r0 + 16 <= M) {
+                                    reinterpret_cast<uint4 *>(mh)[0] = make_uint4(__byte_perm(w[0], w[1], 0x5410), __byte_perm(w[2], w[3], 0x5410),
+                                                                                 __byte_perm(w[4], w[5], 0x5410), __byte_perm(w[6], w[7], 0x5410));
+                                    reinterpret_cast<uint4 *>(mh)[1] = make_uint4(__byte_perm(w[8], w[9], 0x5410), __byte_perm(w[10], w[11], 0x5410),
+                                                                                 __byte_perm(w[12], w[13], 0x5410), __byte_perm(w[14], w[15], 0x5410));
+                                    reinterpret_cast<uint4 *>(ml)[0] = make_uint4(__byte_perm(w[0], w[1], 0x7632), __byte_perm(w[2], w[3], 0x7632),
+                                                                                 __byte_perm(w[4], w[5], 0x7632), __byte_perm(w[6], w[7], 0x7632));
+                                    reinterpret_cast<uint4 *>(ml)[1] = make_uint4(__byte_perm(w[8], w[9], 0x7632), __byte_perm(w[10], w[11], 0x7632),
+                                                                                 __byte_perm(w[12], w[13], 0x7632), __byte_perm(w[14], w[15], 0x7632));
+                                } else {
+#pragma unroll
+                                    for (int j = 0; j < 16; j++)
+                                        if (r0 + j < M) {
+                                            reinterpret_cast<uint16_t *>(mh)[j] = (uint16_t)(w[j] & 0xffffu);
+                                            reinterpret_cast<uint16_t *>(ml)[j] = (uint16_t)(w[j] >> 16);
+                                        }
+                                }
                             }
+                            __syncwarp();
                         }
                     }
                 }

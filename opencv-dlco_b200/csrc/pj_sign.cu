@@ -308,9 +308,12 @@ int dlco_pj_psd_sign(dlco_ctx *ctx, int D, int nCfg, float *d_A, int32_t *d_rank
     const int row0 = design * (SIGN_MAX_STEPS + 1);
     const float (*h_coef)[3] = h_sign_coef[design];
     const char *fe = getenv("DLCO_SIGN_FUSED");
-    // DLCO_SIGN_FUSED=1: Y and Z planes written by the GEMM epilogues (direct + mirrored) instead of prep passes.
-    // Bitwise the same result; measured equal at 45 configurations and slower at one: opt-in.
-    const bool fused = f16 && fe && fe[0] == '1';
+    // Fused epilogues: the Y and Z operand planes are written by the GEMM epilogues (directly, and transposed through
+    // shared memory for the tiles below the diagonal that are never computed) instead of by prep passes.  Bitwise the
+    // same result (tests/test_gpu_learn.py).  Measured (tools/psd_time.py, D = 544): 45 configurations 2.94 -> 2.65 ms,
+    // 8: 0.77 -> 0.71 ms, one: 0.57 -> 0.61 ms (a lone 544 x 544 product has 15 tiles: the heavier epilogue is exposed).
+    // Default: fused from 4 configurations up; DLCO_SIGN_FUSED=0 / 1 forces either.
+    const bool fused = f16 && (fe ? fe[0] == '1' : nCfg >= 4);
     if (fused && r == DLCO_OK) {
         // the planes written by GEMM epilogues cover the D x D block only: zero the padding once
         DLCO_CUDA(cudaMemsetAsync(P2, 0, 2 * plane * esz, ctx->stream));

@@ -1,5 +1,7 @@
 """GPU parity tests for the unprojected-distance builder, the hinge pair-sum, the pr-learn and
 pj-learn steps and the FPR95 evaluation -- all through the C ABI, against the CPU oracle."""
+import os
+
 import numpy as np
 import pytest
 
@@ -691,6 +693,32 @@ def test_pj_psd_project_matches_eigh(gpu_ctx, D, n_cfg):
     assert np.abs(out[0] - got[0]).max() <= 3e-5 * np.abs(got[0]).max()
     assert np.abs(out[1]).max() <= 3e-5 * np.abs(got[0]).max()
     assert not out[2].any() and int(rk[2]) == 0
+
+
+@pytest.mark.parametrize("D,n_cfg", [(544, 3), (480, 2), (100, 2), (72, 1)])
+def test_pj_psd_project_fused_epilogues_are_bit_identical(gpu_ctx, D, n_cfg):
+    """DLCO_SIGN_FUSED=1: the Y and Z operand planes of the sign iteration are written by the GEMM epilogues (directly and,
+    for the tiles below the diagonal that are never computed, transposed through shared memory) instead of by separate
+    passes.  Same arithmetic, so the projected matrices, ranks and sign(A) must equal the unfused route bit for bit --
+    including D that is not a multiple of 16 (ragged 16-row runs of the transposed stores)."""
+    rng = np.random.default_rng(7 * D)
+    xb = rng.standard_normal((n_cfg, 400, D)) * 0.1
+    c = rng.integers(-200, 200, size=(n_cfg, 400, 1)).astype(np.float64)
+    A = -(10.0) * (np.matmul((xb * c).transpose(0, 2, 1), xb) / 40000 + 0.001 * np.eye(D))
+    A = (0.5 * (A + A.transpose(0, 2, 1))).astype(np.float32)
+    out = {}
+    for fused in ("0", "1"):
+        os.environ["DLCO_SIGN_FUSED"] = fused
+        try:
+            d_A = dev_t(gpu_ctx, A.copy())
+            rank, S = gpu_ctx.pj_psd_project(d_A, want_sign=True)
+            rank = rank.cpu().numpy() if hasattr(rank, "cpu") else np.asarray(rank)
+            out[fused] = (d_A.cpu().numpy(), rank.copy(), S.cpu().numpy())
+        finally:
+            os.environ.pop("DLCO_SIGN_FUSED", None)
+    assert np.array_equal(out["0"][1], out["1"][1])
+    assert np.array_equal(out["0"][0], out["1"][0])
+    assert np.array_equal(out["0"][2], out["1"][2])
 
 
 def test_pj_sweep_sign_prox_matches_oracle_and_eig_route(gpu_ctx):
