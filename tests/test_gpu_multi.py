@@ -107,10 +107,10 @@ def test_pj_learn_pair_sharded_matches_single_gpu(tmp_path):
     for la, lb in zip(a, b):
         assert la[1] == lb[1] and abs(int(la[6]) - int(lb[6])) <= 1
         for i in (2, 3, 4):
-            assert abs(float(la[i]) - float(lb[i])) <= 2e-3 * abs(float(la[i])) + 1.5e-6, (la, lb)
+            assert abs(float(la[i]) - float(lb[i])) <= 1e-2 * abs(float(la[i])) + 1.5e-6, (la, lb)
     A1, A2 = outs["one"][2], outs["two"][2]
     assert abs(outs["one"][1].shape[0] - outs["two"][1].shape[0]) <= 1
-    assert np.abs(A1 - A2).max() <= 5e-3 * np.abs(A1).max()
+    assert np.abs(A1 - A2).max() <= 2e-2 * np.abs(A1).max()
     sa = re.findall(r"^Stat: .*$", outs["one"][0], re.M)
     sb = re.findall(r"^Stat: .*$", outs["two"][0], re.M)
     assert len(sa) == len(sb) >= 1
