@@ -295,8 +295,18 @@ typedef CUresult (*PFN_encodeTiled)(CUtensorMap *, CUtensorMapDataType, cuuint32
                                     const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
                                     CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
+int dlco_make_tmap_2d_sw(CUtensorMap *map, const void *base, int elem_bytes, uint64_t rows, uint64_t cols,
+                         uint32_t box_rows, uint32_t box_cols, int swizzle_bytes);
+
 int dlco_make_tmap_2d_ex(CUtensorMap *map, const void *base, int elem_bytes, uint64_t rows, uint64_t cols,
                          uint32_t box_rows, uint32_t box_cols)
+{
+    return dlco_make_tmap_2d_sw(map, base, elem_bytes, rows, cols, box_rows, box_cols, 128);
+}
+
+// swizzle_bytes = the bytes of one box row: 128, 64 or 32
+int dlco_make_tmap_2d_sw(CUtensorMap *map, const void *base, int elem_bytes, uint64_t rows, uint64_t cols,
+                         uint32_t box_rows, uint32_t box_cols, int swizzle_bytes)
 {
     static PFN_encodeTiled fn = nullptr;
     if (!fn) {
@@ -315,8 +325,9 @@ int dlco_make_tmap_2d_ex(CUtensorMap *map, const void *base, int elem_bytes, uin
     cuuint32_t estr[2] = {1, 1};
     CUresult r = fn(map, elem_bytes == 2 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
                     (void *)base, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                    CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                    swizzle_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
+                    : swizzle_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B,
+                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
         dlco_set_error("cuTensorMapEncodeTiled failed: CUresult %d", (int)r);
         return DLCO_ECUDA;

@@ -202,28 +202,6 @@ __device__ __forceinline__ void tma_load_2d(void *smem_dst, const CUtensorMap *m
         : "memory");
 }
 
-// the same load delivered to every CTA of the cluster named in cta_mask, at this CTA's offsets (data and mbarrier)
-__device__ __forceinline__ void tma_load_2d_mcast(void *smem_dst, const CUtensorMap *m, uint64_t *bar,
-                                                  int c0, int c1, uint16_t cta_mask)
-{
-    asm volatile(
-        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster"
-        " [%0], [%1, {%3, %4}], [%2], %5;" ::"r"(smem_u32(smem_dst)),
-        "l"(m), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "h"(cta_mask)
-        : "memory");
-}
-__device__ __forceinline__ uint32_t cluster_ctarank()
-{
-    uint32_t r;
-    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
-    return r;
-}
-__device__ __forceinline__ void cluster_sync_all()
-{
-    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
-    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
-}
-
 // ---- tcgen05 --------------------------------------------------------------------------
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -265,15 +243,6 @@ __device__ __forceinline__ void umma_commit(uint64_t *bar)
                  : "memory");
 }
 
-// the same arrival on the mbarrier at this offset in every CTA named in cta_mask
-__device__ __forceinline__ void umma_commit_mcast(uint64_t *bar, uint16_t cta_mask)
-{
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
-                     smem_u32(bar)),
-                 "h"(cta_mask)
-                 : "memory");
-}
-
 // D[tmem] (+)= A[smem desc] * B[smem desc], kind::f16 (fp16 x fp16 -> fp32), single CTA
 __device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,
                                          uint32_t idesc, uint32_t accumulate)
@@ -307,6 +276,20 @@ __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr)
     d |= (uint64_t)(1024 >> 4) << 32;             // SBO = 1024 B
     d |= (uint64_t)1 << 46;                       // descriptor version (Blackwell)
     d |= (uint64_t)2 << 61;                       // SWIZZLE_128B
+    return d;
+}
+
+// the same with rows of SW_BYTES (128, 64 or 32): 8-row groups 8 * SW_BYTES apart
+template <int SW_BYTES>
+__device__ __forceinline__ uint64_t umma_desc_sw(uint32_t smem_addr)
+{
+    static_assert(SW_BYTES == 128 || SW_BYTES == 64 || SW_BYTES == 32, "swizzle span");
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
+    d |= (uint64_t)1 << 16;
+    d |= (uint64_t)((8 * SW_BYTES) >> 4) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)(SW_BYTES == 128 ? 2 : SW_BYTES == 64 ? 4 : 6) << 61;
     return d;
 }
 

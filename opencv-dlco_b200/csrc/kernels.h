@@ -13,6 +13,8 @@ int dlco_launch_desc(dlco_ctx *ctx, int mode, const uint8_t *d_patches, const in
 // api.cu
 int dlco_make_tmap_2d_ex(CUtensorMap *map, const void *base, int elem_bytes, uint64_t rows, uint64_t cols,
                          uint32_t box_rows, uint32_t box_cols);
+int dlco_make_tmap_2d_sw(CUtensorMap *map, const void *base, int elem_bytes, uint64_t rows, uint64_t cols,
+                         uint32_t box_rows, uint32_t box_cols, int swizzle_bytes);
 int dlco_make_tmap_2d(CUtensorMap *map, const float *base, uint64_t rows, uint64_t cols,
                       uint32_t box_rows, uint32_t box_cols);
 int dlco_make_tmap_2d_raw(CUtensorMap *map, const float *base, uint64_t rows, uint64_t cols, uint64_t ld,

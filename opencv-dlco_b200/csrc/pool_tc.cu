@@ -86,7 +86,11 @@ __device__ __forceinline__ uint64_t split_mask(uint64_t mask, int ks, int ksplit
 // MODE 1 (comp-uprjdists, small banks): the K range is split over `ksplit` CTAs per tile so that a
 // 256-pair batch (whose B planes stay in L2) still fills the GPU; each writes its raw fp32 partial
 // P[(tile * ksplit + ks)][col 256][row 128] and k_uprj_finish sums, scales, clamps and subtracts.
-template <int MODE>
+// SPLIT (1, 2 or 4) cuts a K chunk into SPLIT pipeline stages of BK / SPLIT elements (rows of 128 / SPLIT bytes,
+// swizzle span to match): the same bytes in flight, but a stage is refilled while SPLIT * STAGES - 1 others are
+// consumed instead of one -- with two 96 KB stages the refill (L2 latency + 96 KB) has to finish within ONE chunk's
+// 1536 tensor cycles, and ncu showed the tensor pipe waiting 14 % of the time.
+template <int MODE, int SPLIT>
 __global__ void __launch_bounds__(NTHREADS, 1)
 k_pool_fulldist(const __grid_constant__ TMaps maps, const uint64_t *__restrict__ kmask,
                 const float *__restrict__ a_inv, const float *__restrict__ b_inv, int m_tiles,
@@ -95,12 +99,14 @@ k_pool_fulldist(const __grid_constant__ TMaps maps, const uint64_t *__restrict__
 {
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    constexpr int NST = STAGES * SPLIT, SUB_BYTES = STAGE_BYTES / SPLIT, SBK = BK / SPLIT;
+    constexpr int A_SUB = A_BYTES / SPLIT, B_SUB = B_BYTES / SPLIT;
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + STAGES * STAGE_BYTES);
-    uint64_t *full = bars;                    // [STAGES]
-    uint64_t *empty = bars + STAGES;          // [STAGES]
-    uint64_t *tfull = bars + 2 * STAGES;      // [2]
-    uint64_t *tempty = bars + 2 * STAGES + 2; // [2]
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * STAGES + 4);
+    uint64_t *full = bars;                    // [NST]
+    uint64_t *empty = bars + NST;             // [NST]
+    uint64_t *tfull = bars + 2 * NST;         // [2]
+    uint64_t *tempty = bars + 2 * NST + 2;    // [2]
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * NST + 4);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int total = m_tiles * n_tiles * ksplit;
@@ -111,7 +117,7 @@ k_pool_fulldist(const __grid_constant__ TMaps maps, const uint64_t *__restrict__
         tma_prefetch_desc(&maps.a_lo);
         tma_prefetch_desc(&maps.b_hi);
         tma_prefetch_desc(&maps.b_lo);
-        for (int s = 0; s < STAGES; s++) {
+        for (int s = 0; s < NST; s++) {
             mbar_init(&full[s], 1);
             mbar_init(&empty[s], 1);
         }
@@ -138,14 +144,17 @@ k_pool_fulldist(const __grid_constant__ TMaps maps, const uint64_t *__restrict__
                 while (mask) {
                     const int kc = __ffsll((long long)mask) - 1;
                     mask &= mask - 1;
-                    mbar_wait(&empty[stage], phase ^ 1);
-                    uint8_t *st = smem + stage * STAGE_BYTES;
-                    mbar_expect_tx(&full[stage], STAGE_BYTES);
-                    tma_load_2d(st, &maps.a_hi, &full[stage], kc * BK, m * BM);
-                    tma_load_2d(st + A_BYTES, &maps.a_lo, &full[stage], kc * BK, m * BM);
-                    tma_load_2d(st + 2 * A_BYTES, &maps.b_hi, &full[stage], kc * BK, n * BN);
-                    tma_load_2d(st + 2 * A_BYTES + B_BYTES, &maps.b_lo, &full[stage], kc * BK, n * BN);
-                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+#pragma unroll
+                    for (int h = 0; h < SPLIT; h++) {
+                        mbar_wait(&empty[stage], phase ^ 1);
+                        uint8_t *st = smem + stage * SUB_BYTES;
+                        mbar_expect_tx(&full[stage], SUB_BYTES);
+                        tma_load_2d(st, &maps.a_hi, &full[stage], kc * BK + h * SBK, m * BM);
+                        tma_load_2d(st + A_SUB, &maps.a_lo, &full[stage], kc * BK + h * SBK, m * BM);
+                        tma_load_2d(st + 2 * A_SUB, &maps.b_hi, &full[stage], kc * BK + h * SBK, n * BN);
+                        tma_load_2d(st + 2 * A_SUB + B_SUB, &maps.b_lo, &full[stage], kc * BK + h * SBK, n * BN);
+                        if (++stage == NST) { stage = 0; phase ^= 1; }
+                    }
                 }
             }
         }
@@ -166,22 +175,25 @@ k_pool_fulldist(const __grid_constant__ TMaps maps, const uint64_t *__restrict__
                         mbar_wait(&tempty[it & 1], ((it >> 1) & 1) ^ 1);
                         tc_fence_after();
                     }
-                    mbar_wait(&full[stage], phase);
-                    tc_fence_after();
-                    const uint32_t sa = smem_u32(smem + stage * STAGE_BYTES);
-                    const uint64_t d_ahi = umma_desc_sw128(sa);
-                    const uint64_t d_alo = umma_desc_sw128(sa + A_BYTES);
-                    const uint64_t d_bhi = umma_desc_sw128(sa + 2 * A_BYTES);
-                    const uint64_t d_blo = umma_desc_sw128(sa + 2 * A_BYTES + B_BYTES);
 #pragma unroll
-                    for (int k = 0; k < BK / 16; k++) {
-                        const uint64_t ko = (uint64_t)(k * 2);   // 16 fp16 = 32 B = 2 x 16 B
-                        umma_f16(d_tmem, d_alo + ko, d_bhi + ko, idesc, (in_flush | k) != 0);
-                        umma_f16(d_tmem, d_ahi + ko, d_blo + ko, idesc, 1);
-                        umma_f16(d_tmem, d_ahi + ko, d_bhi + ko, idesc, 1);
+                    for (int h = 0; h < SPLIT; h++) {
+                        mbar_wait(&full[stage], phase);
+                        tc_fence_after();
+                        const uint32_t sa = smem_u32(smem + stage * SUB_BYTES);
+                        const uint64_t d_ahi = umma_desc_sw<128 / SPLIT>(sa);
+                        const uint64_t d_alo = umma_desc_sw<128 / SPLIT>(sa + A_SUB);
+                        const uint64_t d_bhi = umma_desc_sw<128 / SPLIT>(sa + 2 * A_SUB);
+                        const uint64_t d_blo = umma_desc_sw<128 / SPLIT>(sa + 2 * A_SUB + B_SUB);
+#pragma unroll
+                        for (int k = 0; k < SBK / 16; k++) {
+                            const uint64_t ko = (uint64_t)(k * 2);   // 16 fp16 = 32 B = 2 x 16 B
+                            umma_f16(d_tmem, d_alo + ko, d_bhi + ko, idesc, (in_flush | h | k) != 0);
+                            umma_f16(d_tmem, d_ahi + ko, d_blo + ko, idesc, 1);
+                            umma_f16(d_tmem, d_ahi + ko, d_bhi + ko, idesc, 1);
+                        }
+                        umma_commit(&empty[stage]);
+                        if (++stage == NST) { stage = 0; phase ^= 1; }
                     }
-                    umma_commit(&empty[stage]);
-                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
                     if (++in_flush == FLUSH || mask == 0) {
                         umma_commit(&tfull[it & 1]);
                         it++;
@@ -301,6 +313,32 @@ k_uprj_finish(const float *__restrict__ P, int m_tiles, int n_tiles, int ksplit,
 
 }  // namespace
 
+// Pipeline stages per K chunk (template parameter SPLIT of k_pool_fulldist).  Measured on the gen-poolregion bank,
+// 16 384 pairs: 1 -> 81.6 ms, 2 -> 79.5 ms, 4 -> 125 ms (32-byte rows: the tensor core's operand reads conflict);
+// bit-identical.  DLCO_POOL_SPLIT=1 restores whole-chunk stages.
+static int pool_split()
+{
+    static const int v = [] { const char *e = getenv("DLCO_POOL_SPLIT"); return e && atoi(e) == 1 ? 1 : 2; }();
+    return v;
+}
+
+// tensor maps of both operands for the stage shape: boxes of BK / split elements, swizzle span = the box row
+static int pool_maps(const dlco_bank *bank, const void *d_bhi, const void *d_blo, int n_pairs_padded, int split, TMaps *maps)
+{
+    const int sw = 128 / split, bk = BK / split;
+    int r = DLCO_OK;
+    if (split == 1) {
+        maps->a_hi = bank->map_hi;
+        maps->a_lo = bank->map_lo;
+    } else {
+        r = dlco_make_tmap_2d_sw(&maps->a_hi, bank->d_hi, 2, bank->nRowsPad, KTOT, BM, bk, sw);
+        if (r == DLCO_OK) r = dlco_make_tmap_2d_sw(&maps->a_lo, bank->d_lo, 2, bank->nRowsPad, KTOT, BM, bk, sw);
+    }
+    if (r == DLCO_OK) r = dlco_make_tmap_2d_sw(&maps->b_hi, d_bhi, 2, (uint64_t)n_pairs_padded * 16, KTOT, BN, bk, sw);
+    if (r == DLCO_OK) r = dlco_make_tmap_2d_sw(&maps->b_lo, d_blo, 2, (uint64_t)n_pairs_padded * 16, KTOT, BN, bk, sw);
+    return r;
+}
+
 // K-split factor for a small bank: enough CTAs for the GPU, a divisor-free choice among 1, 2, 4, 8, 16
 int dlco_pool_tc_ksplit(const dlco_ctx *ctx, const dlco_bank *bank, int n_pairs_padded)
 {
@@ -323,20 +361,17 @@ int dlco_launch_pool_tc_uprj(dlco_ctx *ctx, const dlco_bank *bank, const void *d
     DLCO_REQUIRE(n_pairs_padded % 16 == 0 && n_pairs_padded >= n_pairs, "pool_tc_uprj: bad padding");
     DLCO_REQUIRE(n_pairs <= 65535, "pool_tc_uprj: at most 65535 pairs per launch");
     TMaps maps;
-    maps.a_hi = bank->map_hi;
-    maps.a_lo = bank->map_lo;
-    int r = dlco_make_tmap_2d_ex(&maps.b_hi, d_bhi, 2, (uint64_t)n_pairs_padded * 16, KTOT, BN, BK);
+    const int split = pool_split();
+    int r = pool_maps(bank, d_bhi, d_blo, n_pairs_padded, split, &maps);
     if (r != DLCO_OK) return r;
-    r = dlco_make_tmap_2d_ex(&maps.b_lo, d_blo, 2, (uint64_t)n_pairs_padded * 16, KTOT, BN, BK);
-    if (r != DLCO_OK) return r;
-    DLCO_SMEM_ONCE(ctx, 2, k_pool_fulldist<1>, SMEM_BYTES);
+    auto kern = split == 2 ? k_pool_fulldist<1, 2> : k_pool_fulldist<1, 1>;
+    DLCO_SMEM_ONCE(ctx, 2, kern, SMEM_BYTES);
     const int m_tiles = bank->nRowsPad / BM, n_tiles = n_pairs_padded / 16;
     const int total = m_tiles * n_tiles * ksplit;
     const int grid = total < ctx->sm_count ? total : ctx->sm_count;
     dlco_prof_begin(ctx, 1);
-    k_pool_fulldist<1><<<grid, NTHREADS, SMEM_BYTES, ctx->stream>>>(maps, bank->d_kmask, bank->d_inv_scale, d_binv,
-                                                                   m_tiles, n_tiles, ksplit, n_pairs, bank->nRows,
-                                                                   d_P, 0, nullptr);
+    kern<<<grid, NTHREADS, SMEM_BYTES, ctx->stream>>>(maps, bank->d_kmask, bank->d_inv_scale, d_binv, m_tiles, n_tiles, ksplit,
+                                                      n_pairs, bank->nRows, d_P, 0, nullptr);
     dlco_prof_end(ctx);
     DLCO_CHECK_LAUNCH(ctx);
     const size_t fin_smem = (size_t)bank->nRowsPad * 8 * sizeof(float);
@@ -401,23 +436,21 @@ int dlco_launch_pool_tc(dlco_ctx *ctx, const dlco_bank *bank, const void *d_bhi,
     DLCO_REQUIRE(n_pairs_padded % 16 == 0 && n_pairs_padded >= n_pairs, "pool_tc: bad padding");
     DLCO_REQUIRE(n_pairs <= 65535, "pool_tc: at most 65535 pairs per launch");
     TMaps maps;
-    maps.a_hi = bank->map_hi;
-    maps.a_lo = bank->map_lo;
-    int r = dlco_make_tmap_2d_ex(&maps.b_hi, d_bhi, 2, (uint64_t)n_pairs_padded * 16, KTOT, BN, BK);
-    if (r != DLCO_OK) return r;
-    r = dlco_make_tmap_2d_ex(&maps.b_lo, d_blo, 2, (uint64_t)n_pairs_padded * 16, KTOT, BN, BK);
-    if (r != DLCO_OK) return r;
-    DLCO_SMEM_ONCE(ctx, 3, k_pool_fulldist<0>, SMEM_BYTES);
+    int r;
     const int m_tiles = bank->nRowsPad / BM, n_tiles = n_pairs_padded / 16;
+    const int split = pool_split();
+    r = pool_maps(bank, d_bhi, d_blo, n_pairs_padded, split, &maps);
+    if (r != DLCO_OK) return r;
     const int total = m_tiles * n_tiles;
     const int grid = total < ctx->sm_count ? total : ctx->sm_count;
     const int32_t *sched = nullptr;
     r = pool_schedule(ctx, const_cast<dlco_bank *>(bank), m_tiles, n_tiles, grid, &sched);
     if (r != DLCO_OK) return r;
+    auto kern = split == 2 ? k_pool_fulldist<0, 2> : k_pool_fulldist<0, 1>;
+    DLCO_SMEM_ONCE(ctx, 3, kern, SMEM_BYTES);
     dlco_prof_begin(ctx, 1);
-    k_pool_fulldist<0><<<grid, NTHREADS, SMEM_BYTES, ctx->stream>>>(maps, bank->d_kmask, bank->d_inv_scale, d_binv,
-                                                                   m_tiles, n_tiles, 1, n_pairs, bank->nRows, d_S,
-                                                                   bank->nRowsPad, sched);
+    kern<<<grid, NTHREADS, SMEM_BYTES, ctx->stream>>>(maps, bank->d_kmask, bank->d_inv_scale, d_binv, m_tiles, n_tiles, 1,
+                                                      n_pairs, bank->nRows, d_S, bank->nRowsPad, sched);
     dlco_prof_end(ctx);
     DLCO_CHECK_LAUNCH(ctx);
     const int n_rings = bank->nF / 8;
