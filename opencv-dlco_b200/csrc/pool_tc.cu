@@ -384,6 +384,13 @@ int dlco_launch_pool_tc_uprj(dlco_ctx *ctx, const dlco_bank *bank, const void *d
     return DLCO_OK;
 }
 
+// groups of pair tiles a launch walks one after the other: at most 8 tiles (128 pairs, 34 MB of planes) each
+static int pool_groups(int n_tiles)
+{
+    static const int per = [] { const char *e = getenv("DLCO_POOL_GROUP_TILES"); const int v = e ? atoi(e) : 8; return v > 0 ? v : 8; }();
+    return (n_tiles + per - 1) / per;
+}
+
 // Static work schedule of k_pool_fulldist<0>: items (m tile, n tile) cost popcount(kmask[m]) K chunks plus an
 // epilogue, between 8 and 64 chunks for the gen-poolregion bank, so dealing them out round-robin leaves the CTAs
 // 3 % apart.  Longest-processing-time-first instead: items in tile order (n fastest: the CTAs running at one time
@@ -393,22 +400,31 @@ static int pool_schedule(dlco_ctx *ctx, dlco_bank *bank, int m_tiles, int n_tile
     *out = nullptr;
     if (!bank->h_kmask || m_tiles * n_tiles <= grid || n_tiles < 8) return DLCO_OK;   // small launches (a ragged last batch): round-robin
     if (bank->d_sched && bank->sched_n_tiles == n_tiles && bank->sched_grid == grid) { *out = bank->d_sched; return DLCO_OK; }
-    const int total = m_tiles * n_tiles;
-    std::vector<int> order(total);
-    for (int t = 0; t < total; t++) order[t] = t;
     auto cost = [&](int t) { return 2 * __builtin_popcountll(bank->h_kmask[t / n_tiles]) + 1; };   // epilogue ~ half a chunk
-    std::stable_sort(order.begin(), order.end(), [&](int a, int c) { return cost(a) > cost(c); });
     std::vector<std::vector<int32_t>> items(grid);
     typedef std::pair<int64_t, int> Load;                      // (load, cta): the least loaded CTA, lowest index first
     std::priority_queue<Load, std::vector<Load>, std::greater<Load>> heap;
     for (int c = 0; c < grid; c++) heap.push(Load(0, c));
     size_t len = 0;
-    for (int t : order) {
-        Load l = heap.top();
-        heap.pop();
-        items[l.second].push_back(t);
-        len = std::max(len, items[l.second].size());
-        heap.push(Load(l.first + cost(t), l.second));
+    // The pair tiles are taken in groups, one group after the other on every CTA (the loads carry over, so the
+    // groups end level): every filter tile meets every pair tile, so one operand has to stay in L2 while the other
+    // streams, and 16 pair tiles (67 MB of planes) next to the streaming 320 MB bank do not stay -- ncu counted
+    // 1.43 GB of DRAM traffic per 256-pair launch.  Eight tiles (34 MB) do: 0.87 GB, and 79.7 -> 76.6 ms per 16 384
+    // pairs; four tiles stream the bank four times and lose (83.1 ms, 1.47 GB).
+    const int n_groups = pool_groups(n_tiles);
+    for (int g = 0; g < n_groups; g++) {
+        const int n_lo = (int)((int64_t)n_tiles * g / n_groups), n_hi = (int)((int64_t)n_tiles * (g + 1) / n_groups);
+        std::vector<int> order;
+        for (int m = 0; m < m_tiles; m++)
+            for (int n = n_lo; n < n_hi; n++) order.push_back(m * n_tiles + n);
+        std::stable_sort(order.begin(), order.end(), [&](int a, int c) { return cost(a) > cost(c); });
+        for (int t : order) {
+            Load l = heap.top();
+            heap.pop();
+            items[l.second].push_back(t);
+            len = std::max(len, items[l.second].size());
+            heap.push(Load(l.first + cost(t), l.second));
+        }
     }
     std::vector<int32_t> tab((len + 1) * grid, -1);
     for (int c = 0; c < grid; c++)
