@@ -267,6 +267,15 @@ int dlco_pj_patchdist(dlco_ctx *ctx, const float *d_dists, int64_t N, int64_t ld
                       const float *d_W, int rank, float *d_pd);
 int dlco_roc_stats(dlco_ctx *ctx, const float *d_pd, const uint8_t *d_labels, int64_t N,
                    float *h_fpr95, double *h_auc);
+/* dlco_roc_stats without any allocation: no counterpart in the reference; added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  The sort's scratch is a file-scope __device__ array of 10.3 MB that every GPU loading the library holds until
+ * exit; N is limited to dlco_roc_stats_static_max_n() = 2^20 scores and a larger N is rejected with DLCO_EINVAL.
+ * Same results as dlco_roc_stats, bit for bit.  All calls on a GPU share the array (it keeps the previous call's
+ * contents; nothing in it has to start at zero): calls that overlap on one GPU race and must be serialised. */
+int dlco_roc_stats_static(dlco_ctx *ctx, const float *d_pd, const uint8_t *d_labels, int64_t N,
+                          float *h_fpr95, double *h_auc);
+int64_t dlco_roc_stats_static_max_n(void);
 
 /* ---- pair-sharded runs over the GPUs of one box (north_star: "sharding training pairs, with an all-reduce over
  *      NVLink of the per-step gradient") ----------------------------------------------------------------------------

@@ -106,6 +106,8 @@ SIGNATURES = {
     "dlco_gather_f32": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
     "dlco_gemm3x_nt_f32": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_int, c_void_p]),
     "dlco_roc_stats": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, P(c_float), P(c_double)]),
+    "dlco_roc_stats_static": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, P(c_float), P(c_double)]),
+    "dlco_roc_stats_static_max_n": (c_int64, []),
 }
 
 
@@ -539,6 +541,14 @@ class Context:
         f, a = c_float(), c_double()
         _check(self.lib.dlco_roc_stats(self.handle, _ptr(patch_dist), _ptr(labels), patch_dist.numel(),
                                        ctypes.byref(f), ctypes.byref(a)))
+        return f.value, a.value
+
+    def roc_stats_static(self, patch_dist, labels):
+        """roc_stats through dlco_roc_stats_static: scratch in a fixed __device__ array, nothing allocated; at most
+        lib.dlco_roc_stats_static_max_n() scores.  Not in the reference (see include/dlco_b200.h)."""
+        f, a = c_float(), c_double()
+        _check(self.lib.dlco_roc_stats_static(self.handle, _ptr(patch_dist), _ptr(labels), patch_dist.numel(),
+                                              ctypes.byref(f), ctypes.byref(a)))
         return f.value, a.value
 
     def gemm3x_nt(self, A, B):

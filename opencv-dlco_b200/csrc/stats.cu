@@ -236,3 +236,75 @@ extern "C" int dlco_roc_stats(dlco_ctx *ctx, const float *d_pd, const uint8_t *d
     *h_fpr95 = f;
     return DLCO_OK;
 }
+
+// ---- dlco_roc_stats_static: the same evaluation with no allocation anywhere ---------------------------------------
+// No counterpart in the reference; added for callers that cannot call
+// cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The sort's scratch
+// (two key buffers, two label buffers, the per-tile digit counts and the 64-byte result block) lives in one file-scope
+// __device__ array of fixed size instead of the context's growable scratch slots: every GPU that loads the library
+// holds DLCO_ROC_STATIC_BYTES (10.3 MB) until exit, and N is limited to DLCO_ROC_STATIC_MAX_N = 2^20 scores.
+// Every call on a device shares the array and finds the previous call's contents in it.  Nothing has to start at
+// zero: k_rs_count writes every (digit, tile) count it later reads, the scatter passes write all N keys / labels and
+// k_roc writes the whole result block -- so nothing is cleared.  Calls that overlap on one GPU (two contexts, two
+// streams, two host threads) race on the array: serialise them.
+#define DLCO_ROC_STATIC_MAX_N (1 << 20)
+#define DLCO_ROC_STATIC_TILES (DLCO_ROC_STATIC_MAX_N / RS_TILE)
+#define DLCO_ROC_STATIC_OFF_VALS ((size_t)2 * DLCO_ROC_STATIC_MAX_N * sizeof(uint32_t))
+#define DLCO_ROC_STATIC_OFF_COUNTS (DLCO_ROC_STATIC_OFF_VALS + (size_t)2 * DLCO_ROC_STATIC_MAX_N)
+#define DLCO_ROC_STATIC_OFF_RES (DLCO_ROC_STATIC_OFF_COUNTS + (size_t)256 * DLCO_ROC_STATIC_TILES * sizeof(uint32_t))
+#define DLCO_ROC_STATIC_BYTES (DLCO_ROC_STATIC_OFF_RES + 256)
+#define DLCO_ROC_STATIC_MAX_DEVICES 64
+
+static __device__ __align__(256) unsigned char g_roc_static[DLCO_ROC_STATIC_BYTES];
+
+// device address of g_roc_static on the context's device.  In host code the array's name is only a handle: the
+// address a kernel may use comes from cudaGetSymbolAddress, per device, with that device current.
+static int roc_static_base(dlco_ctx *ctx, unsigned char **out)
+{
+    static unsigned char *base[DLCO_ROC_STATIC_MAX_DEVICES];
+    DLCO_REQUIRE(ctx->device >= 0 && ctx->device < DLCO_ROC_STATIC_MAX_DEVICES, "dlco_roc_stats_static: device %d out of range", ctx->device);
+    DLCO_CUDA(cudaSetDevice(ctx->device));
+    unsigned char *p = __atomic_load_n(&base[ctx->device], __ATOMIC_ACQUIRE);
+    if (!p) {
+        cudaError_t e = cudaGetSymbolAddress((void **)&p, g_roc_static);
+        if (e != cudaSuccess || !p) {
+            dlco_set_error("dlco_roc_stats_static: cudaGetSymbolAddress on device %d: %s", ctx->device, cudaGetErrorString(e));
+            return DLCO_ECUDA;
+        }
+        __atomic_store_n(&base[ctx->device], p, __ATOMIC_RELEASE);     // the same value from every thread that races here
+    }
+    *out = p;
+    return DLCO_OK;
+}
+
+extern "C" int dlco_roc_stats_static(dlco_ctx *ctx, const float *d_pd, const uint8_t *d_labels, int64_t N,
+                                     float *h_fpr95, double *h_auc)
+{
+    DLCO_REQUIRE(ctx && d_pd && d_labels && h_fpr95 && h_auc, "dlco_roc_stats_static: NULL argument");
+    DLCO_REQUIRE(N > 0, "dlco_roc_stats_static: N=%lld out of range", (long long)N);
+    DLCO_REQUIRE(N <= DLCO_ROC_STATIC_MAX_N,
+                 "dlco_roc_stats_static: N=%lld exceeds the static scratch (at most %d scores; use dlco_roc_stats)",
+                 (long long)N, DLCO_ROC_STATIC_MAX_N);
+    unsigned char *base = nullptr;
+    int rc = roc_static_base(ctx, &base);
+    if (rc != DLCO_OK) return rc;
+    uint32_t *keys = (uint32_t *)base;
+    uint8_t *vals2 = base + DLCO_ROC_STATIC_OFF_VALS;
+    uint32_t *counts = (uint32_t *)(base + DLCO_ROC_STATIC_OFF_COUNTS);
+    double *res = (double *)(base + DLCO_ROC_STATIC_OFF_RES);
+    uint8_t *vals = vals2 + N;
+    rc = rs_sort_labels(ctx, d_pd, d_labels, N, keys, keys + N, vals2, vals, counts);
+    if (rc != DLCO_OK) return rc;
+    k_roc<<<1, ROC_THREADS, 0, ctx->stream>>>(vals, N, (float *)(res + 1), res, (int64_t *)(res + 2));
+    DLCO_CHECK_LAUNCH(ctx);
+    double h[4];
+    DLCO_CUDA(cudaMemcpyAsync(h, res, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream));
+    DLCO_CUDA(cudaStreamSynchronize(ctx->stream));
+    *h_auc = h[0];
+    float f;
+    memcpy(&f, &h[1], sizeof(float));
+    *h_fpr95 = f;
+    return DLCO_OK;
+}
+
+extern "C" int64_t dlco_roc_stats_static_max_n(void) { return DLCO_ROC_STATIC_MAX_N; }
