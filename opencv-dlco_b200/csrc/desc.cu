@@ -102,21 +102,87 @@ __device__ __forceinline__ uint32_t block_max(uint32_t c, uint32_t *buf)
     return max(max(max(a.x, a.y), max(a.z, a.w)), max(max(b.x, b.y), max(b.z, b.w)));
 }
 
-// exact k-th smallest (0-based rank) of the 4096 non-negative floats held 16 per thread (as uint
-// bits; non-negative floats order like their bit patterns): the largest t with #{v < t} <= rank,
-// built bit by bit from the top -- 31 block-wide counts, no shared-memory histogram (the top byte
-// of a patch's gradient magnitudes is almost constant: a 256-bin histogram pass serialises on one
-// or two bins).
-__device__ uint32_t block_select(const uint32_t (&v)[NPIX / DESC_THREADS], uint32_t rank, uint32_t (*red)[8])
+// #{v[i] < t}: compare + predicated add, 2 instructions per value
+template <int NV>
+__device__ __forceinline__ uint32_t count_below(const uint32_t (&v)[NV], uint32_t t)
 {
-    uint32_t ans = 0;
-    for (int bit = 30; bit >= 0; bit--) {
-        const uint32_t t = ans | (1u << bit);
-        uint32_t c = 0;
+    uint32_t c = 0;
 #pragma unroll
-        for (int i = 0; i < NPIX / DESC_THREADS; i++)      // compare + predicated add: 2 instructions per value
-            asm("{ .reg .pred p; setp.lt.u32 p, %1, %2; @p add.u32 %0, %0, 1; }" : "+r"(c) : "r"(v[i]), "r"(t));
-        if (block_sum(c, red[bit & 1]) <= rank) ans = t;
+    for (int i = 0; i < NV; i++)
+        asm("{ .reg .pred p; setp.lt.u32 p, %1, %2; @p add.u32 %0, %0, 1; }" : "+r"(c) : "r"(v[i]), "r"(t));
+    return c;
+}
+
+// exact k-th smallest (0-based rank) of the 4096 non-negative floats held 16 per thread (as uint bits; non-negative
+// floats order like their bit patterns): the largest t with #{v < t} <= rank, built bit by bit from the top with
+// block-wide counts -- no shared-memory histogram (the top byte of a patch's gradient magnitudes is almost constant: a
+// 256-bin histogram pass serialises on one or two bins).  Every count narrows the interval the answer lies in and
+// tells how many values are left inside it, so the values are thinned out as the interval shrinks (round 1 counted
+// all 4096 values 31 times: 1540 of the kernel's 6340 instructions per thread):
+//   stage 1  bits for which ans | bit exceeds the largest value are decided without a count; the others count the 16
+//            register values per thread, until <= SEL_LIST values are left in the interval;
+//   stage 2  those are compacted into shared memory (`list`), 4 per thread, and counted from there until <= 32 are left;
+//   stage 3  those go to a 32-entry list that every warp holds one per lane: the remaining bits are warp ballots, no
+//            block barrier.
+// Values that repeat past these limits (a flat patch) simply stay in the earlier stage down to bit 0.
+// `par` is the buffer of `red` the next block reduction uses (they alternate, see block_sum); sel[0] = sel[1] = 0 on
+// entry (the list lengths), sel[4..36) is the stage-3 list.
+#define SEL_LIST 1024
+__device__ uint32_t block_select(const uint32_t (&v)[NPIX / DESC_THREADS], uint32_t rank, uint32_t vmax, uint32_t (*red)[8],
+                                 int &par, uint32_t *list, uint32_t *sel)
+{
+    uint32_t ans = 0, lo = 0, hi = NPIX;           // lo = #{v < ans}, hi = #{v < ans + 2^(bit + 1)}
+    int bit = 30;
+    for (; bit >= 0 && hi - lo > SEL_LIST; bit--) {
+        const uint32_t t = ans | (1u << bit);
+        if (t > vmax) continue;                    // #{v < t} = NPIX > rank
+        const uint32_t c = block_sum(count_below(v, t), red[par]);
+        par ^= 1;
+        if (c <= rank) { ans = t; lo = c; }
+        else hi = c;
+    }
+    if (bit < 0) return ans;
+    // stage 2: the hi - lo values in [ans, ans + span)
+    uint32_t span = 2u << bit;
+    uint32_t mine = 0;
+#pragma unroll
+    for (int i = 0; i < NPIX / DESC_THREADS; i++) mine += (v[i] - ans < span);
+    uint32_t pos = mine ? atomicAdd(&sel[0], mine) : 0u;
+#pragma unroll
+    for (int i = 0; i < NPIX / DESC_THREADS; i++)
+        if (v[i] - ans < span) list[pos++] = v[i];
+    __syncthreads();
+    const uint32_t nc = hi - lo, r2 = rank - lo;
+    uint32_t u[SEL_LIST / DESC_THREADS];
+#pragma unroll
+    for (int j = 0; j < SEL_LIST / DESC_THREADS; j++) {
+        const uint32_t idx = threadIdx.x + DESC_THREADS * j;
+        u[j] = idx < nc ? list[idx] : 0xffffffffu;
+    }
+    uint32_t lo2 = 0, hi2 = nc;
+    for (; bit >= 0 && hi2 - lo2 > 32; bit--) {
+        const uint32_t t = ans | (1u << bit);
+        const uint32_t c = block_sum(count_below(u, t), red[par]);
+        par ^= 1;
+        if (c <= r2) { ans = t; lo2 = c; }
+        else hi2 = c;
+    }
+    if (bit < 0) return ans;
+    // stage 3: the hi2 - lo2 <= 32 values in [ans, ans + span), one per lane in every warp
+    span = 2u << bit;
+    mine = 0;
+#pragma unroll
+    for (int j = 0; j < SEL_LIST / DESC_THREADS; j++) mine += (u[j] - ans < span);
+    pos = mine ? atomicAdd(&sel[1], mine) : 0u;
+#pragma unroll
+    for (int j = 0; j < SEL_LIST / DESC_THREADS; j++)
+        if (u[j] - ans < span) sel[4 + pos++] = u[j];
+    __syncthreads();
+    const uint32_t n3 = hi2 - lo2, r3 = r2 - lo2, lane = threadIdx.x & 31;
+    const uint32_t x = lane < n3 ? sel[4 + lane] : 0xffffffffu;
+    for (; bit >= 0; bit--) {
+        const uint32_t t = ans | (1u << bit);
+        if ((uint32_t)__popc(__ballot_sync(0xffffffffu, x < t)) <= r3) ans = t;
     }
     return ans;
 }
@@ -160,13 +226,17 @@ k_desc(const uint8_t *__restrict__ patches, const int32_t *__restrict__ ids, int
        int n_slots, DescParams prm, float *__restrict__ out0, float *__restrict__ out1,
        float *__restrict__ inv_scale)
 {
-    __shared__ __align__(16) float s_a[PS * OROW];     // PS * SROW while blurring, PS * OROW as output staging
-    __shared__ __align__(16) float s_b[PS * OROW];
+    // s_a, s_b: PS * SROW each while blurring (s_b then holds block_select's list), PS * OROW each as output staging of
+    // the fp32 rows; the fp16 planes stage through both as one [8 bins][TROW] tile of packed hi | lo << 16 words
+    __shared__ __align__(16) float s_ab[2 * PS * OROW];
     __shared__ __align__(16) uint32_t s_red[2][8];
     __shared__ __align__(16) uint8_t s_bin[NPIX];
+    __shared__ uint32_t s_sel[36];
+    float *const s_a = s_ab, *const s_b = s_ab + PS * OROW;
 
     const int slot = blockIdx.x;
     const int tid = threadIdx.x;
+    if (tid < 2) s_sel[tid] = 0u;           // list lengths of block_select (barriers follow before it runs)
     // slots beyond n_slots are padding rows of the GEMM operand: write zeros
     const bool valid = slot < n_slots;
     if (!valid) {
@@ -261,7 +331,12 @@ k_desc(const uint8_t *__restrict__ patches, const int32_t *__restrict__ ids, int
         if (k <= 1) k = 1;
         float gamma = aleph - (float)k;
         gamma = fminf(fmaxf(gamma, 0.f), 1.f);
-        const uint32_t v1 = block_select(magu, (uint32_t)(k - 1), s_red);      // S[k-1]
+        uint32_t vmax = 0;
+#pragma unroll
+        for (int i = 0; i < NPIX / DESC_THREADS; i++) vmax = max(vmax, magu[i]);
+        vmax = block_max(vmax, s_red[0]);
+        int par = 1;
+        const uint32_t v1 = block_select(magu, (uint32_t)(k - 1), vmax, s_red, par, reinterpret_cast<uint32_t *>(s_b), s_sel);      // S[k-1]
         // S[k]: v1 again if duplicated past rank k, else the smallest value above v1
         uint32_t cnt = 0, mn = 0x7f800000u;
 #pragma unroll
@@ -269,7 +344,8 @@ k_desc(const uint8_t *__restrict__ patches, const int32_t *__restrict__ ids, int
             cnt += (magu[i] <= v1);
             if (magu[i] > v1) mn = min(mn, magu[i]);
         }
-        cnt = block_sum(cnt, s_red[1]);        // block_select ended on s_red[0]
+        __syncthreads();                       // whichever buffer block_select ended on
+        cnt = block_sum(cnt, s_red[1]);
         mn = block_min(mn, s_red[0]);
         const uint32_t v2 = (cnt >= (uint32_t)(k + 1)) ? v1 : mn;
         // two rounded products and a rounded sum (the reference builds without -march: no contraction)
@@ -301,35 +377,81 @@ k_desc(const uint8_t *__restrict__ patches, const int32_t *__restrict__ ids, int
         return;
     }
 
-    // K-major row layouts: stage (v1, v2, bin1) per pixel in shared memory (s_a / s_b are free once
-    // every thread has its gradients), then each thread assembles 8 consecutive pixels of a bin row
-    // and writes 16 bytes per plane.
-    float pscale = 1.0f;       // fp16 planes: power-of-two scale of this patch
-    float mx = 0.f;
+    if (MODE == DESC_OUT_SPLIT) {
+        // fp16 planes.  A row of the output (slot, bin) is zero except where a pixel's bin1 or bin2 is that bin, so
+        // instead of selecting per (bin, pixel) in registers (8 x 8 x 4 selects per 8 pixels: 1 900 instructions per
+        // thread in round 1) every pixel scatters its two packed words (hi | lo << 16) into a zeroed shared-memory
+        // tile [8 bins][TROW] and the rows are copied out, 8 pixels = 16 bytes per plane at a time.  The tile takes a
+        // quarter of the patch (16 x, all y) at a time; its row index q = pl + 4 * (pl >> 6) pads every x by 4 words so
+        // that 8 threads reading the 8 x of one pixel block hit different banks.
+        constexpr int TROW = 16 * OROW;             // 1088 words per bin
+        static_assert(8 * TROW == 2 * PS * OROW, "tile = s_a + s_b");
+        uint32_t *const tile = reinterpret_cast<uint32_t *>(s_ab);
+        float mx = 0.f;
+#pragma unroll
+        for (int i = 0; i < NPIX / DESC_THREADS; i++) mx = fmaxf(mx, prm.bnorm ? mag[i] * scale : mag[i]);
+        // the barrier inside: every thread is past its gradient reads of s_a and block_select's list in s_b
+        mx = __uint_as_float(block_max(__float_as_uint(mx), s_red[1]));     // non-negative floats order as uints
+        float pscale = 1.0f;                        // power-of-two scale of this patch
+        if (mx > 0.f && isfinite(mx)) pscale = exp2f((float)(14 - ilogbf(mx)));
+        if (tid == 0) inv_scale[slot] = 1.0f / pscale;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            if (k) __syncthreads();                 // the rows of quarter k - 1 have been read
+            for (int i = tid; i < 8 * TROW / 4; i += DESC_THREADS) reinterpret_cast<uint4 *>(tile)[i] = make_uint4(0u, 0u, 0u, 0u);
+            __syncthreads();
+#pragma unroll
+            for (int ii = 0; ii < 4; ii++) {
+                const int i = 4 * k + ii;
+                const int pl = tid + DESC_THREADS * ii;              // pixel p = 1024 k + pl
+                const float g = prm.bnorm ? mag[i] * scale : mag[i];
+                const float s1 = ((1.0f - off1[i]) * g) * pscale, s2 = (off1[i] * g) * pscale;
+                const __half x1 = __float2half_rn(s1), x2 = __float2half_rn(s2);
+                const uint32_t w1 = (uint32_t)__half_as_ushort(x1) | ((uint32_t)__half_as_ushort(__float2half_rn(s1 - __half2float(x1))) << 16);
+                const uint32_t w2 = (uint32_t)__half_as_ushort(x2) | ((uint32_t)__half_as_ushort(__float2half_rn(s2 - __half2float(x2))) << 16);
+                const int b1 = (int)((binp[i >> 3] >> (4 * (i & 7))) & 15u);
+                const int b2 = (b1 + 1 > nb - 1) ? 0 : b1 + 1;
+                const int q = pl + 4 * (pl >> 6);
+                tile[b1 * TROW + q] = w1;
+                tile[b2 * TROW + q] = w2;
+            }
+            __syncthreads();
+#pragma unroll
+            for (int m = 0; m < 4; m++) {
+                // (bin, group of 8 pixels = one x, 8 consecutive y); 8 consecutive threads take the 8 x of one pixel
+                // block (dlco_kperm order: they write its 128 bytes together, a warp writes 4 adjacent blocks)
+                const int b = 2 * m + (tid >> 7), g = 128 * k + (tid & 127);
+                const int p0 = ((((g >> 6) << 3) | (g & 7)) << 6) | (((g >> 3) & 7) << 3);
+                const int pl0 = p0 - 1024 * k;
+                const uint32_t *src_w = tile + b * TROW + pl0 + 4 * (pl0 >> 6);
+                const uint4 wa = *reinterpret_cast<const uint4 *>(src_w), wb = *reinterpret_cast<const uint4 *>(src_w + 4);
+                const size_t o = ((size_t)slot * 8 + b) * NPIX + dlco_kperm(p0);      // 8 x 8 pixel blocks, see kernels.h
+                *reinterpret_cast<uint4 *>(reinterpret_cast<__half *>(out0) + o) =
+                    make_uint4(__byte_perm(wa.x, wa.y, 0x5410), __byte_perm(wa.z, wa.w, 0x5410),
+                               __byte_perm(wb.x, wb.y, 0x5410), __byte_perm(wb.z, wb.w, 0x5410));
+                *reinterpret_cast<uint4 *>(reinterpret_cast<__half *>(out1) + o) =
+                    make_uint4(__byte_perm(wa.x, wa.y, 0x7632), __byte_perm(wa.z, wa.w, 0x7632),
+                               __byte_perm(wb.x, wb.y, 0x7632), __byte_perm(wb.z, wb.w, 0x7632));
+            }
+        }
+        return;
+    }
+
+    // fp32 rows (DESC_OUT_ROWS): stage (v1, v2, bin1) per pixel in shared memory (s_a / s_b are free once every thread
+    // has its gradients), then each thread assembles 8 consecutive pixels of a bin row and writes 32 bytes.
     __syncthreads();           // all gradient reads of s_a are done (needed when bnorm = 0)
 #pragma unroll
     for (int i = 0; i < NPIX / DESC_THREADS; i++) {
         const int p = tid + DESC_THREADS * i;
         const float g = prm.bnorm ? mag[i] * scale : mag[i];
-        mx = fmaxf(mx, g);
         s_a[p + 4 * (p >> 6)] = (1.0f - off1[i]) * g;
         s_b[p + 4 * (p >> 6)] = off1[i] * g;
         s_bin[p] = (uint8_t)((binp[i >> 3] >> (4 * (i & 7))) & 15u);
     }
-    if (MODE == DESC_OUT_SPLIT) {
-        mx = __uint_as_float(block_max(__float_as_uint(mx), s_red[1]));     // non-negative floats order as uints
-        if (mx > 0.f && isfinite(mx)) pscale = exp2f((float)(14 - ilogbf(mx)));
-        if (tid == 0) inv_scale[slot] = 1.0f / pscale;
-    } else {
-        __syncthreads();
-    }
+    __syncthreads();
 #pragma unroll
     for (int k = 0; k < NPIX / 8 / DESC_THREADS; k++) {
-        // group of 8 pixels (one x, 8 consecutive y).  Plain rows: consecutive threads take consecutive groups.
-        // fp16 planes in dlco_kperm order: 8 consecutive threads take the 8 x of one pixel block, so that they
-        // write its 128 bytes together and a warp writes 4 adjacent blocks.
-        const int g = tid + DESC_THREADS * k;
-        const int p0 = MODE == DESC_OUT_SPLIT ? ((((g >> 6) << 3) | (g & 7)) << 6) | (((g >> 3) & 7) << 3) : 8 * g;
+        const int p0 = 8 * (tid + DESC_THREADS * k);       // 8 pixels: one x, 8 consecutive y
         const int q0 = p0 + 4 * (p0 >> 6);
         float a1[8], a2[8];
         *reinterpret_cast<float4 *>(a1) = *reinterpret_cast<const float4 *>(s_a + q0);
@@ -343,45 +465,17 @@ k_desc(const uint8_t *__restrict__ patches, const int32_t *__restrict__ ids, int
             b1[j] = (int)(((j < 4 ? bb.x : bb.y) >> (8 * (j & 3))) & 255u);
             b2[j] = (b1[j] + 1 > nb - 1) ? 0 : b1[j] + 1;
         }
-        if (MODE == DESC_OUT_ROWS) {
 #pragma unroll
-            for (int b = 0; b < 8; b++) {
-                float v[8];
-#pragma unroll
-                for (int j = 0; j < 8; j++) {
-                    v[j] = (b == b1[j]) ? a1[j] : 0.f;
-                    if (b == b2[j]) v[j] = a2[j];
-                }
-                float4 *dst = reinterpret_cast<float4 *>(out0 + ((size_t)slot * 8 + b) * NPIX + p0);
-                dst[0] = make_float4(v[0], v[1], v[2], v[3]);
-                dst[1] = make_float4(v[4], v[5], v[6], v[7]);
-            }
-        } else {
-            uint32_t h1[8], l1[8], h2[8], l2[8];       // fp16 bit patterns
+        for (int b = 0; b < 8; b++) {
+            float v[8];
 #pragma unroll
             for (int j = 0; j < 8; j++) {
-                const float s1 = a1[j] * pscale, s2 = a2[j] * pscale;
-                const __half x1 = __float2half_rn(s1), x2 = __float2half_rn(s2);
-                h1[j] = __half_as_ushort(x1);
-                h2[j] = __half_as_ushort(x2);
-                l1[j] = __half_as_ushort(__float2half_rn(s1 - __half2float(x1)));
-                l2[j] = __half_as_ushort(__float2half_rn(s2 - __half2float(x2)));
+                v[j] = (b == b1[j]) ? a1[j] : 0.f;
+                if (b == b2[j]) v[j] = a2[j];
             }
-#pragma unroll
-            for (int b = 0; b < 8; b++) {
-                uint32_t hv[8], lv[8];
-#pragma unroll
-                for (int j = 0; j < 8; j++) {
-                    hv[j] = (b == b1[j]) ? h1[j] : 0u;
-                    lv[j] = (b == b1[j]) ? l1[j] : 0u;
-                    if (b == b2[j]) { hv[j] = h2[j]; lv[j] = l2[j]; }
-                }
-                const size_t o = ((size_t)slot * 8 + b) * NPIX + dlco_kperm(p0);      // 8 x 8 pixel blocks, see kernels.h
-                *reinterpret_cast<uint4 *>(reinterpret_cast<__half *>(out0) + o) =
-                    make_uint4(hv[0] | (hv[1] << 16), hv[2] | (hv[3] << 16), hv[4] | (hv[5] << 16), hv[6] | (hv[7] << 16));
-                *reinterpret_cast<uint4 *>(reinterpret_cast<__half *>(out1) + o) =
-                    make_uint4(lv[0] | (lv[1] << 16), lv[2] | (lv[3] << 16), lv[4] | (lv[5] << 16), lv[6] | (lv[7] << 16));
-            }
+            float4 *dst = reinterpret_cast<float4 *>(out0 + ((size_t)slot * 8 + b) * NPIX + p0);
+            dst[0] = make_float4(v[0], v[1], v[2], v[3]);
+            dst[1] = make_float4(v[4], v[5], v[6], v[7]);
         }
     }
 }
