@@ -667,7 +667,7 @@ def main():
     avg_ms = pool_ms / max(pool_n, 1)
     issued_tflops = issued_per_step * prof_steps / (pool_ms * 1e-3) / 1e12 if pool_n else None
     dense_equiv_tflops = FLOP_PER_PAIR * n_pairs * prof_steps / (pool_ms * 1e-3) / 1e12 if pool_n else None
-    traffic, traffic_src = ncu_traffic("k_pool_fulldist<0>")
+    traffic, traffic_src = ncu_traffic("k_pool_fulldist<0")
     roofline = {
         "bound": "tensor", "kernel": "k_pool_fulldist (tcgen05 kind::f16, 3 fp16 passes = fp32-equivalent)",
         "achieved": issued_tflops, "peak": bf16, "unit": "TFLOP/s",
