@@ -171,6 +171,7 @@ int main(int argc, char **argv)
         unsigned int step = 0;
         double t_train = now_sec();
         const double t_all = now_sec();
+        double t_factor = 0.0, t_validate = 0.0, t_stats = 0.0;      // where the validation points spend their time
         n_iter = max_iters_cap(n_iter);                    // DLCO_MAX_ITERS, see tools/common.hpp
         for (unsigned int t = 0; t <= n_iter; t++) {
             if (prox_sign)
@@ -184,11 +185,14 @@ int main(int argc, char **argv)
                                             d_work.p),
                       "dlco_pj_rda_step_grid");
             if (step == log_step) {
+                ctx.sync();                                    // the iterations queued so far: training time, not validation
+                const double t_f = now_sec();
                 if (prox_sign)      // W of the projected A for validation, statistics and the saved model (synchronises)
                     check(dlco_pj_factor_grid(ctx.h, D, n_cfg, d_A.p, d_rank.p, d_W.p, (int64_t)DD, d_work.p), "dlco_pj_factor_grid");
                 else
                     check(dlco_pj_grid_check(ctx.h, n_cfg), "dlco_pj_grid_check");      // synchronises
                 d_rank.download(ranks.data(), n_cfg);
+                t_factor += now_sec() - t_f;
                 const double ttime = now_sec() - t_train;
                 for (int c = 0; c < n_cfg; c++) {
                     Cfg &k = cfgs[c];
@@ -200,6 +204,7 @@ int main(int argc, char **argv)
                                            d_neg.p + sp.n_neg_trn, (int64_t)sp.n_neg_val(), Wc, rank, Ac, k.mu, &loss, &regul),
                           "dlco_pj_validate");
                     const double vtime = now_sec() - t_valid;
+                    t_validate += vtime;
                     const float obj = loss + regul;
                     const int w_rows = rank > 0 ? rank : D;
                     if (obj < k.obj_best) {
@@ -209,6 +214,7 @@ int main(int argc, char **argv)
                                 loss, regul, obj, k.obj_best, w_rows, k.rows_best, ttime, vtime);
                         float fpr95 = 0.f;
                         double auc = 0.0;
+                        const double t_s = now_sec();
                         check(dlco_pj_patchdist(ctx.h, d_dists.p, (int64_t)df.n, D, D, Wc, rank, d_pd.p), "dlco_pj_patchdist");
                         check(dlco_roc_stats(ctx.h, d_pd.p, d_labels.p, (int64_t)df.n, &fpr95, &auc), "dlco_roc_stats");
                         const bool keep = k.auc_best <= auc && k.fpr95_best >= fpr95;       // :560-566
@@ -221,6 +227,7 @@ int main(int argc, char **argv)
                             d_W.download(k.W_save.data(), k.W_save.size(), c * DD);
                             d_A.download(k.A_save.data(), DD, c * DD);
                         }
+                        t_stats += now_sec() - t_s;
                         fprintf(k.log, "Stat: Dim [%i] AUC: %.6f (%.6f) FPR95: %.2f (%.2f)%s\n", rank, auc, k.auc_best, fpr95 * 100,
                                 k.fpr95_best * 100, keep ? " [saved]" : "");
                     } else {
@@ -252,6 +259,8 @@ int main(int argc, char **argv)
         }
         printf("pj-sweep: %d grid points x %u iterations in %.2f s (%.1f config-iterations/s)\n", n_cfg, n_iter + 1, secs,
                (double)n_cfg * (n_iter + 1) / secs);
+        printf("pj-sweep: validation points took %.2f s (factor / sync %.2f, validate %.2f, statistics + model copies %.2f)\n",
+               t_factor + t_validate + t_stats, t_factor, t_validate, t_stats);
         return 0;
     } catch (const std::exception &e) {
         fprintf(stderr, "\npj-sweep: %s\n", e.what());
