@@ -211,6 +211,29 @@ def test_fulldist_full_bank_three_batches(gpu_ctx, synth, full_bank):
         assert np.abs(got[k, rings] - want).max() / scale <= DIST_RTOL, k
 
 
+def test_pool_kernel_variants_are_bit_identical(gpu_ctx, tmp_path):
+    """The pooling kernel's tuning knobs are read once per process: whole-chunk stages (DLCO_POOL_SPLIT=1), other
+    pair-tile groupings of the work schedule (DLCO_POOL_GROUP_TILES), get_desc over several batches
+    (DLCO_FULLDIST_DESC_GROUP) and the SIMT cross-check path must all give the default's distances -- the first three
+    bit for bit (same products, same accumulation order), the SIMT path within the distance bar."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    outs = {}
+    for name, env in (("default", {}), ("split1", {"DLCO_POOL_SPLIT": "1"}), ("group3", {"DLCO_POOL_GROUP_TILES": "3"}),
+                      ("group16", {"DLCO_POOL_GROUP_TILES": "16"}), ("desc3", {"DLCO_FULLDIST_DESC_GROUP": "3"})):
+        path = str(tmp_path / (name + ".npy"))
+        e = dict(os.environ)
+        e.update(env)
+        r = subprocess.run([sys.executable, os.path.join(root, "tools", "pool_ab.py"), path, "--quick"], env=e,
+                           stdout=subprocess.PIPE, stderr=subprocess.STDOUT, timeout=300)
+        assert r.returncode == 0, r.stdout.decode()[-2000:]
+        outs[name] = np.load(path)
+    assert np.isfinite(outs["default"]).all() and outs["default"].shape == (600, 5120)
+    for name in ("split1", "group3", "group16", "desc3"):
+        assert np.array_equal(outs[name], outs["default"]), name
+
+
 def test_fulldist_identical_patches_give_zero(gpu_ctx, synth, small_bank):
     patches, pid, _ = synth
     filt, _ = small_bank

@@ -1,7 +1,8 @@
 """A/B of a pooling-kernel variant selected by an environment variable read once per process (DLCO_POOL_SPLIT=1|2,
 DLCO_POOL_IMPL, ...): run once per setting; each run saves its distances (compare with numpy.array_equal: a variant
 must not change a bit) and prints the time of 16 384 pairs through dlco_fulldist_build.
-    DLCO_POOL_SPLIT=1 python tools/pool_ab.py a.npy;  python tools/pool_ab.py b.npy"""
+    DLCO_POOL_SPLIT=1 python tools/pool_ab.py a.npy;  python tools/pool_ab.py b.npy
+The first process on a cold GPU measures ~5 % slower than the following ones: interleave the settings (a b a b)."""
 import importlib
 import os
 import sys
@@ -19,7 +20,8 @@ def main():
     ctx = B.Context(0)
     bank = ctx.bank_analytic(B.ring_params())
     rng = np.random.default_rng(3)
-    n_patches, n_pairs = 4096, 8192 * 2 + 300
+    quick = len(sys.argv) > 2 and sys.argv[2] == "--quick"        # distances of 600 pairs only (tests/test_gpu_kernels.py)
+    n_patches, n_pairs = 4096, (600 if quick else 8192 * 2 + 300)
     patches = torch.from_numpy(rng.integers(0, 256, (n_patches, 64, 64), dtype=np.uint8)).to(ctx.device)
     idx = np.zeros((n_pairs, 4), np.int32)
     idx[:, 0] = rng.integers(0, n_patches, n_pairs)
@@ -28,6 +30,8 @@ def main():
     out = ctx.fulldist_build(bank, patches, d_i)
     torch.cuda.synchronize()
     np.save(sys.argv[1], out.cpu().numpy())
+    if quick:
+        return
     ts = []
     for _ in range(5):
         torch.cuda.synchronize()
