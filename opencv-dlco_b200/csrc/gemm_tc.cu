@@ -6,7 +6,7 @@
 // over all batch entries (the (mu, gamma) configurations of a pj-learn sweep); 3 stages of 64 KB.
 // The kernel is bound by the operand bytes in flight from L2, not by the tensor pipe: 128 x 192
 // tiles with two 80 KB stages were slower although they read fewer bytes per flop.
-// Roles: warp 0 = TMA producer, warp 1 = MMA issuer + TMEM owner, warps 2..9 = epilogue (drains).
+// Roles: warp 0 = TMA producer, warp 1 = MMA issuer + TMEM owner, warps 2..17 = epilogue (drains).
 #include "common.cuh"
 #include "kernels.h"
 #include <cuda_fp16.h>
@@ -24,12 +24,25 @@ constexpr int STAGE_BYTES = 2 * A_BYTES + 2 * B_BYTES;
 // per epilogue warp: a 16-column x 32-row block of packed (hi | lo << 16) plane words, row stride 33 words, for the
 // transposed ("mirror") plane stores of the symmetric products whose lower tiles are skipped
 constexpr int TSM_WORDS = 16 * 33;
-constexpr int TSM_BYTES = 8 * TSM_WORDS * 4;
+#ifndef DLCO_GEMM_EPI_WARPS
+#define DLCO_GEMM_EPI_WARPS 8
+#endif
+constexpr int EPI_WARPS = DLCO_GEMM_EPI_WARPS;          // 8 or 16 (measured the same: 3.02 ms per 45-configuration sweep iteration)
+constexpr int TSM_BYTES = EPI_WARPS * TSM_WORDS * 4;
 constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256 + TSM_BYTES;
-constexpr int EPI_WARPS = 8;
 constexpr int NTHREADS = 64 + EPI_WARPS * 32;
 constexpr int TMEM_COLS = 2 * BN <= 256 ? 256 : 512;   // two BN-column accumulators
-constexpr int EN = BN / 2;                   // columns per epilogue warp
+constexpr int EN = BN / (EPI_WARPS / 4);     // columns per epilogue warp
+static_assert(EN % 32 == 0 && SMEM_BYTES <= 227 * 1024, "epilogue slices / shared memory");
+
+// one 32-byte store per lane (STG.256): a full sector, half the store instructions of two 16-byte ones -- the epilogue's
+// row-per-lane stores were throttled on the load/store queue (ncu: lg_throttle the top stall of the epilogue warps)
+__device__ __forceinline__ void st_global_v8(void *p, uint4 a, uint4 b)
+{
+    asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(a.x), "r"(a.y), "r"(a.z), "r"(a.w), "r"(b.x),
+                 "r"(b.y), "r"(b.z), "r"(b.w)
+                 : "memory");
+}
 
 struct __align__(64) GemmMaps {
     CUtensorMap a_hi, a_lo, b_hi, b_lo;
@@ -177,7 +190,7 @@ k_gemm3x_nt(const __grid_constant__ GemmMaps maps, const __grid_constant__ GemmT
             }
         }
     } else {
-        // epilogue warps 2..9: TMEM lane quarter = warp % 4, column half = (warp - 2) / 4
+        // epilogue warps 2..: TMEM lane quarter = warp % 4, column slice = (warp - 2) / 4
         const int q = warp & 3, half = (warp - 2) >> 2;
         const int n_flush = (k_chunks + FLUSH - 1) / FLUSH;
         uint32_t it = 0;
@@ -225,6 +238,8 @@ k_gemm3x_nt(const __grid_constant__ GemmMaps maps, const __grid_constant__ GemmT
                 __half *ph = reinterpret_cast<__half *>(epi.phi) + ((size_t)g * epi.rows_pad + row) * epi.k_pad;
                 __half *pl = reinterpret_cast<__half *>(epi.plo) + ((size_t)g * epi.rows_pad + row) * epi.k_pad;
                 uint32_t *tsm = reinterpret_cast<uint32_t *>(smem + STAGES * STAGE_BYTES + 256) + (warp - 2) * TSM_WORDS;
+                const bool wide = (epi.k_pad & 15) == 0 && ((reinterpret_cast<uintptr_t>(epi.phi) | reinterpret_cast<uintptr_t>(epi.plo)) & 31) == 0;
+                uint4 h_even = make_uint4(0u, 0u, 0u, 0u), l_even = h_even;
 #pragma unroll
                 for (int e = 0; e < EN; e += 8) {
                     if (col0 + e + 8 > epi.k_pad) break;                 // warp-uniform
@@ -252,13 +267,25 @@ k_gemm3x_nt(const __grid_constant__ GemmMaps maps, const __grid_constant__ GemmT
                         const __half l = __float2half_rn(sv - __half2float(h));
                         pk[u] = (uint32_t)__half_as_ushort(h) | ((uint32_t)__half_as_ushort(l) << 16);
                     }
-                    if (rok) {
-                        *reinterpret_cast<uint4 *>(ph + col0 + e) =
-                            make_uint4(__byte_perm(pk[0], pk[1], 0x5410), __byte_perm(pk[2], pk[3], 0x5410),
-                                       __byte_perm(pk[4], pk[5], 0x5410), __byte_perm(pk[6], pk[7], 0x5410));
-                        *reinterpret_cast<uint4 *>(pl + col0 + e) =
-                            make_uint4(__byte_perm(pk[0], pk[1], 0x7632), __byte_perm(pk[2], pk[3], 0x7632),
-                                       __byte_perm(pk[4], pk[5], 0x7632), __byte_perm(pk[6], pk[7], 0x7632));
+                    {
+                        const uint4 hq = make_uint4(__byte_perm(pk[0], pk[1], 0x5410), __byte_perm(pk[2], pk[3], 0x5410),
+                                                    __byte_perm(pk[4], pk[5], 0x5410), __byte_perm(pk[6], pk[7], 0x5410));
+                        const uint4 lq = make_uint4(__byte_perm(pk[0], pk[1], 0x7632), __byte_perm(pk[2], pk[3], 0x7632),
+                                                    __byte_perm(pk[4], pk[5], 0x7632), __byte_perm(pk[6], pk[7], 0x7632));
+                        // 16 columns = 32 bytes per plane and store where the pitch allows (warp-uniform conditions)
+                        const bool pair = wide && col0 + (e | 8) + 8 <= epi.k_pad;
+                        if (pair && !(e & 8)) {
+                            h_even = hq;
+                            l_even = lq;
+                        } else if (rok) {
+                            if (pair) {
+                                st_global_v8(ph + col0 + e - 8, h_even, hq);
+                                st_global_v8(pl + col0 + e - 8, l_even, lq);
+                            } else {
+                                *reinterpret_cast<uint4 *>(ph + col0 + e) = hq;
+                                *reinterpret_cast<uint4 *>(pl + col0 + e) = lq;
+                            }
+                        }
                     }
                     if (mirror) {
 #pragma unroll
@@ -275,14 +302,23 @@ k_gemm3x_nt(const __grid_constant__ GemmMaps maps, const __grid_constant__ GemmT
                                 const size_t mo = ((size_t)g * epi.rows_pad + col) * epi.k_pad + r0;
                                 __half *mh = reinterpret_cast<__half *>(epi.phi) + mo, *ml = reinterpret_cast<__half *>(epi.plo) + mo;
                                 if (r0 + 16 <= M) {
-                                    reinterpret_cast<uint4 *>(mh)[0] = make_uint4(__byte_perm(w[0], w[1], 0x5410), __byte_perm(w[2], w[3], 0x5410),
-                                                                                 __byte_perm(w[4], w[5], 0x5410), __byte_perm(w[6], w[7], 0x5410));
-                                    reinterpret_cast<uint4 *>(mh)[1] = make_uint4(__byte_perm(w[8], w[9], 0x5410), __byte_perm(w[10], w[11], 0x5410),
-                                                                                 __byte_perm(w[12], w[13], 0x5410), __byte_perm(w[14], w[15], 0x5410));
-                                    reinterpret_cast<uint4 *>(ml)[0] = make_uint4(__byte_perm(w[0], w[1], 0x7632), __byte_perm(w[2], w[3], 0x7632),
-                                                                                 __byte_perm(w[4], w[5], 0x7632), __byte_perm(w[6], w[7], 0x7632));
-                                    reinterpret_cast<uint4 *>(ml)[1] = make_uint4(__byte_perm(w[8], w[9], 0x7632), __byte_perm(w[10], w[11], 0x7632),
-                                                                                 __byte_perm(w[12], w[13], 0x7632), __byte_perm(w[14], w[15], 0x7632));
+                                    const uint4 h0 = make_uint4(__byte_perm(w[0], w[1], 0x5410), __byte_perm(w[2], w[3], 0x5410),
+                                                                __byte_perm(w[4], w[5], 0x5410), __byte_perm(w[6], w[7], 0x5410));
+                                    const uint4 h1 = make_uint4(__byte_perm(w[8], w[9], 0x5410), __byte_perm(w[10], w[11], 0x5410),
+                                                                __byte_perm(w[12], w[13], 0x5410), __byte_perm(w[14], w[15], 0x5410));
+                                    const uint4 l0 = make_uint4(__byte_perm(w[0], w[1], 0x7632), __byte_perm(w[2], w[3], 0x7632),
+                                                                __byte_perm(w[4], w[5], 0x7632), __byte_perm(w[6], w[7], 0x7632));
+                                    const uint4 l1 = make_uint4(__byte_perm(w[8], w[9], 0x7632), __byte_perm(w[10], w[11], 0x7632),
+                                                                __byte_perm(w[12], w[13], 0x7632), __byte_perm(w[14], w[15], 0x7632));
+                                    if (wide) {
+                                        st_global_v8(mh, h0, h1);
+                                        st_global_v8(ml, l0, l1);
+                                    } else {
+                                        reinterpret_cast<uint4 *>(mh)[0] = h0;
+                                        reinterpret_cast<uint4 *>(mh)[1] = h1;
+                                        reinterpret_cast<uint4 *>(ml)[0] = l0;
+                                        reinterpret_cast<uint4 *>(ml)[1] = l1;
+                                    }
                                 } else {
 #pragma unroll
                                     for (int j = 0; j < 16; j++)
@@ -299,7 +335,13 @@ k_gemm3x_nt(const __grid_constant__ GemmMaps maps, const __grid_constant__ GemmT
             }
             if (row < M && !(F16 && epi.mode == 2)) {
                 float *crow = C + (size_t)g * c_batch_stride + (size_t)row * ldc + col0;
-                if (col0 + EN <= N && ((reinterpret_cast<uintptr_t>(crow) & 15) == 0)) {
+                if (col0 + EN <= N && ((reinterpret_cast<uintptr_t>(crow) & 31) == 0)) {
+#pragma unroll
+                    for (int e = 0; e < EN; e += 8)
+                        st_global_v8(crow + e,
+                                     make_uint4(__float_as_uint(acc[e]), __float_as_uint(acc[e + 1]), __float_as_uint(acc[e + 2]), __float_as_uint(acc[e + 3])),
+                                     make_uint4(__float_as_uint(acc[e + 4]), __float_as_uint(acc[e + 5]), __float_as_uint(acc[e + 6]), __float_as_uint(acc[e + 7])));
+                } else if (col0 + EN <= N && ((reinterpret_cast<uintptr_t>(crow) & 15) == 0)) {
 #pragma unroll
                     for (int e = 0; e < EN; e += 4)
                         *reinterpret_cast<float4 *>(crow + e) = make_float4(acc[e], acc[e + 1], acc[e + 2], acc[e + 3]);
