@@ -246,7 +246,11 @@ k_gemm3x_nt(const __grid_constant__ GemmMaps maps, const __grid_constant__ GemmT
                     uint32_t pk[8];                                       // hi | lo << 16 per column
                     float ax[8];
                     if (epi.mode == 2) {                                  // aux row: two 16-byte loads where they fit
-                        if (aux && col0 + e + 8 <= N && ((reinterpret_cast<uintptr_t>(aux + col0 + e) & 15) == 0)) {
+                        if (aux && col0 + e + 8 <= N && ((reinterpret_cast<uintptr_t>(aux + col0 + e) & 31) == 0)) {
+                            asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                                         : "=f"(ax[0]), "=f"(ax[1]), "=f"(ax[2]), "=f"(ax[3]), "=f"(ax[4]), "=f"(ax[5]), "=f"(ax[6]), "=f"(ax[7])
+                                         : "l"(aux + col0 + e));
+                        } else if (aux && col0 + e + 8 <= N && ((reinterpret_cast<uintptr_t>(aux + col0 + e) & 15) == 0)) {
                             const float4 a0 = __ldg(reinterpret_cast<const float4 *>(aux + col0 + e));
                             const float4 a1 = __ldg(reinterpret_cast<const float4 *>(aux + col0 + e) + 1);
                             ax[0] = a0.x; ax[1] = a0.y; ax[2] = a0.z; ax[3] = a0.w;
