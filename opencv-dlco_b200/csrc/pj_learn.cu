@@ -618,27 +618,54 @@ extern "C" int dlco_pj_rda_grad_grid_dev(dlco_ctx *ctx, const float *d_dists, in
 
 // K_pj_update for configuration blockIdx.z: same arithmetic as k_pj_update, the per-configuration
 // scalar -sqrt(t+1)/gamma is formed in double and rounded once, as the host version does.
+// Block = the 32 x 32 tile (bi, bj), bi <= bj, and its mirror (bj, bi): both are read and written row-wise (the first
+// version read and wrote the (j, i) elements down a column: 32 sectors per warp access, 131 us per 45 configurations),
+// the transposition goes through shared memory.  Grid ((D + 31) / 32, (D + 31) / 32, nCfg), 256 threads.
 __device__ __forceinline__ void pj_update_body(int D, double t1, float a_avg, float beta, const float *__restrict__ mu,
                                                const float *__restrict__ gamma, const float *__restrict__ dLoss,
                                                float *__restrict__ dfavg, float *__restrict__ A)
 {
-    const int j = blockIdx.x * 32 + (threadIdx.x & 31);
-    const int i = blockIdx.y * 8 + (threadIdx.x >> 5);
-    if (i >= D || j >= D || i > j) return;
+    __shared__ float s_d[32][33], s_a[32][33], s_s[32][33];
+    const int bj = blockIdx.x, bi = blockIdx.y;
+    if (bi > bj) return;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     const int g = blockIdx.z;
     const size_t off = (size_t)g * D * D;
     const float div = (float)(-sqrt(t1) / (double)gamma[g]);
-    const size_t ij = off + (size_t)i * D + j, ji = off + (size_t)j * D + i;
-    const float d_ij = __fadd_rn(__fmul_rn(dfavg[ij], a_avg), __fmul_rn(dLoss[ij], beta));
-    const float d_ji = __fadd_rn(__fmul_rn(dfavg[ji], a_avg), __fmul_rn(dLoss[ji], beta));
-    const float m = (i == j) ? mu[g] : 0.0f;
-    const float a_ij = __fmul_rn(__fadd_rn(d_ij, m), div);
-    const float a_ji = __fmul_rn(__fadd_rn(d_ji, m), div);
-    const float s = __fmul_rn(0.5f, __fadd_rn(a_ij, a_ji));
-    dfavg[ij] = d_ij;
-    dfavg[ji] = d_ji;
-    A[ij] = s;
-    A[ji] = s;
+    const float mu_g = mu[g];
+    // the mirror tile's elements (j, i): rows j of tile bj, columns i of tile bi
+    for (int r = ty; r < 32; r += 8) {
+        const int j = bj * 32 + r, i = bi * 32 + tx;
+        if (i < D && j < D) {
+            const size_t ji = off + (size_t)j * D + i;
+            const float d_ji = __fadd_rn(__fmul_rn(dfavg[ji], a_avg), __fmul_rn(dLoss[ji], beta));
+            s_d[r][tx] = d_ji;
+            s_a[r][tx] = __fmul_rn(__fadd_rn(d_ji, (i == j) ? mu_g : 0.0f), div);
+        }
+    }
+    __syncthreads();
+    for (int r = ty; r < 32; r += 8) {
+        const int i = bi * 32 + r, j = bj * 32 + tx;
+        if (i < D && j < D) {
+            const size_t ij = off + (size_t)i * D + j;
+            const float d_ij = __fadd_rn(__fmul_rn(dfavg[ij], a_avg), __fmul_rn(dLoss[ij], beta));
+            const float a_ij = __fmul_rn(__fadd_rn(d_ij, (i == j) ? mu_g : 0.0f), div);
+            const float s = __fmul_rn(0.5f, __fadd_rn(a_ij, s_a[tx][r]));
+            dfavg[ij] = d_ij;
+            A[ij] = s;
+            s_s[r][tx] = s;
+        }
+    }
+    if (bi == bj) return;                      // a diagonal tile is its own mirror: everything is written
+    __syncthreads();
+    for (int r = ty; r < 32; r += 8) {
+        const int j = bj * 32 + r, i = bi * 32 + tx;
+        if (i < D && j < D) {
+            const size_t ji = off + (size_t)j * D + i;
+            dfavg[ji] = s_d[r][tx];
+            A[ji] = s_s[tx][r];
+        }
+    }
 }
 
 __global__ void __launch_bounds__(256)
@@ -674,7 +701,7 @@ extern "C" int dlco_pj_rda_update_grid(dlco_ctx *ctx, int D, uint64_t t, int szB
     const float a_avg = (float)((double)t / (double)(t + 1));
     const unsigned int den = (unsigned int)szBatch * (unsigned int)szBatch * (unsigned int)(t + 1);
     const float beta = 1.0f / (float)den;
-    dim3 grid((D + 31) / 32, (D + 7) / 8, nCfg);
+    dim3 grid((D + 31) / 32, (D + 31) / 32, nCfg);
     k_pj_update_grid<<<grid, 256, 0, ctx->stream>>>(D, (double)t + 1.0, a_avg, beta, d_mu, d_gamma, d_dLoss, d_dfavg, d_A);
     DLCO_CHECK_LAUNCH(ctx);
     return DLCO_OK;
@@ -903,7 +930,7 @@ static int pj_step_sign_enqueue(dlco_ctx *ctx, const float *d_dists, int64_t ld,
     if (r == DLCO_OK) r = pj_grad_core(ctx, d_dists, ld, D, rows, rows + szBatch, szBatch, nCfg, nullptr, 0, nullptr, d_rank, dLoss, d_A);
     if (r != DLCO_OK) return r;
     if (d_t) {
-        dim3 grid((D + 31) / 32, (D + 7) / 8, nCfg);
+        dim3 grid((D + 31) / 32, (D + 31) / 32, nCfg);
         k_pj_update_grid_dev<<<grid, 256, 0, ctx->stream>>>(D, d_t, (unsigned int)szBatch * (unsigned int)szBatch, d_mu, d_gamma,
                                                             dLoss, d_dfavg, d_A);
         DLCO_CHECK_LAUNCH(ctx);

@@ -160,7 +160,10 @@ k_sign_prep(int D, int rows_pad, int k_pad, const float *__restrict__ in0, const
     const bool tr0 = load_logical(t0, p0, D, i0, j0, sym != 0, tx, ty);
     bool tr1 = false;
     if (MODE == PREP_POLY) tr1 = load_logical(t1, in1 + (size_t)g * dd, D, i0, j0, sym != 0, tx, ty);
-    if (MODE == PREP_SYM || MODE == PREP_FINAL) tr1 = !load_logical(t1, p0, D, j0, i0, sym != 0, tx, ty);
+    // sym(T) needs T^T only inside the diagonal tiles of the GEMM: elsewhere one of (i, j), (j, i) was never computed and
+    // reads as the mirror of the other, so (a + a) / 2 = a and the second block load is skipped
+    const bool own_mirror = (MODE == PREP_SYM || MODE == PREP_FINAL) && sym != 0 && (i0 / 128) != (j0 / DLCO_GEMM_BN) && DLCO_GEMM_BN == 128;
+    if ((MODE == PREP_SYM || MODE == PREP_FINAL) && !own_mirror) tr1 = !load_logical(t1, p0, D, j0, i0, sym != 0, tx, ty);
     __syncthreads();
     float inv_alpha = 0.f, alpha = 0.f, ca = 0.f, cb = 0.f, cc = 0.f;
     if (MODE == PREP_INIT) inv_alpha = sign_inv_alpha(partial, g);
@@ -179,7 +182,7 @@ k_sign_prep(int D, int rows_pad, int k_pad, const float *__restrict__ in0, const
         v[t] = 0.f;
         if (i < D && j < D) {
             const float a = tr0 ? t0[c4 + t][r] : t0[r][c4 + t];           // in0 at (i, j)
-            const float b = tr1 ? t1[c4 + t][r] : t1[r][c4 + t];           // POLY: in1 at (i, j); SYM / FINAL: in0 at (j, i)
+            const float b = own_mirror ? a : (tr1 ? t1[c4 + t][r] : t1[r][c4 + t]);   // POLY: in1 at (i, j); SYM / FINAL: in0 at (j, i)
             if (MODE == PREP_INIT) v[t] = a * inv_alpha;
             else if (MODE == PREP_COPY) v[t] = a;
             else if (MODE == PREP_POLY) v[t] = fmaf(cc, b, fmaf(cb, a, i == j ? ca : 0.f));
