@@ -226,6 +226,92 @@ k_sign_prep(int D, int rows_pad, int k_pad, const float *__restrict__ in0, const
     }
 }
 
+// PREP_SYM for the fp16 route as a kernel of its own (the generic one above reads two blocks through shared memory for
+// every 32 x 32 block of the plane, 54 us per 45 configurations): a block takes the 32 x 32 block (bi, bj), bi <= bj, of
+// the upper triangle, forms v = sym(T) there -- T itself outside the diagonal 128-tiles of the GEMM, (T + T^T) / 2 inside
+// -- and writes both the block and its mirror image: planes (and X when asked) of rows i directly, of rows j transposed
+// through shared memory.  T is read once.  The planes' zero padding (rows and columns >= D) is not touched: PREP_INIT
+// wrote it at the start of the projection.  Same values as k_sign_prep<PREP_SYM, true>, bit for bit.
+__global__ void __launch_bounds__(256)
+k_sign_sym_planes(int D, int rows_pad, int k_pad, const float *__restrict__ T, float pscale, float *__restrict__ out,
+                  __half *__restrict__ hi, __half *__restrict__ lo)
+{
+    __shared__ float t1[32][33];          // the mirror block of T (diagonal tiles only)
+    __shared__ uint32_t tw[32][33];       // packed plane words hi | lo << 16 of v
+    __shared__ float tv[32][33];          // v (only when X is written)
+    const int bj = blockIdx.x, bi = blockIdx.y, g = blockIdx.z;
+    if (bi > bj) return;
+    const int i0 = bi * 32, j0 = bj * 32;
+    const size_t dd = (size_t)D * D;
+    const float *p = T + (size_t)g * dd;
+    const bool diag_tile = (i0 / 128) == (j0 / 128);
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    if (diag_tile && bi != bj) {
+        for (int r = ty; r < 32; r += 8) {
+            const int j = j0 + r, i = i0 + tx;
+            t1[r][tx] = (i < D && j < D) ? p[(size_t)j * D + i] : 0.f;          // T(j, i)
+        }
+    }
+    // thread = (row r, 4 consecutive columns)
+    const int r = threadIdx.x >> 3, c4 = (threadIdx.x & 7) * 4;
+    const int i = i0 + r;
+    float a[4] = {0.f, 0.f, 0.f, 0.f};
+    if (i < D) {
+        const float *src = p + (size_t)i * D + j0 + c4;
+        if (j0 + c4 + 4 <= D && (D & 3) == 0) {
+            const float4 q = *reinterpret_cast<const float4 *>(src);
+            a[0] = q.x; a[1] = q.y; a[2] = q.z; a[3] = q.w;
+        } else {
+            for (int t = 0; t < 4; t++)
+                if (j0 + c4 + t < D) a[t] = src[t];
+        }
+    }
+    if (diag_tile && bi == bj) {          // the block holds its own mirror
+        for (int t = 0; t < 4; t++) tv[r][c4 + t] = a[t];
+    }
+    __syncthreads();
+    float v[4];
+    uint32_t w[4];
+#pragma unroll
+    for (int t = 0; t < 4; t++) {
+        const int j = j0 + c4 + t;
+        v[t] = 0.f;
+        if (i < D && j < D) {
+            if (!diag_tile) v[t] = a[t];
+            else v[t] = 0.5f * (a[t] + (bi == bj ? tv[c4 + t][r] : t1[c4 + t][r]));
+        }
+        const float sv = v[t] * pscale;
+        const __half h = __float2half_rn(sv);
+        const __half l = __float2half_rn(sv - __half2float(h));
+        w[t] = (uint32_t)__half_as_ushort(h) | ((uint32_t)__half_as_ushort(l) << 16);
+    }
+    if (bi == bj) __syncthreads();        // every read of tv is done before it is reused below
+    if (i < D && j0 + c4 < D) {           // D is a multiple of 4 on this path (checked by the launcher)
+        const size_t po = ((size_t)g * rows_pad + i) * k_pad + j0 + c4;
+        *reinterpret_cast<uint2 *>(hi + po) = make_uint2(__byte_perm(w[0], w[1], 0x5410), __byte_perm(w[2], w[3], 0x5410));
+        *reinterpret_cast<uint2 *>(lo + po) = make_uint2(__byte_perm(w[0], w[1], 0x7632), __byte_perm(w[2], w[3], 0x7632));
+        if (out) *reinterpret_cast<float4 *>(out + (size_t)g * dd + (size_t)i * D + j0 + c4) = make_float4(v[0], v[1], v[2], v[3]);
+    }
+    if (bi == bj) return;
+#pragma unroll
+    for (int t = 0; t < 4; t++) {
+        tw[r][c4 + t] = w[t];
+        if (out) tv[r][c4 + t] = v[t];
+    }
+    __syncthreads();
+    // the mirror block: row j = j0 + r, columns i0 + c4 ..
+    const int j = j0 + r;
+    if (j < D && i0 + c4 < D) {
+        const uint32_t m0 = tw[c4][r], m1 = tw[c4 + 1][r], m2 = tw[c4 + 2][r], m3 = tw[c4 + 3][r];
+        const size_t po = ((size_t)g * rows_pad + j) * k_pad + i0 + c4;
+        *reinterpret_cast<uint2 *>(hi + po) = make_uint2(__byte_perm(m0, m1, 0x5410), __byte_perm(m2, m3, 0x5410));
+        *reinterpret_cast<uint2 *>(lo + po) = make_uint2(__byte_perm(m0, m1, 0x7632), __byte_perm(m2, m3, 0x7632));
+        if (out)
+            *reinterpret_cast<float4 *>(out + (size_t)g * dd + (size_t)j * D + i0 + c4) =
+                make_float4(tv[c4][r], tv[c4 + 1][r], tv[c4 + 2][r], tv[c4 + 3][r]);
+    }
+}
+
 // rank[g] = round((D + trace S_g) / 2); a zero matrix (||A||_F = 0) has rank 0
 __global__ void __launch_bounds__(256)
 k_sign_rank(int D, const float *__restrict__ S, const double *__restrict__ partial, int32_t *__restrict__ rank)
@@ -250,6 +336,15 @@ template <int MODE>
 static int sign_prep(dlco_ctx *ctx, bool f16, int D, int nCfg, int rows_pad, int k_pad, const float *in0, const float *in1,
                      const double *partial, int step, int sym, float pscale, float *out, void *hi, void *lo)
 {
+    if (MODE == PREP_SYM && f16 && sym && (D & 3) == 0 && DLCO_GEMM_BN == 128) {
+        static const bool generic = [] { const char *e = getenv("DLCO_SIGN_SYM_GENERIC"); return e && e[0] == '1'; }();
+        if (!generic) {
+            const int nb = (D + 31) / 32;
+            k_sign_sym_planes<<<dim3(nb, nb, nCfg), 256, 0, ctx->stream>>>(D, rows_pad, k_pad, in0, pscale, out, (__half *)hi, (__half *)lo);
+            DLCO_CHECK_LAUNCH(ctx);
+            return DLCO_OK;
+        }
+    }
     dim3 grid(MODE == PREP_FINAL ? (D + 31) / 32 : k_pad / 32, MODE == PREP_FINAL ? (D + 31) / 32 : rows_pad / 32, nCfg);
     if (f16)
         k_sign_prep<MODE, true><<<grid, 256, 0, ctx->stream>>>(D, rows_pad, k_pad, in0, in1, partial, step, sym, pscale, out, hi, lo);

@@ -754,3 +754,25 @@ def test_pj_sweep_sign_prox_matches_oracle_and_eig_route(gpu_ctx):
         fpr_e, auc_e = E.stats(c, int(E.ranks()[c]))
         assert abs(fpr_s - fpr_e) <= 1e-3 and abs(auc_s - auc_e) <= 1e-4      # FPR95 within 0.1 percentage points
     assert int(S.rng_state.cpu().numpy().view(np.uint64)[0]) == st["rng"].state
+
+
+def test_sign_sym_kernel_matches_the_generic_prep(gpu_ctx, tmp_path):
+    """k_sign_sym_planes (csrc/pj_sign.cu: sym(T) written as planes block and mirror block at once) against the generic
+    k_sign_prep<PREP_SYM> it replaced (DLCO_SIGN_SYM_GENERIC=1, read once per process): the projected matrices, sign(A)
+    and the ranks bit for bit, fused and unfused sequences, D a multiple of 128 or not."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    res = {}
+    for name, env in (("new", {}), ("generic", {"DLCO_SIGN_SYM_GENERIC": "1"})):
+        path = str(tmp_path / (name + ".npz"))
+        e = dict(os.environ)
+        e.update(env)
+        r = subprocess.run([sys.executable, os.path.join(root, "tools", "diag", "psd_dump.py"), path], env=e,
+                           stdout=subprocess.PIPE, stderr=subprocess.STDOUT, timeout=300)
+        assert r.returncode == 0, r.stdout.decode()[-2000:]
+        res[name] = np.load(path)
+    assert sorted(res["new"].files) == sorted(res["generic"].files) and len(res["new"].files) == 12
+    for k in res["new"].files:
+        assert np.isfinite(res["new"][k]).all(), k
+        assert np.array_equal(res["new"][k], res["generic"][k]), k
