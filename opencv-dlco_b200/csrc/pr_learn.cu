@@ -36,10 +36,31 @@ __global__ void k_pr_resolve(const int32_t *__restrict__ samples, int64_t n,
     if (i < n) rows[i] = make_int2(idx_pos[samples[2 * i]], idx_neg[samples[2 * i + 1]]);
 }
 
+// The scalars of step t = t0 + s depend on t, mu and gamma only.  Inside the chain every thread used to form them (two
+// fp64 divisions and a square root: ~80 of the ~130 fp64-pipe instructions per thread and step, and the chain is bound
+// by that pipe -- 20 warps x 130 instructions at 64 lanes per clock are 1 300 of its ~2 700 cycles per step).  They are
+// tabulated ahead instead, by this kernel, with the same expressions: avg[s] = (t / (t + 1), 1 / (t + 1)) for all
+// configurations, ab[cfg][s] = (alpha, alpha * mu), alpha = -sqrt(t + 1) / gamma.
+__global__ void __launch_bounds__(256)
+k_pr_scalars(int64_t n_steps, uint64_t t0, int nCfg, const float *__restrict__ mus, const float *__restrict__ gammas,
+             float2 *__restrict__ avg, float2 *__restrict__ ab)
+{
+    const int64_t s = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    if (s >= n_steps) return;
+    const uint64_t t = t0 + (uint64_t)s;
+    const double tp1 = (double)(t + 1);
+    const int cfg = blockIdx.y;
+    if (cfg == 0)
+        avg[s] = make_float2((float)((double)t * (1.0 / tp1)),       // dfAvg = t * dfAvg / (t+1)
+                             (float)(1.0 / tp1));                    // scaleAdd(FeatDiff, 1/(t+1))
+    const double alpha_d = -sqrt(tp1) / (double)gammas[cfg];         // w = -sqrt(t+1)/gamma (dfAvg+mu)
+    ab[(size_t)cfg * n_steps + s] = make_float2((float)alpha_d, (float)(alpha_d * (double)mus[cfg]));
+}
+
 template <int STAGES>
 __global__ void __launch_bounds__(RDA_MAX_THREADS, 1)
 k_pr_rda(const float *__restrict__ dists, int64_t ld, int F, const int2 *__restrict__ rows,
-         int64_t n_steps, uint64_t t0, const float *__restrict__ mus, const float *__restrict__ gammas,
+         int64_t n_steps, const float2 *__restrict__ avg, const float2 *__restrict__ ab,
          float *__restrict__ w_io, float *__restrict__ dfavg_io)
 {
     extern __shared__ float4 s_ring[];           // [STAGES][2][nvec]
@@ -48,7 +69,7 @@ k_pr_rda(const float *__restrict__ dists, int64_t ld, int F, const int2 *__restr
     const int nvec = F >> 2;
     const int nwarps = nthr >> 5;
     const int cfg = blockIdx.x;
-    const double mu = (double)mus[cfg], gamma = (double)gammas[cfg];
+    const float2 *ab_g = ab + (size_t)cfg * n_steps;
     float *w_g = w_io + (size_t)cfg * F, *df_g = dfavg_io + (size_t)cfg * F;
 
     bool have[RDA_VEC];
@@ -81,8 +102,15 @@ k_pr_rda(const float *__restrict__ dists, int64_t ld, int F, const int2 *__restr
 
     for (int s = 0; s < STAGES; s++) issue(s, row_at(s));
     int2 r_next = row_at(STAGES), r_next2 = row_at(STAGES + 1);
+    float2 sc_avg = n_steps > 0 ? __ldg(avg) : make_float2(0.f, 0.f), sc_ab = n_steps > 0 ? __ldg(ab_g) : make_float2(0.f, 0.f);
 
     for (int64_t s = 0; s < n_steps; s++) {
+        // this step's scalars were fetched a step ago; fetch the next step's now
+        const float a_avg = sc_avg.x, a_add = sc_avg.y, alpha = sc_ab.x, beta = sc_ab.y;
+        if (s + 1 < n_steps) {
+            sc_avg = __ldg(avg + s + 1);
+            sc_ab = __ldg(ab_g + s + 1);
+        }
         cp_async_wait<STAGES - 1>();
         const float4 *st = s_ring + (size_t)(s % STAGES) * 2 * nvec;
         float4 d[RDA_VEC];
@@ -114,12 +142,6 @@ k_pr_rda(const float *__restrict__ dists, int64_t ld, int F, const int2 *__restr
         for (int i = 0; i < nwarps; i++) tot += part[i];
         const float f = (float)tot;                                  // gemm(w, FeatDiff) -> f32
 
-        const uint64_t t = t0 + (uint64_t)s;
-        const double tp1 = (double)(t + 1);
-        const float a_avg = (float)((double)t * (1.0 / tp1));        // dfAvg = t * dfAvg / (t+1)
-        const float a_add = (float)(1.0 / tp1);                      // scaleAdd(FeatDiff, 1/(t+1))
-        const double alpha_d = -sqrt(tp1) / gamma;                   // w = -sqrt(t+1)/gamma (dfAvg+mu)
-        const float alpha = (float)alpha_d, beta = (float)(alpha_d * mu);
         const bool hinge = f > -1.0f;
 #pragma unroll
         for (int j = 0; j < RDA_VEC; j++) {
@@ -157,8 +179,10 @@ static inline uint32_t cv_rng_next(uint64_t &s)
 
 static int pr_rda_launch(dlco_ctx *ctx, const float *d_dists, int64_t ld, int F, const int2 *d_rows,
                          int64_t n, uint64_t t0, int nCfg, const float *d_mu, const float *d_gamma,
-                         float *d_w, float *d_dfavg)
+                         float2 *d_avg, float2 *d_ab, float *d_w, float *d_dfavg)
 {
+    k_pr_scalars<<<dim3((unsigned)((n + 255) / 256), nCfg), 256, 0, ctx->stream>>>(n, t0, nCfg, d_mu, d_gamma, d_avg, d_ab);
+    DLCO_CHECK_LAUNCH(ctx);
     const int nvec = F / 4;
     int threads = ((nvec + RDA_VEC - 1) / RDA_VEC + 31) / 32 * 32;
     const size_t stage = (size_t)2 * F * sizeof(float);
@@ -167,9 +191,9 @@ static int pr_rda_launch(dlco_ctx *ctx, const float *d_dists, int64_t ld, int F,
     DLCO_SMEM_ONCE(ctx, 4, k_pr_rda<4>, 220 * 1024);
     DLCO_SMEM_ONCE(ctx, 5, k_pr_rda<2>, 220 * 1024);
     if (stages == 4)
-        k_pr_rda<4><<<nCfg, threads, smem, ctx->stream>>>(d_dists, ld, F, d_rows, n, t0, d_mu, d_gamma, d_w, d_dfavg);
+        k_pr_rda<4><<<nCfg, threads, smem, ctx->stream>>>(d_dists, ld, F, d_rows, n, d_avg, d_ab, d_w, d_dfavg);
     else
-        k_pr_rda<2><<<nCfg, threads, smem, ctx->stream>>>(d_dists, ld, F, d_rows, n, t0, d_mu, d_gamma, d_w, d_dfavg);
+        k_pr_rda<2><<<nCfg, threads, smem, ctx->stream>>>(d_dists, ld, F, d_rows, n, d_avg, d_ab, d_w, d_dfavg);
     DLCO_CHECK_LAUNCH(ctx);
     return DLCO_OK;
 }
@@ -195,7 +219,12 @@ extern "C" int dlco_pr_rda_run_grid(dlco_ctx *ctx, const float *d_dists, int64_t
     if (!d_cfg) return DLCO_ENOMEM;
     DLCO_CUDA(cudaMemcpyAsync(d_cfg, h_mu, nCfg * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
     DLCO_CUDA(cudaMemcpyAsync(d_cfg + nCfg, h_gamma, nCfg * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
-    const uint64_t SEG = 1u << 20;                       // steps per segment (8 MB of samples)
+    // steps per segment: 8 MB of samples, and 8 bytes of tabulated scalars per step and configuration (at most 256 MB)
+    uint64_t SEG = 1u << 20;
+    if ((uint64_t)nCfg * SEG * sizeof(float2) > (256u << 20)) {
+        SEG = ((256u << 20) / sizeof(float2) / (uint64_t)nCfg) & ~(uint64_t)1023;
+        if (SEG < 4096) SEG = 4096;
+    }
     const uint64_t seg_max = nSteps < SEG ? nSteps : SEG;
     int32_t *h_s[2];
     for (int b = 0; b < 2; b++) {
@@ -204,7 +233,9 @@ extern "C" int dlco_pr_rda_run_grid(dlco_ctx *ctx, const float *d_dists, int64_t
     }
     int32_t *d_s = (int32_t *)dlco_scratch(ctx, 7, 2 * seg_max * 2 * sizeof(int32_t));
     int2 *d_rows = (int2 *)dlco_scratch(ctx, 8, 2 * seg_max * sizeof(int2));
-    if (!d_s || !d_rows) return DLCO_ENOMEM;
+    float2 *d_avg = (float2 *)dlco_scratch(ctx, 46, seg_max * sizeof(float2));
+    float2 *d_ab = (float2 *)dlco_scratch(ctx, 47, (size_t)nCfg * seg_max * sizeof(float2));
+    if (!d_s || !d_rows || !d_avg || !d_ab) return DLCO_ENOMEM;
     cudaEvent_t ev[2];
     for (int b = 0; b < 2; b++) DLCO_CUDA(cudaEventCreateWithFlags(&ev[b], cudaEventDisableTiming));
     uint64_t st = *rng_state;
@@ -227,7 +258,7 @@ extern "C" int dlco_pr_rda_run_grid(dlco_ctx *ctx, const float *d_dists, int64_t
         k_pr_resolve<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(ds, (int64_t)n, d_idx_pos, d_idx_neg, dr);
         ctx->launches++;
         dlco_prof_begin(ctx, 4);
-        rc = pr_rda_launch(ctx, d_dists, ld, F, dr, (int64_t)n, t0 + done, nCfg, d_cfg, d_cfg + nCfg, d_w, d_dfavg);
+        rc = pr_rda_launch(ctx, d_dists, ld, F, dr, (int64_t)n, t0 + done, nCfg, d_cfg, d_cfg + nCfg, d_avg, d_ab, d_w, d_dfavg);
         dlco_prof_end(ctx);
     }
     // the pinned sample buffers are reused by the next call: wait for the uploads
