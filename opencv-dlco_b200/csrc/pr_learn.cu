@@ -16,8 +16,8 @@
 #include <math.h>
 #include <vector>
 
-#define RDA_MAX_THREADS 1024
-#define RDA_VEC 2            // float4 vectors per thread
+#define RDA_MAX_THREADS 512
+#define RDA_VEC 4            // float4 vectors per thread
 
 __device__ __forceinline__ void cp_async16(void *smem, const void *gmem)
 {
@@ -27,13 +27,15 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
-// rows[s] = (row of the positive sample, row of the negative sample) for step s
-__global__ void k_pr_resolve(const int32_t *__restrict__ samples, int64_t n,
+// rows[s] = byte offsets of (the positive sample's row, the negative sample's row) of step s in the distance matrix;
+// entries n .. n_pad - 1 repeat row 0 (the chain prefetches past the end of the segment without bounds checks)
+__global__ void k_pr_resolve(const int32_t *__restrict__ samples, int64_t n, int64_t n_pad,
                              const int32_t *__restrict__ idx_pos, const int32_t *__restrict__ idx_neg,
-                             int2 *__restrict__ rows)
+                             int64_t row_bytes, longlong2 *__restrict__ rows)
 {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) rows[i] = make_int2(idx_pos[samples[2 * i]], idx_neg[samples[2 * i + 1]]);
+    if (i < n) rows[i] = make_longlong2((long long)idx_pos[samples[2 * i]] * row_bytes, (long long)idx_neg[samples[2 * i + 1]] * row_bytes);
+    else if (i < n_pad) rows[i] = make_longlong2(0, 0);
 }
 
 // The scalars of step t = t0 + s depend on t, mu and gamma only.  Inside the chain every thread used to form them (two
@@ -46,7 +48,7 @@ k_pr_scalars(int64_t n_steps, uint64_t t0, int nCfg, const float *__restrict__ m
              float2 *__restrict__ avg, float2 *__restrict__ ab)
 {
     const int64_t s = (int64_t)blockIdx.x * 256 + threadIdx.x;
-    if (s >= n_steps) return;
+    if (s > n_steps) return;                                         // n_steps + 1 entries: the chain fetches one ahead
     const uint64_t t = t0 + (uint64_t)s;
     const double tp1 = (double)(t + 1);
     const int cfg = blockIdx.y;
@@ -54,92 +56,109 @@ k_pr_scalars(int64_t n_steps, uint64_t t0, int nCfg, const float *__restrict__ m
         avg[s] = make_float2((float)((double)t * (1.0 / tp1)),       // dfAvg = t * dfAvg / (t+1)
                              (float)(1.0 / tp1));                    // scaleAdd(FeatDiff, 1/(t+1))
     const double alpha_d = -sqrt(tp1) / (double)gammas[cfg];         // w = -sqrt(t+1)/gamma (dfAvg+mu)
-    ab[(size_t)cfg * n_steps + s] = make_float2((float)alpha_d, (float)(alpha_d * (double)mus[cfg]));
+    ab[(size_t)cfg * (n_steps + 1) + s] = make_float2((float)alpha_d, (float)(alpha_d * (double)mus[cfg]));
 }
 
-template <int STAGES>
+// NWARPS > 0: the block has exactly NWARPS warps and F = 4 * RDA_VEC * 32 * NWARPS (every thread owns RDA_VEC full
+// vectors: no bounds predicates, the reduction tree is unrolled for NWARPS); NWARPS = 0: any F, sizes at run time.
+// The chain is bound by instruction issue (ncu: 308 instructions per warp and step at 60 % issue utilisation), so the
+// loop keeps its indexing to pointer bumps: ring slots by a wrapping counter, the row list and the scalar tables by
+// running pointers, row addresses as byte offsets resolved by k_pr_resolve.
+template <int STAGES, int NWARPS>
 __global__ void __launch_bounds__(RDA_MAX_THREADS, 1)
-k_pr_rda(const float *__restrict__ dists, int64_t ld, int F, const int2 *__restrict__ rows,
+k_pr_rda(const float *__restrict__ dists, int F, const longlong2 *__restrict__ rows,
          int64_t n_steps, const float2 *__restrict__ avg, const float2 *__restrict__ ab,
          float *__restrict__ w_io, float *__restrict__ dfavg_io)
 {
     extern __shared__ float4 s_ring[];           // [STAGES][2][nvec]
-    __shared__ double s_part[2][32];
-    const int tid = threadIdx.x, nthr = blockDim.x;
-    const int nvec = F >> 2;
-    const int nwarps = nthr >> 5;
+    __shared__ double s_part[2][16];
+    constexpr bool FULL = NWARPS > 0;
+    const int tid = threadIdx.x, nthr = FULL ? NWARPS * 32 : (int)blockDim.x;
+    const int nvec = FULL ? NWARPS * 32 * RDA_VEC : F >> 2;
+    const int nwarps = FULL ? NWARPS : nthr >> 5;
     const int cfg = blockIdx.x;
-    const float2 *ab_g = ab + (size_t)cfg * n_steps;
+    const float2 *ab_p = ab + (size_t)cfg * (n_steps + 1);
+    const float2 *avg_p = avg;
     float *w_g = w_io + (size_t)cfg * F, *df_g = dfavg_io + (size_t)cfg * F;
+    const char *dbase = reinterpret_cast<const char *>(dists) + (size_t)tid * 16;
 
     bool have[RDA_VEC];
     float4 w[RDA_VEC], df[RDA_VEC];
 #pragma unroll
     for (int j = 0; j < RDA_VEC; j++) {
         const int v = j * nthr + tid;
-        have[j] = v < nvec;
+        have[j] = FULL || v < nvec;
         w[j] = have[j] ? reinterpret_cast<const float4 *>(w_g)[v] : make_float4(0, 0, 0, 0);
         df[j] = have[j] ? reinterpret_cast<const float4 *>(df_g)[v] : make_float4(0, 0, 0, 0);
     }
 
-    auto issue = [&](int64_t s, int2 r) {
-        if (s < n_steps) {
-            float4 *st = s_ring + (size_t)(s % STAGES) * 2 * nvec;
-            const float4 *gp = reinterpret_cast<const float4 *>(dists + (size_t)r.x * ld);
-            const float4 *gn = reinterpret_cast<const float4 *>(dists + (size_t)r.y * ld);
+    // this thread's slice of ring slot `slot`: vectors tid, tid + nthr, ... of the positive row, then of the negative row
+    auto issue = [&](int slot, longlong2 r) {
+        float4 *st = s_ring + (size_t)slot * 2 * nvec + tid;
+        const char *gp = dbase + r.x, *gn = dbase + r.y;
 #pragma unroll
-            for (int j = 0; j < RDA_VEC; j++) {
-                const int v = j * nthr + tid;
-                if (have[j]) {
-                    cp_async16(st + v, gp + v);
-                    cp_async16(st + nvec + v, gn + v);
-                }
+        for (int j = 0; j < RDA_VEC; j++) {
+            if (have[j]) {
+                cp_async16(st + j * nthr, gp + (size_t)j * nthr * 16);
+                cp_async16(st + nvec + j * nthr, gn + (size_t)j * nthr * 16);
             }
         }
-        cp_async_commit();
     };
-    auto row_at = [&](int64_t s) { return s < n_steps ? rows[s] : make_int2(0, 0); };
-
-    for (int s = 0; s < STAGES; s++) issue(s, row_at(s));
-    int2 r_next = row_at(STAGES), r_next2 = row_at(STAGES + 1);
-    float2 sc_avg = n_steps > 0 ? __ldg(avg) : make_float2(0.f, 0.f), sc_ab = n_steps > 0 ? __ldg(ab_g) : make_float2(0.f, 0.f);
+    // rows has n_steps + STAGES + 2 entries (k_pr_resolve pads the tail with row 0): no bounds checks in the loop
+    const longlong2 *rp = rows;
+    for (int q = 0; q < STAGES; q++) {
+        issue(q, *rp++);
+        cp_async_commit();
+    }
+    longlong2 r_next = *rp++, r_next2 = *rp++;
+    float2 sc_avg = __ldg(avg_p++), sc_ab = __ldg(ab_p++);     // the tables have n_steps + 1 entries
+    int slot = 0;
 
     for (int64_t s = 0; s < n_steps; s++) {
         // this step's scalars were fetched a step ago; fetch the next step's now
         const float a_avg = sc_avg.x, a_add = sc_avg.y, alpha = sc_ab.x, beta = sc_ab.y;
-        if (s + 1 < n_steps) {
-            sc_avg = __ldg(avg + s + 1);
-            sc_ab = __ldg(ab_g + s + 1);
-        }
+        sc_avg = __ldg(avg_p++);
+        sc_ab = __ldg(ab_p++);
         cp_async_wait<STAGES - 1>();
-        const float4 *st = s_ring + (size_t)(s % STAGES) * 2 * nvec;
+        const float4 *st = s_ring + (size_t)slot * 2 * nvec + tid;
         float4 d[RDA_VEC];
-        double acc = 0.0;
+        double acc2[RDA_VEC];                    // one chain of 4 dependent fp64 FMAs per vector, then a tree
 #pragma unroll
         for (int j = 0; j < RDA_VEC; j++) {
-            const int v = j * nthr + tid;
+            acc2[j] = 0.0;
+            d[j] = make_float4(0, 0, 0, 0);
             if (have[j]) {
-                const float4 p = st[v], n = st[nvec + v];
+                const float4 p = st[j * nthr], n = st[nvec + j * nthr];
                 d[j] = make_float4(__fsub_rn(p.x, n.x), __fsub_rn(p.y, n.y), __fsub_rn(p.z, n.z),
                                    __fsub_rn(p.w, n.w));
-                acc = fma((double)w[j].x, (double)d[j].x, acc);
-                acc = fma((double)w[j].y, (double)d[j].y, acc);
-                acc = fma((double)w[j].z, (double)d[j].z, acc);
-                acc = fma((double)w[j].w, (double)d[j].w, acc);
-            } else {
-                d[j] = make_float4(0, 0, 0, 0);
+                double a = fma((double)w[j].x, (double)d[j].x, 0.0);
+                a = fma((double)w[j].y, (double)d[j].y, a);
+                a = fma((double)w[j].z, (double)d[j].z, a);
+                acc2[j] = fma((double)w[j].w, (double)d[j].w, a);
             }
         }
-        issue(s + STAGES, r_next);          // the slot just read is free again (thread-private)
+        double acc = (acc2[0] + acc2[1]) + (acc2[2] + acc2[3]);
+        static_assert(RDA_VEC == 4, "the tree above");
+        issue(slot, r_next);                // the slot just read is free again (thread-private)
+        cp_async_commit();
+        if (++slot == STAGES) slot = 0;
         r_next = r_next2;
-        r_next2 = row_at(s + STAGES + 2);
+        r_next2 = *rp++;
 
         acc = warp_sum_d(acc);
         double *part = s_part[s & 1];
         if ((tid & 31) == 0) part[tid >> 5] = acc;
         __syncthreads();
-        double tot = 0.0;
-        for (int i = 0; i < nwarps; i++) tot += part[i];
+        // fixed-order pairwise tree over the warps' partial sums (at most 16 warps: 512 threads): 4 dependent fp64
+        // additions instead of nwarps
+        double pw[16];
+#pragma unroll
+        for (int i = 0; i < 16; i++) pw[i] = i < nwarps ? part[i] : 0.0;
+#pragma unroll
+        for (int o = 8; o > 0; o >>= 1)
+#pragma unroll
+            for (int i = 0; i < o; i++) pw[i] += pw[i + o];
+        const double tot = pw[0];
         const float f = (float)tot;                                  // gemm(w, FeatDiff) -> f32
 
         const bool hinge = f > -1.0f;
@@ -177,23 +196,29 @@ static inline uint32_t cv_rng_next(uint64_t &s)
     return (uint32_t)s;
 }
 
-static int pr_rda_launch(dlco_ctx *ctx, const float *d_dists, int64_t ld, int F, const int2 *d_rows,
+#define RDA_PAD 8            // entries the row list is padded by (STAGES + 2 are read past the end)
+
+static int pr_rda_launch(dlco_ctx *ctx, const float *d_dists, int F, const longlong2 *d_rows,
                          int64_t n, uint64_t t0, int nCfg, const float *d_mu, const float *d_gamma,
                          float2 *d_avg, float2 *d_ab, float *d_w, float *d_dfavg)
 {
-    k_pr_scalars<<<dim3((unsigned)((n + 255) / 256), nCfg), 256, 0, ctx->stream>>>(n, t0, nCfg, d_mu, d_gamma, d_avg, d_ab);
+    k_pr_scalars<<<dim3((unsigned)((n + 1 + 255) / 256), nCfg), 256, 0, ctx->stream>>>(n, t0, nCfg, d_mu, d_gamma, d_avg, d_ab);
     DLCO_CHECK_LAUNCH(ctx);
     const int nvec = F / 4;
     int threads = ((nvec + RDA_VEC - 1) / RDA_VEC + 31) / 32 * 32;
     const size_t stage = (size_t)2 * F * sizeof(float);
     const int stages = stage * 4 <= 200 * 1024 ? 4 : 2;
     const size_t smem = stage * stages;
-    DLCO_SMEM_ONCE(ctx, 4, k_pr_rda<4>, 220 * 1024);
-    DLCO_SMEM_ONCE(ctx, 5, k_pr_rda<2>, 220 * 1024);
-    if (stages == 4)
-        k_pr_rda<4><<<nCfg, threads, smem, ctx->stream>>>(d_dists, ld, F, d_rows, n, d_avg, d_ab, d_w, d_dfavg);
-    else
-        k_pr_rda<2><<<nCfg, threads, smem, ctx->stream>>>(d_dists, ld, F, d_rows, n, d_avg, d_ab, d_w, d_dfavg);
+    if (stages == 4 && F == 5120) {            // the reference's width: 10 full warps, everything at compile time
+        DLCO_SMEM_ONCE(ctx, 9, (k_pr_rda<4, 10>), 220 * 1024);
+        k_pr_rda<4, 10><<<nCfg, 320, smem, ctx->stream>>>(d_dists, F, d_rows, n, d_avg, d_ab, d_w, d_dfavg);
+    } else if (stages == 4) {
+        DLCO_SMEM_ONCE(ctx, 4, (k_pr_rda<4, 0>), 220 * 1024);
+        k_pr_rda<4, 0><<<nCfg, threads, smem, ctx->stream>>>(d_dists, F, d_rows, n, d_avg, d_ab, d_w, d_dfavg);
+    } else {
+        DLCO_SMEM_ONCE(ctx, 5, (k_pr_rda<2, 0>), 220 * 1024);
+        k_pr_rda<2, 0><<<nCfg, threads, smem, ctx->stream>>>(d_dists, F, d_rows, n, d_avg, d_ab, d_w, d_dfavg);
+    }
     DLCO_CHECK_LAUNCH(ctx);
     return DLCO_OK;
 }
@@ -232,9 +257,9 @@ extern "C" int dlco_pr_rda_run_grid(dlco_ctx *ctx, const float *d_dists, int64_t
         if (!h_s[b]) return DLCO_ENOMEM;
     }
     int32_t *d_s = (int32_t *)dlco_scratch(ctx, 7, 2 * seg_max * 2 * sizeof(int32_t));
-    int2 *d_rows = (int2 *)dlco_scratch(ctx, 8, 2 * seg_max * sizeof(int2));
-    float2 *d_avg = (float2 *)dlco_scratch(ctx, 46, seg_max * sizeof(float2));
-    float2 *d_ab = (float2 *)dlco_scratch(ctx, 47, (size_t)nCfg * seg_max * sizeof(float2));
+    longlong2 *d_rows = (longlong2 *)dlco_scratch(ctx, 8, 2 * (seg_max + RDA_PAD) * sizeof(longlong2));
+    float2 *d_avg = (float2 *)dlco_scratch(ctx, 46, (seg_max + 1) * sizeof(float2));
+    float2 *d_ab = (float2 *)dlco_scratch(ctx, 47, (size_t)nCfg * (seg_max + 1) * sizeof(float2));
     if (!d_s || !d_rows || !d_avg || !d_ab) return DLCO_ENOMEM;
     cudaEvent_t ev[2];
     for (int b = 0; b < 2; b++) DLCO_CUDA(cudaEventCreateWithFlags(&ev[b], cudaEventDisableTiming));
@@ -251,14 +276,15 @@ extern "C" int dlco_pr_rda_run_grid(dlco_ctx *ctx, const float *d_dists, int64_t
             hs[2 * s + 1] = (int32_t)(cv_rng_next(st) % (uint32_t)nNegTrn);
         }
         int32_t *ds = d_s + (size_t)b * seg_max * 2;
-        int2 *dr = d_rows + (size_t)b * seg_max;
+        longlong2 *dr = d_rows + (size_t)b * (seg_max + RDA_PAD);
         cudaError_t e = cudaMemcpyAsync(ds, hs, n * 2 * sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream);
         if (e == cudaSuccess) e = cudaEventRecord(ev[b], ctx->stream);
         if (e != cudaSuccess) { dlco_set_error("pr_rda: sample upload: %s", cudaGetErrorString(e)); rc = DLCO_ECUDA; break; }
-        k_pr_resolve<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(ds, (int64_t)n, d_idx_pos, d_idx_neg, dr);
+        k_pr_resolve<<<(unsigned)((n + RDA_PAD + 255) / 256), 256, 0, ctx->stream>>>(ds, (int64_t)n, (int64_t)n + RDA_PAD, d_idx_pos, d_idx_neg,
+                                                                                 ld * (int64_t)sizeof(float), dr);
         ctx->launches++;
         dlco_prof_begin(ctx, 4);
-        rc = pr_rda_launch(ctx, d_dists, ld, F, dr, (int64_t)n, t0 + done, nCfg, d_cfg, d_cfg + nCfg, d_avg, d_ab, d_w, d_dfavg);
+        rc = pr_rda_launch(ctx, d_dists, F, dr, (int64_t)n, t0 + done, nCfg, d_cfg, d_cfg + nCfg, d_avg, d_ab, d_w, d_dfavg);
         dlco_prof_end(ctx);
     }
     // the pinned sample buffers are reused by the next call: wait for the uploads
