@@ -1,6 +1,7 @@
 // Shared host/device helpers for libdlco_b200 (sm_100a only).
 #pragma once
 #include <cuda_runtime.h>
+#include <stdlib.h>
 #include <cuda.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -201,6 +202,37 @@ __device__ __forceinline__ void tma_load_2d(void *smem_dst, const CUtensorMap *m
         "l"(m), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
         : "memory");
 }
+
+// ---- programmatic dependent launch ----------------------------------------------------------
+// A kernel launched through dlco_launch_pdl may start (block scheduling, barrier / TMEM set-up) while its predecessor
+// on the stream is still running; pdl_wait() blocks until the predecessor has completed and its writes are visible,
+// so it comes before the kernel's first global access (reads of the predecessor's output, and writes to anything the
+// predecessor may still read).  pdl_trigger() lets the successor's blocks be scheduled early.  Both are no-ops in a
+// kernel that was launched without the attribute.  DLCO_PDL=0 launches without it.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+#ifdef __CUDACC__
+static inline bool dlco_pdl_enabled()
+{
+    static const bool on = [] { const char *e = getenv("DLCO_PDL"); return !(e && e[0] == '0'); }();
+    return on;
+}
+template <typename... KArgs, typename... Args>
+static inline cudaError_t dlco_launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args)
+{
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = dlco_pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+#endif
 
 // ---- tcgen05 --------------------------------------------------------------------------
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }

@@ -122,6 +122,9 @@ k_gemm3x_nt(const __grid_constant__ GemmMaps maps, const __grid_constant__ GemmT
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    // launched with programmatic dependent launch (fp16 route): everything above ran under the predecessor's tail
+    pdl_wait();
+    pdl_trigger();
 
     if (warp == 0) {
         if (lane == 0) {
@@ -467,9 +470,9 @@ static int gemm3h_launch(dlco_ctx *ctx, int sym, const GemmEpi &epi, const void 
     const int total = batch * tl.n;
     const int grid = total < ctx->sm_count ? total : ctx->sm_count;
     dlco_prof_begin(ctx, 2);
-    k_gemm3x_nt<true><<<grid, NTHREADS, SMEM_BYTES, ctx->stream>>>(maps, tl, total, k_pad / (2 * BK), flush, a_rows_pad,
-                                                                 b_batched ? b_rows_pad : 0, M, N, d_C, ldc,
-                                                                 c_batch_stride, out_scale, epi);
+    DLCO_CUDA(dlco_launch_pdl(k_gemm3x_nt<true>, dim3(grid), dim3(NTHREADS), (size_t)SMEM_BYTES, ctx->stream, maps, tl, total,
+                              k_pad / (2 * BK), flush, a_rows_pad, b_batched ? b_rows_pad : 0, M, N, d_C, ldc, c_batch_stride,
+                              out_scale, epi));
     dlco_prof_end(ctx);
     DLCO_CHECK_LAUNCH(ctx);
     return DLCO_OK;

@@ -82,6 +82,8 @@ constexpr int NORM_BLOCKS = 32;
 __global__ void __launch_bounds__(256)
 k_sign_norm(const float *__restrict__ A, size_t dd, double *__restrict__ partial)
 {
+    pdl_wait();
+    pdl_trigger();
     __shared__ double s[8];
     const int g = blockIdx.y;
     const float *a = A + (size_t)g * dd;
@@ -150,6 +152,8 @@ k_sign_prep(int D, int rows_pad, int k_pad, const float *__restrict__ in0, const
             const double *__restrict__ partial, int step, int sym, float pscale, float *__restrict__ out,
             void *__restrict__ hi, void *__restrict__ lo)
 {
+    pdl_wait();
+    pdl_trigger();
     __shared__ float t0[32][33];
     __shared__ float t1[32][33];
     const int g = blockIdx.z;
@@ -236,6 +240,8 @@ __global__ void __launch_bounds__(256)
 k_sign_sym_planes(int D, int rows_pad, int k_pad, const float *__restrict__ T, float pscale, float *__restrict__ out,
                   __half *__restrict__ hi, __half *__restrict__ lo)
 {
+    pdl_wait();
+    pdl_trigger();
     __shared__ float t1[32][33];          // the mirror block of T (diagonal tiles only)
     __shared__ uint32_t tw[32][33];       // packed plane words hi | lo << 16 of v
     __shared__ float tv[32][33];          // v (only when X is written)
@@ -316,6 +322,8 @@ k_sign_sym_planes(int D, int rows_pad, int k_pad, const float *__restrict__ T, f
 __global__ void __launch_bounds__(256)
 k_sign_rank(int D, const float *__restrict__ S, const double *__restrict__ partial, int32_t *__restrict__ rank)
 {
+    pdl_wait();
+    pdl_trigger();
     __shared__ double s[8];
     const int g = blockIdx.x;
     double acc = 0.0;
@@ -340,16 +348,17 @@ static int sign_prep(dlco_ctx *ctx, bool f16, int D, int nCfg, int rows_pad, int
         static const bool generic = [] { const char *e = getenv("DLCO_SIGN_SYM_GENERIC"); return e && e[0] == '1'; }();
         if (!generic) {
             const int nb = (D + 31) / 32;
-            k_sign_sym_planes<<<dim3(nb, nb, nCfg), 256, 0, ctx->stream>>>(D, rows_pad, k_pad, in0, pscale, out, (__half *)hi, (__half *)lo);
+            DLCO_CUDA(dlco_launch_pdl(k_sign_sym_planes, dim3(nb, nb, nCfg), dim3(256), 0, ctx->stream, D, rows_pad, k_pad, in0, pscale, out,
+                                      (__half *)hi, (__half *)lo));
             DLCO_CHECK_LAUNCH(ctx);
             return DLCO_OK;
         }
     }
     dim3 grid(MODE == PREP_FINAL ? (D + 31) / 32 : k_pad / 32, MODE == PREP_FINAL ? (D + 31) / 32 : rows_pad / 32, nCfg);
     if (f16)
-        k_sign_prep<MODE, true><<<grid, 256, 0, ctx->stream>>>(D, rows_pad, k_pad, in0, in1, partial, step, sym, pscale, out, hi, lo);
+        DLCO_CUDA(dlco_launch_pdl(k_sign_prep<MODE, true>, grid, dim3(256), 0, ctx->stream, D, rows_pad, k_pad, in0, in1, partial, step, sym, pscale, out, hi, lo));
     else
-        k_sign_prep<MODE, false><<<grid, 256, 0, ctx->stream>>>(D, rows_pad, k_pad, in0, in1, partial, step, sym, pscale, out, hi, lo);
+        DLCO_CUDA(dlco_launch_pdl(k_sign_prep<MODE, false>, grid, dim3(256), 0, ctx->stream, D, rows_pad, k_pad, in0, in1, partial, step, sym, pscale, out, hi, lo));
     DLCO_CHECK_LAUNCH(ctx);
     return DLCO_OK;
 }
@@ -396,7 +405,7 @@ int dlco_pj_psd_sign(dlco_ctx *ctx, int D, int nCfg, float *d_A, int32_t *d_rank
                                          (const float *)bl, rows_pad, 1, k_pad, nCfg, D, D, C, D, cs);
     };
     int r;
-    k_sign_norm<<<dim3(NORM_BLOCKS, nCfg), 256, 0, ctx->stream>>>(d_A, dd, partial);
+    DLCO_CUDA(dlco_launch_pdl(k_sign_norm, dim3(NORM_BLOCKS, nCfg), dim3(256), 0, ctx->stream, (const float *)d_A, dd, partial));
     DLCO_CHECK_LAUNCH(ctx);
     r = sign_prep<PREP_INIT>(ctx, f16, D, nCfg, rows_pad, k_pad, d_A, nullptr, partial, 0, 0, sx, nullptr, p1h, p1l);   // X lives in its planes
     // table 0 (DLCO_SIGN_LO=1e-5): [1e-5, 1], 10 quintics + cubic; table 1 (default): [1e-4, 1], 8 quintics + cubic
@@ -452,7 +461,7 @@ int dlco_pj_psd_sign(dlco_ctx *ctx, int D, int nCfg, float *d_A, int32_t *d_rank
     if (r == DLCO_OK) r = gemm(p2h, p2l, p1h, p1l, sx, sx, T);
     if (r == DLCO_OK) r = sign_prep<PREP_FINAL>(ctx, f16, D, nCfg, rows_pad, k_pad, T, nullptr, partial, 0, 1, 1.f, d_A, nullptr, nullptr);
     if (r != DLCO_OK) return r;
-    k_sign_rank<<<nCfg, 256, 0, ctx->stream>>>(D, X, partial, d_rank);
+    DLCO_CUDA(dlco_launch_pdl(k_sign_rank, dim3(nCfg), dim3(256), 0, ctx->stream, D, (const float *)X, (const double *)partial, d_rank));
     DLCO_CHECK_LAUNCH(ctx);
     return DLCO_OK;
 }
