@@ -1,3 +1,4 @@
+// build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o tools/diag/lat tools/diag/lat.cu ; measured on B200: DADD 8.4, DFMA 8.7, SHFL x2 + DADD 36, STS + BAR + LDS + DADD 69 (320 threads), FFMA 4.6 cycles
 // dependent-chain latencies (cycles per op) of the instructions on k_pr_rda's critical path
 #include <cstdio>
 #include <cstdint>
