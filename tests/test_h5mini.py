@@ -261,3 +261,36 @@ def test_writer_structure_matches_libhdf5_written_file(h5tool, tmp_path):
     assert {0x01, 0x03, 0x08, 0x0B} <= set(got["msg_types"])
     if ref["fill"] is not None and got["fill"] is not None:
         assert got["fill"][:4] == ref["fill"][:4]                            # fill value message version / times / defined
+
+
+def test_reads_every_file_of_the_reference_workspace(h5tool, tmp_path):
+    """SURVEY 7 step 1 / VERDICT r1 weak 13: every .h5 file libhdf5 wrote under the reference's workspace (1 181 models:
+    pr-learn's appendable, chunked, deflated `w`, pj-learn's contiguous W / A, the rank files) parses with h5mini, with
+    the shapes the tools rely on; every tenth one is read in full.  Only where the reference is present (this
+    container); the GPU box does not have it."""
+    ws = "/root/reference/workspace"
+    if not os.path.isdir(ws):
+        pytest.skip("reference workspace not present")
+    files = sorted(os.path.join(d, f) for d, _, fs in os.walk(ws) for f in fs if f.endswith(".h5"))
+    assert len(files) >= 1000
+    n_pr = n_pj = 0
+    for k, path in enumerate(files):
+        out = subprocess.run([h5tool, "ls", path], stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+        assert out.returncode == 0, (path, out.stderr.decode())
+        sets = {ln.split()[0]: ln.split() for ln in out.stdout.decode().splitlines() if ln.strip()}
+        if path.endswith("-pr.h5"):
+            n_pr += 1
+            assert sets["w"][1] == "f32" and int(sets["w"][3]) == 5120 and "chunk" in sets["w"], path
+            name, cols = "w", 5120
+        elif path.endswith("-pj.h5"):
+            n_pj += 1
+            d = int(sets["A"][2])
+            assert sets["A"][1:4] == ["f32", str(d), str(d)] and int(sets["W"][3]) == d and 0 < int(sets["W"][2]) <= d, path
+            name, cols = "W", d
+        else:
+            assert sets, path
+            continue
+        if k % 10 == 0:
+            got = raw(h5tool, path, name, np.float32, str(tmp_path))
+            assert got.size % cols == 0 and got.size > 0 and np.isfinite(got).all(), path
+    assert n_pr >= 700 and n_pj >= 400
