@@ -65,3 +65,38 @@ def test_product_does_not_import_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
                 src = open(os.path.join(dirpath, f)).read()
                 assert "import oracle" not in src and "from oracle" not in src and "dlco_oracle" not in src, f
+
+
+def test_tools_fail_loudly_without_a_gpu(tmp_path):
+    """The C++ tools over the ABI have no CPU path either: on a machine without a CUDA device each one exits non-zero,
+    says why on stderr and leaves no output file behind.  (On a GPU box this test has nothing to check.)"""
+    import subprocess
+    import numpy as np
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a CUDA device is present")
+    import __graft_entry__
+    __graft_entry__.build()
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    bin_ = os.path.join(root, "bin")
+    # a small valid unprojected-distance file and a pr model for the tools that read one
+    dist = str(tmp_path / "yosemite-m-unproj.h5")
+    x = np.random.default_rng(0).random((64, 32), dtype=np.float32)
+    lab = (np.arange(64) % 2).astype(np.uint8).reshape(-1, 1)
+    for name, arr, dt in (("Label", lab, "u8"), ("Distance", x, "f32")):
+        arr.tofile(str(tmp_path / (name + ".bin")))
+    subprocess.check_call([os.path.join(bin_, "h5tool"), "pack", dist,
+                           "Label", "u8", "2", "64", "1", str(tmp_path / "Label.bin"), "64", "1",
+                           "Distance", "f32", "2", "64", "32", str(tmp_path / "Distance.bin"), "64", "0"])
+    os.makedirs(str(tmp_path / "out" / "logging"))
+    runs = [
+        ([os.path.join(bin_, "gen-poolregion"), str(tmp_path / "filters.h5")], str(tmp_path / "filters.h5")),
+        ([os.path.join(bin_, "pj-learn"), "-iters", "10", dist, str(tmp_path / "pj.h5")], str(tmp_path / "pj.h5")),
+        ([os.path.join(bin_, "pj-sweep"), dist, str(tmp_path / "out"), "-iters", "10", "-mu", "0.001", "-gamma", "0.1"],
+         str(tmp_path / "out" / "yosemite-m-0.001-0.1-pj.h5")),
+    ]
+    for cmd, product in runs:
+        r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, timeout=120)
+        assert r.returncode != 0, cmd
+        assert b"no CUDA device" in r.stderr and b"no CPU fallback" in r.stderr, (cmd, r.stderr)
+        assert not os.path.exists(product), product

@@ -49,6 +49,7 @@ int main(int argc, char **argv)
         std::vector<double> rings((size_t)n_params * 3, 0.0);
         check(dlco_ring_params(patch, nr, nphi, nsigma, rings.data(), n_params, &n_rings), "dlco_ring_params");
 
+        Ctx ctx(0);                                           // before the output file exists: no GPU, no partial file
         h5mini::Writer out(dst);
         printf("Export RingParams: #%d\n", n_params);
         {
@@ -59,7 +60,6 @@ int main(int argc, char **argv)
         }
         const int nPR = n_params * 8;
         printf("Export Projection: #%d\n", nPR);
-        Ctx ctx(0);
         const int hp = out.create_chunked("PRParams", h5mini::F32, {3}, sChunk, deflate_level(), false);
         const int hf = out.create_chunked("PRFilters", h5mini::F32, {(uint64_t)patch, (uint64_t)patch}, sChunk, deflate_level(), false);
         const int block_rings = 256;                          // 2048 filters = 32 MB per block
