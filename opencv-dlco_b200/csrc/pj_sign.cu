@@ -495,35 +495,42 @@ k_rows_planes(const float *__restrict__ dists, int64_t ld, int D, const int32_t 
     }
 }
 
-// m[g][i] = sum_j Ct[g][j][i] * x_i[j]; block = 32 samples x 8 j-lanes, fixed summation order
+// m[g][i] = sum_j Ct[g][j][i] * x_i[j]; block = 32 samples x 8 j-lanes, fixed summation order (lane ty adds the terms
+// j = ty, ty + 8, ... in increasing j, then the 8 lanes' sums are added in order).  The 32 sample rows are gathered into
+// shared memory once (row stride D + 1: conflict-free reads down a column), so the loop over j has no barrier and its
+// loads are independent; the first version staged 32 x 32 tiles with two barriers per tile (17 serial round trips,
+// 74 us per 45 configurations).
 __global__ void __launch_bounds__(256)
 k_quad_coldot(const float *__restrict__ Ct, const float *__restrict__ dists, int64_t ld, int D,
               const int32_t *__restrict__ rows, int nk, float *__restrict__ m)
 {
-    __shared__ float tile[32][33];
+    extern __shared__ float xs[];               // [32][D + 1]
     __shared__ float part[8][32];
     const int g = blockIdx.y, i0 = blockIdx.x * 32;
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int xld = D + 1;
+    for (int r = ty; r < 32; r += 8) {
+        const int i = i0 + r;
+        if (i < nk) {
+            const float *src = dists + (int64_t)rows[i] * ld;
+            for (int j = tx; j < D; j += 32) xs[r * xld + j] = src[j];
+        }
+    }
+    __syncthreads();
     const float *ct = Ct + (size_t)g * D * nk;
+    const int i = i0 + tx;
     float acc = 0.f;
-    for (int j0 = 0; j0 < D; j0 += 32) {
-        for (int r = ty; r < 32; r += 8) {
-            const int i = i0 + r, j = j0 + tx;
-            tile[r][tx] = (i < nk && j < D) ? dists[(int64_t)rows[i] * ld + j] : 0.f;
-        }
-        __syncthreads();
-        for (int jj = ty; jj < 32; jj += 8) {
-            const int i = i0 + tx, j = j0 + jj;
-            if (i < nk && j < D) acc = fmaf(ct[(size_t)j * nk + i], tile[tx][jj], acc);
-        }
-        __syncthreads();
+    if (i < nk) {
+        const float *x = xs + tx * xld;
+#pragma unroll 4
+        for (int j = ty; j < D; j += 8) acc = fmaf(ct[(size_t)j * nk + i], x[j], acc);
     }
     part[ty][tx] = acc;
     __syncthreads();
-    if (ty == 0 && i0 + tx < nk) {
+    if (ty == 0 && i < nk) {
         float t = 0.f;
         for (int w = 0; w < 8; w++) t += part[w][tx];
-        m[(size_t)g * nk + i0 + tx] = t;
+        m[(size_t)g * nk + i] = t;
     }
 }
 
@@ -547,7 +554,10 @@ int dlco_pj_margins_quad_grid(dlco_ctx *ctx, const float *d_dists, int64_t ld, i
     r = dlco_launch_gemm3x_nt(ctx, PA, PA + plane, rows_pad, PX, PX + xplane, xrows_pad, 0, k_pad, nCfg, D, nk, Ct, nk,
                               (int64_t)D * nk);
     if (r != DLCO_OK) return r;
-    k_quad_coldot<<<dim3((nk + 31) / 32, nCfg), 256, 0, ctx->stream>>>(Ct, d_dists, ld, D, d_rows, nk, d_m);
+    const size_t xs_bytes = (size_t)32 * (D + 1) * sizeof(float);
+    DLCO_REQUIRE(xs_bytes <= 200 * 1024, "pj margins: D=%d too large for the sample tile", D);
+    DLCO_SMEM_ONCE(ctx, 11, k_quad_coldot, 200 * 1024);
+    k_quad_coldot<<<dim3((nk + 31) / 32, nCfg), 256, xs_bytes, ctx->stream>>>(Ct, d_dists, ld, D, d_rows, nk, d_m);
     DLCO_CHECK_LAUNCH(ctx);
     return DLCO_OK;
 }
